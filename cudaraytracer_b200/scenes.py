@@ -1,0 +1,342 @@
+"""Synthetic scenes and ray sets of BASELINE.json's configs.
+
+Everything is generated on the host from a 64-bit seed with the integer hash of
+``include/crt_rng.h`` (re-stated in numpy below), so the same arrays come out on
+every machine. A scene is a plain dict of numpy arrays in the layout of
+``include/crt.h``:
+
+    tri      (n, 12) float32  vertices[0..2] + stored normal   (shapes/triangle.h:49-50)
+    tri_mat  (n,)    uint32
+    sph      (m, 4)  float32  centre + radius                  (shapes/sphere.h:22)
+    sph_mat  (m,)    uint32
+    mats     list of (type, (r, g, b), param)                  (material/material.h:57-143)
+    camera   dict(lookfrom, lookat, vup, vfov, aperture, focus_dist)
+    nx, ny, spp, max_depth
+
+Reference paths are relative to /root/reference/CudaTest/src/.
+"""
+import os
+
+import numpy as np
+
+LAMBERTIAN, METAL, DIELECTRIC, DIFFUSE_LIGHT = 0, 1, 2, 3
+
+_GOLDEN = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden")
+
+
+# ----------------------------------------------------------------- hashing
+def mix32(x):
+    """include/crt_rng.h crt_mix32 on a uint32 array."""
+    x = np.asarray(x, dtype=np.uint32).copy()
+    with np.errstate(over="ignore"):
+        x ^= x >> np.uint32(16)
+        x *= np.uint32(0x7FEB352D)
+        x ^= x >> np.uint32(15)
+        x *= np.uint32(0x846CA68B)
+        x ^= x >> np.uint32(16)
+    return x
+
+
+def rng_key(seed, pixel, sample):
+    """include/crt_rng.h crt_rng_key."""
+    seed = int(seed) & 0xFFFFFFFFFFFFFFFF
+    with np.errstate(over="ignore"):
+        k = mix32(np.uint32((seed & 0xFFFFFFFF) ^ 0x9E3779B9))
+        k = mix32(k + np.uint32(seed >> 32))
+        k = mix32(k ^ mix32(np.asarray(sample, np.uint32) + np.uint32(0x85EBCA6B)))
+        k = mix32(k + np.asarray(pixel, np.uint32))
+    return k
+
+
+def rng_uniform(key, ctr):
+    """include/crt_rng.h crt_rng_uniform: float32 in (0, 1]."""
+    with np.errstate(over="ignore"):
+        c = np.asarray(ctr, np.uint32) * np.uint32(0x9E3779B1) + np.uint32(0x7F4A7C15)
+        bits = mix32(np.asarray(key, np.uint32) ^ mix32(c))
+    return ((bits >> np.uint32(8)) + np.uint32(1)).astype(np.float32) * np.float32(1.0 / 16777216.0)
+
+
+class Stream:
+    """Sequential (0, 1] draws of one stream, for host-side scene generation."""
+
+    def __init__(self, seed, stream=0):
+        self.key = rng_key(seed, np.uint32(stream), np.uint32(0xC0FFEE))
+        self.ctr = 0
+
+    def draw(self, n=None):
+        if n is None:
+            v = rng_uniform(self.key, np.uint32(self.ctr))
+            self.ctr += 1
+            return float(v)
+        v = rng_uniform(self.key, np.arange(self.ctr, self.ctr + n, dtype=np.uint32))
+        self.ctr += n
+        return v
+
+
+# ------------------------------------------------------------ mesh helpers
+def tri_normals(v0, v1, v2):
+    """Triangle constructor normal, unit(cross(v1-v0, v2-v0)) in float32 with
+    the reference's operation order (shapes/triangle.h:14-17, core/vec3.h:113-117,38-40,191-193)."""
+    v0 = np.asarray(v0, np.float32)
+    e1 = np.asarray(v1, np.float32) - v0
+    e2 = np.asarray(v2, np.float32) - v0
+    cx = e1[:, 1] * e2[:, 2] - e1[:, 2] * e2[:, 1]
+    cy = -(e1[:, 0] * e2[:, 2] - e1[:, 2] * e2[:, 0])
+    cz = e1[:, 0] * e2[:, 1] - e1[:, 1] * e2[:, 0]
+    ln = np.sqrt(cx * cx + cy * cy + cz * cz)
+    with np.errstate(invalid="ignore", divide="ignore"):
+        return np.stack([cx / ln, cy / ln, cz / ln], axis=1).astype(np.float32)
+
+
+def pack_tris(v0, v1, v2, normals=None, flip_normals=False):
+    v0, v1, v2 = (np.asarray(a, np.float32) for a in (v0, v1, v2))
+    n = tri_normals(v0, v1, v2) if normals is None else np.asarray(normals, np.float32)
+    if flip_normals:
+        n = -n
+    return np.ascontiguousarray(np.concatenate([v0, v1, v2, n], axis=1), dtype=np.float32)
+
+
+def mesh_from_indexed(points, idx_1based_float, scale=1.0):
+    """add_mesh_withNormal's triangle assembly (createScene.h:175-190) for an
+    OBJ mesh: indices are the loader's 1-based floats (obj_loader.h:62-64,
+    SURVEY §9 Q14), winding reversed to idx[2], idx[1], idx[0]
+    (createScene.h:183); normals from the Triangle constructor."""
+    pts = np.asarray(points, np.float32) * np.float32(scale)
+    idx = np.asarray(idx_1based_float).astype(np.int64) - 1
+    v0, v1, v2 = pts[idx[:, 2]], pts[idx[:, 1]], pts[idx[:, 0]]
+    return pack_tris(v0, v1, v2)
+
+
+def load_bunny_arrays():
+    """points (2503,3) mean-centred + 1-based float indices (4968,3) exactly as
+    the reference's parseObjByName returns them for objects/small_bunny.obj;
+    stored as a fixture because /root/reference does not travel."""
+    z = np.load(os.path.join(_GOLDEN, "small_bunny_parsed.npz"))
+    return z["points"], z["idx"]
+
+
+def camera_dict(lookfrom, lookat, vfov, aperture=0.0, focus_dist=10.0, vup=(0, 1, 0)):
+    return dict(lookfrom=tuple(map(float, lookfrom)), lookat=tuple(map(float, lookat)),
+                vup=tuple(map(float, vup)), vfov=float(vfov), aperture=float(aperture),
+                focus_dist=float(focus_dist))
+
+
+def _empty_tris():
+    return np.zeros((0, 12), np.float32), np.zeros((0,), np.uint32)
+
+
+def _empty_sph():
+    return np.zeros((0, 4), np.float32), np.zeros((0,), np.uint32)
+
+
+# ------------------------------------------------------------------ configs
+def c1_bunny(camera="framed", nx=1024, ny=512, spp=4):
+    """C1: bundled small_bunny.obj, points x100 (obj_loader.h:164), one
+    Lambertian(0.65, 0.05, 0.05) (createScene.h:180); 1024x512, 4 spp, depth 8
+    (kernel.cu:44-49). camera="reference" uses the literals of
+    createScene.h:160, which do not frame a +-10 unit mesh; "framed" looks at it."""
+    pts, idx = load_bunny_arrays()
+    tri = mesh_from_indexed(pts, idx, scale=100.0)
+    sph, sph_mat = _empty_sph()
+    cam = camera_dict((0, 100, 1000), (0, 150, 0), 40) if camera == "reference" else camera_dict((0, 0, 30), (0, 0, 0), 40)
+    return dict(name="C1_bunny", tri=tri, tri_mat=np.zeros(len(tri), np.uint32), sph=sph, sph_mat=sph_mat,
+                mats=[(LAMBERTIAN, (0.65, 0.05, 0.05), 0.0)], camera=cam, nx=nx, ny=ny, spp=spp, max_depth=8)
+
+
+def c2_spheres(seed=1, nx=1200, ny=800, spp=64):
+    """C2: the random-spheres layout: ground sphere, 22x22 grid of
+    radius-0.2 spheres with materials drawn uniformly, three radius-1 spheres."""
+    st = Stream(seed, 2)
+    mats = [(LAMBERTIAN, (0.5, 0.5, 0.5), 0.0)]
+    sph = [(0.0, -1000.0, 0.0, 1000.0)]
+    sph_mat = [0]
+    for a in range(-11, 11):
+        for b in range(-11, 11):
+            choose = st.draw()
+            cx = a + 0.9 * st.draw()
+            cz = b + 0.9 * st.draw()
+            r = [st.draw() for _ in range(6)]
+            if np.sqrt((cx - 4.0) ** 2 + (0.2 - 0.2) ** 2 + cz ** 2) <= 0.9:
+                continue
+            if choose < 0.8:
+                mats.append((LAMBERTIAN, (r[0] * r[1], r[2] * r[3], r[4] * r[5]), 0.0))
+            elif choose < 0.95:
+                mats.append((METAL, (0.5 * (1 + r[0]), 0.5 * (1 + r[1]), 0.5 * (1 + r[2])), 0.5 * r[3]))
+            else:
+                mats.append((DIELECTRIC, (1.0, 1.0, 1.0), 1.5))
+            sph.append((cx, 0.2, cz, 0.2))
+            sph_mat.append(len(mats) - 1)
+    for centre, m in (((0, 1, 0), (DIELECTRIC, (1, 1, 1), 1.5)),
+                      ((-4, 1, 0), (LAMBERTIAN, (0.4, 0.2, 0.1), 0.0)),
+                      ((4, 1, 0), (METAL, (0.7, 0.6, 0.5), 0.0))):
+        mats.append(m)
+        sph.append((centre[0], centre[1], centre[2], 1.0))
+        sph_mat.append(len(mats) - 1)
+    tri, tri_mat = _empty_tris()
+    return dict(name="C2_spheres", tri=tri, tri_mat=tri_mat, sph=np.asarray(sph, np.float32),
+                sph_mat=np.asarray(sph_mat, np.uint32), mats=mats,
+                camera=camera_dict((13, 2, 3), (0, 0, 0), 20, aperture=0.1, focus_dist=10.0),
+                nx=nx, ny=ny, spp=spp, max_depth=8)
+
+
+def displaced_sphere(n_theta, n_phi, radius=100.0, amp=5.0, centre=(0.0, 0.0, 0.0)):
+    """UV sphere with radial displacement amp*sin(8 theta)*sin(6 phi).
+    n_theta segments around, n_phi from pole to pole:
+    2*n_theta*(n_phi-1) triangles. Returns v0, v1, v2 (outward winding) and the
+    latitude band of each triangle."""
+    th = (np.arange(n_theta + 1, dtype=np.float64) % n_theta) * (2.0 * np.pi / n_theta)
+    ph = np.arange(n_phi + 1, dtype=np.float64) * (np.pi / n_phi)
+    T, P = np.meshgrid(th, ph, indexing="xy")          # (n_phi+1, n_theta+1)
+    R = radius + amp * np.sin(8.0 * T) * np.sin(6.0 * P)
+    X = R * np.sin(P) * np.cos(T) + centre[0]
+    Y = R * np.cos(P) + centre[1]
+    Z = R * np.sin(P) * np.sin(T) + centre[2]
+    V = np.stack([X, Y, Z], axis=-1).astype(np.float32)
+    a = V[:-1, :-1]   # (j, i)
+    b = V[:-1, 1:]    # (j, i+1)
+    c = V[1:, :-1]    # (j+1, i)
+    d = V[1:, 1:]     # (j+1, i+1)
+    band = np.broadcast_to(np.arange(n_phi)[:, None], (n_phi, n_theta))
+    # upper triangles (a, b, d) exist for j >= 1 (a == b at the north pole);
+    # lower triangles (a, d, c) exist for j <= n_phi-2 (c == d at the south pole)
+    up = (slice(1, None), slice(None))
+    lo = (slice(0, n_phi - 1), slice(None))
+    v0 = np.concatenate([a[up].reshape(-1, 3), a[lo].reshape(-1, 3)])
+    v1 = np.concatenate([b[up].reshape(-1, 3), d[lo].reshape(-1, 3)])
+    v2 = np.concatenate([d[up].reshape(-1, 3), c[lo].reshape(-1, 3)])
+    bands = np.concatenate([band[up].reshape(-1), band[lo].reshape(-1)])
+    return v0, v1, v2, bands
+
+
+def ground_quad(y, half, normal_down=True):
+    p = np.asarray([[-half, y, -half], [half, y, -half], [half, y, half], [-half, y, half]], np.float32)
+    v0 = p[[0, 0]]
+    v1 = p[[1, 2]]
+    v2 = p[[2, 3]]
+    n = np.asarray([[0, -1.0 if normal_down else 1.0, 0]] * 2, np.float32)
+    return v0, v1, v2, n
+
+
+def c3_mesh(n_theta=1000, n_phi=500, nx=1920, ny=1080, spp=16, centre=(0.0, 0.0, 0.0)):
+    """C3: displaced UV sphere, 1000x500 segments = 998,000 triangles, radius
+    100, plus a 2-triangle ground quad; Lambertian on even latitude bands,
+    Metal(0.8,0.8,0.8) fuzz 0.1 on odd bands.
+
+    Stored normals point INTO the sphere and the ground's points DOWN: the
+    reference triangle test only reports hits with dot(direction, normal) >= 0
+    (shapes/triangle.h:61), so this is the orientation that shows
+    the mesh as a solid from the outside."""
+    v0, v1, v2, bands = displaced_sphere(n_theta, n_phi, centre=centre)
+    n = -tri_normals(v0, v1, v2)
+    # guard against degenerate pole slivers producing NaN normals
+    bad = ~np.isfinite(n).all(axis=1)
+    if bad.any():
+        n[bad] = np.asarray([0, 1, 0], np.float32)
+    g0, g1, g2, gn = ground_quad(-110.0, 2000.0)
+    tri = np.concatenate([np.concatenate([v0, v1, v2, n], axis=1),
+                          np.concatenate([g0, g1, g2, gn], axis=1)]).astype(np.float32)
+    tri_mat = np.concatenate([(bands % 2).astype(np.uint32), np.asarray([2, 2], np.uint32)])
+    sph, sph_mat = _empty_sph()
+    mats = [(LAMBERTIAN, (0.7, 0.3, 0.2), 0.0), (METAL, (0.8, 0.8, 0.8), 0.1), (LAMBERTIAN, (0.5, 0.5, 0.5), 0.0)]
+    return dict(name="C3_mesh_%dk" % (len(tri) // 1000), tri=np.ascontiguousarray(tri), tri_mat=tri_mat, sph=sph,
+                sph_mat=sph_mat, mats=mats, camera=camera_dict((0, 60, 320), (0, 0, 0), 40),
+                nx=nx, ny=ny, spp=spp, max_depth=8)
+
+
+def c4_instanced(grid=10, pitch=250.0, n_theta=500, n_phi=101, nx=3840, ny=2160, spp=64):
+    """C4: grid x grid instances of a ~100k-triangle displaced sphere, flattened
+    (the reference's only instancing device, HitableList(list, n, Transform*),
+    hitable_list.h:11, shares children under a translated frame; flattening the
+    translation into the vertices gives the same world-space triangles)."""
+    base = c3_mesh(n_theta, n_phi)
+    tri0 = base["tri"][:-2]
+    mat0 = base["tri_mat"][:-2]
+    tris, mats_idx = [], []
+    off0 = -(grid - 1) * pitch / 2.0
+    for a in range(grid):
+        for b in range(grid):
+            t = tri0.copy()
+            shift = np.asarray([off0 + a * pitch, 0.0, off0 + b * pitch], np.float32)
+            for k in range(3):
+                t[:, 3 * k:3 * k + 3] += shift
+            tris.append(t)
+            mats_idx.append(mat0)
+    g0, g1, g2, gn = ground_quad(-110.0, 20000.0)
+    tris.append(np.concatenate([g0, g1, g2, gn], axis=1))
+    mats_idx.append(np.asarray([2, 2], np.uint32))
+    out = dict(base)
+    out.update(name="C4_instanced_%dM" % round(sum(len(t) for t in tris) / 1e6), tri=np.ascontiguousarray(np.concatenate(tris)),
+               tri_mat=np.concatenate(mats_idx).astype(np.uint32),
+               camera=camera_dict((0, 900, 2600), (0, 0, 0), 40), nx=nx, ny=ny, spp=spp)
+    return out
+
+
+def c5_triangles(n, seed=1):
+    """C5 geometry: n triangles with uniform random centres in the unit cube and
+    edge length n^(-1/3); random orientation, Triangle-constructor normals."""
+    key = rng_key(seed, np.uint32(5), np.uint32(n & 0xFFFFFFFF))
+    i = np.arange(n, dtype=np.uint64)
+
+    def u(k):
+        return rng_uniform(key, (i * np.uint64(12) + np.uint64(k)).astype(np.uint32)).astype(np.float32)
+
+    c = np.stack([u(0), u(1), u(2)], axis=1)
+    edge = np.float32(float(n) ** (-1.0 / 3.0))
+    offs = [np.stack([u(3 + 3 * j), u(4 + 3 * j), u(5 + 3 * j)], axis=1) - np.float32(0.5) for j in range(3)]
+    v0, v1, v2 = (c + edge * o for o in offs)
+    tri = pack_tris(v0, v1, v2)
+    bad = ~np.isfinite(tri).all(axis=1)
+    tri[bad, 9:12] = np.asarray([0, 1, 0], np.float32)
+    sph, sph_mat = _empty_sph()
+    return dict(name="C5_%d" % n, tri=tri, tri_mat=np.zeros(n, np.uint32), sph=sph, sph_mat=sph_mat,
+                mats=[(LAMBERTIAN, (0.5, 0.5, 0.5), 0.0)], camera=camera_dict((0.5, 0.5, 3.0), (0.5, 0.5, 0.5), 40),
+                nx=1920, ny=1080, spp=1, max_depth=8)
+
+
+def c5_incoherent_rays(n=1 << 21, seed=1):
+    """Uniform random origins in the unit cube, uniform directions on the sphere."""
+    key = rng_key(seed, np.uint32(55), np.uint32(n & 0xFFFFFFFF))
+    i = np.arange(n, dtype=np.uint64)
+
+    def u(k):
+        return rng_uniform(key, (i * np.uint64(8) + np.uint64(k)).astype(np.uint32)).astype(np.float32)
+
+    o = np.stack([u(0), u(1), u(2)], axis=1)
+    z = np.float32(2.0) * u(3) - np.float32(1.0)
+    phi = np.float32(2.0 * np.pi) * u(4)
+    r = np.sqrt(np.maximum(np.float32(0), np.float32(1.0) - z * z))
+    d = np.stack([r * np.cos(phi), r * np.sin(phi), z], axis=1).astype(np.float32)
+    return np.ascontiguousarray(np.concatenate([o, d], axis=1), dtype=np.float32)
+
+
+def primary_rays(cam22, nx, ny, sx=0.5, sy=0.5):
+    """Pinhole primary rays through pixel centres (no lens, no jitter):
+    Camera::get_ray with offset 0 (core/camera.h:40-44), float32 op order kept.
+    Row-major, row 0 at the bottom like the reference's colorBuffer."""
+    c = np.asarray(cam22, np.float32)
+    llc, hor, ver, org = c[0:3], c[3:6], c[6:9], c[9:12]
+    x = np.arange(nx, dtype=np.float32)
+    y = np.arange(ny, dtype=np.float32)
+    u = ((x + np.float32(sx)) / np.float32(nx)).astype(np.float32)
+    v = ((y + np.float32(sy)) / np.float32(ny)).astype(np.float32)
+    U, Vv = np.meshgrid(u, v, indexing="xy")
+    U = U.reshape(-1, 1)
+    Vv = Vv.reshape(-1, 1)
+    zero = np.zeros(3, np.float32)
+    d = (((llc + U * hor) + Vv * ver) - org) - zero
+    o = np.broadcast_to(org + zero, d.shape)
+    return np.ascontiguousarray(np.concatenate([o, d], axis=1), dtype=np.float32)
+
+
+def scene_bounds(scene):
+    lo = np.full(3, np.inf)
+    hi = np.full(3, -np.inf)
+    if len(scene["tri"]):
+        v = scene["tri"][:, :9].reshape(-1, 3)
+        lo = np.minimum(lo, v.min(0))
+        hi = np.maximum(hi, v.max(0))
+    if len(scene["sph"]):
+        s = scene["sph"]
+        lo = np.minimum(lo, (s[:, :3] - np.abs(s[:, 3:4])).min(0))
+        hi = np.maximum(hi, (s[:, :3] + np.abs(s[:, 3:4])).max(0))
+    return lo, hi

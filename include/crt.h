@@ -1,0 +1,198 @@
+/* crt.h — C ABI of the B200-native render path for CudaRaytracer scenes.
+ *
+ * This is the drop-in boundary. The reference has no FFI; the
+ * surface a replacement sits behind is the set of host functions and the one
+ * kernel launch that CudaTest/src/kernel.cu uses. Each entry point below names
+ * the reference call it replaces. All paths are relative to
+ * /root/reference/CudaTest/src/.
+ *
+ * Conventions
+ *   - plain pointers and sizes; no C++ or torch types;
+ *   - every function returns 0 on success and a negative crt_status on
+ *     failure, never calls exit() (the reference's checkCudaErrors/CHECK do,
+ *     core/deviceManage.h:3-17); crt_last_error() gives the message of the
+ *     last failure on the calling thread;
+ *   - the caller owns every host array it passes; uploads are complete when
+ *     the call returns;
+ *   - one host thread per context, contexts are independent, one context
+ *     drives one GPU (one process per GPU under torchrun);
+ *   - there is no CPU fallback: without a CUDA device crt_create fails.
+ */
+#ifndef CRT_H
+#define CRT_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CRT_ABI_VERSION 1
+
+typedef struct crt_ctx crt_ctx;
+
+typedef enum {
+    CRT_OK = 0,
+    CRT_ERR_INVALID = -1,   /* bad argument */
+    CRT_ERR_CUDA = -2,      /* CUDA runtime error, see crt_last_error() */
+    CRT_ERR_STATE = -3,     /* call out of order (e.g. trace before accel build) */
+    CRT_ERR_NOMEM = -4
+} crt_status;
+
+#define CRT_MISS 0xFFFFFFFFu
+
+/* A ray as the reference's Ray (core/ray.h:7-23) minus the unused time:
+ * origin and a direction of any non-zero length. */
+typedef struct { float o[3]; float d[3]; } crt_ray;
+
+/* Closest hit. t is measured along the unit direction, as in the reference
+ * where every Hitable::hit() re-normalises the direction
+ * (hitable/transform.h:50-54). prim_id is the caller's primitive id
+ * (position in the reference's HitableList) or CRT_MISS. u, v are the
+ * triangle barycentrics (the reference leaves rec.u/rec.v unset);
+ * 0 for spheres. */
+typedef struct { float t; uint32_t prim_id; float u; float v; } crt_hit;
+
+/* material/material.h:57-161. param: Metal fuzz (clamped to 1 like
+ * material.h:80), Dielectric ref_idx; unused otherwise. albedo: Lambertian
+ * ConstantTexture colour (material/texture.h:12-22), Metal albedo,
+ * DiffuseLight emission. */
+typedef enum {
+    CRT_MAT_LAMBERTIAN = 0,
+    CRT_MAT_METAL = 1,
+    CRT_MAT_DIELECTRIC = 2,
+    CRT_MAT_DIFFUSE_LIGHT = 3
+} crt_material_type;
+
+typedef struct { uint32_t type; float albedo[3]; float param; } crt_material;
+
+/* The members of the reference Camera after its constructor ran
+ * (core/camera.h:46-53), computed once on the host and passed by value so
+ * that host and device agree on tan(). */
+typedef struct {
+    float lower_left_corner[3];
+    float horizontal[3];
+    float vertical[3];
+    float origin[3];
+    float x[3], y[3], z[3];
+    float lens_radius;
+} crt_camera;
+
+/* Which of the reference's three shaders runs per camera sample. */
+typedef enum {
+    CRT_SHADE_PATH = 0,     /* shade()        core/render.h:48-67  (north-star path tracer) */
+    CRT_SHADE_LAMBERT = 1,  /* LambertShade() core/render.h:70-87  (reference's active default) */
+    CRT_SHADE_NORMAL = 2    /* shade_normal() core/render.h:90-103 */
+} crt_shade_mode;
+
+typedef enum {
+    CRT_ACCEL_LBVH = 0,     /* Morton LBVH traversal (replaces hitable/bvh.h:160-190) */
+    CRT_ACCEL_BRUTE = 1     /* linear scan over all primitives (hitable/hitable_list.h:76-91) */
+} crt_accel_kind;
+
+typedef enum {
+    CRT_OPT_LEAF_MAX = 1,   /* max primitives per LBVH leaf, 1..8 (default 4); takes effect at the next build */
+    CRT_OPT_COUNTERS = 2,   /* 1: run the instrumented kernels that count nodes/primitives visited */
+    CRT_OPT_BATCH_PATHS = 3 /* max camera samples in flight per wavefront batch (default 1<<25) */
+} crt_option;
+
+/* Work counters for the roofline and the reference's CSV columns
+ * "rendering, update, build" (kernel.cu:61, core/render.h:230). The integer
+ * counters other than rays are only maintained while CRT_OPT_COUNTERS is 1. */
+typedef struct {
+    uint64_t rays;            /* closest-hit queries issued */
+    uint64_t nodes_visited;   /* BVH2 nodes fetched (two child boxes each) */
+    uint64_t tris_tested;
+    uint64_t spheres_tested;
+    uint64_t scatters;        /* material scatter evaluations */
+    uint64_t paths;           /* camera samples started */
+    float    build_ms;        /* last crt_accel_build */
+    float    refit_ms;        /* last crt_accel_refit */
+    float    render_ms;       /* last crt_render* call, device time */
+    float    trace_ms;        /* last crt_trace* call, device time */
+} crt_counters;
+
+/* Image partition for one-process-per-GPU rendering. The image is cut into
+ * CRT_TILE x CRT_TILE tiles numbered row-major; part `rank` of `world` owns
+ * the tiles with index % world == rank. Pixels a part does not own are
+ * written as 0, so parts combine with a plain sum (ncclReduce) bit-exactly. */
+#define CRT_TILE 32
+
+/* ---- context: replaces main()'s setup and CudaPointerList (kernel.cu:56-81,
+ *      core/deviceManage.h:39-105) ---- */
+int  crt_abi_version(void);
+int  crt_create(int device, crt_ctx** out);
+void crt_destroy(crt_ctx* ctx);
+const char* crt_last_error(void);
+int  crt_set_option(crt_ctx* ctx, int option, int64_t value);
+int  crt_sync(crt_ctx* ctx);
+/* The CUDA stream (cudaStream_t) every call of this context is issued on. */
+void* crt_stream(crt_ctx* ctx);
+
+/* ---- scene upload: replaces add_mesh_withNormal / create_List
+ *      (createScene.h:27-38,175-210) ----
+ * tri: n x 12 floats = vertices[0..2] and the stored normal of the reference
+ *      Triangle (shapes/triangle.h:49-50), already in world space.
+ * sph: n x 4 floats = centre (the Transform position, hitable/transform.h:33)
+ *      and radius (shapes/sphere.h:22).
+ * mat_id indexes the table given to crt_scene_set_materials.
+ * prim_id: the id reported in crt_hit and used to break ties (lowest wins, as
+ *      the first list entry wins in hitable_list.h:84); NULL numbers triangles
+ *      0..n_tri-1 and spheres n_tri..n_tri+n_sph-1. */
+int crt_scene_set_materials(crt_ctx* ctx, const crt_material* mats, size_t n);
+int crt_scene_set_triangles(crt_ctx* ctx, const float* tri, const uint32_t* mat_id,
+                            const uint32_t* prim_id, size_t n);
+int crt_scene_set_spheres(crt_ctx* ctx, const float* sph, const uint32_t* mat_id,
+                          const uint32_t* prim_id, size_t n);
+/* Replaces updateFBXObj / update_pose (createScene.h:99-140): overwrite the
+ * vertices of triangles [first, first+n) with n x 9 floats. Like
+ * Triangle::SetVertices (shapes/triangle.h:40-45) the stored normals stay. */
+int crt_scene_update_vertices(crt_ctx* ctx, const float* verts, size_t first, size_t n);
+
+/* ---- acceleration structure: replaces create_BVHfromList and Update_BVH
+ *      (createScene.h:212-219, 46-58) ---- */
+int crt_accel_build(crt_ctx* ctx);
+int crt_accel_refit(crt_ctx* ctx);
+
+/* ---- closest hit: replaces (*world)->hit(r, t_min, t_max, rec, frame)
+ *      (core/render.h:53, hitable/hitable.h:29-38) for n rays ----
+ * Host-buffer form copies in and out; the _device form takes device pointers,
+ * is asynchronous on crt_stream() and is what the C5 sweep times. */
+int crt_trace(crt_ctx* ctx, const crt_ray* rays, size_t n, float t_min, float t_max,
+              int accel, crt_hit* hits);
+int crt_trace_device(crt_ctx* ctx, const crt_ray* d_rays, size_t n, float t_min, float t_max,
+                     int accel, crt_hit* d_hits);
+
+/* ---- render: replaces render<<<>>> + the D2H copy (core/render.h:105-129,
+ *      222-226) ----
+ * rgb_out: caller-owned host array of nx*ny*3 floats in the reference's
+ * colorBuffer layout: row 0 at the bottom, values after /spp, sqrt and clip. */
+int crt_render(crt_ctx* ctx, const crt_camera* cam, int nx, int ny, int spp, int max_depth,
+               int shade_mode, uint64_t seed, float* rgb_out);
+
+/* Multi-GPU building blocks (device pointers, asynchronous on crt_stream()).
+ * crt_render_accum_device adds nothing to d_accum: it overwrites it with, per
+ * pixel this part owns, the sum over samples [sample_begin, sample_end) in
+ * sample order, and 0 elsewhere. crt_resolve_device applies
+ * render.h:123-128 (divide by spp, sqrt, clip). */
+int crt_render_accum_device(crt_ctx* ctx, const crt_camera* cam, int nx, int ny,
+                            int sample_begin, int sample_end, int max_depth, int shade_mode,
+                            uint64_t seed, int rank, int world, float* d_accum);
+int crt_resolve_device(crt_ctx* ctx, const float* d_accum, size_t n_pixels, int spp, float* d_rgb);
+/* WritePng's conversion (core/render.h:137-146) on the GPU: vertical flip,
+ * char(255.99*c), alpha 255. d_rgba8: nx*ny*4 bytes, row 0 at the top. */
+int crt_pack_rgba8_device(crt_ctx* ctx, const float* d_rgb, int nx, int ny, uint8_t* d_rgba8);
+
+/* ---- timing and work counters: replaces StopWatch + CSV
+ *      (swatch.h:4-18, Loader/CSVWriter.h:8-32) ---- */
+int crt_get_counters(crt_ctx* ctx, crt_counters* out);
+int crt_reset_counters(crt_ctx* ctx);
+
+/* Sizes of the acceleration structure, for reports. */
+int crt_accel_info(crt_ctx* ctx, uint64_t* n_prims, uint64_t* n_nodes, uint64_t* bytes, int* max_depth);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CRT_H */

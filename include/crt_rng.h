@@ -1,0 +1,62 @@
+/* crt_rng.h — counter-based per-(pixel, sample) random numbers.
+ *
+ * Replaces the reference's per-pixel XORWOW curandState
+ * (CudaTest/src/core/deviceManage.h:120-136, 48 B of state per pixel) with a
+ * stateless generator: draw k of the path that belongs to camera sample
+ * `sample` of pixel `pixel` is a pure function of (seed, pixel, sample, k).
+ * The only thing a path carries is the 32-bit draw counter k.
+ *
+ * Like curand_uniform (used at render.h:116-117, camera.h:10,
+ * material.h:14-16,134) the float result lies in (0, 1].
+ *
+ * Integer-only arithmetic, so the CUDA kernels, the C oracle and the shim
+ * that feeds the unmodified reference headers all produce the same stream.
+ * Plain C; also valid C++ and CUDA (define CRT_HD before including).
+ */
+#ifndef CRT_RNG_H
+#define CRT_RNG_H
+
+#include <stdint.h>
+
+#ifndef CRT_HD
+#  ifdef __CUDACC__
+#    define CRT_HD __host__ __device__ __forceinline__
+#  else
+#    define CRT_HD static inline
+#  endif
+#endif
+
+/* 32-bit finaliser ("lowbias32" constants); a bijection on uint32. */
+CRT_HD uint32_t crt_mix32(uint32_t x)
+{
+    x ^= x >> 16;
+    x *= 0x7feb352dU;
+    x ^= x >> 15;
+    x *= 0x846ca68bU;
+    x ^= x >> 16;
+    return x;
+}
+
+/* Stream key of one camera sample. */
+CRT_HD uint32_t crt_rng_key(uint64_t seed, uint32_t pixel, uint32_t sample)
+{
+    uint32_t k = crt_mix32((uint32_t)seed ^ 0x9e3779b9U);
+    k = crt_mix32(k + (uint32_t)(seed >> 32));
+    k = crt_mix32(k ^ crt_mix32(sample + 0x85ebca6bU));
+    k = crt_mix32(k + pixel);
+    return k;
+}
+
+/* Raw 32-bit draw number `ctr` of stream `key`. */
+CRT_HD uint32_t crt_rng_bits(uint32_t key, uint32_t ctr)
+{
+    return crt_mix32(key ^ crt_mix32(ctr * 0x9e3779b1U + 0x7f4a7c15U));
+}
+
+/* Uniform float in (0, 1]: 24 random bits, never 0, may be exactly 1. */
+CRT_HD float crt_rng_uniform(uint32_t key, uint32_t ctr)
+{
+    return (float)((crt_rng_bits(key, ctr) >> 8) + 1U) * (1.0f / 16777216.0f);
+}
+
+#endif /* CRT_RNG_H */
