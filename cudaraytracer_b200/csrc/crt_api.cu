@@ -1,0 +1,351 @@
+// crt_api.cu — the C ABI of include/crt.h: context, scene upload, dispatch.
+#include "crt_internal.h"
+
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+#include <vector>
+
+namespace crt {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof g_err, fmt, ap);
+    va_end(ap);
+}
+
+int cuda_fail(cudaError_t e, const char* what, const char* file, int line)
+{
+    set_error("CUDA error %d (%s) at %s:%d: %s", (int)e, cudaGetErrorString(e), file, line, what);
+    (void)cudaGetLastError();
+    return e == cudaErrorMemoryAllocation ? CRT_ERR_NOMEM : CRT_ERR_CUDA;
+}
+
+static int upload(DevBuf& buf, const void* host, size_t bytes, cudaStream_t st)
+{
+    if (bytes == 0) return CRT_OK;
+    CRT_CUDA(buf.reserve(bytes));
+    CRT_CUDA(cudaMemcpyAsync(buf.p, host, bytes, cudaMemcpyHostToDevice, st));
+    return CRT_OK;
+}
+
+static int upload_ids(DevBuf& buf, const uint32_t* ids, size_t n, uint32_t first, cudaStream_t st)
+{
+    if (n == 0) return CRT_OK;
+    if (ids) return upload(buf, ids, n * 4, st);
+    std::vector<uint32_t> seq(n);
+    for (size_t i = 0; i < n; i++) seq[i] = first + (uint32_t)i;
+    int r = upload(buf, seq.data(), n * 4, st);
+    if (r == CRT_OK) CRT_CUDA(cudaStreamSynchronize(st));   // seq dies with this scope
+    return r;
+}
+
+// Triangle::SetVertices (shapes/triangle.h:40-45) for a range of triangles: the
+// reference's update_pose runs this loop on one device thread
+// (createScene.h:99-109); here one thread per vertex component.
+__global__ void __launch_bounds__(256)
+k_update_vertices(const float* __restrict__ verts, size_t n_values, size_t first, float* __restrict__ tri_in)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_values) return;
+    const size_t t = i / 9, k = i - t * 9;
+    tri_in[(first + t) * 12 + k] = verts[i];
+}
+
+}  // namespace crt
+
+using namespace crt;
+
+#define CRT_CHECK_CTX(c)                                                \
+    do {                                                                \
+        if (!(c)) { set_error("null context"); return CRT_ERR_INVALID; } \
+        cudaError_t e__ = cudaSetDevice((c)->device);                   \
+        if (e__ != cudaSuccess) return cuda_fail(e__, "cudaSetDevice", __FILE__, __LINE__); \
+    } while (0)
+
+extern "C" {
+
+int crt_abi_version(void) { return CRT_ABI_VERSION; }
+
+const char* crt_last_error(void) { return g_err; }
+
+int crt_create(int device, crt_ctx** out)
+{
+    if (!out) { set_error("crt_create: out is null"); return CRT_ERR_INVALID; }
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0) {
+        (void)cudaGetLastError();
+        set_error("crt_create: no CUDA device (%s); this library has no CPU path",
+                  e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+        return CRT_ERR_CUDA;
+    }
+    if (device < 0 || device >= count) { set_error("crt_create: device %d out of range [0, %d)", device, count); return CRT_ERR_INVALID; }
+    CRT_CUDA(cudaSetDevice(device));
+    crt_ctx* c = new crt_ctx();
+    c->device = device;
+    cudaDeviceProp prop;
+    CRT_CUDA(cudaGetDeviceProperties(&prop, device));
+    c->sm_count = prop.multiProcessorCount;
+    CRT_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    CRT_CUDA(cudaEventCreate(&c->ev0));
+    CRT_CUDA(cudaEventCreate(&c->ev1));
+    CRT_CUDA(c->counters.reserve(sizeof(unsigned long long) * CNT_COUNT));
+    CRT_CUDA(cudaMemsetAsync(c->counters.p, 0, sizeof(unsigned long long) * CNT_COUNT, c->stream));
+    CRT_CUDA(cudaStreamSynchronize(c->stream));
+    *out = c;
+    return CRT_OK;
+}
+
+void crt_destroy(crt_ctx* c)
+{
+    if (!c) return;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    DevBuf* bufs[] = {&c->tri_in, &c->tri_mat, &c->tri_id, &c->sph_in, &c->sph_mat, &c->sph_id, &c->mats,
+                      &c->keys[0], &c->keys[1], &c->vals[0], &c->vals[1], &c->hist, &c->nodes, &c->recs, &c->info,
+                      &c->child, &c->parent, &c->leaf_parent, &c->range, &c->node_box, &c->leaf_box, &c->flags,
+                      &c->bounds, &c->depth_out, &c->queue[0], &c->queue[1], &c->qcount, &c->rad, &c->accum, &c->rgb,
+                      &c->rays_tmp, &c->hits_tmp, &c->counters};
+    for (DevBuf* b : bufs) b->release();
+    if (c->ev0) cudaEventDestroy(c->ev0);
+    if (c->ev1) cudaEventDestroy(c->ev1);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+int crt_set_option(crt_ctx* c, int option, int64_t value)
+{
+    CRT_CHECK_CTX(c);
+    switch (option) {
+    case CRT_OPT_LEAF_MAX:
+        if (value < 1 || value > 8) { set_error("CRT_OPT_LEAF_MAX must be in [1, 8]"); return CRT_ERR_INVALID; }
+        c->leaf_max = (int)value;
+        return CRT_OK;
+    case CRT_OPT_COUNTERS:
+        c->count_work = value != 0;
+        return CRT_OK;
+    case CRT_OPT_BATCH_PATHS:
+        if (value < 1) { set_error("CRT_OPT_BATCH_PATHS must be >= 1"); return CRT_ERR_INVALID; }
+        c->batch_paths = value;
+        return CRT_OK;
+    }
+    set_error("crt_set_option: unknown option %d", option);
+    return CRT_ERR_INVALID;
+}
+
+int crt_sync(crt_ctx* c)
+{
+    CRT_CHECK_CTX(c);
+    CRT_CUDA(cudaStreamSynchronize(c->stream));
+    return CRT_OK;
+}
+
+void* crt_stream(crt_ctx* c) { return c ? (void*)c->stream : nullptr; }
+
+int crt_scene_set_materials(crt_ctx* c, const crt_material* mats, size_t n)
+{
+    CRT_CHECK_CTX(c);
+    if (n > 0 && !mats) { set_error("crt_scene_set_materials: null table"); return CRT_ERR_INVALID; }
+    if (n > 65535) { set_error("crt_scene_set_materials: at most 65535 materials (got %zu)", n); return CRT_ERR_INVALID; }
+    std::vector<DMat> d(n);
+    for (size_t i = 0; i < n; i++) {
+        if (mats[i].type > CRT_MAT_DIFFUSE_LIGHT) { set_error("crt_scene_set_materials: material %zu has unknown type %u", i, mats[i].type); return CRT_ERR_INVALID; }
+        d[i].r = mats[i].albedo[0]; d[i].g = mats[i].albedo[1]; d[i].b = mats[i].albedo[2];
+        d[i].param = mats[i].param;
+        d[i].type = mats[i].type;
+        d[i].pad0 = d[i].pad1 = d[i].pad2 = 0;
+    }
+    int r = upload(c->mats, d.data(), n * sizeof(DMat), c->stream);
+    if (r != CRT_OK) return r;
+    CRT_CUDA(cudaStreamSynchronize(c->stream));
+    c->n_mats = n;
+    return CRT_OK;
+}
+
+static int check_mat_ids(const crt_ctx* c, const uint32_t* mat_id, size_t n, const char* who)
+{
+    if (!mat_id) return CRT_OK;
+    for (size_t i = 0; i < n; i++)
+        if (mat_id[i] >= c->n_mats) { set_error("%s: primitive %zu uses material %u but only %zu are set", who, i, mat_id[i], c->n_mats); return CRT_ERR_INVALID; }
+    return CRT_OK;
+}
+
+int crt_scene_set_triangles(crt_ctx* c, const float* tri, const uint32_t* mat_id, const uint32_t* prim_id, size_t n)
+{
+    CRT_CHECK_CTX(c);
+    if (n > 0 && !tri) { set_error("crt_scene_set_triangles: null vertex array"); return CRT_ERR_INVALID; }
+    if (n >= (1ull << 28)) { set_error("crt_scene_set_triangles: too many triangles"); return CRT_ERR_INVALID; }
+    int r = check_mat_ids(c, mat_id, n, "crt_scene_set_triangles");
+    if (r != CRT_OK) return r;
+    if ((r = upload(c->tri_in, tri, n * 48, c->stream)) != CRT_OK) return r;
+    if (mat_id) { if ((r = upload(c->tri_mat, mat_id, n * 4, c->stream)) != CRT_OK) return r; }
+    else if (n) { CRT_CUDA(c->tri_mat.reserve(n * 4)); CRT_CUDA(cudaMemsetAsync(c->tri_mat.p, 0, n * 4, c->stream)); }
+    if ((r = upload_ids(c->tri_id, prim_id, n, 0u, c->stream)) != CRT_OK) return r;
+    CRT_CUDA(cudaStreamSynchronize(c->stream));
+    c->n_tri = n;
+    c->accel_valid = false;
+    // default sphere ids follow the triangles; renumber them if they were defaulted earlier
+    return CRT_OK;
+}
+
+int crt_scene_set_spheres(crt_ctx* c, const float* sph, const uint32_t* mat_id, const uint32_t* prim_id, size_t n)
+{
+    CRT_CHECK_CTX(c);
+    if (n > 0 && !sph) { set_error("crt_scene_set_spheres: null array"); return CRT_ERR_INVALID; }
+    if (n >= (1ull << 28)) { set_error("crt_scene_set_spheres: too many spheres"); return CRT_ERR_INVALID; }
+    int r = check_mat_ids(c, mat_id, n, "crt_scene_set_spheres");
+    if (r != CRT_OK) return r;
+    if ((r = upload(c->sph_in, sph, n * 16, c->stream)) != CRT_OK) return r;
+    if (mat_id) { if ((r = upload(c->sph_mat, mat_id, n * 4, c->stream)) != CRT_OK) return r; }
+    else if (n) { CRT_CUDA(c->sph_mat.reserve(n * 4)); CRT_CUDA(cudaMemsetAsync(c->sph_mat.p, 0, n * 4, c->stream)); }
+    if ((r = upload_ids(c->sph_id, prim_id, n, (uint32_t)c->n_tri, c->stream)) != CRT_OK) return r;
+    CRT_CUDA(cudaStreamSynchronize(c->stream));
+    c->n_sph = n;
+    c->accel_valid = false;
+    return CRT_OK;
+}
+
+int crt_scene_update_vertices(crt_ctx* c, const float* verts, size_t first, size_t n)
+{
+    CRT_CHECK_CTX(c);
+    if (n == 0) return CRT_OK;
+    if (!verts) { set_error("crt_scene_update_vertices: null array"); return CRT_ERR_INVALID; }
+    if (first + n > c->n_tri) { set_error("crt_scene_update_vertices: range [%zu, %zu) exceeds %zu triangles", first, first + n, c->n_tri); return CRT_ERR_INVALID; }
+    // staged through the (otherwise idle) ray upload buffer
+    CRT_CUDA(c->rays_tmp.reserve(n * 36));
+    CRT_CUDA(cudaMemcpyAsync(c->rays_tmp.p, verts, n * 36, cudaMemcpyHostToDevice, c->stream));
+    const size_t nv = n * 9;
+    k_update_vertices<<<(unsigned int)((nv + 255) / 256), 256, 0, c->stream>>>(c->rays_tmp.as<float>(), nv, first, c->tri_in.as<float>());
+    CRT_CUDA(cudaGetLastError());
+    CRT_CUDA(cudaStreamSynchronize(c->stream));
+    return CRT_OK;
+}
+
+int crt_accel_build(crt_ctx* c)
+{
+    CRT_CHECK_CTX(c);
+    return lbvh_build(c, false);
+}
+
+int crt_accel_refit(crt_ctx* c)
+{
+    CRT_CHECK_CTX(c);
+    return lbvh_build(c, true);
+}
+
+int crt_trace_device(crt_ctx* c, const crt_ray* d_rays, size_t n, float t_min, float t_max, int accel, crt_hit* d_hits)
+{
+    CRT_CHECK_CTX(c);
+    if (n > 0 && (!d_rays || !d_hits)) { set_error("crt_trace_device: null buffer"); return CRT_ERR_INVALID; }
+    int r = launch_trace(c, d_rays, n, t_min, t_max, accel, d_hits);
+    if (r == CRT_OK) c->host_counters.rays += n;
+    return r;
+}
+
+int crt_trace(crt_ctx* c, const crt_ray* rays, size_t n, float t_min, float t_max, int accel, crt_hit* hits)
+{
+    CRT_CHECK_CTX(c);
+    if (n == 0) return CRT_OK;
+    if (!rays || !hits) { set_error("crt_trace: null buffer"); return CRT_ERR_INVALID; }
+    CRT_CUDA(c->rays_tmp.reserve(n * sizeof(crt_ray)));
+    CRT_CUDA(c->hits_tmp.reserve(n * sizeof(crt_hit)));
+    CRT_CUDA(cudaMemcpyAsync(c->rays_tmp.p, rays, n * sizeof(crt_ray), cudaMemcpyHostToDevice, c->stream));
+    CRT_CUDA(cudaEventRecord(c->ev0, c->stream));
+    int r = launch_trace(c, c->rays_tmp.as<crt_ray>(), n, t_min, t_max, accel, c->hits_tmp.as<crt_hit>());
+    if (r != CRT_OK) return r;
+    CRT_CUDA(cudaEventRecord(c->ev1, c->stream));
+    CRT_CUDA(cudaMemcpyAsync(hits, c->hits_tmp.p, n * sizeof(crt_hit), cudaMemcpyDeviceToHost, c->stream));
+    CRT_CUDA(cudaStreamSynchronize(c->stream));
+    CRT_CUDA(cudaGetLastError());
+    float ms = 0.f;
+    CRT_CUDA(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+    c->host_counters.trace_ms = ms;
+    c->host_counters.rays += n;
+    return CRT_OK;
+}
+
+int crt_render_accum_device(crt_ctx* c, const crt_camera* cam, int nx, int ny, int sample_begin, int sample_end,
+                            int max_depth, int shade_mode, uint64_t seed, int rank, int world, float* d_accum)
+{
+    CRT_CHECK_CTX(c);
+    return render_accum(c, cam, nx, ny, sample_begin, sample_end, max_depth, shade_mode, seed, rank, world, d_accum);
+}
+
+int crt_resolve_device(crt_ctx* c, const float* d_accum, size_t n_pixels, int spp, float* d_rgb)
+{
+    CRT_CHECK_CTX(c);
+    if (n_pixels > 0 && (!d_accum || !d_rgb)) { set_error("crt_resolve_device: null buffer"); return CRT_ERR_INVALID; }
+    return launch_resolve(c, d_accum, n_pixels, spp, d_rgb);
+}
+
+int crt_pack_rgba8_device(crt_ctx* c, const float* d_rgb, int nx, int ny, uint8_t* d_rgba8)
+{
+    CRT_CHECK_CTX(c);
+    if (nx < 0 || ny < 0 || ((size_t)nx * ny > 0 && (!d_rgb || !d_rgba8))) { set_error("crt_pack_rgba8_device: bad arguments"); return CRT_ERR_INVALID; }
+    return launch_pack_rgba8(c, d_rgb, nx, ny, d_rgba8);
+}
+
+int crt_render(crt_ctx* c, const crt_camera* cam, int nx, int ny, int spp, int max_depth, int shade_mode,
+               uint64_t seed, float* rgb_out)
+{
+    CRT_CHECK_CTX(c);
+    if (!rgb_out) { set_error("crt_render: rgb_out is null"); return CRT_ERR_INVALID; }
+    if (nx <= 0 || ny <= 0 || spp < 1) { set_error("crt_render: nx, ny and spp must be positive"); return CRT_ERR_INVALID; }
+    const size_t npix = (size_t)nx * ny;
+    CRT_CUDA(c->accum.reserve(npix * 12));
+    CRT_CUDA(c->rgb.reserve(npix * 12));
+    int r = render_accum(c, cam, nx, ny, 0, spp, max_depth, shade_mode, seed, 0, 1, c->accum.as<float>());
+    if (r != CRT_OK) return r;
+    if ((r = launch_resolve(c, c->accum.as<float>(), npix, spp, c->rgb.as<float>())) != CRT_OK) return r;
+    CRT_CUDA(cudaMemcpyAsync(rgb_out, c->rgb.p, npix * 12, cudaMemcpyDeviceToHost, c->stream));
+    CRT_CUDA(cudaStreamSynchronize(c->stream));
+    CRT_CUDA(cudaGetLastError());
+    return CRT_OK;
+}
+
+int crt_get_counters(crt_ctx* c, crt_counters* out)
+{
+    CRT_CHECK_CTX(c);
+    if (!out) { set_error("crt_get_counters: out is null"); return CRT_ERR_INVALID; }
+    unsigned long long h[CNT_COUNT];
+    CRT_CUDA(cudaMemcpyAsync(h, c->counters.p, sizeof h, cudaMemcpyDeviceToHost, c->stream));
+    CRT_CUDA(cudaStreamSynchronize(c->stream));
+    *out = c->host_counters;
+    out->nodes_visited = h[CNT_NODES];
+    out->tris_tested = h[CNT_TRIS];
+    out->spheres_tested = h[CNT_SPHERES];
+    out->scatters = h[CNT_SCATTERS];
+    return CRT_OK;
+}
+
+int crt_reset_counters(crt_ctx* c)
+{
+    CRT_CHECK_CTX(c);
+    CRT_CUDA(cudaMemsetAsync(c->counters.p, 0, sizeof(unsigned long long) * CNT_COUNT, c->stream));
+    CRT_CUDA(cudaStreamSynchronize(c->stream));
+    const float b = c->host_counters.build_ms, r = c->host_counters.refit_ms;
+    c->host_counters = crt_counters{};
+    c->host_counters.build_ms = b;
+    c->host_counters.refit_ms = r;
+    return CRT_OK;
+}
+
+int crt_accel_info(crt_ctx* c, uint64_t* n_prims, uint64_t* n_nodes, uint64_t* bytes, int* max_depth)
+{
+    CRT_CHECK_CTX(c);
+    if (!c->accel_valid) { set_error("crt_accel_info: no acceleration structure"); return CRT_ERR_STATE; }
+    const uint64_t n = c->n_prims;
+    if (n_prims) *n_prims = n;
+    if (n_nodes) *n_nodes = n > 1 ? n - 1 : 0;
+    if (bytes) *bytes = n * 48 + n * 8 + (n > 1 ? (n - 1) * 64 : 0);
+    if (max_depth) *max_depth = c->tree_depth;
+    return CRT_OK;
+}
+
+}  // extern "C"

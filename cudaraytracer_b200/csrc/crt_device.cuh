@@ -1,0 +1,222 @@
+// crt_device.cuh — per-ray device functions of the render hot path:
+// primitive tests, camera, materials, sky. Each follows the reference lines it
+// cites (paths relative to /root/reference/CudaTest/src/) operation for
+// operation, in the non-fused arithmetic of crt_math.cuh.
+#pragma once
+#include "crt_math.cuh"
+
+namespace crt {
+
+#ifndef CRT_MISS_ID
+#define CRT_MISS_ID 0xFFFFFFFFu
+#endif
+
+// ---- HBM layouts -----------------------------------------------------------
+// Sorted primitive record, 48 B = 3 x float4 (one 128-bit load each):
+//   triangle: r0 = {v0.xyz, n.x}  r1 = {e1.xyz, n.y}  r2 = {e2.xyz, n.z}
+//             e1 = v1 - v0, e2 = v2 - v0 (the subtraction triangle.h:69-70
+//             performs per test, done once; same float result)
+//   sphere:   r0 = {centre.xyz, radius}, r1 = r2 = 0
+// Per sorted primitive info, 8 B: {prim_id, mat_id | kind << 31}.
+// BVH2 node, 64 B = 4 x float4, holds BOTH children's boxes:
+//   n0 = {c0.lo.x, c0.hi.x, c0.lo.y, c0.hi.y}
+//   n1 = {c1.lo.x, c1.hi.x, c1.lo.y, c1.hi.y}
+//   n2 = {c0.lo.z, c0.hi.z, c1.lo.z, c1.hi.z}
+//   n3 = {child0, child1, -, -} as int bits; child >= 0: node index,
+//        child < 0: leaf, ~child = (first sorted primitive << 3) | (count - 1)
+#define CRT_KIND_SPHERE 0x80000000u
+
+struct DMat { float r, g, b, param; uint32_t type; uint32_t pad0, pad1, pad2; };  // 32 B
+
+struct AccelView {
+    const float4* nodes;
+    const float4* recs;
+    const uint2* info;
+    int root;            // child-style reference of the root
+    uint32_t n_prims;
+};
+
+struct DCamera {         // core/camera.h:46-53
+    v3 llc, horizontal, vertical, origin, x, y, z;
+    float lens_radius;
+};
+
+struct Hit {
+    float t;
+    uint32_t k;          // sorted primitive position (traversal) or input index (brute force)
+    uint32_t id;         // caller's primitive id, CRT_MISS_ID on miss
+    float u, v;
+};
+
+// The direction every primitive test sees: the world list's Hitable::hit
+// normalises once and each primitive's normalises again
+// (hitable/hitable.h:34, hitable/transform.h:50-54).
+CRT_HD v3 ray_dir_local(v3 d) { return vunit(vunit(d)); }
+
+// shapes/triangle.h:57-100 plus deviation D1 (accept only t_min < t < t_max;
+// SURVEY §9 Q2). v0/e1/e2/n as stored in the record. A candidate with t equal
+// to the current best is still returned (t <= t_best); the caller breaks the
+// tie by primitive id.
+CRT_HD bool triangle_test(v3 o, v3 d, v3 v0, v3 e1, v3 e2, v3 n, float t_min, float t_best,
+                          float& t_out, float& u_out, float& v_out)
+{
+    const float EPSILON = 0.000001f;                       // triangle.h:9,22
+    if (vdot(d, n) < 0.0f) return false;                   // triangle.h:61
+    v3 h = vcross(d, e2);
+    float a = vdot(e1, h);
+    if (a > -EPSILON && a < EPSILON) return false;         // triangle.h:77
+    float f = x::rcp(a);                                   // triangle.h:80
+    v3 s = vsub(o, v0);
+    float u = x::mul(f, vdot(s, h));
+    if (u < 0.0f || u > 1.0f) return false;                // triangle.h:84
+    v3 q = vcross(s, e1);
+    float v = x::mul(f, vdot(d, q));
+    if (v < 0.0f || x::add(u, v) > 1.0f) return false;     // triangle.h:89
+    float t = x::mul(f, vdot(e2, q));                      // triangle.h:92
+    if (!(t > t_min && t <= t_best)) return false;         // D1
+    t_out = t; u_out = u; v_out = v;
+    return true;
+}
+
+// shapes/sphere.h:27-55; oc = origin in the sphere's frame (origin - centre,
+// hitable/transform.h:38-41).
+CRT_HD bool sphere_test(v3 oc, v3 d, float radius, float t_min, float t_best, float& t_out)
+{
+    float a = vdot(d, d);
+    float b = vdot(oc, d);
+    float c = x::sub(vdot(oc, oc), x::mul(radius, radius));
+    float disc = x::sub(x::mul(b, b), x::mul(a, c));
+    if (disc > 0.0f) {
+        float sq = x::sqrt(disc);
+        float tmp = x::div(x::sub(-b, sq), a);
+        if (tmp <= t_best && tmp > t_min) { t_out = tmp; return true; }
+        tmp = x::div(x::add(-b, sq), a);
+        if (tmp <= t_best && tmp > t_min) { t_out = tmp; return true; }
+    }
+    return false;
+}
+
+// ---- camera ----------------------------------------------------------------
+struct Rng { uint32_t key, ctr; };
+CRT_HD float rnd(Rng& r) { return crt_rng_uniform(r.key, r.ctr++); }
+
+// core/camera.h:6-13. C++ leaves the evaluation order of the two constructor
+// arguments unspecified; the reference as compiled for oracle/_ref draws right
+// to left, so the first draw is y.
+CRT_HD v3 random_in_unit_disk(Rng& r)
+{
+    v3 p;
+    do {
+        float b = rnd(r), a = rnd(r);
+        p = vsub(vscale(2.0f, V(a, b, 0.0f)), V(1.0f, 1.0f, 0.0f));
+    } while (vdot(p, p) >= 1.0f);
+    return p;
+}
+
+// core/camera.h:40-44
+CRT_HD void camera_get_ray(const DCamera& c, float s, float t, Rng& r, v3& o, v3& d)
+{
+    v3 rd = vscale(c.lens_radius, random_in_unit_disk(r));
+    v3 offset = vadd(vscale(rd.x, c.x), vscale(rd.y, c.y));
+    o = vadd(c.origin, offset);
+    d = vsub(vsub(vadd(vadd(c.llc, vscale(s, c.horizontal)), vscale(t, c.vertical)), c.origin), offset);
+}
+
+// ---- materials -------------------------------------------------------------
+CRT_HD v3 reflect(v3 v, v3 n) { return vsub(v, vscale(x::mul(2.0f, vdot(v, n)), n)); }   // material.h:6-8
+
+// material.h:11-19; right-to-left draws, see random_in_unit_disk.
+CRT_HD v3 random_in_unit_sphere(Rng& r)
+{
+    v3 p;
+    do {
+        float c = rnd(r), b = rnd(r), a = rnd(r);
+        p = vsub(vscale(2.0f, V(a, b, c)), V(1.0f, 1.0f, 1.0f));
+    } while (vlen2(p) >= 1.0f);
+    return p;
+}
+
+// material.h:22-26. powf(x, 5) is evaluated as a double product rounded once,
+// which agrees with glibc's (double-precision-internal) powf.
+CRT_HD float schlick(float cosine, float ref_idx)
+{
+    float r0 = x::div(x::sub(1.0f, ref_idx), x::add(1.0f, ref_idx));
+    r0 = x::mul(r0, r0);
+    double b = (double)x::sub(1.0f, cosine);
+    float p5 = (float)(b * b * b * b * b);
+    return x::add(r0, x::mul(x::sub(1.0f, r0), p5));
+}
+
+// material.h:29-39
+CRT_HD bool refract(v3 v, v3 n, float ni_over_nt, v3& refracted)
+{
+    v3 uv = vunit(v);
+    float dt = vdot(uv, n);
+    float disc = x::sub(1.0f, x::mul(x::mul(ni_over_nt, ni_over_nt), x::sub(1.0f, x::mul(dt, dt))));
+    if (disc > 0.0f) {
+        refracted = vsub(vscale(ni_over_nt, vsub(uv, vscale(dt, n))), vscale(x::sqrt(disc), n));
+        return true;
+    }
+    return false;
+}
+
+// Material::scatter, material.h:57-155. in_d: direction of the incoming ray as
+// shade() holds it (not normalised). Returns the bool of scatter(); att and
+// out_d are written as the reference writes them.
+CRT_HD bool scatter(const DMat& m, v3 in_d, v3 p, v3 n, Rng& r, v3& att, v3& out_d)
+{
+    if (m.type == 0u) {                                    // Lambertian, material.h:61-71
+        v3 target = vadd(vadd(p, n), random_in_unit_sphere(r));
+        out_d = vsub(target, p);
+        att = V(m.r, m.g, m.b);
+        return true;
+    }
+    if (m.type == 1u) {                                    // Metal, material.h:83-92 (fuzz clamp :80)
+        float fuzz = m.param < 1.0f ? m.param : 1.0f;
+        v3 reflected = reflect(vunit(in_d), n);
+        out_d = vadd(reflected, vscale(fuzz, random_in_unit_sphere(r)));
+        att = V(m.r, m.g, m.b);
+        return vdot(out_d, n) > 0.0f;
+    }
+    if (m.type == 2u) {                                    // Dielectric, material.h:103-141
+        float ref_idx = m.param;
+        v3 outward, refracted = V(0.0f, 0.0f, 0.0f);
+        v3 reflected = reflect(in_d, n);
+        float ni_over_nt, reflect_prob, cosine;
+        att = V(1.0f, 1.0f, 1.0f);
+        float dn = vdot(in_d, n);
+        if (dn > 0.0f) {
+            outward = vneg(n);
+            ni_over_nt = ref_idx;
+            cosine = x::div(dn, vlen(in_d));
+            cosine = x::sqrt(x::sub(1.0f, x::mul(x::mul(ref_idx, ref_idx), x::sub(1.0f, x::mul(cosine, cosine)))));
+        } else {
+            outward = n;
+            ni_over_nt = x::div(1.0f, ref_idx);
+            cosine = x::div(-dn, vlen(in_d));
+        }
+        if (refract(in_d, outward, ni_over_nt, refracted)) reflect_prob = schlick(cosine, ref_idx);
+        else reflect_prob = 1.0f;
+        if (rnd(r) < reflect_prob) out_d = reflected;
+        else out_d = refracted;
+        return true;
+    }
+    att = V(0.0f, 0.0f, 0.0f);                             // DiffuseLight, material.h:149-155
+    out_d = V(0.0f, 0.0f, 0.0f);
+    return false;
+}
+
+CRT_HD v3 emitted(const DMat& m)                           // material.h:49-53,156-158
+{
+    return m.type == 3u ? V(m.r, m.g, m.b) : V(0.0f, 0.0f, 0.0f);
+}
+
+// core/render.h:41-46
+CRT_HD v3 background_sky(v3 d)
+{
+    v3 n = vunit(d);
+    float t = x::mul(0.5f, x::add(n.y, 1.0f));
+    return vlerp(t, V(1.0f, 1.0f, 1.0f), V(0.5f, 0.7f, 1.0f));
+}
+
+}  // namespace crt

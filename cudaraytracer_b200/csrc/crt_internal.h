@@ -1,0 +1,108 @@
+// crt_internal.h — context and cross-file declarations of libcrt_b200.so.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+#include <string>
+
+#include "../../include/crt.h"
+#include "crt_device.cuh"
+
+namespace crt {
+
+void set_error(const char* fmt, ...);
+int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
+
+#define CRT_CUDA(call)                                                          \
+    do {                                                                        \
+        cudaError_t e__ = (call);                                               \
+        if (e__ != cudaSuccess) return crt::cuda_fail(e__, #call, __FILE__, __LINE__); \
+    } while (0)
+
+// Grow-only device allocation.
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    cudaError_t reserve(size_t bytes)
+    {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) { cudaFree(p); p = nullptr; cap = 0; }
+        size_t want = bytes + bytes / 8 + 256;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e != cudaSuccess) { (void)cudaGetLastError(); e = cudaMalloc(&p, bytes); want = bytes; }
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release()
+    {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+    template <class T> T* as() const { return (T*)p; }
+};
+
+// Device-side work counters, one 64-bit word each.
+enum { CNT_RAYS = 0, CNT_NODES, CNT_TRIS, CNT_SPHERES, CNT_SCATTERS, CNT_PATHS, CNT_COUNT };
+
+// Wavefront path state, 64 B = 4 x 128-bit words (SoA by word):
+//   w0 = {o.x, o.y, o.z, d.x}
+//   w1 = {d.y, d.z, path_id, ctr | depth_left << 24}
+//   w2, w3 = the material ids of the bounces so far, 16 bits each (<= 16 bounces)
+constexpr int CRT_MAX_DEPTH = 16;
+
+}  // namespace crt
+
+struct crt_ctx {
+    int device = 0;
+    int sm_count = 148;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+
+    // scene as uploaded (caller's order)
+    crt::DevBuf tri_in, tri_mat, tri_id;   // n_tri x 12 floats, u32, u32
+    crt::DevBuf sph_in, sph_mat, sph_id;   // n_sph x 4 floats
+    crt::DevBuf mats;                      // DMat
+    size_t n_tri = 0, n_sph = 0, n_mats = 0;
+
+    // LBVH
+    crt::DevBuf keys[2], vals[2], hist;
+    crt::DevBuf nodes, recs, info;
+    crt::DevBuf child, parent, leaf_parent, range, node_box, leaf_box, flags, bounds, depth_out;
+    bool accel_valid = false;
+    int root = 0;
+    int perm_buf = 0;                      // which vals[] holds the sorted permutation
+    uint32_t n_prims = 0;
+    int leaf_max = 4;
+    int tree_depth = 0;
+
+    // render
+    crt::DevBuf queue[2], qcount, rad, accum, rgb, rays_tmp, hits_tmp;
+    crt::DevBuf counters;                  // CNT_COUNT x uint64
+    int count_work = 0;
+    int64_t batch_paths = 1ll << 25;
+
+    crt_counters host_counters = {};
+};
+
+namespace crt {
+
+// radix_sort.cu
+int radix_sort_pairs(cudaStream_t stream, uint64_t* keys[2], uint32_t* vals[2], uint32_t n, int begin_bit,
+                     int end_bit, uint32_t* hist);
+size_t radix_sort_hist_bytes();
+
+// lbvh.cu
+int lbvh_build(crt_ctx* c, bool refit_only);
+
+// trace.cu
+int launch_trace(crt_ctx* c, const crt_ray* d_rays, size_t n, float t_min, float t_max, int accel, crt_hit* d_hits);
+AccelView accel_view(const crt_ctx* c);
+
+// render.cu
+int render_accum(crt_ctx* c, const crt_camera* cam, int nx, int ny, int s0, int s1, int max_depth, int mode,
+                 uint64_t seed, int rank, int world, float* d_accum);
+int launch_resolve(crt_ctx* c, const float* d_accum, size_t n_pixels, int spp, float* d_rgb);
+int launch_pack_rgba8(crt_ctx* c, const float* d_rgb, int nx, int ny, uint8_t* d_rgba8);
+
+}  // namespace crt

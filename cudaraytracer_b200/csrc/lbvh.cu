@@ -1,0 +1,363 @@
+// lbvh.cu — GPU LBVH build and refit.
+//
+// Replaces create_BVH<<<1,1>>> (createScene.h:42-44 -> hitable/bvh.h:76-125:
+// recursive median split with a sequential sort per node on ONE device thread)
+// and UpdateBVH<<<1,1>>> (createScene.h:46-58 -> hitable/bvh.h:135-158:
+// recursive refit on one thread) with data-parallel passes:
+//   1. k_scene_bounds : primitive boxes -> scene box (warp shuffles + float atomics)
+//   2. k_morton       : 63-bit Morton code of each box centre (21 bits per axis)
+//   3. radix_sort_pairs (radix_sort.cu): (code, primitive) pairs
+//   4. k_hierarchy    : Karras 2012 binary radix tree, one thread per internal
+//                       node, ties between equal codes broken by position
+//   5. k_fit          : one thread per sorted primitive writes its 48-byte record
+//                       and box, then climbs; the second thread to reach a node
+//                       (atomic flag) merges the children's boxes
+//   6. k_emit_nodes   : writes the 64-byte traversal nodes; subtrees covering
+//                       <= leaf_max primitives collapse into one leaf (a Karras
+//                       node always covers a contiguous range of sorted primitives)
+// Refit = steps 5 and 6 on the existing topology.
+#include "crt_internal.h"
+
+namespace crt {
+
+struct Box { float lx, ly, lz, hx, hy, hz; };
+
+__device__ __forceinline__ Box box_union(const Box& a, const Box& b)
+{
+    Box r;
+    r.lx = fminf(a.lx, b.lx); r.ly = fminf(a.ly, b.ly); r.lz = fminf(a.lz, b.lz);
+    r.hx = fmaxf(a.hx, b.hx); r.hy = fmaxf(a.hy, b.hy); r.hz = fmaxf(a.hz, b.hz);
+    return r;
+}
+
+// Box of input primitive p (triangles first, then spheres): the reference's
+// Triangle::bounding_box / Sphere::bounding_box + TransformAABB for a pure
+// translation (shapes/triangle.h:102-115, shapes/sphere.h:58-62,
+// hitable/transform.h:22-31), widened by a relative 2^-21 so that ulp-level
+// differences between the box test and the exact primitive test cannot cull a hit.
+__device__ __forceinline__ Box prim_box(const float* __restrict__ tri_in, const float* __restrict__ sph_in,
+                                        uint32_t n_tri, uint32_t p)
+{
+    Box b;
+    if (p < n_tri) {
+        const float* t = tri_in + 12 * (size_t)p;
+        const float x0 = t[0], y0 = t[1], z0 = t[2], x1 = t[3], y1 = t[4], z1 = t[5], x2 = t[6], y2 = t[7], z2 = t[8];
+        b.lx = fminf(x0, fminf(x1, x2)); b.ly = fminf(y0, fminf(y1, y2)); b.lz = fminf(z0, fminf(z1, z2));
+        b.hx = fmaxf(x0, fmaxf(x1, x2)); b.hy = fmaxf(y0, fmaxf(y1, y2)); b.hz = fmaxf(z0, fmaxf(z1, z2));
+    } else {
+        const float* s = sph_in + 4 * (size_t)(p - n_tri);
+        const float r = fabsf(s[3]);
+        b.lx = s[0] - r; b.ly = s[1] - r; b.lz = s[2] - r;
+        b.hx = s[0] + r; b.hy = s[1] + r; b.hz = s[2] + r;
+    }
+    const float k = 4.76837158e-7f;   // 2^-21
+    const float tiny = 1e-30f;
+    b.lx -= fabsf(b.lx) * k + tiny; b.ly -= fabsf(b.ly) * k + tiny; b.lz -= fabsf(b.lz) * k + tiny;
+    b.hx += fabsf(b.hx) * k + tiny; b.hy += fabsf(b.hy) * k + tiny; b.hz += fabsf(b.hz) * k + tiny;
+    return b;
+}
+
+__device__ __forceinline__ void atomic_min_f(float* a, float v)
+{
+    if (v >= 0.0f) atomicMin((int*)a, __float_as_int(v));
+    else atomicMax((unsigned int*)a, __float_as_uint(v));
+}
+__device__ __forceinline__ void atomic_max_f(float* a, float v)
+{
+    if (v >= 0.0f) atomicMax((int*)a, __float_as_int(v));
+    else atomicMin((unsigned int*)a, __float_as_uint(v));
+}
+
+__global__ void k_init_bounds(float* bounds)
+{
+    if (threadIdx.x < 3) bounds[threadIdx.x] = INFINITY;
+    else if (threadIdx.x < 6) bounds[threadIdx.x] = -INFINITY;
+}
+
+__global__ void __launch_bounds__(256)
+k_scene_bounds(const float* __restrict__ tri_in, const float* __restrict__ sph_in, uint32_t n_tri, uint32_t n,
+               float* __restrict__ bounds)
+{
+    Box b = {INFINITY, INFINITY, INFINITY, -INFINITY, -INFINITY, -INFINITY};
+    for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x)
+        b = box_union(b, prim_box(tri_in, sph_in, n_tri, p));
+    for (int o = 16; o > 0; o >>= 1) {
+        b.lx = fminf(b.lx, __shfl_xor_sync(0xffffffffu, b.lx, o));
+        b.ly = fminf(b.ly, __shfl_xor_sync(0xffffffffu, b.ly, o));
+        b.lz = fminf(b.lz, __shfl_xor_sync(0xffffffffu, b.lz, o));
+        b.hx = fmaxf(b.hx, __shfl_xor_sync(0xffffffffu, b.hx, o));
+        b.hy = fmaxf(b.hy, __shfl_xor_sync(0xffffffffu, b.hy, o));
+        b.hz = fmaxf(b.hz, __shfl_xor_sync(0xffffffffu, b.hz, o));
+    }
+    if ((threadIdx.x & 31) == 0 && b.lx <= b.hx) {
+        atomic_min_f(bounds + 0, b.lx); atomic_min_f(bounds + 1, b.ly); atomic_min_f(bounds + 2, b.lz);
+        atomic_max_f(bounds + 3, b.hx); atomic_max_f(bounds + 4, b.hy); atomic_max_f(bounds + 5, b.hz);
+    }
+}
+
+__device__ __forceinline__ uint64_t expand21(uint64_t v)
+{
+    v &= 0x1fffffull;
+    v = (v | v << 32) & 0x1f00000000ffffull;
+    v = (v | v << 16) & 0x1f0000ff0000ffull;
+    v = (v | v << 8) & 0x100f00f00f00f00full;
+    v = (v | v << 4) & 0x10c30c30c30c30c3ull;
+    v = (v | v << 2) & 0x1249249249249249ull;
+    return v;
+}
+
+__global__ void __launch_bounds__(256)
+k_morton(const float* __restrict__ tri_in, const float* __restrict__ sph_in, uint32_t n_tri, uint32_t n,
+         const float* __restrict__ bounds, uint64_t* __restrict__ keys, uint32_t* __restrict__ vals)
+{
+    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n) return;
+    const Box b = prim_box(tri_in, sph_in, n_tri, p);
+    const float lx = bounds[0], ly = bounds[1], lz = bounds[2];
+    const float ex = bounds[3] - lx, ey = bounds[4] - ly, ez = bounds[5] - lz;
+    const float scale = 2097152.0f;   // 2^21
+    const float fx = ex > 0.0f ? (0.5f * (b.lx + b.hx) - lx) / ex : 0.0f;
+    const float fy = ey > 0.0f ? (0.5f * (b.ly + b.hy) - ly) / ey : 0.0f;
+    const float fz = ez > 0.0f ? (0.5f * (b.lz + b.hz) - lz) / ez : 0.0f;
+    const uint64_t qx = (uint64_t)fminf(fmaxf(fx * scale, 0.0f), scale - 1.0f);
+    const uint64_t qy = (uint64_t)fminf(fmaxf(fy * scale, 0.0f), scale - 1.0f);
+    const uint64_t qz = (uint64_t)fminf(fmaxf(fz * scale, 0.0f), scale - 1.0f);
+    keys[p] = (expand21(qx) << 2) | (expand21(qy) << 1) | expand21(qz);
+    vals[p] = p;
+}
+
+// Common-prefix length of sorted codes i and j; equal codes fall back to the
+// positions so the tree stays a proper binary tree with duplicate codes.
+__device__ __forceinline__ int delta(const uint64_t* __restrict__ keys, int n, int i, int j)
+{
+    if (j < 0 || j >= n) return -1;
+    const uint64_t a = keys[i], b = keys[j];
+    if (a == b) return 64 + __clz(i ^ j);
+    return __clzll((long long)(a ^ b));
+}
+
+// Karras, "Maximizing Parallelism in the Construction of BVHs, Octrees, and
+// k-d Trees" (HPG 2012), Algorithm 1. child: >= 0 internal node, < 0: ~leaf position.
+__global__ void __launch_bounds__(256)
+k_hierarchy(const uint64_t* __restrict__ keys, int n, int2* __restrict__ child, int2* __restrict__ range,
+            int* __restrict__ parent, int* __restrict__ leaf_parent)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    const int d = (delta(keys, n, i, i + 1) - delta(keys, n, i, i - 1)) >= 0 ? 1 : -1;
+    const int dmin = delta(keys, n, i, i - d);
+    int lmax = 2;
+    while (delta(keys, n, i, i + lmax * d) > dmin) lmax *= 2;
+    int l = 0;
+    for (int t = lmax / 2; t >= 1; t /= 2)
+        if (delta(keys, n, i, i + (l + t) * d) > dmin) l += t;
+    const int j = i + l * d;
+    const int dnode = delta(keys, n, i, j);
+    int s = 0;
+    int t = l;
+    do {
+        t = (t + 1) >> 1;
+        if (delta(keys, n, i, i + (s + t) * d) > dnode) s += t;
+    } while (t > 1);
+    const int gamma = i + s * d + min(d, 0);
+    const int first = min(i, j), last = max(i, j);
+    const int left = (first == gamma) ? ~gamma : gamma;
+    const int right = (last == gamma + 1) ? ~(gamma + 1) : gamma + 1;
+    child[i] = make_int2(left, right);
+    range[i] = make_int2(first, last);
+    if (left < 0) leaf_parent[gamma] = i; else parent[left] = i;
+    if (right < 0) leaf_parent[gamma + 1] = i; else parent[right] = i;
+    if (i == 0) parent[0] = -1;
+}
+
+__device__ __forceinline__ Box load_box(const float4* __restrict__ base, size_t idx)
+{
+    const float4 a = __ldcg(base + 2 * idx), b = __ldcg(base + 2 * idx + 1);
+    Box r = {a.x, a.y, a.z, b.x, b.y, b.z};
+    return r;
+}
+__device__ __forceinline__ void store_box(float4* __restrict__ base, size_t idx, const Box& b)
+{
+    base[2 * idx] = make_float4(b.lx, b.ly, b.lz, 0.0f);
+    base[2 * idx + 1] = make_float4(b.hx, b.hy, b.hz, 0.0f);
+}
+
+__global__ void __launch_bounds__(256)
+k_fit(const float* __restrict__ tri_in, const uint32_t* __restrict__ tri_mat, const uint32_t* __restrict__ tri_id,
+      const float* __restrict__ sph_in, const uint32_t* __restrict__ sph_mat, const uint32_t* __restrict__ sph_id,
+      uint32_t n_tri, uint32_t n, const uint32_t* __restrict__ perm, const int2* __restrict__ child,
+      const int* __restrict__ parent, const int* __restrict__ leaf_parent, int* __restrict__ flags,
+      float4* __restrict__ recs, uint2* __restrict__ info, float4* __restrict__ leaf_box, float4* __restrict__ node_box)
+{
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    const uint32_t p = perm[k];
+    if (p < n_tri) {
+        const float* t = tri_in + 12 * (size_t)p;
+        const v3 v0 = V(t[0], t[1], t[2]);
+        const v3 e1 = vsub(V(t[3], t[4], t[5]), v0);       // triangle.h:69
+        const v3 e2 = vsub(V(t[6], t[7], t[8]), v0);       // triangle.h:70
+        recs[3 * (size_t)k] = make_float4(v0.x, v0.y, v0.z, t[9]);
+        recs[3 * (size_t)k + 1] = make_float4(e1.x, e1.y, e1.z, t[10]);
+        recs[3 * (size_t)k + 2] = make_float4(e2.x, e2.y, e2.z, t[11]);
+        info[k] = make_uint2(tri_id[p], tri_mat[p]);
+    } else {
+        const uint32_t q = p - n_tri;
+        const float* s = sph_in + 4 * (size_t)q;
+        recs[3 * (size_t)k] = make_float4(s[0], s[1], s[2], s[3]);
+        recs[3 * (size_t)k + 1] = make_float4(0.f, 0.f, 0.f, 0.f);
+        recs[3 * (size_t)k + 2] = make_float4(0.f, 0.f, 0.f, 0.f);
+        info[k] = make_uint2(sph_id[q], sph_mat[q] | CRT_KIND_SPHERE);
+    }
+    store_box(leaf_box, k, prim_box(tri_in, sph_in, n_tri, p));
+    if (n < 2) return;
+    __threadfence();
+    int node = leaf_parent[k];
+    while (node >= 0) {
+        if (atomicAdd(&flags[node], 1) == 0) return;       // first arrival: the sibling is not done
+        __threadfence();
+        const int2 ch = child[node];
+        const Box a = ch.x < 0 ? load_box(leaf_box, (size_t)(~ch.x)) : load_box(node_box, (size_t)ch.x);
+        const Box b = ch.y < 0 ? load_box(leaf_box, (size_t)(~ch.y)) : load_box(node_box, (size_t)ch.y);
+        store_box(node_box, (size_t)node, box_union(a, b));
+        __threadfence();
+        node = parent[node];
+    }
+}
+
+__global__ void __launch_bounds__(256)
+k_emit_nodes(int n, int leaf_max, const int2* __restrict__ child, const int2* __restrict__ range,
+             const float4* __restrict__ leaf_box, const float4* __restrict__ node_box, float4* __restrict__ nodes)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    const int2 rg = range[i];
+    if (rg.y - rg.x + 1 <= leaf_max) return;               // collapsed into a leaf of an ancestor
+    const int2 ch = child[i];
+    int ref[2];
+    Box bx[2];
+    const int cc[2] = {ch.x, ch.y};
+#pragma unroll
+    for (int s = 0; s < 2; s++) {
+        const int c = cc[s];
+        if (c < 0) {
+            const uint32_t pos = (uint32_t)(~c);
+            ref[s] = ~(int)(pos << 3);
+            bx[s] = load_box(leaf_box, pos);
+        } else {
+            const int2 cr = range[c];
+            const int size = cr.y - cr.x + 1;
+            ref[s] = size <= leaf_max ? ~(int)(((uint32_t)cr.x << 3) | (uint32_t)(size - 1)) : c;
+            bx[s] = load_box(node_box, (size_t)c);
+        }
+    }
+    float4* np = nodes + 4 * (size_t)i;
+    np[0] = make_float4(bx[0].lx, bx[0].hx, bx[0].ly, bx[0].hy);
+    np[1] = make_float4(bx[1].lx, bx[1].hx, bx[1].ly, bx[1].hy);
+    np[2] = make_float4(bx[0].lz, bx[0].hz, bx[1].lz, bx[1].hz);
+    np[3] = make_float4(__int_as_float(ref[0]), __int_as_float(ref[1]), 0.0f, 0.0f);
+}
+
+__global__ void __launch_bounds__(256)
+k_depth(int n, const int* __restrict__ parent, const int* __restrict__ leaf_parent, int* __restrict__ out)
+{
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    int d = 1;
+    for (int node = leaf_parent[k]; node >= 0; node = parent[node]) d++;
+    const unsigned int act = __activemask();
+    d = __reduce_max_sync(act, d);
+    if ((threadIdx.x & 31) == (unsigned int)(__ffs(act) - 1)) atomicMax(out, d);
+}
+
+static inline unsigned int grid_for(size_t n, int block) { return (unsigned int)((n + block - 1) / block); }
+
+int lbvh_build(crt_ctx* c, bool refit_only)
+{
+    const size_t n = c->n_tri + c->n_sph;
+    if (n >= (1ull << 28)) { set_error("too many primitives (%zu), limit is 2^28", n); return CRT_ERR_INVALID; }
+    cudaStream_t st = c->stream;
+    if (refit_only && (!c->accel_valid || c->n_prims != (uint32_t)n)) {
+        set_error("crt_accel_refit: no acceleration structure for the current primitive count");
+        return CRT_ERR_STATE;
+    }
+    c->n_prims = (uint32_t)n;
+    CRT_CUDA(cudaEventRecord(c->ev0, st));
+    if (n == 0) {
+        c->accel_valid = true;
+        c->root = -1;
+        c->tree_depth = 0;
+        CRT_CUDA(cudaEventRecord(c->ev1, st));
+        CRT_CUDA(cudaEventSynchronize(c->ev1));
+        return CRT_OK;
+    }
+    const float* tri_in = c->tri_in.as<float>();
+    const float* sph_in = c->sph_in.as<float>();
+    const uint32_t n_tri = (uint32_t)c->n_tri;
+    const uint32_t un = (uint32_t)n;
+
+    if (!refit_only) {
+        CRT_CUDA(c->keys[0].reserve(n * 8)); CRT_CUDA(c->keys[1].reserve(n * 8));
+        CRT_CUDA(c->vals[0].reserve(n * 4)); CRT_CUDA(c->vals[1].reserve(n * 4));
+        CRT_CUDA(c->hist.reserve(radix_sort_hist_bytes()));
+        CRT_CUDA(c->bounds.reserve(6 * sizeof(float)));
+        CRT_CUDA(c->recs.reserve(n * 48));
+        CRT_CUDA(c->info.reserve(n * 8));
+        CRT_CUDA(c->leaf_box.reserve(n * 32));
+        CRT_CUDA(c->leaf_parent.reserve(n * 4));
+        CRT_CUDA(c->depth_out.reserve(sizeof(int)));
+        const size_t ni = n > 1 ? n - 1 : 1;
+        CRT_CUDA(c->nodes.reserve(ni * 64));
+        CRT_CUDA(c->child.reserve(ni * 8));
+        CRT_CUDA(c->range.reserve(ni * 8));
+        CRT_CUDA(c->parent.reserve(ni * 4));
+        CRT_CUDA(c->node_box.reserve(ni * 32));
+        CRT_CUDA(c->flags.reserve(ni * 4));
+
+        k_init_bounds<<<1, 32, 0, st>>>(c->bounds.as<float>());
+        const unsigned int gb = min(grid_for(n, 256), (unsigned int)(c->sm_count * 8));
+        k_scene_bounds<<<gb, 256, 0, st>>>(tri_in, sph_in, n_tri, un, c->bounds.as<float>());
+        k_morton<<<grid_for(n, 256), 256, 0, st>>>(tri_in, sph_in, n_tri, un, c->bounds.as<float>(),
+                                                    c->keys[0].as<uint64_t>(), c->vals[0].as<uint32_t>());
+        uint64_t* keys[2] = {c->keys[0].as<uint64_t>(), c->keys[1].as<uint64_t>()};
+        uint32_t* vals[2] = {c->vals[0].as<uint32_t>(), c->vals[1].as<uint32_t>()};
+        c->perm_buf = radix_sort_pairs(st, keys, vals, un, 0, 64, c->hist.as<uint32_t>());
+        if (n > 1)
+            k_hierarchy<<<grid_for(n - 1, 256), 256, 0, st>>>(keys[c->perm_buf], (int)n, c->child.as<int2>(),
+                                                              c->range.as<int2>(), c->parent.as<int>(),
+                                                              c->leaf_parent.as<int>());
+    }
+    if (n > 1) CRT_CUDA(cudaMemsetAsync(c->flags.p, 0, (n - 1) * 4, st));
+    k_fit<<<grid_for(n, 256), 256, 0, st>>>(tri_in, c->tri_mat.as<uint32_t>(), c->tri_id.as<uint32_t>(), sph_in,
+                                            c->sph_mat.as<uint32_t>(), c->sph_id.as<uint32_t>(), n_tri, un,
+                                            c->vals[c->perm_buf].as<uint32_t>(), c->child.as<int2>(),
+                                            c->parent.as<int>(), c->leaf_parent.as<int>(), c->flags.as<int>(),
+                                            c->recs.as<float4>(), c->info.as<uint2>(), c->leaf_box.as<float4>(),
+                                            c->node_box.as<float4>());
+    const int leaf_max = c->leaf_max;
+    if (n > 1)
+        k_emit_nodes<<<grid_for(n - 1, 256), 256, 0, st>>>((int)n, leaf_max, c->child.as<int2>(), c->range.as<int2>(),
+                                                           c->leaf_box.as<float4>(), c->node_box.as<float4>(),
+                                                           c->nodes.as<float4>());
+    c->root = (n <= (size_t)leaf_max) ? ~(int)(n - 1) : 0;
+    CRT_CUDA(cudaEventRecord(c->ev1, st));
+    if (!refit_only) {
+        CRT_CUDA(cudaMemsetAsync(c->depth_out.p, 0, sizeof(int), st));
+        if (n > 1)
+            k_depth<<<grid_for(n, 256), 256, 0, st>>>((int)n, c->parent.as<int>(), c->leaf_parent.as<int>(),
+                                                      c->depth_out.as<int>());
+        int depth = 1;
+        CRT_CUDA(cudaMemcpyAsync(&depth, c->depth_out.p, sizeof(int), cudaMemcpyDeviceToHost, st));
+        CRT_CUDA(cudaStreamSynchronize(st));
+        c->tree_depth = n > 1 ? depth : 1;
+    }
+    CRT_CUDA(cudaEventSynchronize(c->ev1));
+    CRT_CUDA(cudaGetLastError());
+    float ms = 0.f;
+    CRT_CUDA(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+    if (refit_only) c->host_counters.refit_ms = ms; else c->host_counters.build_ms = ms;
+    c->accel_valid = true;
+    return CRT_OK;
+}
+
+}  // namespace crt

@@ -1,0 +1,423 @@
+// render.cu — wavefront path tracer behind crt_render*.
+//
+// Replaces the reference's render<<<>>> kernel (core/render.h:105-129: one
+// thread per pixel, a serial spp loop, recursive shade() with virtual scatter
+// calls on a 16 KiB per-thread stack) with a wavefront over camera samples:
+//
+//   k_raygen      one thread per (pixel, sample): jitter + Camera::get_ray
+//                 (render.h:116-118, camera.h:40-44) -> path queue
+//   k_bounce      one launch per bounce over the live queue: LBVH closest hit
+//                 (crt_traverse.cuh), material scatter (material.h:57-143), and
+//                 either a new ray into the next queue (warp-ballot compaction,
+//                 one atomic per warp) or the path's radiance
+//   k_accumulate  per pixel, adds the batch's samples IN SAMPLE ORDER, as the
+//                 reference's "col += shade(...)" loop does (render.h:115-122)
+//   k_resolve     col /= ns; sqrt; clip (render.h:123-128)
+//   k_pack_rgba8  WritePng's float -> RGBA8 + vertical flip (render.h:137-146)
+//
+// shade() is a recursion "emitted + attenuation * shade(next)" (render.h:58).
+// A path therefore records the material id of every bounce (16 bits each in
+// its queue entry) and, when it ends, folds the product from the innermost
+// term outwards, which gives the same rounding as the recursion.
+//
+// Random numbers: include/crt_rng.h, keyed by (seed, pixel, sample); a path
+// carries only its draw counter.
+#include "crt_internal.h"
+#include "crt_traverse.cuh"
+
+namespace crt {
+
+constexpr int RB = 128;   // threads per block of the wavefront kernels
+
+struct RenderParams {
+    DCamera cam;
+    int nx, ny;
+    int tiles_x;
+    int rank, world;
+    uint32_t n_slots;     // local tiles * CRT_TILE^2
+    int s_begin;          // first sample index of this batch
+    int s_count;          // samples in this batch
+    int max_depth;
+    int mode;
+    uint64_t seed;
+    uint32_t cap;         // queue capacity (entries per SoA word)
+};
+
+// slot -> pixel. 10 low bits address a pixel inside a 32x32 tile so that 32
+// consecutive slots (one warp) cover an 8x4 block.
+__device__ __forceinline__ bool slot_to_pixel(const RenderParams& P, uint32_t slot, int& x, int& y)
+{
+    const uint32_t lt = slot >> 10, s = slot & 1023u;
+    const uint32_t t = lt * (uint32_t)P.world + (uint32_t)P.rank;
+    const uint32_t ty = t / (uint32_t)P.tiles_x, tx = t - ty * (uint32_t)P.tiles_x;
+    const uint32_t px = (s & 7u) | (((s >> 5) & 3u) << 3);
+    const uint32_t py = ((s >> 3) & 3u) | (((s >> 7) & 7u) << 2);
+    x = (int)(tx * CRT_TILE + px);
+    y = (int)(ty * CRT_TILE + py);
+    return x < P.nx && y < P.ny;
+}
+
+// Warp-aggregated append: every lane of the warp must call this.
+__device__ __forceinline__ uint32_t warp_append(bool want, uint32_t* counter)
+{
+    const uint32_t m = __ballot_sync(0xffffffffu, want);
+    if (m == 0u) return 0u;
+    const uint32_t lane = threadIdx.x & 31u;
+    const int leader = __ffs(m) - 1;
+    uint32_t base = 0;
+    if ((int)lane == leader) base = atomicAdd(counter, (uint32_t)__popc(m));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    return base + (uint32_t)__popc(m & ((1u << lane) - 1u));
+}
+
+__global__ void __launch_bounds__(RB)
+k_raygen(RenderParams P, float4* __restrict__ q, uint32_t* __restrict__ q_count)
+{
+    const uint32_t total = P.n_slots * (uint32_t)P.s_count;
+    const uint32_t lane = threadIdx.x & 31u;
+    for (uint32_t base = (blockIdx.x * RB + (threadIdx.x & ~31u)); base < total; base += gridDim.x * RB) {
+        const uint32_t id = base + lane;
+        bool live = id < total;
+        float4 w0 = make_float4(0, 0, 0, 0), w1 = w0;
+        if (live) {
+            const uint32_t s_local = id / P.n_slots;
+            const uint32_t slot = id - s_local * P.n_slots;
+            int x, y;
+            live = slot_to_pixel(P, slot, x, y);
+            if (live) {
+                const uint32_t pixel = (uint32_t)y * (uint32_t)P.nx + (uint32_t)x;
+                Rng rng;
+                rng.key = crt_rng_key(P.seed, pixel, (uint32_t)(P.s_begin + (int)s_local));
+                rng.ctr = 0;
+                const float u = x::div(x::add((float)x, rnd(rng)), (float)P.nx);   // render.h:116
+                const float v = x::div(x::add((float)y, rnd(rng)), (float)P.ny);   // render.h:117
+                v3 o, d;
+                camera_get_ray(P.cam, u, v, rng, o, d);                            // render.h:118
+                w0 = make_float4(o.x, o.y, o.z, d.x);
+                w1 = make_float4(d.y, d.z, __uint_as_float(id), __uint_as_float(rng.ctr | ((uint32_t)P.max_depth << 24)));
+            }
+        }
+        const uint32_t pos = warp_append(live, q_count);
+        if (live) {
+            q[pos] = w0;
+            q[(size_t)P.cap + pos] = w1;
+            q[2 * (size_t)P.cap + pos] = make_float4(0, 0, 0, 0);
+            q[3 * (size_t)P.cap + pos] = make_float4(0, 0, 0, 0);
+        }
+    }
+}
+
+// attenuation a finished bounce contributed, by material (material.h:69,90,111)
+__device__ __forceinline__ v3 bounce_attenuation(const DMat& m)
+{
+    return m.type == 2u ? V(1.0f, 1.0f, 1.0f) : V(m.r, m.g, m.b);
+}
+
+__device__ __forceinline__ DMat load_mat(const DMat* __restrict__ mats, uint32_t id)
+{
+    const float4* p = reinterpret_cast<const float4*>(mats + id);
+    const float4 a = __ldg(p);
+    const uint4 b = __ldg(reinterpret_cast<const uint4*>(p + 1));
+    DMat m;
+    m.r = a.x; m.g = a.y; m.b = a.z; m.param = a.w; m.type = b.x; m.pad0 = m.pad1 = m.pad2 = 0;
+    return m;
+}
+
+template <bool COUNT, bool HAS_SPH>
+__global__ void __launch_bounds__(RB)
+k_bounce(RenderParams P, AccelView A, const DMat* __restrict__ mats, const float4* __restrict__ q_in,
+         const uint32_t* __restrict__ n_in_ptr, float4* __restrict__ q_out, uint32_t* __restrict__ n_out_ptr,
+         float4* __restrict__ rad, unsigned long long* __restrict__ counters)
+{
+    __shared__ int s_stack[CRT_STACK_SMEM * RB];
+    const uint32_t n_in = *n_in_ptr;
+    const uint32_t lane = threadIdx.x & 31u;
+    TraceCounters cnt = {0u, 0u, 0u};
+    uint32_t n_scatter = 0;
+
+    for (uint32_t base = (blockIdx.x * RB + (threadIdx.x & ~31u)); base < n_in; base += gridDim.x * RB) {
+        const uint32_t i = base + lane;
+        const bool live = i < n_in;
+        bool next = false;
+        float4 w0 = make_float4(0, 0, 0, 0), w1 = w0;
+        uint32_t ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        if (live) {
+            w0 = q_in[i];
+            w1 = q_in[(size_t)P.cap + i];
+            const uint4 a2 = reinterpret_cast<const uint4*>(q_in)[2 * (size_t)P.cap + i];
+            const uint4 a3 = reinterpret_cast<const uint4*>(q_in)[3 * (size_t)P.cap + i];
+            ms[0] = a2.x; ms[1] = a2.y; ms[2] = a2.z; ms[3] = a2.w;
+            ms[4] = a3.x; ms[5] = a3.y; ms[6] = a3.z; ms[7] = a3.w;
+            const v3 o = V(w0.x, w0.y, w0.z), d = V(w0.w, w1.x, w1.y);
+            const uint32_t path_id = __float_as_uint(w1.z);
+            const uint32_t pack = __float_as_uint(w1.w);
+            const int depth_left = (int)(pack >> 24);
+            const int bounces = P.max_depth - depth_left;
+            Rng rng;
+            {
+                const uint32_t s_local = path_id / P.n_slots;
+                const uint32_t slot = path_id - s_local * P.n_slots;
+                int px, py;
+                slot_to_pixel(P, slot, px, py);
+                rng.key = crt_rng_key(P.seed, (uint32_t)py * (uint32_t)P.nx + (uint32_t)px, (uint32_t)(P.s_begin + (int)s_local));
+                rng.ctr = pack & 0xFFFFFFu;
+            }
+
+            const v3 dl = ray_dir_local(d);
+            Hit h;
+            traverse<COUNT, HAS_SPH>(A, o, dl, 0.001f, FLT_MAX, h, s_stack + threadIdx.x, RB, cnt);   // render.h:53
+
+            v3 L;
+            if (h.id == CRT_MISS_ID) {
+                L = background_sky(d);                                             // render.h:65
+            } else {
+                const uint2 inf = __ldg(&A.info[h.k]);
+                const float4 r0 = ldg4(A.recs + 3 * (size_t)h.k);
+                v3 p, n;
+                if (HAS_SPH && (inf.y & CRT_KIND_SPHERE)) {
+                    p = vadd(vsub(o, V(r0.x, r0.y, r0.z)), vscale(h.t, dl));       // sphere.h:40 (local frame)
+                    n = vdivf(p, r0.w);                                            // sphere.h:41
+                } else {
+                    const float4 r1 = ldg4(A.recs + 3 * (size_t)h.k + 1), r2 = ldg4(A.recs + 3 * (size_t)h.k + 2);
+                    p = vadd(o, vscale(h.t, dl));                                  // triangle.h:95
+                    n = V(r0.w, r1.w, r2.w);                                       // triangle.h:96
+                }
+                const uint32_t mat_id = inf.y & 0x7FFFFFFFu;
+                const DMat m = load_mat(mats, mat_id);
+                const v3 e = emitted(m);                                           // render.h:56
+                if (P.mode == CRT_SHADE_PATH) {
+                    v3 att, out_d;
+                    if (COUNT && depth_left > 0) n_scatter++;
+                    if (depth_left > 0 && scatter(m, d, p, n, rng, att, out_d)) {  // render.h:57
+                        next = true;
+#pragma unroll
+                        for (int j = 0; j < 8; j++)
+                            if (j == (bounces >> 1))
+                                ms[j] = (bounces & 1) ? ((ms[j] & 0xFFFFu) | (mat_id << 16)) : (mat_id & 0xFFFFu);
+                        w0 = make_float4(p.x, p.y, p.z, out_d.x);
+                        w1 = make_float4(out_d.y, out_d.z, __uint_as_float(path_id),
+                                         __uint_as_float((rng.ctr & 0xFFFFFFu) | ((uint32_t)(depth_left - 1) << 24)));
+                    } else {
+                        L = vadd(e, V(0.1f, 0.1f, 0.1f));                          // render.h:61
+                    }
+                } else if (P.mode == CRT_SHADE_LAMBERT) {                          // render.h:70-87
+                    v3 att, out_d;
+                    if (COUNT) n_scatter++;
+                    scatter(m, d, p, n, rng, att, out_d);
+                    float c = vdot(d, n);
+                    if (c < 0.0f) c = 0.0f;
+                    L = vadd(vscale(0.2f, vmul(vscale(c, att), background_sky(d))), e);
+                } else {                                                           // render.h:90-103
+                    L = n;
+                }
+            }
+            if (!next) {
+                // unwind "emitted + attenuation * shade(next)" (render.h:58), innermost first
+#pragma unroll
+                for (int j = CRT_MAX_DEPTH - 1; j >= 0; j--) {
+                    if (j < bounces) {
+                        const uint32_t id = (ms[j >> 1] >> ((j & 1) * 16)) & 0xFFFFu;
+                        const DMat mj = load_mat(mats, id);
+                        L = vadd(emitted(mj), vmul(bounce_attenuation(mj), L));
+                    }
+                }
+                rad[path_id] = make_float4(L.x, L.y, L.z, 0.0f);
+            }
+        }
+        const uint32_t pos = warp_append(next, n_out_ptr);
+        if (next) {
+            q_out[pos] = w0;
+            q_out[(size_t)P.cap + pos] = w1;
+            reinterpret_cast<uint4*>(q_out)[2 * (size_t)P.cap + pos] = make_uint4(ms[0], ms[1], ms[2], ms[3]);
+            reinterpret_cast<uint4*>(q_out)[3 * (size_t)P.cap + pos] = make_uint4(ms[4], ms[5], ms[6], ms[7]);
+        }
+    }
+    if (COUNT) {
+        const uint32_t nodes = __reduce_add_sync(0xffffffffu, cnt.nodes);
+        const uint32_t tris = __reduce_add_sync(0xffffffffu, cnt.tris);
+        const uint32_t sph = __reduce_add_sync(0xffffffffu, cnt.spheres);
+        const uint32_t sc = __reduce_add_sync(0xffffffffu, n_scatter);
+        if (lane == 0) {
+            atomicAdd(counters + CNT_NODES, (unsigned long long)nodes);
+            atomicAdd(counters + CNT_TRIS, (unsigned long long)tris);
+            atomicAdd(counters + CNT_SPHERES, (unsigned long long)sph);
+            atomicAdd(counters + CNT_SCATTERS, (unsigned long long)sc);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256)
+k_accumulate(RenderParams P, const float4* __restrict__ rad, float* __restrict__ accum)
+{
+    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+    if (slot >= P.n_slots) return;
+    int x, y;
+    if (!slot_to_pixel(P, slot, x, y)) return;
+    const size_t pixel = (size_t)y * P.nx + x;
+    v3 col = V(accum[3 * pixel], accum[3 * pixel + 1], accum[3 * pixel + 2]);
+    for (int s = 0; s < P.s_count; s++) {
+        const float4 r = rad[(size_t)s * P.n_slots + slot];
+        col = vadd(col, V(r.x, r.y, r.z));                                         // render.h:119-121
+    }
+    accum[3 * pixel] = col.x;
+    accum[3 * pixel + 1] = col.y;
+    accum[3 * pixel + 2] = col.z;
+}
+
+__global__ void __launch_bounds__(256)
+k_resolve(const float* __restrict__ accum, size_t n_values, float inv_ns, float* __restrict__ rgb)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_values) return;
+    rgb[i] = clip01(x::sqrt(x::mul(accum[i], inv_ns)));                            // render.h:123-128, vec3.h:182-189
+}
+
+__global__ void __launch_bounds__(256)
+k_pack_rgba8(const float* __restrict__ rgb, int nx, int ny, uchar4* __restrict__ out)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (size_t)nx * ny) return;
+    const int row = (int)(i / nx), col = (int)(i - (size_t)row * nx);
+    const size_t src = (size_t)(ny - 1 - row) * nx + col;                          // render.h:140
+    uchar4 o;
+    o.x = (unsigned char)(int)(255.99 * (double)rgb[3 * src]);                     // render.h:141-143
+    o.y = (unsigned char)(int)(255.99 * (double)rgb[3 * src + 1]);
+    o.z = (unsigned char)(int)(255.99 * (double)rgb[3 * src + 2]);
+    o.w = 255;
+    out[i] = o;
+}
+
+static DCamera to_dcamera(const crt_camera* c)
+{
+    DCamera d;
+    d.llc = V(c->lower_left_corner[0], c->lower_left_corner[1], c->lower_left_corner[2]);
+    d.horizontal = V(c->horizontal[0], c->horizontal[1], c->horizontal[2]);
+    d.vertical = V(c->vertical[0], c->vertical[1], c->vertical[2]);
+    d.origin = V(c->origin[0], c->origin[1], c->origin[2]);
+    d.x = V(c->x[0], c->x[1], c->x[2]);
+    d.y = V(c->y[0], c->y[1], c->y[2]);
+    d.z = V(c->z[0], c->z[1], c->z[2]);
+    d.lens_radius = c->lens_radius;
+    return d;
+}
+
+template <bool COUNT, bool HAS_SPH>
+static void launch_bounce(crt_ctx* c, int grid, const RenderParams& P, const AccelView& A, const float4* q_in,
+                          const uint32_t* n_in, float4* q_out, uint32_t* n_out)
+{
+    k_bounce<COUNT, HAS_SPH><<<grid, RB, 0, c->stream>>>(P, A, c->mats.as<DMat>(), q_in, n_in, q_out, n_out,
+                                                         c->rad.as<float4>(), c->counters.as<unsigned long long>());
+}
+
+int render_accum(crt_ctx* c, const crt_camera* cam, int nx, int ny, int s0, int s1, int max_depth, int mode,
+                 uint64_t seed, int rank, int world, float* d_accum)
+{
+    if (!cam || nx <= 0 || ny <= 0 || s1 < s0 || !d_accum) { set_error("crt_render: bad arguments"); return CRT_ERR_INVALID; }
+    if (max_depth < 0 || max_depth > CRT_MAX_DEPTH) { set_error("crt_render: max_depth must be in [0, %d]", CRT_MAX_DEPTH); return CRT_ERR_INVALID; }
+    if (mode < 0 || mode > 2) { set_error("crt_render: unknown shade mode %d", mode); return CRT_ERR_INVALID; }
+    if (world < 1 || rank < 0 || rank >= world) { set_error("crt_render: bad rank/world %d/%d", rank, world); return CRT_ERR_INVALID; }
+    if (!c->accel_valid) { set_error("crt_render: call crt_accel_build first"); return CRT_ERR_STATE; }
+    if (c->n_prims > 0 && c->n_mats == 0) { set_error("crt_render: no materials set"); return CRT_ERR_STATE; }
+    cudaStream_t st = c->stream;
+
+    RenderParams P;
+    P.cam = to_dcamera(cam);
+    P.nx = nx; P.ny = ny;
+    P.tiles_x = (nx + CRT_TILE - 1) / CRT_TILE;
+    const int tiles_y = (ny + CRT_TILE - 1) / CRT_TILE;
+    const long long tiles = (long long)P.tiles_x * tiles_y;
+    const long long local_tiles = tiles > rank ? (tiles - rank + world - 1) / world : 0;
+    P.rank = rank; P.world = world;
+    if (local_tiles * CRT_TILE * CRT_TILE >= (1ll << 31)) { set_error("crt_render: image too large"); return CRT_ERR_INVALID; }
+    P.n_slots = (uint32_t)(local_tiles * CRT_TILE * CRT_TILE);
+    P.max_depth = max_depth; P.mode = mode; P.seed = seed;
+
+    CRT_CUDA(cudaEventRecord(c->ev0, st));
+    CRT_CUDA(cudaMemsetAsync(d_accum, 0, (size_t)nx * ny * 3 * sizeof(float), st));
+    const int n_samples = s1 - s0;
+    uint64_t total_rays = 0, total_paths = 0;
+    if (P.n_slots > 0 && n_samples > 0) {
+        long long per_batch = c->batch_paths / (long long)P.n_slots;
+        if (per_batch < 1) per_batch = 1;
+        if (per_batch > n_samples) per_batch = n_samples;
+        while ((long long)P.n_slots * per_batch >= (1ll << 31) && per_batch > 1) per_batch--;
+        const size_t cap = (size_t)P.n_slots * (size_t)per_batch;
+        P.cap = (uint32_t)cap;
+        CRT_CUDA(c->queue[0].reserve(cap * 64));
+        CRT_CUDA(c->queue[1].reserve(cap * 64));
+        CRT_CUDA(c->rad.reserve(cap * 16));
+        const int n_levels = CRT_MAX_DEPTH + 3;
+        CRT_CUDA(c->qcount.reserve(sizeof(uint32_t) * n_levels));
+        uint32_t h_counts[CRT_MAX_DEPTH + 3];
+
+        int bps = 1;
+        int grid;
+        {
+            // all four instantiations have the same resource needs; size the persistent grid from one
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_bounce<false, false>, RB, 0);
+            if (bps < 1) bps = 1;
+            grid = c->sm_count * bps;
+        }
+        const AccelView A = accel_view(c);
+        const bool sph = c->n_sph > 0;
+        const int bounces = mode == CRT_SHADE_PATH ? max_depth + 1 : 1;
+
+        for (int sb = s0; sb < s1; sb += (int)per_batch) {
+            P.s_begin = sb;
+            P.s_count = (s1 - sb) < per_batch ? (s1 - sb) : (int)per_batch;
+            CRT_CUDA(cudaMemsetAsync(c->qcount.p, 0, sizeof(uint32_t) * n_levels, st));
+            const uint32_t total = P.n_slots * (uint32_t)P.s_count;
+            const unsigned int rg = (unsigned int)min((size_t)(total + RB - 1) / RB, (size_t)c->sm_count * 32);
+            k_raygen<<<rg, RB, 0, st>>>(P, c->queue[0].as<float4>(), c->qcount.as<uint32_t>());
+            for (int b = 0; b < bounces; b++) {
+                const float4* qi = c->queue[b & 1].as<float4>();
+                float4* qo = c->queue[(b + 1) & 1].as<float4>();
+                const uint32_t* ni = c->qcount.as<uint32_t>() + b;
+                uint32_t* no = c->qcount.as<uint32_t>() + b + 1;
+                if (c->count_work) {
+                    if (sph) launch_bounce<true, true>(c, grid, P, A, qi, ni, qo, no);
+                    else launch_bounce<true, false>(c, grid, P, A, qi, ni, qo, no);
+                } else {
+                    if (sph) launch_bounce<false, true>(c, grid, P, A, qi, ni, qo, no);
+                    else launch_bounce<false, false>(c, grid, P, A, qi, ni, qo, no);
+                }
+            }
+            k_accumulate<<<(P.n_slots + 255) / 256, 256, 0, st>>>(P, c->rad.as<float4>(), d_accum);
+            CRT_CUDA(cudaMemcpyAsync(h_counts, c->qcount.p, sizeof(uint32_t) * n_levels, cudaMemcpyDeviceToHost, st));
+            CRT_CUDA(cudaStreamSynchronize(st));
+            total_paths += h_counts[0];
+            for (int b = 0; b < bounces; b++) total_rays += h_counts[b];
+        }
+    }
+    CRT_CUDA(cudaEventRecord(c->ev1, st));
+    CRT_CUDA(cudaEventSynchronize(c->ev1));
+    CRT_CUDA(cudaGetLastError());
+    float ms = 0.f;
+    CRT_CUDA(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+    c->host_counters.render_ms = ms;
+    c->host_counters.rays += total_rays;
+    c->host_counters.paths += total_paths;
+    return CRT_OK;
+}
+
+int launch_resolve(crt_ctx* c, const float* d_accum, size_t n_pixels, int spp, float* d_rgb)
+{
+    if (spp < 1) { set_error("crt_resolve: spp must be >= 1"); return CRT_ERR_INVALID; }
+    const size_t nv = n_pixels * 3;
+    if (nv == 0) return CRT_OK;
+    const float inv_ns = 1.0f / (float)spp;   // float(1.0 / t), vec3.h:183 (correctly rounded either way)
+    k_resolve<<<(unsigned int)((nv + 255) / 256), 256, 0, c->stream>>>(d_accum, nv, inv_ns, d_rgb);
+    CRT_CUDA(cudaGetLastError());
+    return CRT_OK;
+}
+
+int launch_pack_rgba8(crt_ctx* c, const float* d_rgb, int nx, int ny, uint8_t* d_rgba8)
+{
+    const size_t n = (size_t)nx * ny;
+    if (n == 0) return CRT_OK;
+    k_pack_rgba8<<<(unsigned int)((n + 255) / 256), 256, 0, c->stream>>>(d_rgb, nx, ny, reinterpret_cast<uchar4*>(d_rgba8));
+    CRT_CUDA(cudaGetLastError());
+    return CRT_OK;
+}
+
+}  // namespace crt

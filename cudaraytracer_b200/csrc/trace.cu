@@ -1,0 +1,170 @@
+// trace.cu — closest-hit kernels behind crt_trace / crt_trace_device:
+//   k_trace_lbvh  : one ray per thread through the LBVH (crt_traverse.cuh)
+//   k_trace_brute : the reference's linear scan (hitable/hitable_list.h:76-91)
+//                   over the primitives exactly as uploaded; primitives are
+//                   staged through shared memory and every thread of the block
+//                   tests them against its own ray. It shares no code with the
+//                   LBVH build or traversal, which makes it the on-GPU cross
+//                   check of both, and it serves scenes before crt_accel_build.
+#include "crt_internal.h"
+#include "crt_traverse.cuh"
+
+namespace crt {
+
+constexpr int TRACE_BLOCK = 128;
+
+AccelView accel_view(const crt_ctx* c)
+{
+    AccelView a;
+    a.nodes = c->nodes.as<float4>();
+    a.recs = c->recs.as<float4>();
+    a.info = c->info.as<uint2>();
+    a.root = c->root;
+    a.n_prims = c->n_prims;
+    return a;
+}
+
+__device__ __forceinline__ void load_ray(const crt_ray* __restrict__ rays, size_t i, v3& o, v3& d)
+{
+    const float2* p = reinterpret_cast<const float2*>(rays + i);   // 24-byte records, 8-byte aligned
+    const float2 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
+    o = V(a.x, a.y, b.x);
+    d = V(b.y, c.x, c.y);
+}
+
+__device__ __forceinline__ void flush_counters(unsigned long long* counters, const TraceCounters& cnt, uint32_t rays)
+{
+    const unsigned int act = __activemask();
+    const uint32_t nodes = __reduce_add_sync(act, cnt.nodes);
+    const uint32_t tris = __reduce_add_sync(act, cnt.tris);
+    const uint32_t sph = __reduce_add_sync(act, cnt.spheres);
+    const uint32_t r = __reduce_add_sync(act, rays);
+    if ((threadIdx.x & 31) == (unsigned int)(__ffs(act) - 1)) {
+        atomicAdd(counters + CNT_NODES, (unsigned long long)nodes);
+        atomicAdd(counters + CNT_TRIS, (unsigned long long)tris);
+        atomicAdd(counters + CNT_SPHERES, (unsigned long long)sph);
+        atomicAdd(counters + CNT_RAYS, (unsigned long long)r);
+    }
+}
+
+template <bool COUNT, bool HAS_SPH>
+__global__ void __launch_bounds__(TRACE_BLOCK)
+k_trace_lbvh(AccelView A, const crt_ray* __restrict__ rays, size_t n, float t_min, float t_max,
+             crt_hit* __restrict__ hits, unsigned long long* __restrict__ counters)
+{
+    __shared__ int s_stack[CRT_STACK_SMEM * TRACE_BLOCK];
+    TraceCounters cnt = {0u, 0u, 0u};
+    uint32_t my_rays = 0;
+    for (size_t i = (size_t)blockIdx.x * TRACE_BLOCK + threadIdx.x; i < n; i += (size_t)gridDim.x * TRACE_BLOCK) {
+        v3 o, d;
+        load_ray(rays, i, o, d);
+        Hit h;
+        traverse<COUNT, HAS_SPH>(A, o, ray_dir_local(d), t_min, t_max, h, s_stack + threadIdx.x, TRACE_BLOCK, cnt);
+        const bool hit = h.id != CRT_MISS_ID;
+        reinterpret_cast<float4*>(hits)[i] =
+            make_float4(hit ? h.t : 0.0f, __uint_as_float(h.id), hit ? h.u : 0.0f, hit ? h.v : 0.0f);
+        my_rays++;
+    }
+    if (COUNT) flush_counters(counters, cnt, my_rays);
+}
+
+constexpr int BRUTE_TILE = 64;
+
+template <bool COUNT>
+__global__ void __launch_bounds__(TRACE_BLOCK)
+k_trace_brute(const float* __restrict__ tri_in, const uint32_t* __restrict__ tri_id, uint32_t n_tri,
+              const float* __restrict__ sph_in, const uint32_t* __restrict__ sph_id, uint32_t n_sph,
+              const crt_ray* __restrict__ rays, size_t n, float t_min, float t_max, crt_hit* __restrict__ hits,
+              unsigned long long* __restrict__ counters)
+{
+    __shared__ float s_prim[BRUTE_TILE * 12];
+    __shared__ uint32_t s_id[BRUTE_TILE];
+    const size_t i = (size_t)blockIdx.x * TRACE_BLOCK + threadIdx.x;
+    const bool live = i < n;
+    v3 o = V(0.f, 0.f, 0.f), d = V(0.f, 0.f, 1.f);
+    if (live) { load_ray(rays, i, o, d); d = ray_dir_local(d); }
+    float best_t = t_max, best_u = 0.f, best_v = 0.f;
+    uint32_t best_id = CRT_MISS_ID;
+    TraceCounters cnt = {0u, 0u, 0u};
+
+    for (uint32_t base = 0; base < n_tri; base += BRUTE_TILE) {
+        const uint32_t m = min((uint32_t)BRUTE_TILE, n_tri - base);
+        __syncthreads();
+        for (uint32_t j = threadIdx.x; j < m * 12; j += TRACE_BLOCK) s_prim[j] = tri_in[(size_t)base * 12 + j];
+        for (uint32_t j = threadIdx.x; j < m; j += TRACE_BLOCK) s_id[j] = tri_id[base + j];
+        __syncthreads();
+        if (!live) continue;
+        for (uint32_t j = 0; j < m; j++) {
+            const float* t = s_prim + 12 * j;
+            const v3 v0 = V(t[0], t[1], t[2]);
+            const v3 e1 = vsub(V(t[3], t[4], t[5]), v0);
+            const v3 e2 = vsub(V(t[6], t[7], t[8]), v0);
+            float tt, u, v;
+            if (COUNT) cnt.tris++;
+            if (!triangle_test(o, d, v0, e1, e2, V(t[9], t[10], t[11]), t_min, best_t, tt, u, v)) continue;
+            if (tt == best_t && (best_id == CRT_MISS_ID || s_id[j] >= best_id)) continue;
+            best_t = tt; best_u = u; best_v = v; best_id = s_id[j];
+        }
+    }
+    for (uint32_t base = 0; base < n_sph; base += BRUTE_TILE) {
+        const uint32_t m = min((uint32_t)BRUTE_TILE, n_sph - base);
+        __syncthreads();
+        for (uint32_t j = threadIdx.x; j < m * 4; j += TRACE_BLOCK) s_prim[j] = sph_in[(size_t)base * 4 + j];
+        for (uint32_t j = threadIdx.x; j < m; j += TRACE_BLOCK) s_id[j] = sph_id[base + j];
+        __syncthreads();
+        if (!live) continue;
+        for (uint32_t j = 0; j < m; j++) {
+            const float* s = s_prim + 4 * j;
+            float tt;
+            if (COUNT) cnt.spheres++;
+            if (!sphere_test(vsub(o, V(s[0], s[1], s[2])), d, s[3], t_min, best_t, tt)) continue;
+            if (tt == best_t && (best_id == CRT_MISS_ID || s_id[j] >= best_id)) continue;
+            best_t = tt; best_u = 0.f; best_v = 0.f; best_id = s_id[j];
+        }
+    }
+    if (live) {
+        const bool hit = best_id != CRT_MISS_ID;
+        reinterpret_cast<float4*>(hits)[i] =
+            make_float4(hit ? best_t : 0.0f, __uint_as_float(best_id), hit ? best_u : 0.0f, hit ? best_v : 0.0f);
+    }
+    if (COUNT) flush_counters(counters, cnt, live ? 1u : 0u);
+}
+
+int launch_trace(crt_ctx* c, const crt_ray* d_rays, size_t n, float t_min, float t_max, int accel, crt_hit* d_hits)
+{
+    if (n == 0) return CRT_OK;
+    unsigned long long* counters = c->counters.as<unsigned long long>();
+    cudaStream_t st = c->stream;
+    if (accel == CRT_ACCEL_BRUTE) {
+        const unsigned int grid = (unsigned int)((n + TRACE_BLOCK - 1) / TRACE_BLOCK);
+        if (c->count_work)
+            k_trace_brute<true><<<grid, TRACE_BLOCK, 0, st>>>(c->tri_in.as<float>(), c->tri_id.as<uint32_t>(), (uint32_t)c->n_tri,
+                                                              c->sph_in.as<float>(), c->sph_id.as<uint32_t>(), (uint32_t)c->n_sph,
+                                                              d_rays, n, t_min, t_max, d_hits, counters);
+        else
+            k_trace_brute<false><<<grid, TRACE_BLOCK, 0, st>>>(c->tri_in.as<float>(), c->tri_id.as<uint32_t>(), (uint32_t)c->n_tri,
+                                                               c->sph_in.as<float>(), c->sph_id.as<uint32_t>(), (uint32_t)c->n_sph,
+                                                               d_rays, n, t_min, t_max, d_hits, counters);
+    } else if (accel == CRT_ACCEL_LBVH) {
+        if (!c->accel_valid) { set_error("crt_trace: call crt_accel_build first"); return CRT_ERR_STATE; }
+        const AccelView A = accel_view(c);
+        size_t blocks = (n + TRACE_BLOCK - 1) / TRACE_BLOCK;
+        const size_t cap = (size_t)c->sm_count * 64;
+        const unsigned int grid = (unsigned int)(blocks < cap ? blocks : cap);
+        const bool sph = c->n_sph > 0;
+        if (c->count_work) {
+            if (sph) k_trace_lbvh<true, true><<<grid, TRACE_BLOCK, 0, st>>>(A, d_rays, n, t_min, t_max, d_hits, counters);
+            else k_trace_lbvh<true, false><<<grid, TRACE_BLOCK, 0, st>>>(A, d_rays, n, t_min, t_max, d_hits, counters);
+        } else {
+            if (sph) k_trace_lbvh<false, true><<<grid, TRACE_BLOCK, 0, st>>>(A, d_rays, n, t_min, t_max, d_hits, counters);
+            else k_trace_lbvh<false, false><<<grid, TRACE_BLOCK, 0, st>>>(A, d_rays, n, t_min, t_max, d_hits, counters);
+        }
+    } else {
+        set_error("crt_trace: unknown accel kind %d", accel);
+        return CRT_ERR_INVALID;
+    }
+    CRT_CUDA(cudaGetLastError());
+    return CRT_OK;
+}
+
+}  // namespace crt

@@ -1,0 +1,85 @@
+// emu.cu — TEST INFRASTRUCTURE. Compiles the per-ray device functions of
+// cudaraytracer_b200/csrc/crt_device.cuh for the HOST (they are
+// __host__ __device__) so the CPU-only test tier can compare the exact code the
+// kernels inline against the oracle before any GPU is involved. Not part of
+// the product; nothing in cudaraytracer_b200/ loads it.
+#include "../../cudaraytracer_b200/csrc/crt_device.cuh"
+#include <string.h>
+
+using namespace crt;
+
+extern "C" {
+
+// same contract as oracle_scatter / ref_scatter but with the counter stream
+int emu_scatter(uint32_t type, const float* albedo, float param, const float* ray, const float* recpn,
+                uint32_t key, uint32_t ctr, float* out, uint32_t* ctr_out)
+{
+    DMat m;
+    m.r = albedo[0]; m.g = albedo[1]; m.b = albedo[2]; m.param = param; m.type = type;
+    m.pad0 = m.pad1 = m.pad2 = 0;
+    Rng r; r.key = key; r.ctr = ctr;
+    v3 att, od;
+    bool ok = scatter(m, V(ray[3], ray[4], ray[5]), V(recpn[0], recpn[1], recpn[2]), V(recpn[3], recpn[4], recpn[5]), r, att, od);
+    out[0] = att.x; out[1] = att.y; out[2] = att.z;
+    out[3] = recpn[0]; out[4] = recpn[1]; out[5] = recpn[2];
+    out[6] = od.x; out[7] = od.y; out[8] = od.z;
+    *ctr_out = r.ctr;
+    return ok ? 1 : 0;
+}
+
+uint32_t emu_get_ray(const float* c, float s, float t, uint64_t seed, uint32_t pixel, uint32_t sample, uint32_t ctr,
+                     float* out6)
+{
+    DCamera cam;
+    cam.llc = V(c[0], c[1], c[2]); cam.horizontal = V(c[3], c[4], c[5]); cam.vertical = V(c[6], c[7], c[8]);
+    cam.origin = V(c[9], c[10], c[11]); cam.x = V(c[12], c[13], c[14]); cam.y = V(c[15], c[16], c[17]);
+    cam.z = V(c[18], c[19], c[20]); cam.lens_radius = c[21];
+    Rng r; r.key = crt_rng_key(seed, pixel, sample); r.ctr = ctr;
+    v3 o, d;
+    camera_get_ray(cam, s, t, r, o, d);
+    out6[0] = o.x; out6[1] = o.y; out6[2] = o.z; out6[3] = d.x; out6[4] = d.y; out6[5] = d.z;
+    return r.ctr;
+}
+
+// Linear scan with the device primitive tests and tie rule: the host twin of
+// k_trace_brute. tri: n x 12 (v0 v1 v2 n), sph: m x 4.
+void emu_trace(const float* tri, const uint32_t* tri_id, uint32_t n_tri, const float* sph, const uint32_t* sph_id,
+               uint32_t n_sph, const float* rays, size_t n, float t_min, float t_max, float* out_t, uint32_t* out_id)
+{
+    for (size_t i = 0; i < n; i++) {
+        const float* q = rays + 6 * i;
+        v3 o = V(q[0], q[1], q[2]);
+        v3 d = ray_dir_local(V(q[3], q[4], q[5]));
+        float best = t_max;
+        uint32_t best_id = CRT_MISS_ID;
+        for (uint32_t j = 0; j < n_tri; j++) {
+            const float* t = tri + 12 * (size_t)j;
+            v3 v0 = V(t[0], t[1], t[2]);
+            float tt, u, v;
+            if (!triangle_test(o, d, v0, vsub(V(t[3], t[4], t[5]), v0), vsub(V(t[6], t[7], t[8]), v0),
+                               V(t[9], t[10], t[11]), t_min, best, tt, u, v)) continue;
+            if (tt == best && (best_id == CRT_MISS_ID || tri_id[j] >= best_id)) continue;
+            best = tt; best_id = tri_id[j];
+        }
+        for (uint32_t j = 0; j < n_sph; j++) {
+            const float* s = sph + 4 * (size_t)j;
+            float tt;
+            if (!sphere_test(vsub(o, V(s[0], s[1], s[2])), d, s[3], t_min, best, tt)) continue;
+            if (tt == best && (best_id == CRT_MISS_ID || sph_id[j] >= best_id)) continue;
+            best = tt; best_id = sph_id[j];
+        }
+        out_t[i] = best_id != CRT_MISS_ID ? best : 0.f;
+        out_id[i] = best_id;
+    }
+}
+
+void emu_sky(const float* d, float* out)
+{
+    v3 s = background_sky(V(d[0], d[1], d[2]));
+    out[0] = s.x; out[1] = s.y; out[2] = s.z;
+}
+
+float emu_uniform(uint32_t key, uint32_t ctr) { return crt_rng_uniform(key, ctr); }
+uint32_t emu_key(uint64_t seed, uint32_t pixel, uint32_t sample) { return crt_rng_key(seed, pixel, sample); }
+
+}  // extern "C"
