@@ -16,7 +16,7 @@ LIB_PATH = os.path.join(_HERE, "libcrt_b200.so")
 MISS = 0xFFFFFFFF
 SHADE_PATH, SHADE_LAMBERT, SHADE_NORMAL = 0, 1, 2
 ACCEL_LBVH, ACCEL_BRUTE = 0, 1
-OPT_LEAF_MAX, OPT_COUNTERS, OPT_BATCH_PATHS = 1, 2, 3
+OPT_LEAF_MAX, OPT_COUNTERS, OPT_BATCH_PATHS, OPT_REFILL, OPT_LEAF_THRESH = 1, 2, 3, 4, 5
 TILE = 32
 
 # every symbol include/crt.h declares
@@ -44,7 +44,8 @@ class Camera(C.Structure):
 class Counters(C.Structure):
     _fields_ = [("rays", C.c_uint64), ("nodes_visited", C.c_uint64), ("tris_tested", C.c_uint64),
                 ("spheres_tested", C.c_uint64), ("scatters", C.c_uint64), ("paths", C.c_uint64),
-                ("build_ms", C.c_float), ("refit_ms", C.c_float), ("render_ms", C.c_float), ("trace_ms", C.c_float)]
+                ("build_ms", C.c_float), ("refit_ms", C.c_float), ("render_ms", C.c_float), ("trace_ms", C.c_float),
+                ("bounce_ms", C.c_float), ("trace_queue_ms", C.c_float)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}

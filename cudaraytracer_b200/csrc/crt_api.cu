@@ -95,6 +95,9 @@ int crt_create(int device, crt_ctx** out)
     CRT_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     CRT_CUDA(cudaEventCreate(&c->ev0));
     CRT_CUDA(cudaEventCreate(&c->ev1));
+    CRT_CUDA(cudaEventCreate(&c->ev2));
+    CRT_CUDA(cudaEventCreate(&c->ev3));
+    for (auto& e : c->ev_trace) CRT_CUDA(cudaEventCreate(&e));
     CRT_CUDA(c->counters.reserve(sizeof(unsigned long long) * CNT_COUNT));
     CRT_CUDA(cudaMemsetAsync(c->counters.p, 0, sizeof(unsigned long long) * CNT_COUNT, c->stream));
     CRT_CUDA(cudaStreamSynchronize(c->stream));
@@ -110,11 +113,14 @@ void crt_destroy(crt_ctx* c)
     DevBuf* bufs[] = {&c->tri_in, &c->tri_mat, &c->tri_id, &c->sph_in, &c->sph_mat, &c->sph_id, &c->mats,
                       &c->keys[0], &c->keys[1], &c->vals[0], &c->vals[1], &c->hist, &c->nodes, &c->recs, &c->info,
                       &c->child, &c->parent, &c->leaf_parent, &c->range, &c->node_box, &c->leaf_box, &c->flags,
-                      &c->bounds, &c->depth_out, &c->queue[0], &c->queue[1], &c->qcount, &c->rad, &c->accum, &c->rgb,
+                      &c->bounds, &c->depth_out, &c->queue[0], &c->queue[1], &c->qcount, &c->work_ctr, &c->hitbuf, &c->rad, &c->accum, &c->rgb,
                       &c->rays_tmp, &c->hits_tmp, &c->counters};
     for (DevBuf* b : bufs) b->release();
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
+    if (c->ev2) cudaEventDestroy(c->ev2);
+    if (c->ev3) cudaEventDestroy(c->ev3);
+    for (auto& e : c->ev_trace) if (e) cudaEventDestroy(e);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -129,6 +135,14 @@ int crt_set_option(crt_ctx* c, int option, int64_t value)
         return CRT_OK;
     case CRT_OPT_COUNTERS:
         c->count_work = value != 0;
+        return CRT_OK;
+    case CRT_OPT_REFILL:
+        if (value < 1 || value > 32) { set_error("CRT_OPT_REFILL must be in [1, 32]"); return CRT_ERR_INVALID; }
+        c->refill = (int)value;
+        return CRT_OK;
+    case CRT_OPT_LEAF_THRESH:
+        if (value < 1 || value > 32) { set_error("CRT_OPT_LEAF_THRESH must be in [1, 32]"); return CRT_ERR_INVALID; }
+        c->leaf_thresh = (int)value;
         return CRT_OK;
     case CRT_OPT_BATCH_PATHS:
         if (value < 1) { set_error("CRT_OPT_BATCH_PATHS must be >= 1"); return CRT_ERR_INVALID; }

@@ -57,7 +57,8 @@ struct crt_ctx {
     int device = 0;
     int sm_count = 148;
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr, ev3 = nullptr;
+    cudaEvent_t ev_trace[2 * (crt::CRT_MAX_DEPTH + 1)] = {};
 
     // scene as uploaded (caller's order)
     crt::DevBuf tri_in, tri_mat, tri_id;   // n_tri x 12 floats, u32, u32
@@ -77,9 +78,11 @@ struct crt_ctx {
     int tree_depth = 0;
 
     // render
-    crt::DevBuf queue[2], qcount, rad, accum, rgb, rays_tmp, hits_tmp;
+    crt::DevBuf queue[2], qcount, work_ctr, hitbuf, rad, accum, rgb, rays_tmp, hits_tmp;
     crt::DevBuf counters;                  // CNT_COUNT x uint64
     int count_work = 0;
+    int leaf_thresh = 16;                  // parked lanes that trigger the primitive-test phase
+    int refill = 8;                        // idle lanes that trigger a refill in the persistent traversal
     int64_t batch_paths = 1ll << 25;
 
     crt_counters host_counters = {};

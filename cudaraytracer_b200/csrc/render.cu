@@ -123,16 +123,58 @@ __device__ __forceinline__ DMat load_mat(const DMat* __restrict__ mats, uint32_t
     return m;
 }
 
+// ---- closest hit for every queue entry (persistent warps, crt_traverse.cuh) ----
+struct QueueSrc {
+    const float4* q;
+    size_t cap;
+    __device__ __forceinline__ void load(uint32_t i, v3& o, v3& d) const
+    {
+        const float4 w0 = q[i];
+        const float4 w1 = q[cap + i];
+        o = V(w0.x, w0.y, w0.z);
+        d = V(w0.w, w1.x, w1.y);
+    }
+};
+struct QueueSink {
+    float4* hits;   // {t, sorted primitive position, u, v} per queue entry
+    __device__ __forceinline__ void store(uint32_t i, const Hit& h) const
+    {
+        hits[i] = make_float4(h.t, __uint_as_float(h.k), h.u, h.v);
+    }
+};
+
+template <bool COUNT, bool HAS_SPH>
+__global__ void __launch_bounds__(TP_BLOCK)
+k_trace_queue(AccelView A, const float4* __restrict__ q, uint32_t cap, const uint32_t* __restrict__ n_ptr,
+              uint32_t* __restrict__ work_ctr, float4* __restrict__ hits, unsigned long long* __restrict__ counters,
+              uint32_t refill, uint32_t leaf_thresh)
+{
+    __shared__ int s_stack[CRT_STACK_SMEM * TP_BLOCK];
+    TraceCounters cnt = {0u, 0u, 0u};
+    QueueSrc src = {q, cap};
+    QueueSink sink = {hits};
+    traverse_persistent<COUNT, HAS_SPH>(A, *n_ptr, work_ctr, 0.001f, FLT_MAX, src, sink, s_stack, cnt, refill, leaf_thresh);   // render.h:53
+    if (COUNT) {
+        const uint32_t nodes = __reduce_add_sync(0xffffffffu, cnt.nodes);
+        const uint32_t tris = __reduce_add_sync(0xffffffffu, cnt.tris);
+        const uint32_t sph = __reduce_add_sync(0xffffffffu, cnt.spheres);
+        if ((threadIdx.x & 31u) == 0u) {
+            atomicAdd(counters + CNT_NODES, (unsigned long long)nodes);
+            atomicAdd(counters + CNT_TRIS, (unsigned long long)tris);
+            atomicAdd(counters + CNT_SPHERES, (unsigned long long)sph);
+        }
+    }
+}
+
+// ---- shade(): one thread per queue entry, fully converged ----
 template <bool COUNT, bool HAS_SPH>
 __global__ void __launch_bounds__(RB)
-k_bounce(RenderParams P, AccelView A, const DMat* __restrict__ mats, const float4* __restrict__ q_in,
-         const uint32_t* __restrict__ n_in_ptr, float4* __restrict__ q_out, uint32_t* __restrict__ n_out_ptr,
-         float4* __restrict__ rad, unsigned long long* __restrict__ counters)
+k_shade(RenderParams P, AccelView A, const DMat* __restrict__ mats, const float4* __restrict__ q_in,
+        const float4* __restrict__ hits, const uint32_t* __restrict__ n_in_ptr, float4* __restrict__ q_out,
+        uint32_t* __restrict__ n_out_ptr, float4* __restrict__ rad, unsigned long long* __restrict__ counters)
 {
-    __shared__ int s_stack[CRT_STACK_SMEM * RB];
     const uint32_t n_in = *n_in_ptr;
     const uint32_t lane = threadIdx.x & 31u;
-    TraceCounters cnt = {0u, 0u, 0u};
     uint32_t n_scatter = 0;
 
     for (uint32_t base = (blockIdx.x * RB + (threadIdx.x & ~31u)); base < n_in; base += gridDim.x * RB) {
@@ -144,42 +186,46 @@ k_bounce(RenderParams P, AccelView A, const DMat* __restrict__ mats, const float
         if (live) {
             w0 = q_in[i];
             w1 = q_in[(size_t)P.cap + i];
-            const uint4 a2 = reinterpret_cast<const uint4*>(q_in)[2 * (size_t)P.cap + i];
-            const uint4 a3 = reinterpret_cast<const uint4*>(q_in)[3 * (size_t)P.cap + i];
-            ms[0] = a2.x; ms[1] = a2.y; ms[2] = a2.z; ms[3] = a2.w;
-            ms[4] = a3.x; ms[5] = a3.y; ms[6] = a3.z; ms[7] = a3.w;
+            const float4 hr = hits[i];
             const v3 o = V(w0.x, w0.y, w0.z), d = V(w0.w, w1.x, w1.y);
             const uint32_t path_id = __float_as_uint(w1.z);
             const uint32_t pack = __float_as_uint(w1.w);
             const int depth_left = (int)(pack >> 24);
             const int bounces = P.max_depth - depth_left;
-            Rng rng;
-            {
-                const uint32_t s_local = path_id / P.n_slots;
-                const uint32_t slot = path_id - s_local * P.n_slots;
-                int px, py;
-                slot_to_pixel(P, slot, px, py);
-                rng.key = crt_rng_key(P.seed, (uint32_t)py * (uint32_t)P.nx + (uint32_t)px, (uint32_t)(P.s_begin + (int)s_local));
-                rng.ctr = pack & 0xFFFFFFu;
+            if (bounces > 0) {
+                const uint4 a2 = reinterpret_cast<const uint4*>(q_in)[2 * (size_t)P.cap + i];
+                ms[0] = a2.x; ms[1] = a2.y; ms[2] = a2.z; ms[3] = a2.w;
+                if (bounces > 8) {
+                    const uint4 a3 = reinterpret_cast<const uint4*>(q_in)[3 * (size_t)P.cap + i];
+                    ms[4] = a3.x; ms[5] = a3.y; ms[6] = a3.z; ms[7] = a3.w;
+                }
             }
-
-            const v3 dl = ray_dir_local(d);
-            Hit h;
-            traverse<COUNT, HAS_SPH>(A, o, dl, 0.001f, FLT_MAX, h, s_stack + threadIdx.x, RB, cnt);   // render.h:53
+            const uint32_t hk = __float_as_uint(hr.y);
 
             v3 L;
-            if (h.id == CRT_MISS_ID) {
+            if (hk == 0xFFFFFFFFu) {
                 L = background_sky(d);                                             // render.h:65
             } else {
-                const uint2 inf = __ldg(&A.info[h.k]);
-                const float4 r0 = ldg4(A.recs + 3 * (size_t)h.k);
+                Rng rng;
+                {
+                    const uint32_t s_local = path_id / P.n_slots;
+                    const uint32_t slot = path_id - s_local * P.n_slots;
+                    int px, py;
+                    slot_to_pixel(P, slot, px, py);
+                    rng.key = crt_rng_key(P.seed, (uint32_t)py * (uint32_t)P.nx + (uint32_t)px, (uint32_t)(P.s_begin + (int)s_local));
+                    rng.ctr = pack & 0xFFFFFFu;
+                }
+                const v3 dl = ray_dir_local(d);
+                const float ht = hr.x;
+                const uint2 inf = __ldg(&A.info[hk]);
+                const float4 r0 = ldg4(A.recs + 3 * (size_t)hk);
                 v3 p, n;
                 if (HAS_SPH && (inf.y & CRT_KIND_SPHERE)) {
-                    p = vadd(vsub(o, V(r0.x, r0.y, r0.z)), vscale(h.t, dl));       // sphere.h:40 (local frame)
+                    p = vadd(vsub(o, V(r0.x, r0.y, r0.z)), vscale(ht, dl));        // sphere.h:40 (local frame)
                     n = vdivf(p, r0.w);                                            // sphere.h:41
                 } else {
-                    const float4 r1 = ldg4(A.recs + 3 * (size_t)h.k + 1), r2 = ldg4(A.recs + 3 * (size_t)h.k + 2);
-                    p = vadd(o, vscale(h.t, dl));                                  // triangle.h:95
+                    const float4 r1 = ldg4(A.recs + 3 * (size_t)hk + 1), r2 = ldg4(A.recs + 3 * (size_t)hk + 2);
+                    p = vadd(o, vscale(ht, dl));                                   // triangle.h:95
                     n = V(r0.w, r1.w, r2.w);                                       // triangle.h:96
                 }
                 const uint32_t mat_id = inf.y & 0x7FFFFFFFu;
@@ -229,20 +275,13 @@ k_bounce(RenderParams P, AccelView A, const DMat* __restrict__ mats, const float
             q_out[pos] = w0;
             q_out[(size_t)P.cap + pos] = w1;
             reinterpret_cast<uint4*>(q_out)[2 * (size_t)P.cap + pos] = make_uint4(ms[0], ms[1], ms[2], ms[3]);
-            reinterpret_cast<uint4*>(q_out)[3 * (size_t)P.cap + pos] = make_uint4(ms[4], ms[5], ms[6], ms[7]);
+            if (P.max_depth > 8)
+                reinterpret_cast<uint4*>(q_out)[3 * (size_t)P.cap + pos] = make_uint4(ms[4], ms[5], ms[6], ms[7]);
         }
     }
     if (COUNT) {
-        const uint32_t nodes = __reduce_add_sync(0xffffffffu, cnt.nodes);
-        const uint32_t tris = __reduce_add_sync(0xffffffffu, cnt.tris);
-        const uint32_t sph = __reduce_add_sync(0xffffffffu, cnt.spheres);
         const uint32_t sc = __reduce_add_sync(0xffffffffu, n_scatter);
-        if (lane == 0) {
-            atomicAdd(counters + CNT_NODES, (unsigned long long)nodes);
-            atomicAdd(counters + CNT_TRIS, (unsigned long long)tris);
-            atomicAdd(counters + CNT_SPHERES, (unsigned long long)sph);
-            atomicAdd(counters + CNT_SCATTERS, (unsigned long long)sc);
-        }
+        if (lane == 0) atomicAdd(counters + CNT_SCATTERS, (unsigned long long)sc);
     }
 }
 
@@ -302,11 +341,15 @@ static DCamera to_dcamera(const crt_camera* c)
 }
 
 template <bool COUNT, bool HAS_SPH>
-static void launch_bounce(crt_ctx* c, int grid, const RenderParams& P, const AccelView& A, const float4* q_in,
-                          const uint32_t* n_in, float4* q_out, uint32_t* n_out)
+static void launch_bounce(crt_ctx* c, int b, int grid_trace, int grid_shade, const RenderParams& P, const AccelView& A,
+                          const float4* q_in, const uint32_t* n_in, uint32_t* work_ctr, float4* q_out, uint32_t* n_out)
 {
-    k_bounce<COUNT, HAS_SPH><<<grid, RB, 0, c->stream>>>(P, A, c->mats.as<DMat>(), q_in, n_in, q_out, n_out,
-                                                         c->rad.as<float4>(), c->counters.as<unsigned long long>());
+    cudaEventRecord(c->ev_trace[2 * b], c->stream);
+    k_trace_queue<COUNT, HAS_SPH><<<grid_trace, TP_BLOCK, 0, c->stream>>>(A, q_in, P.cap, n_in, work_ctr, c->hitbuf.as<float4>(),
+                                                                          c->counters.as<unsigned long long>(), (uint32_t)c->refill, (uint32_t)c->leaf_thresh);
+    cudaEventRecord(c->ev_trace[2 * b + 1], c->stream);
+    k_shade<COUNT, HAS_SPH><<<grid_shade, RB, 0, c->stream>>>(P, A, c->mats.as<DMat>(), q_in, c->hitbuf.as<float4>(), n_in, q_out,
+                                                              n_out, c->rad.as<float4>(), c->counters.as<unsigned long long>());
 }
 
 int render_accum(crt_ctx* c, const crt_camera* cam, int nx, int ny, int s0, int s1, int max_depth, int mode,
@@ -336,6 +379,7 @@ int render_accum(crt_ctx* c, const crt_camera* cam, int nx, int ny, int s0, int 
     CRT_CUDA(cudaMemsetAsync(d_accum, 0, (size_t)nx * ny * 3 * sizeof(float), st));
     const int n_samples = s1 - s0;
     uint64_t total_rays = 0, total_paths = 0;
+    float bounce_ms = 0.f, trace_q_ms = 0.f;
     if (P.n_slots > 0 && n_samples > 0) {
         long long per_batch = c->batch_paths / (long long)P.n_slots;
         if (per_batch < 1) per_batch = 1;
@@ -348,16 +392,18 @@ int render_accum(crt_ctx* c, const crt_camera* cam, int nx, int ny, int s0, int 
         CRT_CUDA(c->rad.reserve(cap * 16));
         const int n_levels = CRT_MAX_DEPTH + 3;
         CRT_CUDA(c->qcount.reserve(sizeof(uint32_t) * n_levels));
+        CRT_CUDA(c->work_ctr.reserve(sizeof(uint32_t) * 64));
+        CRT_CUDA(c->hitbuf.reserve(cap * 16));
         uint32_t h_counts[CRT_MAX_DEPTH + 3];
 
-        int bps = 1;
-        int grid;
-        {
-            // all four instantiations have the same resource needs; size the persistent grid from one
-            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_bounce<false, false>, RB, 0);
-            if (bps < 1) bps = 1;
-            grid = c->sm_count * bps;
-        }
+        int bps = 1, bps_shade = 1;
+        // the instantiations have near-identical resource needs; size the persistent grids from one
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_trace_queue<false, false>, TP_BLOCK, 0);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps_shade, k_shade<false, false>, RB, 0);
+        if (bps < 1) bps = 1;
+        if (bps_shade < 1) bps_shade = 1;
+        const int grid = c->sm_count * bps;
+        const int grid_shade = c->sm_count * bps_shade;
         const AccelView A = accel_view(c);
         const bool sph = c->n_sph > 0;
         const int bounces = mode == CRT_SHADE_PATH ? max_depth + 1 : 1;
@@ -366,25 +412,37 @@ int render_accum(crt_ctx* c, const crt_camera* cam, int nx, int ny, int s0, int 
             P.s_begin = sb;
             P.s_count = (s1 - sb) < per_batch ? (s1 - sb) : (int)per_batch;
             CRT_CUDA(cudaMemsetAsync(c->qcount.p, 0, sizeof(uint32_t) * n_levels, st));
+            CRT_CUDA(cudaMemsetAsync(c->work_ctr.p, 0, sizeof(uint32_t) * 64, st));
             const uint32_t total = P.n_slots * (uint32_t)P.s_count;
             const unsigned int rg = (unsigned int)min((size_t)(total + RB - 1) / RB, (size_t)c->sm_count * 32);
             k_raygen<<<rg, RB, 0, st>>>(P, c->queue[0].as<float4>(), c->qcount.as<uint32_t>());
+            CRT_CUDA(cudaEventRecord(c->ev2, st));
             for (int b = 0; b < bounces; b++) {
                 const float4* qi = c->queue[b & 1].as<float4>();
                 float4* qo = c->queue[(b + 1) & 1].as<float4>();
                 const uint32_t* ni = c->qcount.as<uint32_t>() + b;
                 uint32_t* no = c->qcount.as<uint32_t>() + b + 1;
+                uint32_t* wc = c->work_ctr.as<uint32_t>() + b;
                 if (c->count_work) {
-                    if (sph) launch_bounce<true, true>(c, grid, P, A, qi, ni, qo, no);
-                    else launch_bounce<true, false>(c, grid, P, A, qi, ni, qo, no);
+                    if (sph) launch_bounce<true, true>(c, b, grid, grid_shade, P, A, qi, ni, wc, qo, no);
+                    else launch_bounce<true, false>(c, b, grid, grid_shade, P, A, qi, ni, wc, qo, no);
                 } else {
-                    if (sph) launch_bounce<false, true>(c, grid, P, A, qi, ni, qo, no);
-                    else launch_bounce<false, false>(c, grid, P, A, qi, ni, qo, no);
+                    if (sph) launch_bounce<false, true>(c, b, grid, grid_shade, P, A, qi, ni, wc, qo, no);
+                    else launch_bounce<false, false>(c, b, grid, grid_shade, P, A, qi, ni, wc, qo, no);
                 }
             }
+            CRT_CUDA(cudaEventRecord(c->ev3, st));
             k_accumulate<<<(P.n_slots + 255) / 256, 256, 0, st>>>(P, c->rad.as<float4>(), d_accum);
             CRT_CUDA(cudaMemcpyAsync(h_counts, c->qcount.p, sizeof(uint32_t) * n_levels, cudaMemcpyDeviceToHost, st));
             CRT_CUDA(cudaStreamSynchronize(st));
+            float bms = 0.f;
+            CRT_CUDA(cudaEventElapsedTime(&bms, c->ev2, c->ev3));
+            bounce_ms += bms;
+            for (int b = 0; b < bounces; b++) {
+                float tms = 0.f;
+                CRT_CUDA(cudaEventElapsedTime(&tms, c->ev_trace[2 * b], c->ev_trace[2 * b + 1]));
+                trace_q_ms += tms;
+            }
             total_paths += h_counts[0];
             for (int b = 0; b < bounces; b++) total_rays += h_counts[b];
         }
@@ -395,6 +453,8 @@ int render_accum(crt_ctx* c, const crt_camera* cam, int nx, int ny, int s0, int 
     float ms = 0.f;
     CRT_CUDA(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
     c->host_counters.render_ms = ms;
+    c->host_counters.bounce_ms += bounce_ms;
+    c->host_counters.trace_queue_ms += trace_q_ms;
     c->host_counters.rays += total_rays;
     c->host_counters.paths += total_paths;
     return CRT_OK;

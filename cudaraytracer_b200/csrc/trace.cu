@@ -11,7 +11,7 @@
 
 namespace crt {
 
-constexpr int TRACE_BLOCK = 128;
+constexpr int TRACE_BLOCK = TP_BLOCK;
 
 AccelView accel_view(const crt_ctx* c)
 {
@@ -47,25 +47,33 @@ __device__ __forceinline__ void flush_counters(unsigned long long* counters, con
     }
 }
 
-template <bool COUNT, bool HAS_SPH>
-__global__ void __launch_bounds__(TRACE_BLOCK)
-k_trace_lbvh(AccelView A, const crt_ray* __restrict__ rays, size_t n, float t_min, float t_max,
-             crt_hit* __restrict__ hits, unsigned long long* __restrict__ counters)
-{
-    __shared__ int s_stack[CRT_STACK_SMEM * TRACE_BLOCK];
-    TraceCounters cnt = {0u, 0u, 0u};
-    uint32_t my_rays = 0;
-    for (size_t i = (size_t)blockIdx.x * TRACE_BLOCK + threadIdx.x; i < n; i += (size_t)gridDim.x * TRACE_BLOCK) {
-        v3 o, d;
-        load_ray(rays, i, o, d);
-        Hit h;
-        traverse<COUNT, HAS_SPH>(A, o, ray_dir_local(d), t_min, t_max, h, s_stack + threadIdx.x, TRACE_BLOCK, cnt);
-        const bool hit = h.id != CRT_MISS_ID;
+struct RaySrc {
+    const crt_ray* rays;
+    __device__ __forceinline__ void load(uint32_t i, v3& o, v3& d) const { load_ray(rays, i, o, d); }
+};
+struct HitSink {
+    crt_hit* hits;
+    const uint2* info;
+    __device__ __forceinline__ void store(uint32_t i, const Hit& h) const
+    {
+        const bool hit = h.k != 0xFFFFFFFFu;
+        const uint32_t id = hit ? __ldg(&info[h.k]).x : CRT_MISS_ID;
         reinterpret_cast<float4*>(hits)[i] =
-            make_float4(hit ? h.t : 0.0f, __uint_as_float(h.id), hit ? h.u : 0.0f, hit ? h.v : 0.0f);
-        my_rays++;
+            make_float4(hit ? h.t : 0.0f, __uint_as_float(id), hit ? h.u : 0.0f, hit ? h.v : 0.0f);
     }
-    if (COUNT) flush_counters(counters, cnt, my_rays);
+};
+
+template <bool COUNT, bool HAS_SPH>
+__global__ void __launch_bounds__(TP_BLOCK)
+k_trace_lbvh(AccelView A, const crt_ray* __restrict__ rays, uint32_t n, uint32_t* __restrict__ work_ctr, float t_min,
+             float t_max, crt_hit* __restrict__ hits, unsigned long long* __restrict__ counters, uint32_t refill, uint32_t leaf_thresh)
+{
+    __shared__ int s_stack[CRT_STACK_SMEM * TP_BLOCK];
+    TraceCounters cnt = {0u, 0u, 0u};
+    RaySrc src = {rays};
+    HitSink sink = {hits, A.info};
+    traverse_persistent<COUNT, HAS_SPH>(A, n, work_ctr, t_min, t_max, src, sink, s_stack, cnt, refill, leaf_thresh);
+    if (COUNT) flush_counters(counters, cnt, 0u);
 }
 
 constexpr int BRUTE_TILE = 64;
@@ -147,17 +155,26 @@ int launch_trace(crt_ctx* c, const crt_ray* d_rays, size_t n, float t_min, float
                                                                d_rays, n, t_min, t_max, d_hits, counters);
     } else if (accel == CRT_ACCEL_LBVH) {
         if (!c->accel_valid) { set_error("crt_trace: call crt_accel_build first"); return CRT_ERR_STATE; }
+        if (n >= (1ull << 32) - TP_CHUNK * 4096ull) { set_error("crt_trace: at most 2^32 - 2^20 rays per call"); return CRT_ERR_INVALID; }
         const AccelView A = accel_view(c);
-        size_t blocks = (n + TRACE_BLOCK - 1) / TRACE_BLOCK;
-        const size_t cap = (size_t)c->sm_count * 64;
+        CRT_CUDA(c->work_ctr.reserve(sizeof(uint32_t) * 64));
+        CRT_CUDA(cudaMemsetAsync(c->work_ctr.p, 0, sizeof(uint32_t), st));
+        int bps = 1;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_trace_lbvh<false, false>, TP_BLOCK, 0);
+        if (bps < 1) bps = 1;
+        const size_t want = (n + 31) / 32;                           // warps that can get a (smallest) chunk
+        size_t blocks = (want + (TP_BLOCK / 32) - 1) / (TP_BLOCK / 32);
+        const size_t cap = (size_t)c->sm_count * bps;
         const unsigned int grid = (unsigned int)(blocks < cap ? blocks : cap);
         const bool sph = c->n_sph > 0;
+        uint32_t* wc = c->work_ctr.as<uint32_t>();
+        const uint32_t un = (uint32_t)n;
         if (c->count_work) {
-            if (sph) k_trace_lbvh<true, true><<<grid, TRACE_BLOCK, 0, st>>>(A, d_rays, n, t_min, t_max, d_hits, counters);
-            else k_trace_lbvh<true, false><<<grid, TRACE_BLOCK, 0, st>>>(A, d_rays, n, t_min, t_max, d_hits, counters);
+            if (sph) k_trace_lbvh<true, true><<<grid, TP_BLOCK, 0, st>>>(A, d_rays, un, wc, t_min, t_max, d_hits, counters, (uint32_t)c->refill, (uint32_t)c->leaf_thresh);
+            else k_trace_lbvh<true, false><<<grid, TP_BLOCK, 0, st>>>(A, d_rays, un, wc, t_min, t_max, d_hits, counters, (uint32_t)c->refill, (uint32_t)c->leaf_thresh);
         } else {
-            if (sph) k_trace_lbvh<false, true><<<grid, TRACE_BLOCK, 0, st>>>(A, d_rays, n, t_min, t_max, d_hits, counters);
-            else k_trace_lbvh<false, false><<<grid, TRACE_BLOCK, 0, st>>>(A, d_rays, n, t_min, t_max, d_hits, counters);
+            if (sph) k_trace_lbvh<false, true><<<grid, TP_BLOCK, 0, st>>>(A, d_rays, un, wc, t_min, t_max, d_hits, counters, (uint32_t)c->refill, (uint32_t)c->leaf_thresh);
+            else k_trace_lbvh<false, false><<<grid, TP_BLOCK, 0, st>>>(A, d_rays, un, wc, t_min, t_max, d_hits, counters, (uint32_t)c->refill, (uint32_t)c->leaf_thresh);
         }
     } else {
         set_error("crt_trace: unknown accel kind %d", accel);

@@ -94,7 +94,9 @@ typedef enum {
 typedef enum {
     CRT_OPT_LEAF_MAX = 1,   /* max primitives per LBVH leaf, 1..8 (default 4); takes effect at the next build */
     CRT_OPT_COUNTERS = 2,   /* 1: run the instrumented kernels that count nodes/primitives visited */
-    CRT_OPT_BATCH_PATHS = 3 /* max camera samples in flight per wavefront batch (default 1<<25) */
+    CRT_OPT_BATCH_PATHS = 3,/* max camera samples in flight per wavefront batch (default 1<<25) */
+    CRT_OPT_LEAF_THRESH = 5,/* tuning: lanes parked on a leaf that trigger the primitive-test phase, 1..32 (default 16) */
+    CRT_OPT_REFILL = 4      /* tuning: idle lanes per warp that trigger a refill from the ray queue, 1..32 (default 8) */
 } crt_option;
 
 /* Work counters for the roofline and the reference's CSV columns
@@ -110,7 +112,9 @@ typedef struct {
     float    build_ms;        /* last crt_accel_build */
     float    refit_ms;        /* last crt_accel_refit */
     float    render_ms;       /* last crt_render* call, device time */
-    float    trace_ms;        /* last crt_trace* call, device time */
+    float    trace_ms;        /* last crt_trace (host-buffer form), device time of the kernel */
+    float    bounce_ms;       /* device time of all trace+shade launches since crt_reset_counters */
+    float    trace_queue_ms;  /* of which k_trace_queue (closest hit) alone */
 } crt_counters;
 
 /* Image partition for one-process-per-GPU rendering. The image is cut into

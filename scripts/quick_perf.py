@@ -15,6 +15,8 @@ from cudaraytracer_b200 import scenes
 def main():
     which = sys.argv[1] if len(sys.argv) > 1 else "c3"
     leaf_max = int(sys.argv[2]) if len(sys.argv) > 2 else 4
+    refill = int(sys.argv[3]) if len(sys.argv) > 3 else 8
+    lthr = int(sys.argv[4]) if len(sys.argv) > 4 else 16
     t0 = time.time()
     if which == "c3":
         sc = scenes.c3_mesh()
@@ -27,6 +29,8 @@ def main():
     print("scene %s: %d tris %d spheres (%.1fs to generate)" % (sc["name"], len(sc["tri"]), len(sc["sph"]), time.time() - t0))
     ctx = crt.Context(0)
     ctx.set_option(crt.OPT_LEAF_MAX, leaf_max)
+    ctx.set_option(crt.OPT_REFILL, refill)
+    ctx.set_option(crt.OPT_LEAF_THRESH, lthr)
     t0 = time.time()
     ctx.set_scene(sc)
     print("upload %.3fs" % (time.time() - t0))
