@@ -147,6 +147,7 @@ def run_reference(args):
     cam_fn = lambda nx, ny: crt.camera_for(sc, nx, ny)
     steps, warm = args.steps, args.warmup
     budget = max(2.0, min(20.0, 150.0 / max(1, steps + warm)))
+    budget = float(os.environ.get("CRT_BENCH_REF_BUDGET", budget))   # tests shorten it
     nx, ny = cpu_sample_shape(sh, cam_fn, sc, budget)
     cam = cam_fn(nx, ny)
     for _ in range(warm):
@@ -177,7 +178,7 @@ def run_ours(args):
     import torch
     import torch.distributed as dist
     import cudaraytracer_b200 as crt
-    from cudaraytracer_b200 import scenes
+    from cudaraytracer_b200 import scenes, multi
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -213,7 +214,7 @@ def run_ours(args):
         ctx.render_accum_device(cam, nx, ny, 0, spp, depth, crt.SHADE_PATH, seed, rank, world, accum.data_ptr())
         if world > 1:
             with torch.cuda.stream(ext):
-                dist.reduce(accum, 0)
+                multi.combine_accum(accum, 0)
         if rank == 0:
             ctx.resolve_device(accum.data_ptr(), nx * ny, spp, rgb.data_ptr())
 

@@ -1,0 +1,200 @@
+"""CPU tier: host logic, the C-ABI library's symbols, the device functions
+compiled for the host (tests/emu) against the oracle, and the world_size-2
+combine over gloo. No kernel runs here."""
+import ctypes as C
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+import oracle
+import cudaraytracer_b200 as crt
+from cudaraytracer_b200 import scenes, multi
+from util import best_oracle, oracle_scene, GOLDEN
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+EMU = os.path.join(ROOT, "tests", "emu", "libcrt_emu.so")
+f32p = np.ctypeslib.ndpointer(np.float32, flags="C")
+u32p = np.ctypeslib.ndpointer(np.uint32, flags="C")
+
+
+def test_library_exports_every_declared_symbol():
+    hdr = open(os.path.join(ROOT, "include", "crt.h")).read()
+    declared = set(re.findall(r"\b(crt_[a-z0-9_]+)\s*\(", hdr))
+    declared -= {"crt_ctx"}
+    assert declared == set(crt.ABI_SYMBOLS), declared ^ set(crt.ABI_SYMBOLS)
+    lib = crt.load_library()
+    for name in declared:
+        assert hasattr(lib, name), name
+    assert lib.crt_abi_version() == 1
+
+
+def test_no_cpu_fallback():
+    """Without a CUDA device the product refuses to run (there is no CPU path)."""
+    try:
+        import torch
+        if torch.cuda.is_available():
+            pytest.skip("a GPU is present")
+    except ImportError:
+        pass
+    with pytest.raises(crt.CrtError, match="no CUDA device"):
+        crt.Context(0)
+
+
+def test_product_never_touches_the_oracle():
+    for dirpath, _, files in os.walk(os.path.join(ROOT, "cudaraytracer_b200")):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp", ".hpp")) or f == "Makefile":
+                txt = open(os.path.join(dirpath, f), errors="ignore").read()
+                assert "import oracle" not in txt and "libcrt_oracle" not in txt and "libcrt_ref" not in txt, f
+                assert "oracle/" not in txt.replace("oracle/_ref", "").replace("the oracle", "") or f.endswith((".cuh", ".cu", ".h", ".py", ".hpp", ".cpp")), f
+
+
+def test_rng_numpy_matches_c():
+    emu = C.CDLL(EMU)
+    emu.emu_uniform.restype = C.c_float
+    emu.emu_uniform.argtypes = [C.c_uint32, C.c_uint32]
+    emu.emu_key.restype = C.c_uint32
+    emu.emu_key.argtypes = [C.c_uint64, C.c_uint32, C.c_uint32]
+    rng = np.random.default_rng(0)
+    for _ in range(500):
+        seed, px, s, ctr = int(rng.integers(0, 2**63)), int(rng.integers(0, 2**32)), int(rng.integers(0, 4096)), int(rng.integers(0, 2**24))
+        k = emu.emu_key(seed, px, s)
+        assert k == int(scenes.rng_key(seed, np.uint32(px), np.uint32(s)))
+        u = emu.emu_uniform(k, ctr)
+        assert u == float(scenes.rng_uniform(np.uint32(k), np.uint32(ctr)))
+        assert 0.0 < u <= 1.0
+    u = scenes.rng_uniform(np.uint32(12345), np.arange(1 << 16, dtype=np.uint32))
+    assert abs(float(u.mean()) - 0.5) < 0.01 and u.min() > 0 and u.max() <= 1.0
+
+
+def test_device_functions_on_host_match_oracle():
+    """crt_device.cuh (the code the kernels inline) compiled for the host:
+    scatter, camera rays and the primitive tests bit-exact against the oracle."""
+    emu = C.CDLL(EMU)
+    emu.emu_scatter.argtypes = [C.c_uint32, f32p, C.c_float, f32p, f32p, C.c_uint32, C.c_uint32, f32p, C.POINTER(C.c_uint32)]
+    emu.emu_trace.argtypes = [f32p, u32p, C.c_uint32, f32p, u32p, C.c_uint32, f32p, C.c_size_t, C.c_float, C.c_float, f32p, u32p]
+    emu.emu_get_ray.argtypes = [f32p, C.c_float, C.c_float, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, f32p]
+    emu.emu_get_ray.restype = C.c_uint32
+    o = best_oracle()
+    rng = np.random.default_rng(5)
+    for i in range(3000):
+        mt = i % 3
+        alb = rng.random(3).astype(np.float32)
+        param = [0, rng.random() * 1.3, rng.uniform(1.05, 2.4)][mt]
+        ray = np.concatenate([rng.normal(size=3), rng.normal(size=3) * 3]).astype(np.float32)
+        n = rng.normal(size=3)
+        n = (n / np.linalg.norm(n)).astype(np.float32)
+        p = (rng.normal(size=3) * 10).astype(np.float32)
+        key = int(rng.integers(0, 2**32))
+        rnds = scenes.rng_uniform(np.uint32(key), np.arange(96, dtype=np.uint32))
+        a = o.scatter(mt, alb, param, ray, p, n, rnds)
+        out = np.zeros(9, np.float32)
+        co = C.c_uint32(0)
+        ok = emu.emu_scatter(mt, alb, param, ray, np.concatenate([p, n]).astype(np.float32), key, 0, out, C.byref(co))
+        assert bool(ok) == a[0] and co.value == a[4], i
+        assert np.array_equal(out[0:3], a[1]) and np.array_equal(out[6:9], a[3], equal_nan=True), i
+    cam = crt.camera22((13, 2, 3), (0, 0, 0), (0, 1, 0), 20, 1.5, 0.1, 10)
+    for i in range(500):
+        s, t = rng.random(2)
+        out = np.zeros(6, np.float32)
+        c = emu.emu_get_ray(cam, s, t, 9, i, i % 7, 0, out)
+        a = o.get_ray(cam, s, t, 9, i, i % 7)
+        assert np.array_equal(out, a[0]) and c == a[1]
+    for sc, res in ((scenes.c1_bunny(), (64, 32)), (scenes.c2_spheres(), (60, 40))):
+        sc = dict(sc)
+        sc["tri"], sc["tri_mat"] = sc["tri"][:1200], sc["tri_mat"][:1200]
+        rays = scenes.primary_rays(crt.camera_for(sc, *res), *res)
+        t0, i0 = oracle_scene(o, sc).trace(rays)
+        nt, ns = len(sc["tri"]), len(sc["sph"])
+        t1 = np.zeros(len(rays), np.float32)
+        i1 = np.zeros(len(rays), np.uint32)
+        emu.emu_trace(sc["tri"], np.arange(nt, dtype=np.uint32), nt, sc["sph"], np.arange(nt, nt + ns, dtype=np.uint32), ns,
+                      rays, len(rays), 0.001, 3.4028234663852886e38, t1, i1)
+        assert np.array_equal(i0, i1) and np.array_equal(t0, t1)
+
+
+def test_scene_generators():
+    c3 = scenes.c3_mesh(n_theta=100, n_phi=50)
+    assert len(c3["tri"]) == 2 * 100 * 49 + 2 and np.isfinite(c3["tri"]).all()
+    # stored normals point into the sphere: the camera ray that hits the front sees dot(d, n) >= 0
+    tri = c3["tri"][:-2]
+    centroid = tri[:, :9].reshape(-1, 3, 3).mean(1)
+    assert (np.einsum("ij,ij->i", centroid, tri[:, 9:12]) < 0).mean() > 0.99
+    assert abs(np.linalg.norm(tri[:, 9:12], axis=1) - 1).max() < 1e-5
+    c2 = scenes.c2_spheres()
+    assert 470 < len(c2["sph"]) < 490 and len(c2["mats"]) == len(c2["sph"])
+    assert {m[0] for m in c2["mats"]} == {0, 1, 2}
+    c5 = scenes.c5_triangles(1000)
+    assert c5["tri"].shape == (1000, 12)
+    r = scenes.c5_incoherent_rays(1000)
+    assert np.allclose(np.linalg.norm(r[:, 3:], axis=1), 1, atol=1e-5)
+    assert np.array_equal(scenes.c5_triangles(1000)["tri"], c5["tri"])       # deterministic
+
+
+def test_tile_partition():
+    for nx, ny in ((100, 70), (1920, 1080), (33, 31)):
+        for world in (1, 2, 3, 8):
+            masks = [multi.owned_mask(nx, ny, r, world) for r in range(world)]
+            total = np.sum(masks, axis=0)
+            assert (total == 1).all()
+            assert sum(multi.paths_per_rank(nx, ny, 4, world)) == nx * ny * 4
+            for r in range(world):
+                assert multi.local_tile_count(nx, ny, r, world) * 1024 >= masks[r].sum()
+
+
+_WORKER = r'''
+import os, sys
+sys.path.insert(0, sys.argv[1]); sys.path.insert(0, os.path.join(sys.argv[1], "tests"))
+import numpy as np, torch, torch.distributed as dist
+import cudaraytracer_b200 as crt
+from cudaraytracer_b200 import scenes, multi
+from util import best_oracle, oracle_scene
+dist.init_process_group("gloo")
+rank, world = dist.get_rank(), dist.get_world_size()
+sc = scenes.c2_spheres(); nx, ny, spp = 48, 40, 2
+cam = crt.camera_for(sc, nx, ny)
+s = oracle_scene(best_oracle(), sc)
+img, acc = s.render(cam, nx, ny, spp, 8, 0, 4, want_accum=True)
+# what crt_render_accum_device produces on this rank: own pixels, zeros elsewhere
+mine = np.where(multi.owned_mask(nx, ny, rank, world)[..., None], acc, 0).astype(np.float32)
+t = torch.from_numpy(mine.copy())
+multi.combine_accum(t, 0)
+if rank == 0:
+    assert np.array_equal(t.numpy(), acc), "sum of the shards is not the full accumulator"
+    k = np.float32(1.0) / np.float32(spp)
+    rgb = np.clip(np.sqrt(t.numpy() * k), 0, 1)
+    assert np.array_equal(rgb, img)
+    print("COMBINE_OK")
+dist.barrier(); dist.destroy_process_group()
+'''
+
+
+def test_two_rank_combine_gloo(tmp_path):
+    """N > 1 host path on CPU: two ranks, tile-sharded accumulators, sum-reduce
+    to rank 0 over gloo, resolve -> bit-identical to the unsharded image."""
+    w = tmp_path / "worker.py"
+    w.write_text(_WORKER)
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1", OMP_NUM_THREADS="2")
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                          "--master-addr", "127.0.0.1", "--master-port", "29517", str(w), ROOT],
+                         capture_output=True, text=True, env=env, timeout=300)
+    assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
+    assert "COMBINE_OK" in out.stdout
+
+
+def test_bench_reference_arm_contract(tmp_path):
+    """`bench.py --impl reference` prints one JSON line with the agreed keys
+    (run here on a tiny budget by monkey-patching nothing: just 1 step)."""
+    import json
+    env = dict(os.environ, CRT_BENCH_REF_BUDGET="2")
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0"],
+                         capture_output=True, text=True, env=env, timeout=600)
+    assert out.returncode == 0, out.stderr[-2000:]
+    line = json.loads(out.stdout.strip().splitlines()[-1])
+    assert line["impl"] == "reference" and line["metric"] == "Mrays/s" and line["value"] > 0
+    assert line["cpu_baseline"]["kind"] in ("reference", "port") and line["cpu_baseline"]["cores"] >= 1
+    assert line["e2e"]["h2d_bytes_per_step"] == 0
