@@ -14,8 +14,9 @@ A step is one full frame: 33,177,600 camera samples carried to termination.
   e2e     the reference's per-frame loop (core/render.h:207-234) through the C
           ABI with HOST buffers: vertex upload -> LBVH refit -> render -> image
           download, wall clock around the synchronous calls.
-  roofline  k_bounce (traverse + shade), algorithmic bytes of SURVEY §8d from an
-          instrumented run of the same frame / the kernel's device time.
+  roofline  k_trace_queue (persistent-warp LBVH closest hit), algorithmic bytes of
+          SURVEY §8d from an instrumented run of the same frame / the kernel's
+          device time (CUDA events around each launch on the context's stream).
   cpu_baseline  the reference's own hit/scatter code (oracle/_ref, unmodified
           headers, OpenMP over rows) on a bounded sample of the same workload.
 """
@@ -188,6 +189,7 @@ def run_ours(args):
     torch.cuda.set_device(local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # keep stdout to the one JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     dev = torch.device("cuda", local)
 
@@ -337,9 +339,15 @@ def run_ours(args):
                 "sample": "%dx%d px x 1 spp of the 1920x1080x16 frame (same scene, camera, depth), %.1f s; list scan over %d triangles"
                           % (snx, sny, sh.last_seconds, len(sc["tri"]))}
         print(json.dumps(line), flush=True)
-    ctx.close()
+    # torch tensors that were used on the context's stream must go before the stream does
+    barrier()
+    del accum, rgb, host_rgb, host_verts, e0, e1
+    torch.cuda.synchronize()
+    torch.cuda.empty_cache()
     if world > 1:
         dist.destroy_process_group()
+    del ext
+    ctx.close()
 
 
 def main():
