@@ -111,7 +111,7 @@ void crt_destroy(crt_ctx* c)
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     DevBuf* bufs[] = {&c->tri_in, &c->tri_mat, &c->tri_id, &c->sph_in, &c->sph_mat, &c->sph_id, &c->mats,
-                      &c->keys[0], &c->keys[1], &c->vals[0], &c->vals[1], &c->hist, &c->nodes, &c->recs, &c->info,
+                      &c->keys[0], &c->keys[1], &c->vals[0], &c->vals[1], &c->hist, &c->nodes, &c->recs,
                       &c->child, &c->parent, &c->leaf_parent, &c->range, &c->node_box, &c->leaf_box, &c->flags,
                       &c->bounds, &c->depth_out, &c->queue[0], &c->queue[1], &c->qcount, &c->work_ctr, &c->hitbuf, &c->rad, &c->accum, &c->rgb,
                       &c->rays_tmp, &c->hits_tmp, &c->counters};
@@ -357,7 +357,7 @@ int crt_accel_info(crt_ctx* c, uint64_t* n_prims, uint64_t* n_nodes, uint64_t* b
     const uint64_t n = c->n_prims;
     if (n_prims) *n_prims = n;
     if (n_nodes) *n_nodes = n > 1 ? n - 1 : 0;
-    if (bytes) *bytes = n * 48 + n * 8 + (n > 1 ? (n - 1) * 64 : 0);
+    if (bytes) *bytes = n * 64 + (n > 1 ? (n - 1) * 64 : 0);
     if (max_depth) *max_depth = c->tree_depth;
     return CRT_OK;
 }

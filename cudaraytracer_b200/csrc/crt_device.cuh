@@ -12,13 +12,13 @@ namespace crt {
 #endif
 
 // ---- HBM layouts -----------------------------------------------------------
-// Sorted primitive record, 48 B = 3 x float4 (one 128-bit load each):
+// Sorted primitive record, 64 B = 4 x float4 (two 256-bit loads):
 //   triangle: r0 = {v0.xyz, n.x}  r1 = {e1.xyz, n.y}  r2 = {e2.xyz, n.z}
 //             e1 = v1 - v0, e2 = v2 - v0 (the subtraction triangle.h:69-70
 //             performs per test, done once; same float result)
 //   sphere:   r0 = {centre.xyz, radius}, r1 = r2 = 0
-// Per sorted primitive info, 8 B: {prim_id, mat_id | kind << 31}.
-// BVH2 node, 64 B = 4 x float4, holds BOTH children's boxes:
+//   both:     r3 = {prim_id, mat_id | kind << 31, 0, 0} as uint bits
+// BVH2 node, 64 B = 4 x float4 (two 256-bit loads), holds BOTH children's boxes:
 //   n0 = {c0.lo.x, c0.hi.x, c0.lo.y, c0.hi.y}
 //   n1 = {c1.lo.x, c1.hi.x, c1.lo.y, c1.hi.y}
 //   n2 = {c0.lo.z, c0.hi.z, c1.lo.z, c1.hi.z}
@@ -31,7 +31,6 @@ struct DMat { float r, g, b, param; uint32_t type; uint32_t pad0, pad1, pad2; };
 struct AccelView {
     const float4* nodes;
     const float4* recs;
-    const uint2* info;
     int root;            // child-style reference of the root
     uint32_t n_prims;
 };

@@ -68,20 +68,20 @@ struct crt_ctx {
 
     // LBVH
     crt::DevBuf keys[2], vals[2], hist;
-    crt::DevBuf nodes, recs, info;
+    crt::DevBuf nodes, recs;
     crt::DevBuf child, parent, leaf_parent, range, node_box, leaf_box, flags, bounds, depth_out;
     bool accel_valid = false;
     int root = 0;
     int perm_buf = 0;                      // which vals[] holds the sorted permutation
     uint32_t n_prims = 0;
-    int leaf_max = 4;
+    int leaf_max = 2;
     int tree_depth = 0;
 
     // render
     crt::DevBuf queue[2], qcount, work_ctr, hitbuf, rad, accum, rgb, rays_tmp, hits_tmp;
     crt::DevBuf counters;                  // CNT_COUNT x uint64
     int count_work = 0;
-    int leaf_thresh = 16;                  // parked lanes that trigger the primitive-test phase
+    int leaf_thresh = 8;                   // parked lanes that trigger the primitive-test phase
     int refill = 8;                        // idle lanes that trigger a refill in the persistent traversal
     int64_t batch_paths = 1ll << 25;
 

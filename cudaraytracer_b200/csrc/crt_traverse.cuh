@@ -5,27 +5,34 @@
 // (hitable/bvh.h:160-190, both children always visited, no ordering, no
 // t_max shrink).
 //
-// Execution model (chosen from the ncu capture in profiles/r01_v1_summary.md:
-// the one-ray-per-thread kernel ran with 6 of 32 lanes active on secondary rays):
-//   - persistent warps: a warp grabs chunks of TP_CHUNK rays from the queue with
-//     one atomic and keeps its lanes busy - whenever at least TP_REFILL lanes
-//     have finished their ray they take the next rays of the chunk (ballot +
-//     popc ranks), so a long ray no longer idles the other 31 lanes;
+// Execution model (each choice from an ncu capture, profiles/r01_v*_summary.md):
+//   - persistent warps: a warp grabs chunks of rays from the queue with one
+//     atomic and keeps its lanes busy - whenever at least `refill` lanes have
+//     finished their ray they take the next rays of the chunk (ballot + popc
+//     ranks), so a long ray no longer idles the other 31 lanes (v1: 6 of 32
+//     lanes active on secondary rays);
 //   - phased traversal: per iteration the warp runs EITHER one inner-node step
 //     (lanes that reached a leaf park) OR, once leaf_thresh lanes are parked or
 //     no lane is at a node, one primitive test for every parked lane. Measured
-//     alternatives (profiles/r01_*): while-while ran the node loop with 5 of 32
-//     lanes, if-if ran the primitive test with 1.7 of 32 lanes;
-//   - one 64-byte node = both children's boxes, four 128-bit loads; near child
-//     first, far child pushed; the ray interval shrinks with every hit;
+//     alternatives: while-while ran the node loop with 5 of 32 lanes, if-if ran
+//     the primitive test with 1.7 of 32 lanes. Two ballots per iteration
+//     classify every lane as node / leaf / idle;
+//   - one 64-byte node = both children's boxes, fetched with two 256-bit loads
+//     (LDG.E.256, sm_100); a primitive record is 64 bytes too. v2 used four
+//     128-bit loads per node and was L1-wavefront bound on incoherent rays
+//     (87 % L1/TEX), one wavefront per lane per load instruction;
+//   - slab distances are one FMA per plane, plane * inv_dir - origin * inv_dir,
+//     with a per-axis slack folded into the constant so the test stays
+//     conservative (see RaySlabs); near child first, far child pushed; the ray
+//     interval shrinks with every hit; the push / pop / single-child outcome is
+//     computed branch-free;
 //   - the first CRT_STACK_SMEM stack levels live in shared memory laid out
-//     [level][thread] (bank-conflict free), deeper levels spill to local memory;
+//     [level][thread] (bank-conflict free) and addressed through a byte cursor
+//     kept in a register; deeper levels spill to local memory;
 //   - primitives are tested with the reference's exact arithmetic
 //     (crt_device.cuh), so which primitive wins never depends on the tree;
 //     equal t resolves to the lower primitive id, as the first list entry wins
 //     in hitable_list.h:84.
-// Box tests are conservative: slabs are (plane - origin) * inv_dir (a few ulp
-// of relative error) and the exit distance is widened by 4 ulp.
 #pragma once
 #include "crt_device.cuh"
 
@@ -36,6 +43,9 @@ namespace crt {
 #define CRT_NODE_DONE ((int)0x80000000)
 
 constexpr int TP_BLOCK = 128;    // threads per block of every traversal kernel
+#ifndef CRT_TRACE_MIN_BLOCKS
+#define CRT_TRACE_MIN_BLOCKS 9   // resident blocks per SM the register allocation must allow
+#endif
 constexpr int TP_CHUNK = 256;    // most rays a warp takes from the queue per atomic
 constexpr int TP_REFILL = 8;     // default: refill once this many lanes are idle
 
@@ -48,9 +58,59 @@ __device__ __forceinline__ float safe_rcp(float d)
 
 __device__ __forceinline__ float4 ldg4(const float4* p) { return __ldg(p); }
 
+// 32 bytes with one LDG.E.256 through the read-only path; p must be 32-byte aligned.
+__device__ __forceinline__ void ldg256(const float4* p, float4& a, float4& b)
+{
+    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)
+                 : "l"(p));
+}
+
+__device__ __forceinline__ void sts32(uint32_t addr, int v) { asm volatile("st.shared.b32 [%0], %1;" ::"r"(addr), "r"(v)); }
+__device__ __forceinline__ int lds32(uint32_t addr)
+{
+    int v;
+    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(addr));
+    return v;
+}
+
+// Per-ray constants of the slab test. For a plane at coordinate p the exact
+// distance is (p - o) / d. The kernel evaluates fma(p, inv, c) with
+// inv = rn(1 / d) and c = -(o * inv) moved by a slack s = 2^-22 * |o * inv|
+// TOWARDS the conservative side: the plane that bounds the interval from below
+// (lo for inv >= 0, hi otherwise) gets c - s, the other c + s. s covers the
+// rounding of o * inv (half an ulp of it); the rounding of the FMA itself and
+// of inv are relative to the result and covered by the 2^-21 widening of the
+// boxes at build time plus the factor on the exit distance below. The slack is
+// per axis, so an axis with a huge |o * inv| (direction component near zero)
+// does not switch off culling on the other two.
+struct RaySlabs {
+    float ix, iy, iz;
+    float cx_lo, cx_hi, cy_lo, cy_hi, cz_lo, cz_hi;
+};
+
+__device__ __forceinline__ void slab_axis(float o, float d, float& inv, float& c_lo, float& c_hi)
+{
+    inv = safe_rcp(d);
+    const float oi = o * inv;
+    const float s = fabsf(oi) * 2.384185791015625e-7f + 1e-37f;   // 2^-22
+    const float enter = -oi - s, leave = -oi + s;
+    c_lo = inv >= 0.0f ? enter : leave;
+    c_hi = inv >= 0.0f ? leave : enter;
+}
+
+__device__ __forceinline__ RaySlabs make_slabs(v3 o, v3 d)
+{
+    RaySlabs s;
+    slab_axis(o.x, d.x, s.ix, s.cx_lo, s.cx_hi);
+    slab_axis(o.y, d.y, s.iy, s.cy_lo, s.cy_hi);
+    slab_axis(o.z, d.z, s.iz, s.cz_lo, s.cz_hi);
+    return s;
+}
+
 // Src: bool load(uint32_t i, v3& o, v3& d)  -> origin and raw direction of ray i
-// Sink: void store(uint32_t i, const Hit& h) -> h.k = sorted primitive position or ~0u
-// n_ptr: number of rays (device memory); work_ctr: zeroed queue cursor.
+// Sink: void store(uint32_t i, const Hit& h) -> h.k = sorted primitive position or ~0u, h.id = caller's id
+// work_ctr: zeroed queue cursor.
 template <bool COUNT, bool HAS_SPH, class Src, class Sink>
 __device__ __forceinline__ void traverse_persistent(const AccelView& A, const uint32_t n, uint32_t* work_ctr,
                                                     const float t_min, const float t_max, const Src& src,
@@ -59,14 +119,17 @@ __device__ __forceinline__ void traverse_persistent(const AccelView& A, const ui
 {
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t lt_mask = (1u << lane) - 1u;
-    int* const my_stack = s_stack + threadIdx.x;
+    // shared-memory stack: level L of this thread lives at stack_base + L * (TP_BLOCK * 4)
+    const uint32_t stack_base = (uint32_t)__cvta_generic_to_shared(s_stack + threadIdx.x);
+    constexpr uint32_t LEVEL = TP_BLOCK * 4u;
     int lstack[CRT_STACK_LOCAL];
+    lstack[0] = 0;
 
     int node = CRT_NODE_DONE;
-    int sp = 0;
+    uint32_t sp = 0;                          // stack depth
     uint32_t ray_i = 0;
     v3 o = V(0.f, 0.f, 0.f), d = V(0.f, 0.f, 1.f);
-    float idx = 0.f, idy = 0.f, idz = 0.f;
+    RaySlabs S = make_slabs(o, d);
     Hit best;
     best.t = t_max; best.k = 0xFFFFFFFFu; best.id = CRT_MISS_ID; best.u = best.v = 0.f;
 
@@ -77,11 +140,24 @@ __device__ __forceinline__ void traverse_persistent(const AccelView& A, const ui
     uint32_t chunk_next = 0, chunk_end = 0;   // warp-uniform
     bool more = true;                         // warp-uniform
 
+    auto pop_or_finish = [&]() {
+        if (sp > 0u) {
+            sp--;
+            node = sp < CRT_STACK_SMEM ? lds32(stack_base + sp * LEVEL) : lstack[sp - CRT_STACK_SMEM];
+        } else {
+            sink.store(ray_i, best);
+            node = CRT_NODE_DONE;
+        }
+    };
+
     for (;;) {
-        const uint32_t idle_mask = __ballot_sync(0xffffffffu, node == CRT_NODE_DONE);
-        if (idle_mask) {
+        const uint32_t int_mask = __ballot_sync(0xffffffffu, node >= 0);
+        const uint32_t leaf_mask = __ballot_sync(0xffffffffu, node < 0 && node != CRT_NODE_DONE);
+        const uint32_t busy = int_mask | leaf_mask;
+        if (busy != 0xffffffffu) {
+            const uint32_t idle_mask = ~busy;
             const uint32_t n_idle = (uint32_t)__popc(idle_mask);
-            if (more && (n_idle >= refill || idle_mask == 0xffffffffu)) {
+            if (more && (n_idle >= refill || busy == 0u)) {
                 if (chunk_next >= chunk_end) {
                     uint32_t b = 0;
                     if (lane == 0) b = atomicAdd(work_ctr, chunk);
@@ -97,37 +173,35 @@ __device__ __forceinline__ void traverse_persistent(const AccelView& A, const ui
                         v3 dr;
                         src.load(ray_i, o, dr);
                         d = ray_dir_local(dr);
-                        idx = safe_rcp(d.x); idy = safe_rcp(d.y); idz = safe_rcp(d.z);
-                        best.t = t_max; best.k = 0xFFFFFFFFu; best.u = best.v = 0.f;
+                        S = make_slabs(o, d);
+                        best.t = t_max; best.k = 0xFFFFFFFFu; best.id = CRT_MISS_ID; best.u = best.v = 0.f;
                         sp = 0;
                         node = A.root;
                         if (A.n_prims == 0u) { sink.store(ray_i, best); node = CRT_NODE_DONE; }
                     }
                     chunk_next += min(n_idle, avail);
                 }
+                continue;                      // classify the lanes again
             }
-            if (__ballot_sync(0xffffffffu, node != CRT_NODE_DONE) == 0u) {
-                if (!more) break;
-                continue;
-            }
+            if (busy == 0u) break;             // nothing in flight and the queue is empty
         }
 
         // ---- one phase per iteration: an inner-node step for the lanes at a node,
         //      or - once enough lanes are parked on a leaf, or nobody is at a node -
         //      one primitive test for every parked lane ----
-        const uint32_t leaf_mask = __ballot_sync(0xffffffffu, node < 0 && node != CRT_NODE_DONE);
-        const uint32_t int_mask = __ballot_sync(0xffffffffu, node >= 0);
         if (int_mask != 0u && (uint32_t)__popc(leaf_mask) < leaf_thresh) {
             if (node >= 0) {
-                const float4* np = A.nodes + 4 * (size_t)node;
-                const float4 n0 = ldg4(np), n1 = ldg4(np + 1), n2 = ldg4(np + 2), n3 = ldg4(np + 3);
+                const float4* np = A.nodes + 4 * (size_t)(uint32_t)node;
+                float4 n0, n1, n2, n3;
+                ldg256(np, n0, n1);
+                ldg256(np + 2, n2, n3);
                 if (COUNT) cnt.nodes++;
-                const float c0lox = (n0.x - o.x) * idx, c0hix = (n0.y - o.x) * idx;
-                const float c0loy = (n0.z - o.y) * idy, c0hiy = (n0.w - o.y) * idy;
-                const float c1lox = (n1.x - o.x) * idx, c1hix = (n1.y - o.x) * idx;
-                const float c1loy = (n1.z - o.y) * idy, c1hiy = (n1.w - o.y) * idy;
-                const float c0loz = (n2.x - o.z) * idz, c0hiz = (n2.y - o.z) * idz;
-                const float c1loz = (n2.z - o.z) * idz, c1hiz = (n2.w - o.z) * idz;
+                const float c0lox = fmaf(n0.x, S.ix, S.cx_lo), c0hix = fmaf(n0.y, S.ix, S.cx_hi);
+                const float c0loy = fmaf(n0.z, S.iy, S.cy_lo), c0hiy = fmaf(n0.w, S.iy, S.cy_hi);
+                const float c1lox = fmaf(n1.x, S.ix, S.cx_lo), c1hix = fmaf(n1.y, S.ix, S.cx_hi);
+                const float c1loy = fmaf(n1.z, S.iy, S.cy_lo), c1hiy = fmaf(n1.w, S.iy, S.cy_hi);
+                const float c0loz = fmaf(n2.x, S.iz, S.cz_lo), c0hiz = fmaf(n2.y, S.iz, S.cz_hi);
+                const float c1loz = fmaf(n2.z, S.iz, S.cz_lo), c1hiz = fmaf(n2.w, S.iz, S.cz_hi);
                 const float tn0 = fmaxf(fmaxf(fminf(c0lox, c0hix), fminf(c0loy, c0hiy)), fmaxf(fminf(c0loz, c0hiz), t_min));
                 const float tf0 = fminf(fminf(fmaxf(c0lox, c0hix), fmaxf(c0loy, c0hiy)), fminf(fmaxf(c0loz, c0hiz), best.t));
                 const float tn1 = fmaxf(fmaxf(fminf(c1lox, c1hix), fminf(c1loy, c1hiy)), fmaxf(fminf(c1loz, c1hiz), t_min));
@@ -135,24 +209,15 @@ __device__ __forceinline__ void traverse_persistent(const AccelView& A, const ui
                 const bool h0 = tn0 <= tf0 * 1.0000005f;
                 const bool h1 = tn1 <= tf1 * 1.0000005f;
                 const int c0 = __float_as_int(n3.x), c1 = __float_as_int(n3.y);
+                const bool first1 = h1 && (!h0 || tn1 < tn0);      // child 1 is entered first
                 if (h0 && h1) {
-                    const bool swap = tn1 < tn0;
-                    const int far_c = swap ? c0 : c1;
-                    node = swap ? c1 : c0;
-                    if (sp < CRT_STACK_SMEM) my_stack[sp * TP_BLOCK] = far_c;
+                    const int far_c = first1 ? c0 : c1;
+                    if (sp < CRT_STACK_SMEM) sts32(stack_base + sp * LEVEL, far_c);
                     else if (sp < CRT_STACK_SMEM + CRT_STACK_LOCAL) lstack[sp - CRT_STACK_SMEM] = far_c;
                     sp++;
-                } else if (h0) {
-                    node = c0;
-                } else if (h1) {
-                    node = c1;
-                } else if (sp > 0) {
-                    sp--;
-                    node = sp < CRT_STACK_SMEM ? my_stack[sp * TP_BLOCK] : lstack[sp - CRT_STACK_SMEM];
-                } else {
-                    sink.store(ray_i, best);
-                    node = CRT_NODE_DONE;
                 }
+                if (h0 || h1) node = first1 ? c1 : c0;
+                else pop_or_finish();
             }
         } else if (node < 0 && node != CRT_NODE_DONE) {
             // the leaf reference itself is the cursor: test its first primitive, then shrink it
@@ -160,37 +225,27 @@ __device__ __forceinline__ void traverse_persistent(const AccelView& A, const ui
             const uint32_t k = ref >> 3;
             const uint32_t rest = ref & 7u;
             {
-                const float4* rp = A.recs + 3 * (size_t)k;
-                const float4 r0 = ldg4(rp);
-                bool is_sphere = false;
-                if (HAS_SPH) is_sphere = (__ldg(&A.info[k]).y & CRT_KIND_SPHERE) != 0u;
+                const float4* rp = A.recs + 4 * (size_t)k;
+                float4 r0, r1, r2, r3;
+                ldg256(rp, r0, r1);
+                ldg256(rp + 2, r2, r3);
+                const uint32_t pid = __float_as_uint(r3.x);
                 float t, u = 0.0f, v = 0.0f;
                 bool ok;
-                if (HAS_SPH && is_sphere) {
+                if (HAS_SPH && (__float_as_uint(r3.y) & CRT_KIND_SPHERE)) {
                     if (COUNT) cnt.spheres++;
                     ok = sphere_test(vsub(o, V(r0.x, r0.y, r0.z)), d, r0.w, t_min, best.t, t);
                 } else {
-                    const float4 r1 = ldg4(rp + 1), r2 = ldg4(rp + 2);
                     if (COUNT) cnt.tris++;
                     ok = triangle_test(o, d, V(r0.x, r0.y, r0.z), V(r1.x, r1.y, r1.z), V(r2.x, r2.y, r2.z),
                                        V(r0.w, r1.w, r2.w), t_min, best.t, t, u, v);
                 }
-                if (ok && t == best.t) {
-                    // equal distance: lowest primitive id wins; t == t_max itself never counts
-                    if (best.k == 0xFFFFFFFFu) ok = false;
-                    else if (__ldg(&A.info[k]).x >= __ldg(&A.info[best.k]).x) ok = false;
-                }
-                if (ok) { best.t = t; best.k = k; best.u = u; best.v = v; }
+                // equal distance: lowest primitive id wins; t == t_max itself never counts
+                if (ok && t == best.t && (best.k == 0xFFFFFFFFu || pid >= best.id)) ok = false;
+                if (ok) { best.t = t; best.k = k; best.id = pid; best.u = u; best.v = v; }
             }
-            if (rest != 0u) {
-                node = (int)~(((k + 1u) << 3) | (rest - 1u));
-            } else if (sp > 0) {
-                sp--;
-                node = sp < CRT_STACK_SMEM ? my_stack[sp * TP_BLOCK] : lstack[sp - CRT_STACK_SMEM];
-            } else {
-                sink.store(ray_i, best);
-                node = CRT_NODE_DONE;
-            }
+            if (rest != 0u) node = (int)~(((k + 1u) << 3) | (rest - 1u));
+            else pop_or_finish();
         }
     }
 }

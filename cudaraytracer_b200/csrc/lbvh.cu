@@ -9,7 +9,7 @@
 //   3. radix_sort_pairs (radix_sort.cu): (code, primitive) pairs
 //   4. k_hierarchy    : Karras 2012 binary radix tree, one thread per internal
 //                       node, ties between equal codes broken by position
-//   5. k_fit          : one thread per sorted primitive writes its 48-byte record
+//   5. k_fit          : one thread per sorted primitive writes its 64-byte record
 //                       and box, then climbs; the second thread to reach a node
 //                       (atomic flag) merges the children's boxes
 //   6. k_emit_nodes   : writes the 64-byte traversal nodes; subtrees covering
@@ -187,7 +187,7 @@ k_fit(const float* __restrict__ tri_in, const uint32_t* __restrict__ tri_mat, co
       const float* __restrict__ sph_in, const uint32_t* __restrict__ sph_mat, const uint32_t* __restrict__ sph_id,
       uint32_t n_tri, uint32_t n, const uint32_t* __restrict__ perm, const int2* __restrict__ child,
       const int* __restrict__ parent, const int* __restrict__ leaf_parent, int* __restrict__ flags,
-      float4* __restrict__ recs, uint2* __restrict__ info, float4* __restrict__ leaf_box, float4* __restrict__ node_box)
+      float4* __restrict__ recs, float4* __restrict__ leaf_box, float4* __restrict__ node_box)
 {
     const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= n) return;
@@ -197,17 +197,17 @@ k_fit(const float* __restrict__ tri_in, const uint32_t* __restrict__ tri_mat, co
         const v3 v0 = V(t[0], t[1], t[2]);
         const v3 e1 = vsub(V(t[3], t[4], t[5]), v0);       // triangle.h:69
         const v3 e2 = vsub(V(t[6], t[7], t[8]), v0);       // triangle.h:70
-        recs[3 * (size_t)k] = make_float4(v0.x, v0.y, v0.z, t[9]);
-        recs[3 * (size_t)k + 1] = make_float4(e1.x, e1.y, e1.z, t[10]);
-        recs[3 * (size_t)k + 2] = make_float4(e2.x, e2.y, e2.z, t[11]);
-        info[k] = make_uint2(tri_id[p], tri_mat[p]);
+        recs[4 * (size_t)k] = make_float4(v0.x, v0.y, v0.z, t[9]);
+        recs[4 * (size_t)k + 1] = make_float4(e1.x, e1.y, e1.z, t[10]);
+        recs[4 * (size_t)k + 2] = make_float4(e2.x, e2.y, e2.z, t[11]);
+        recs[4 * (size_t)k + 3] = make_float4(__uint_as_float(tri_id[p]), __uint_as_float(tri_mat[p]), 0.f, 0.f);
     } else {
         const uint32_t q = p - n_tri;
         const float* s = sph_in + 4 * (size_t)q;
-        recs[3 * (size_t)k] = make_float4(s[0], s[1], s[2], s[3]);
-        recs[3 * (size_t)k + 1] = make_float4(0.f, 0.f, 0.f, 0.f);
-        recs[3 * (size_t)k + 2] = make_float4(0.f, 0.f, 0.f, 0.f);
-        info[k] = make_uint2(sph_id[q], sph_mat[q] | CRT_KIND_SPHERE);
+        recs[4 * (size_t)k] = make_float4(s[0], s[1], s[2], s[3]);
+        recs[4 * (size_t)k + 1] = make_float4(0.f, 0.f, 0.f, 0.f);
+        recs[4 * (size_t)k + 2] = make_float4(0.f, 0.f, 0.f, 0.f);
+        recs[4 * (size_t)k + 3] = make_float4(__uint_as_float(sph_id[q]), __uint_as_float(sph_mat[q] | CRT_KIND_SPHERE), 0.f, 0.f);
     }
     store_box(leaf_box, k, prim_box(tri_in, sph_in, n_tri, p));
     if (n < 2) return;
@@ -301,8 +301,7 @@ int lbvh_build(crt_ctx* c, bool refit_only)
         CRT_CUDA(c->vals[0].reserve(n * 4)); CRT_CUDA(c->vals[1].reserve(n * 4));
         CRT_CUDA(c->hist.reserve(radix_sort_hist_bytes()));
         CRT_CUDA(c->bounds.reserve(6 * sizeof(float)));
-        CRT_CUDA(c->recs.reserve(n * 48));
-        CRT_CUDA(c->info.reserve(n * 8));
+        CRT_CUDA(c->recs.reserve(n * 64));
         CRT_CUDA(c->leaf_box.reserve(n * 32));
         CRT_CUDA(c->leaf_parent.reserve(n * 4));
         CRT_CUDA(c->depth_out.reserve(sizeof(int)));
@@ -332,7 +331,7 @@ int lbvh_build(crt_ctx* c, bool refit_only)
                                             c->sph_mat.as<uint32_t>(), c->sph_id.as<uint32_t>(), n_tri, un,
                                             c->vals[c->perm_buf].as<uint32_t>(), c->child.as<int2>(),
                                             c->parent.as<int>(), c->leaf_parent.as<int>(), c->flags.as<int>(),
-                                            c->recs.as<float4>(), c->info.as<uint2>(), c->leaf_box.as<float4>(),
+                                            c->recs.as<float4>(), c->leaf_box.as<float4>(),
                                             c->node_box.as<float4>());
     const int leaf_max = c->leaf_max;
     if (n > 1)

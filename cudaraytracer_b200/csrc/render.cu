@@ -144,7 +144,7 @@ struct QueueSink {
 };
 
 template <bool COUNT, bool HAS_SPH>
-__global__ void __launch_bounds__(TP_BLOCK)
+__global__ void __launch_bounds__(TP_BLOCK, CRT_TRACE_MIN_BLOCKS)
 k_trace_queue(AccelView A, const float4* __restrict__ q, uint32_t cap, const uint32_t* __restrict__ n_ptr,
               uint32_t* __restrict__ work_ctr, float4* __restrict__ hits, unsigned long long* __restrict__ counters,
               uint32_t refill, uint32_t leaf_thresh)
@@ -217,18 +217,19 @@ k_shade(RenderParams P, AccelView A, const DMat* __restrict__ mats, const float4
                 }
                 const v3 dl = ray_dir_local(d);
                 const float ht = hr.x;
-                const uint2 inf = __ldg(&A.info[hk]);
-                const float4 r0 = ldg4(A.recs + 3 * (size_t)hk);
+                float4 r0, r1, r2, r3;
+                ldg256(A.recs + 4 * (size_t)hk, r0, r1);
+                ldg256(A.recs + 4 * (size_t)hk + 2, r2, r3);
+                const uint32_t inf_y = __float_as_uint(r3.y);
                 v3 p, n;
-                if (HAS_SPH && (inf.y & CRT_KIND_SPHERE)) {
+                if (HAS_SPH && (inf_y & CRT_KIND_SPHERE)) {
                     p = vadd(vsub(o, V(r0.x, r0.y, r0.z)), vscale(ht, dl));        // sphere.h:40 (local frame)
                     n = vdivf(p, r0.w);                                            // sphere.h:41
                 } else {
-                    const float4 r1 = ldg4(A.recs + 3 * (size_t)hk + 1), r2 = ldg4(A.recs + 3 * (size_t)hk + 2);
                     p = vadd(o, vscale(ht, dl));                                   // triangle.h:95
                     n = V(r0.w, r1.w, r2.w);                                       // triangle.h:96
                 }
-                const uint32_t mat_id = inf.y & 0x7FFFFFFFu;
+                const uint32_t mat_id = inf_y & 0x7FFFFFFFu;
                 const DMat m = load_mat(mats, mat_id);
                 const v3 e = emitted(m);                                           // render.h:56
                 if (P.mode == CRT_SHADE_PATH) {

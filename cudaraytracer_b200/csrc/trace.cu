@@ -18,7 +18,6 @@ AccelView accel_view(const crt_ctx* c)
     AccelView a;
     a.nodes = c->nodes.as<float4>();
     a.recs = c->recs.as<float4>();
-    a.info = c->info.as<uint2>();
     a.root = c->root;
     a.n_prims = c->n_prims;
     return a;
@@ -53,25 +52,23 @@ struct RaySrc {
 };
 struct HitSink {
     crt_hit* hits;
-    const uint2* info;
     __device__ __forceinline__ void store(uint32_t i, const Hit& h) const
     {
         const bool hit = h.k != 0xFFFFFFFFu;
-        const uint32_t id = hit ? __ldg(&info[h.k]).x : CRT_MISS_ID;
         reinterpret_cast<float4*>(hits)[i] =
-            make_float4(hit ? h.t : 0.0f, __uint_as_float(id), hit ? h.u : 0.0f, hit ? h.v : 0.0f);
+            make_float4(hit ? h.t : 0.0f, __uint_as_float(hit ? h.id : CRT_MISS_ID), hit ? h.u : 0.0f, hit ? h.v : 0.0f);
     }
 };
 
 template <bool COUNT, bool HAS_SPH>
-__global__ void __launch_bounds__(TP_BLOCK)
+__global__ void __launch_bounds__(TP_BLOCK, CRT_TRACE_MIN_BLOCKS)
 k_trace_lbvh(AccelView A, const crt_ray* __restrict__ rays, uint32_t n, uint32_t* __restrict__ work_ctr, float t_min,
              float t_max, crt_hit* __restrict__ hits, unsigned long long* __restrict__ counters, uint32_t refill, uint32_t leaf_thresh)
 {
     __shared__ int s_stack[CRT_STACK_SMEM * TP_BLOCK];
     TraceCounters cnt = {0u, 0u, 0u};
     RaySrc src = {rays};
-    HitSink sink = {hits, A.info};
+    HitSink sink = {hits};
     traverse_persistent<COUNT, HAS_SPH>(A, n, work_ctr, t_min, t_max, src, sink, s_stack, cnt, refill, leaf_thresh);
     if (COUNT) flush_counters(counters, cnt, 0u);
 }

@@ -1,0 +1,135 @@
+// crt_cli.cpp — host driver of the render path: the role of the reference's
+// main() (CudaTest/src/kernel.cu:41-111), with its hard-coded literals turned
+// into flags ("Config / flags").
+//
+//   crt_cli --scene bunny --obj objects/small_bunny.obj --out out/picture_
+//   crt_cli --scene spheres --nx 1200 --ny 800 --spp 64 --mode path
+//   crt_cli --scene mesh --frames 4 --animate --csv output.csv
+//
+// Per frame it does what renderBVHAnimation does (core/render.h:191-237):
+// update the vertices, refit the BVH, render, copy back, write
+// "<out><frame>.png", and it records the reference's three timings
+// (build once; update and rendering per frame) into a CSV with the reference's
+// header "frame,rendering,update,build" (kernel.cu:61).
+// Defaults are the reference's: 1024x512, 4 spp, depth 8, LambertShade
+// (kernel.cu:44-49, render.h:120).
+#include <chrono>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "builtin_scenes.h"
+#include "obj_loader.h"
+#include "png_out.h"
+#include "renderer.h"
+#include "scene.h"
+
+namespace {
+
+struct Options {
+    std::string scene = "bunny", out = "picture_", csv, mode = "lambert";
+    crt_host::SceneOptions sc;
+    int nx = 1024, ny = 512, spp = 4, depth = 8, frames = 1, device = 0;
+    bool animate = false, quiet = false;
+};
+
+double now_s()
+{
+    return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+[[noreturn]] void die(const std::string& msg)
+{
+    std::fprintf(stderr, "crt_cli: %s\n", msg.c_str());               // fail fast like deviceManage.h:3-17
+    std::exit(1);
+}
+
+Options parse(int argc, char** argv)
+{
+    Options o;
+    for (int i = 1; i < argc; i++) {
+        const std::string a = argv[i];
+        auto val = [&]() -> const char* { if (i + 1 >= argc) die("missing value after " + a); return argv[++i]; };
+        if (a == "--scene") o.scene = val();
+        else if (a == "--obj") o.sc.obj = val();
+        else if (a == "--out") o.out = val();
+        else if (a == "--csv") o.csv = val();
+        else if (a == "--mode") o.mode = val();
+        else if (a == "--camera") o.sc.camera = val();
+        else if (a == "--nx") o.nx = std::atoi(val());
+        else if (a == "--ny") o.ny = std::atoi(val());
+        else if (a == "--spp") o.spp = std::atoi(val());
+        else if (a == "--depth") o.depth = std::atoi(val());
+        else if (a == "--frames") o.frames = std::atoi(val());
+        else if (a == "--device") o.device = std::atoi(val());
+        else if (a == "--segments") { o.sc.n_theta = std::atoi(val()); o.sc.n_phi = o.sc.n_theta / 2; }
+        else if (a == "--seed") o.sc.seed = std::strtoull(val(), nullptr, 10);
+        else if (a == "--animate") o.animate = true;
+        else if (a == "--quiet") o.quiet = true;
+        else if (a == "--help" || a == "-h") {
+            std::printf("usage: crt_cli [--scene bunny|spheres|mesh] [--obj FILE] [--camera framed|reference] [--nx N --ny N]\n"
+                        "               [--spp N] [--depth N] [--mode path|lambert|normal] [--seed S] [--frames N] [--animate]\n"
+                        "               [--segments N] [--out PREFIX] [--csv FILE] [--device D] [--quiet]\n");
+            std::exit(0);
+        } else die("unknown flag " + a);
+    }
+    if (o.nx <= 0 || o.ny <= 0 || o.spp <= 0 || o.frames <= 0) die("nx, ny, spp and frames must be positive");
+    return o;
+}
+
+}  // namespace
+
+int main(int argc, char** argv)
+{
+    const Options o = parse(argc, argv);
+    int mode = CRT_SHADE_LAMBERT;
+    if (o.mode == "path") mode = CRT_SHADE_PATH;
+    else if (o.mode == "normal") mode = CRT_SHADE_NORMAL;
+    else if (o.mode != "lambert") die("unknown --mode " + o.mode);
+    try {
+        crt_host::World w;
+        if (o.scene == "bunny") crt_host::build_bunny(w, o.sc);
+        else if (o.scene == "spheres") crt_host::build_spheres(w, o.sc);
+        else if (o.scene == "mesh") crt_host::build_mesh(w, o.sc);
+        else die("unknown --scene " + o.scene);
+
+        crt_host::Renderer r(o.device);
+        r.set_world(w.list);
+        if (!o.quiet) std::printf("scene %s: %zu triangles, %zu spheres, %zu materials\n", o.scene.c_str(), r.flat().n_triangles(), r.flat().n_spheres(), r.flat().mats.size());
+        double t0 = now_s();
+        r.create_BVHfromList();                                       // kernel.cu:29-37 ("build")
+        const double build_s = now_s() - t0;
+        if (!o.quiet) std::printf("BVH build: %g s (device %g ms)\n", build_s, r.counters().build_ms);
+
+        Camera cam(w.lookfrom, w.lookat, vec3(0, 1, 0), w.vfov, float(o.nx) / float(o.ny), w.aperture, w.focus);   // createScene.h:142-154
+        std::vector<vec3> colorBuffer((size_t)o.nx * o.ny);
+        std::vector<crt_host::FrameTiming> rows;
+        std::vector<float> verts;
+        for (int frame = 0; frame < o.frames; frame++) {
+            double update_s = 0.0;
+            if (o.animate && o.scene == "mesh") {                     // render.h:207-217: new pose, then refit
+                t0 = now_s();
+                crt_host::mesh_vertices(o.sc.n_theta, o.sc.n_phi, 0.3 * frame, verts, nullptr);
+                r.update_vertices(verts.data(), 0, verts.size() / 9);
+                r.Update_BVH();
+                update_s = now_s() - t0;
+            }
+            t0 = now_s();
+            r.render(colorBuffer.data(), cam, o.nx, o.ny, o.spp, o.depth, mode, o.sc.seed + (uint64_t)frame);   // render.h:219-228
+            const double render_s = now_s() - t0;
+            if (!WritePng(o.nx, o.ny, frame, colorBuffer.data(), o.out.c_str())) die("cannot write " + o.out + std::to_string(frame) + ".png");
+            rows.push_back({frame, render_s, update_s, frame == 0 ? build_s : 0.0});
+            if (!o.quiet) {
+                const crt_counters c = r.counters();
+                std::printf("frame %d: rendering %g s (device %g ms), update %g s; %llu rays so far\n", frame, render_s, c.render_ms, update_s, (unsigned long long)c.rays);
+            }
+        }
+        if (!o.csv.empty() && !crt_host::write_csv(o.csv, rows)) die("cannot write " + o.csv);
+    } catch (const std::exception& e) {
+        die(e.what());
+    }
+    return 0;
+}

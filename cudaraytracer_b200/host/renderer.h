@@ -1,0 +1,116 @@
+// renderer.h — the reference's host call sequence on top of the C ABI.
+//
+// kernel.cu:41-111 drives the reference through a handful of host functions
+// (SURVEY 8b). Renderer keeps their names and order and forwards each to the
+// entry point of include/crt.h that replaces it:
+//
+//   reference (file:line)                              here                        C ABI
+//   create_FBXMesh / init_List  createScene.h:167,192  set_world(list)             crt_scene_set_*
+//   create_BVHfromList          createScene.h:212      create_BVHfromList()        crt_accel_build
+//   updateFBXObj                createScene.h:125      update_vertices(...)        crt_scene_update_vertices
+//   Update_BVH                  createScene.h:53       Update_BVH()                crt_accel_refit
+//   render<<<>>> + D2H copy     render.h:105,222-226   render(colorBuffer, ...)    crt_render
+//   WritePng                    render.h:135           WritePng (png_out.h)        -
+//   StopWatch + writeCSV        swatch.h, CSVWriter.h  counters(), write_csv()     crt_get_counters
+//
+// Errors: the reference prints and exits (core/deviceManage.h:3-17). The C ABI
+// returns codes; this wrapper turns them into std::runtime_error carrying
+// crt_last_error(), and the CLI prints and exits like the reference.
+// There is no CPU path: constructing a Renderer without a CUDA device throws.
+#pragma once
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../../include/crt.h"
+#include "scene.h"
+
+namespace crt_host {
+
+inline void check(int rc, const char* what)
+{
+    if (rc != CRT_OK) throw std::runtime_error(std::string(what) + ": " + crt_last_error());
+}
+
+struct FrameTiming { int frame; double rendering, update, build; };  // CSV columns of kernel.cu:61
+
+class Renderer {
+public:
+    explicit Renderer(int device = 0) { check(crt_create(device, &ctx_), "crt_create"); }
+    ~Renderer() { crt_destroy(ctx_); }
+    Renderer(const Renderer&) = delete;
+    Renderer& operator=(const Renderer&) = delete;
+
+    crt_ctx* ctx() const { return ctx_; }
+
+    // Flatten a world list and upload it (replaces add_mesh_withNormal / create_List).
+    void set_world(const Hitable& world)
+    {
+        flat_ = flatten_scene(world);
+        upload();
+    }
+    void set_flat(const FlatScene& f) { flat_ = f; upload(); }
+    const FlatScene& flat() const { return flat_; }
+
+    void create_BVHfromList() { check(crt_accel_build(ctx_), "crt_accel_build"); }
+    void Update_BVH() { check(crt_accel_refit(ctx_), "crt_accel_refit"); }
+
+    // New vertex positions of triangles [first, first + n): 9 floats each
+    // (Triangle::SetVertices for every face, shapes/triangle.h:40-45).
+    void update_vertices(const float* verts, size_t first, size_t n)
+    {
+        check(crt_scene_update_vertices(ctx_, verts, first, n), "crt_scene_update_vertices");
+    }
+
+    // render<<<>>> + cudaMemcpy D2H (render.h:222-226): colorBuffer is the
+    // caller's nx*ny vec3 array, row 0 at the bottom, values after gamma and clip.
+    void render(vec3* colorBuffer, const Camera& camera, int nx, int ny, int samples, int max_depth,
+                int shade_mode = CRT_SHADE_LAMBERT, uint64_t seed = 0)
+    {
+        static_assert(sizeof(vec3) == 3 * sizeof(float), "vec3 must be three packed floats");
+        const crt_camera cam = camera.to_crt();
+        check(crt_render(ctx_, &cam, nx, ny, samples, max_depth, shade_mode, seed, &colorBuffer[0].e[0]), "crt_render");
+    }
+
+    // (*world)->hit for a batch of rays (render.h:53).
+    void trace(const std::vector<Ray>& rays, std::vector<crt_hit>& hits, float t_min = 0.001f, float t_max = 3.402823466e38f,
+               int accel = CRT_ACCEL_LBVH)
+    {
+        std::vector<crt_ray> r(rays.size());
+        for (size_t i = 0; i < rays.size(); i++) r[i] = rays[i].to_crt();
+        hits.resize(rays.size());
+        check(crt_trace(ctx_, r.data(), r.size(), t_min, t_max, accel, hits.data()), "crt_trace");
+    }
+
+    crt_counters counters() const
+    {
+        crt_counters c;
+        check(crt_get_counters(ctx_, &c), "crt_get_counters");
+        return c;
+    }
+    void set_option(int option, int64_t value) { check(crt_set_option(ctx_, option, value), "crt_set_option"); }
+
+private:
+    void upload()
+    {
+        check(crt_scene_set_materials(ctx_, flat_.mats.data(), flat_.mats.size()), "crt_scene_set_materials");
+        check(crt_scene_set_triangles(ctx_, flat_.tri.data(), flat_.tri_mat.data(), flat_.tri_id.data(), flat_.n_triangles()),
+              "crt_scene_set_triangles");
+        check(crt_scene_set_spheres(ctx_, flat_.sph.data(), flat_.sph_mat.data(), flat_.sph_id.data(), flat_.n_spheres()),
+              "crt_scene_set_spheres");
+    }
+    crt_ctx* ctx_ = nullptr;
+    FlatScene flat_;
+};
+
+// Loader/CSVWriter.h:8-32: header line, then one row per frame, "\n" endings.
+inline bool write_csv(const std::string& path, const std::vector<FrameTiming>& rows)
+{
+    FILE* f = std::fopen(path.c_str(), "w");
+    if (!f) return false;
+    std::fprintf(f, "frame,rendering,update,build\n");
+    for (const FrameTiming& r : rows) std::fprintf(f, "%d,%g,%g,%g\n", r.frame, r.rendering, r.update, r.build);
+    return std::fclose(f) == 0;
+}
+
+}  // namespace crt_host

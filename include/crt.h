@@ -92,10 +92,10 @@ typedef enum {
 } crt_accel_kind;
 
 typedef enum {
-    CRT_OPT_LEAF_MAX = 1,   /* max primitives per LBVH leaf, 1..8 (default 4); takes effect at the next build */
+    CRT_OPT_LEAF_MAX = 1,   /* max primitives per LBVH leaf, 1..8 (default 2); takes effect at the next build */
     CRT_OPT_COUNTERS = 2,   /* 1: run the instrumented kernels that count nodes/primitives visited */
     CRT_OPT_BATCH_PATHS = 3,/* max camera samples in flight per wavefront batch (default 1<<25) */
-    CRT_OPT_LEAF_THRESH = 5,/* tuning: lanes parked on a leaf that trigger the primitive-test phase, 1..32 (default 16) */
+    CRT_OPT_LEAF_THRESH = 5,/* tuning: lanes parked on a leaf that trigger the primitive-test phase, 1..32 (default 8) */
     CRT_OPT_REFILL = 4      /* tuning: idle lanes per warp that trigger a refill from the ray queue, 1..32 (default 8) */
 } crt_option;
 
