@@ -295,8 +295,8 @@ def run_ours(args):
     if rank == 0:
         peaks, peak_src = measured_peaks()
         n_r = work["rays"]
-        alg_bytes = 64 * work["nodes_visited"] + 48 * work["tris_tested"] + 16 * work["spheres_tested"] + 48 * n_r
-        alg_flops = 48 * work["nodes_visited"] + 50 * work["tris_tested"] + 27 * work["spheres_tested"]
+        alg_bytes = 128 * work["nodes_visited"] + 48 * work["tris_tested"] + 16 * work["spheres_tested"] + 48 * n_r
+        alg_flops = 96 * work["nodes_visited"] + 50 * work["tris_tested"] + 27 * work["spheres_tested"]
         bounce_launches = depth + 1
         per_launch_ms = bounce_ms / max(1, args.steps * bounce_launches)
         achieved = alg_bytes / bounce_launches / (per_launch_ms * 1e-3) / 1e9

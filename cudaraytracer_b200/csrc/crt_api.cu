@@ -357,7 +357,7 @@ int crt_accel_info(crt_ctx* c, uint64_t* n_prims, uint64_t* n_nodes, uint64_t* b
     const uint64_t n = c->n_prims;
     if (n_prims) *n_prims = n;
     if (n_nodes) *n_nodes = n > 1 ? n - 1 : 0;
-    if (bytes) *bytes = n * 64 + (n > 1 ? (n - 1) * 64 : 0);
+    if (bytes) *bytes = n * 64 + (n > 1 ? (n - 1) * 128 : 0);
     if (max_depth) *max_depth = c->tree_depth;
     return CRT_OK;
 }

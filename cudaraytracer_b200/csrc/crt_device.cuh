@@ -18,12 +18,15 @@ namespace crt {
 //             performs per test, done once; same float result)
 //   sphere:   r0 = {centre.xyz, radius}, r1 = r2 = 0
 //   both:     r3 = {prim_id, mat_id | kind << 31, 0, 0} as uint bits
-// BVH2 node, 64 B = 4 x float4 (two 256-bit loads), holds BOTH children's boxes:
-//   n0 = {c0.lo.x, c0.hi.x, c0.lo.y, c0.hi.y}
-//   n1 = {c1.lo.x, c1.hi.x, c1.lo.y, c1.hi.y}
-//   n2 = {c0.lo.z, c0.hi.z, c1.lo.z, c1.hi.z}
-//   n3 = {child0, child1, -, -} as int bits; child >= 0: node index,
-//        child < 0: leaf, ~child = (first sorted primitive << 3) | (count - 1)
+// 4-wide node, 128 B = 8 x float4 = one cache line, holds the boxes of up to
+// four children, one float4 per plane:
+//   n0 = lo.x[0..3]  n1 = hi.x[0..3]  n2 = lo.y[0..3]  n3 = hi.y[0..3]
+//   n4 = lo.z[0..3]  n5 = hi.z[0..3]
+//   n6 = child[0..3] as int bits; child >= 0: node index, child < 0: leaf,
+//        ~child = (first sorted primitive << 3) | (count - 1);
+//        CRT_SLOT_EMPTY: unused slot (a node has 2..4 children)
+//   n7 = padding
+#define CRT_SLOT_EMPTY ((int)0x80000000)
 #define CRT_KIND_SPHERE 0x80000000u
 
 struct DMat { float r, g, b, param; uint32_t type; uint32_t pad0, pad1, pad2; };  // 32 B

@@ -17,15 +17,18 @@
 //     alternatives: while-while ran the node loop with 5 of 32 lanes, if-if ran
 //     the primitive test with 1.7 of 32 lanes. Two ballots per iteration
 //     classify every lane as node / leaf / idle;
-//   - one 64-byte node = both children's boxes, fetched with two 256-bit loads
-//     (LDG.E.256, sm_100); a primitive record is 64 bytes too. v2 used four
-//     128-bit loads per node and was L1-wavefront bound on incoherent rays
-//     (87 % L1/TEX), one wavefront per lane per load instruction;
+//   - one 128-byte node (one cache line) = the boxes of up to four children,
+//     fetched with three 256-bit loads (LDG.E.256, sm_100) + one 128-bit load of
+//     the child references; a primitive record is 64 bytes = two 256-bit loads.
+//     v2 used four 128-bit loads per binary node and was L1-wavefront bound on
+//     incoherent rays (87 % L1/TEX, one wavefront per lane per load
+//     instruction); v3 (binary, 256-bit loads) was bound by the per-iteration
+//     bookkeeping and the dependent node fetch, which a 4-wide node halves;
 //   - slab distances are one FMA per plane, plane * inv_dir - origin * inv_dir,
 //     with a per-axis slack folded into the constant so the test stays
-//     conservative (see RaySlabs); near child first, far child pushed; the ray
-//     interval shrinks with every hit; the push / pop / single-child outcome is
-//     computed branch-free;
+//     conservative (see RaySlabs); the hit children are sorted by entry
+//     distance with a 5-exchange network, the nearest is entered and the others
+//     are pushed farthest first; the ray interval shrinks with every hit;
 //   - the first CRT_STACK_SMEM stack levels live in shared memory laid out
 //     [level][thread] (bank-conflict free) and addressed through a byte cursor
 //     kept in a register; deeper levels spill to local memory;
@@ -44,7 +47,7 @@ namespace crt {
 
 constexpr int TP_BLOCK = 128;    // threads per block of every traversal kernel
 #ifndef CRT_TRACE_MIN_BLOCKS
-#define CRT_TRACE_MIN_BLOCKS 9   // resident blocks per SM the register allocation must allow
+#define CRT_TRACE_MIN_BLOCKS 8   // resident blocks per SM the register allocation must allow
 #endif
 constexpr int TP_CHUNK = 256;    // most rays a warp takes from the queue per atomic
 constexpr int TP_REFILL = 8;     // default: refill once this many lanes are idle
@@ -140,6 +143,11 @@ __device__ __forceinline__ void traverse_persistent(const AccelView& A, const ui
     uint32_t chunk_next = 0, chunk_end = 0;   // warp-uniform
     bool more = true;                         // warp-uniform
 
+    auto push = [&](int r) {
+        if (sp < CRT_STACK_SMEM) sts32(stack_base + sp * LEVEL, r);
+        else if (sp < CRT_STACK_SMEM + CRT_STACK_LOCAL) lstack[sp - CRT_STACK_SMEM] = r;
+        sp++;
+    };
     auto pop_or_finish = [&]() {
         if (sp > 0u) {
             sp--;
@@ -191,32 +199,46 @@ __device__ __forceinline__ void traverse_persistent(const AccelView& A, const ui
         //      one primitive test for every parked lane ----
         if (int_mask != 0u && (uint32_t)__popc(leaf_mask) < leaf_thresh) {
             if (node >= 0) {
-                const float4* np = A.nodes + 4 * (size_t)(uint32_t)node;
-                float4 n0, n1, n2, n3;
-                ldg256(np, n0, n1);
-                ldg256(np + 2, n2, n3);
+                const float4* np = A.nodes + 8 * (size_t)(uint32_t)node;
+                float4 lox, hix, loy, hiy, loz, hiz;
+                ldg256(np, lox, hix);
+                ldg256(np + 2, loy, hiy);
+                ldg256(np + 4, loz, hiz);
+                const int4 refs = __ldg(reinterpret_cast<const int4*>(np + 6));
                 if (COUNT) cnt.nodes++;
-                const float c0lox = fmaf(n0.x, S.ix, S.cx_lo), c0hix = fmaf(n0.y, S.ix, S.cx_hi);
-                const float c0loy = fmaf(n0.z, S.iy, S.cy_lo), c0hiy = fmaf(n0.w, S.iy, S.cy_hi);
-                const float c1lox = fmaf(n1.x, S.ix, S.cx_lo), c1hix = fmaf(n1.y, S.ix, S.cx_hi);
-                const float c1loy = fmaf(n1.z, S.iy, S.cy_lo), c1hiy = fmaf(n1.w, S.iy, S.cy_hi);
-                const float c0loz = fmaf(n2.x, S.iz, S.cz_lo), c0hiz = fmaf(n2.y, S.iz, S.cz_hi);
-                const float c1loz = fmaf(n2.z, S.iz, S.cz_lo), c1hiz = fmaf(n2.w, S.iz, S.cz_hi);
-                const float tn0 = fmaxf(fmaxf(fminf(c0lox, c0hix), fminf(c0loy, c0hiy)), fmaxf(fminf(c0loz, c0hiz), t_min));
-                const float tf0 = fminf(fminf(fmaxf(c0lox, c0hix), fmaxf(c0loy, c0hiy)), fminf(fmaxf(c0loz, c0hiz), best.t));
-                const float tn1 = fmaxf(fmaxf(fminf(c1lox, c1hix), fminf(c1loy, c1hiy)), fmaxf(fminf(c1loz, c1hiz), t_min));
-                const float tf1 = fminf(fminf(fmaxf(c1lox, c1hix), fmaxf(c1loy, c1hiy)), fminf(fmaxf(c1loz, c1hiz), best.t));
-                const bool h0 = tn0 <= tf0 * 1.0000005f;
-                const bool h1 = tn1 <= tf1 * 1.0000005f;
-                const int c0 = __float_as_int(n3.x), c1 = __float_as_int(n3.y);
-                const bool first1 = h1 && (!h0 || tn1 < tn0);      // child 1 is entered first
-                if (h0 && h1) {
-                    const int far_c = first1 ? c0 : c1;
-                    if (sp < CRT_STACK_SMEM) sts32(stack_base + sp * LEVEL, far_c);
-                    else if (sp < CRT_STACK_SMEM + CRT_STACK_LOCAL) lstack[sp - CRT_STACK_SMEM] = far_c;
-                    sp++;
+                float key[4];
+                int ref[4] = {refs.x, refs.y, refs.z, refs.w};
+                const float plo_x[4] = {lox.x, lox.y, lox.z, lox.w}, phi_x[4] = {hix.x, hix.y, hix.z, hix.w};
+                const float plo_y[4] = {loy.x, loy.y, loy.z, loy.w}, phi_y[4] = {hiy.x, hiy.y, hiy.z, hiy.w};
+                const float plo_z[4] = {loz.x, loz.y, loz.z, loz.w}, phi_z[4] = {hiz.x, hiz.y, hiz.z, hiz.w};
+                int n_hit = 0;
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    const float ax = fmaf(plo_x[k], S.ix, S.cx_lo), bx = fmaf(phi_x[k], S.ix, S.cx_hi);
+                    const float ay = fmaf(plo_y[k], S.iy, S.cy_lo), by = fmaf(phi_y[k], S.iy, S.cy_hi);
+                    const float az = fmaf(plo_z[k], S.iz, S.cz_lo), bz = fmaf(phi_z[k], S.iz, S.cz_hi);
+                    const float tn = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), t_min));
+                    const float tf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), best.t));
+                    const bool h = tn <= tf * 1.0000005f && ref[k] != CRT_SLOT_EMPTY;
+                    key[k] = h ? tn : INFINITY;
+                    n_hit += h ? 1 : 0;
                 }
-                if (h0 || h1) node = first1 ? c1 : c0;
+                // order the four slots by entry distance (misses last): 5 compare-exchanges
+#define CRT_CSWAP(a, b)                                                                    \
+                {                                                                          \
+                    const bool sw = key[b] < key[a];                                       \
+                    const float ka = key[a], kb = key[b];                                  \
+                    const int ra = ref[a], rb = ref[b];                                    \
+                    key[a] = sw ? kb : ka; key[b] = sw ? ka : kb;                          \
+                    ref[a] = sw ? rb : ra; ref[b] = sw ? ra : rb;                          \
+                }
+                CRT_CSWAP(0, 1) CRT_CSWAP(2, 3) CRT_CSWAP(0, 2) CRT_CSWAP(1, 3) CRT_CSWAP(1, 2)
+#undef CRT_CSWAP
+                // farthest first, so the nearest pending child is popped first
+                if (n_hit > 3) push(ref[3]);
+                if (n_hit > 2) push(ref[2]);
+                if (n_hit > 1) push(ref[1]);
+                if (n_hit > 0) node = ref[0];
                 else pop_or_finish();
             }
         } else if (node < 0 && node != CRT_NODE_DONE) {

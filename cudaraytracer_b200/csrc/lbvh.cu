@@ -12,7 +12,8 @@
 //   5. k_fit          : one thread per sorted primitive writes its 64-byte record
 //                       and box, then climbs; the second thread to reach a node
 //                       (atomic flag) merges the children's boxes
-//   6. k_emit_nodes   : writes the 64-byte traversal nodes; subtrees covering
+//   6. k_emit_nodes   : writes the 128-byte 4-wide traversal nodes (the boxes of
+//                       a binary node's grandchildren); subtrees covering
 //                       <= leaf_max primitives collapse into one leaf (a Karras
 //                       node always covers a contiguous range of sorted primitives)
 // Refit = steps 5 and 6 on the existing topology.
@@ -225,6 +226,34 @@ k_fit(const float* __restrict__ tri_in, const uint32_t* __restrict__ tri_mat, co
     }
 }
 
+// One 4-wide traversal node per binary node i that is not collapsed into a
+// leaf: its slots are i's grandchildren (a child that is a leaf, or a subtree
+// of <= leaf_max primitives, keeps its own slot). Every binary node gets its
+// wide node at the same index, so no renumbering pass is needed; only the
+// nodes reachable from the root through slot references are ever fetched.
+struct Slot { int ref; Box box; };
+
+__device__ __forceinline__ bool resolve_child(int c, int leaf_max, const int2* __restrict__ range,
+                                              const float4* __restrict__ leaf_box, const float4* __restrict__ node_box,
+                                              Slot& out)
+{
+    if (c < 0) {
+        const uint32_t pos = (uint32_t)(~c);
+        out.ref = ~(int)(pos << 3);
+        out.box = load_box(leaf_box, pos);
+        return true;                                       // a leaf
+    }
+    const int2 cr = range[c];
+    const int size = cr.y - cr.x + 1;
+    out.box = load_box(node_box, (size_t)c);
+    if (size <= leaf_max) {
+        out.ref = ~(int)(((uint32_t)cr.x << 3) | (uint32_t)(size - 1));
+        return true;
+    }
+    out.ref = c;
+    return false;                                          // an inner node
+}
+
 __global__ void __launch_bounds__(256)
 k_emit_nodes(int n, int leaf_max, const int2* __restrict__ child, const int2* __restrict__ range,
              const float4* __restrict__ leaf_box, const float4* __restrict__ node_box, float4* __restrict__ nodes)
@@ -234,28 +263,34 @@ k_emit_nodes(int n, int leaf_max, const int2* __restrict__ child, const int2* __
     const int2 rg = range[i];
     if (rg.y - rg.x + 1 <= leaf_max) return;               // collapsed into a leaf of an ancestor
     const int2 ch = child[i];
-    int ref[2];
-    Box bx[2];
+    Slot slot[4];
+    int ns = 0;
     const int cc[2] = {ch.x, ch.y};
 #pragma unroll
     for (int s = 0; s < 2; s++) {
-        const int c = cc[s];
-        if (c < 0) {
-            const uint32_t pos = (uint32_t)(~c);
-            ref[s] = ~(int)(pos << 3);
-            bx[s] = load_box(leaf_box, pos);
+        Slot c;
+        if (resolve_child(cc[s], leaf_max, range, leaf_box, node_box, c)) {
+            slot[ns++] = c;
         } else {
-            const int2 cr = range[c];
-            const int size = cr.y - cr.x + 1;
-            ref[s] = size <= leaf_max ? ~(int)(((uint32_t)cr.x << 3) | (uint32_t)(size - 1)) : c;
-            bx[s] = load_box(node_box, (size_t)c);
+            const int2 gc = child[c.ref];
+            resolve_child(gc.x, leaf_max, range, leaf_box, node_box, slot[ns++]);
+            resolve_child(gc.y, leaf_max, range, leaf_box, node_box, slot[ns++]);
         }
     }
-    float4* np = nodes + 4 * (size_t)i;
-    np[0] = make_float4(bx[0].lx, bx[0].hx, bx[0].ly, bx[0].hy);
-    np[1] = make_float4(bx[1].lx, bx[1].hx, bx[1].ly, bx[1].hy);
-    np[2] = make_float4(bx[0].lz, bx[0].hz, bx[1].lz, bx[1].hz);
-    np[3] = make_float4(__int_as_float(ref[0]), __int_as_float(ref[1]), 0.0f, 0.0f);
+    for (int s = ns; s < 4; s++) {
+        slot[s].ref = CRT_SLOT_EMPTY;
+        slot[s].box = Box{0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    }
+    float4* np = nodes + 8 * (size_t)i;
+    np[0] = make_float4(slot[0].box.lx, slot[1].box.lx, slot[2].box.lx, slot[3].box.lx);
+    np[1] = make_float4(slot[0].box.hx, slot[1].box.hx, slot[2].box.hx, slot[3].box.hx);
+    np[2] = make_float4(slot[0].box.ly, slot[1].box.ly, slot[2].box.ly, slot[3].box.ly);
+    np[3] = make_float4(slot[0].box.hy, slot[1].box.hy, slot[2].box.hy, slot[3].box.hy);
+    np[4] = make_float4(slot[0].box.lz, slot[1].box.lz, slot[2].box.lz, slot[3].box.lz);
+    np[5] = make_float4(slot[0].box.hz, slot[1].box.hz, slot[2].box.hz, slot[3].box.hz);
+    np[6] = make_float4(__int_as_float(slot[0].ref), __int_as_float(slot[1].ref), __int_as_float(slot[2].ref),
+                        __int_as_float(slot[3].ref));
+    np[7] = make_float4(0.f, 0.f, 0.f, 0.f);
 }
 
 __global__ void __launch_bounds__(256)
@@ -306,7 +341,7 @@ int lbvh_build(crt_ctx* c, bool refit_only)
         CRT_CUDA(c->leaf_parent.reserve(n * 4));
         CRT_CUDA(c->depth_out.reserve(sizeof(int)));
         const size_t ni = n > 1 ? n - 1 : 1;
-        CRT_CUDA(c->nodes.reserve(ni * 64));
+        CRT_CUDA(c->nodes.reserve(ni * 128));
         CRT_CUDA(c->child.reserve(ni * 8));
         CRT_CUDA(c->range.reserve(ni * 8));
         CRT_CUDA(c->parent.reserve(ni * 4));

@@ -24,6 +24,8 @@
 // carries only its draw counter.
 #include "crt_internal.h"
 #include "crt_traverse.cuh"
+#include <stdio.h>
+#include <stdlib.h>
 
 namespace crt {
 
@@ -439,11 +441,14 @@ int render_accum(crt_ctx* c, const crt_camera* cam, int nx, int ny, int s0, int 
             float bms = 0.f;
             CRT_CUDA(cudaEventElapsedTime(&bms, c->ev2, c->ev3));
             bounce_ms += bms;
+            static const bool verbose = getenv("CRT_TRACE_TIMING") != nullptr;   // development aid
             for (int b = 0; b < bounces; b++) {
                 float tms = 0.f;
                 CRT_CUDA(cudaEventElapsedTime(&tms, c->ev_trace[2 * b], c->ev_trace[2 * b + 1]));
                 trace_q_ms += tms;
+                if (verbose) fprintf(stderr, "[crt] bounce %d: %u rays, trace %.3f ms\n", b, h_counts[b], tms);
             }
+            if (verbose) fprintf(stderr, "[crt] batch: raygen..accumulate %.3f ms, bounces %.3f ms\n", 0.f, bms);
             total_paths += h_counts[0];
             for (int b = 0; b < bounces; b++) total_rays += h_counts[b];
         }

@@ -67,7 +67,7 @@ def main():
         ms = e0.elapsed_time(e1) / reps
         n = len(rays)
         hitf = float((d_hits[:, 1].view(torch.int32) != -1).float().mean())
-        byts = 64 * c["nodes_visited"] + 48 * c["tris_tested"] + 16 * c["spheres_tested"] + 40 * n
+        byts = 128 * c["nodes_visited"] + 48 * c["tris_tested"] + 16 * c["spheres_tested"] + 40 * n
         print("%-10s %8d rays %.3f ms  %.1f Mrays/s  hit %.2f  nodes/ray %.1f tris/ray %.1f  alg %.1f GB/s" % (
             name, n, ms, n / ms / 1e3, hitf, c["nodes_visited"] / n, c["tris_tested"] / n, byts / ms / 1e6))
     for mode, nm in ((crt.SHADE_PATH, "path"), (crt.SHADE_LAMBERT, "lambert")):
