@@ -9,8 +9,11 @@ Workload (BASELINE.json configs[2], "C3"): synthetic 998,002-triangle mesh,
 A step is one full frame: 33,177,600 camera samples carried to termination.
 
   value   Mrays/s with the scene, LBVH and framebuffers resident in HBM
-          (crt_render_accum_device + resolve; tiles sharded over the ranks and
-          summed with an NCCL reduce when N > 1), CUDA events, max over ranks.
+          (crt_render_accum_device + resolve), CUDA events, max over ranks.
+          N > 1 (--scaling weak, the default): every rank renders the frame's
+          full work, 16 samples of every pixel on its own sample range, and the
+          accumulators are summed with one NCCL reduce (16 N spp in the combined
+          frame). --scaling strong splits the 16-spp frame by 32x32 tiles instead.
   e2e     the reference's per-frame loop (core/render.h:207-234) through the C
           ABI with HOST buffers: vertex upload -> LBVH refit -> render -> image
           download, wall clock around the synchronous calls.
@@ -165,7 +168,7 @@ def run_reference(args):
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": args.gpus,
         "steps": steps, "warmup": warm, "ms_per_step": 1e3 * secs / max(1, steps), "higher_is_better": True,
-        "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "paths_per_s": paths / secs,
         "config": {"workload": WORKLOAD, "sample": sample},
         "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": lib.num_threads(), "kind": kind, "sample": sample},
@@ -212,13 +215,21 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    weak = args.scaling == "weak"
+
     def step(seed):
-        ctx.render_accum_device(cam, nx, ny, 0, spp, depth, crt.SHADE_PATH, seed, rank, world, accum.data_ptr())
+        if weak:
+            # every rank renders the named frame's full work: its own range of 16 samples of every pixel
+            ctx.render_accum_device(cam, nx, ny, spp * rank, spp * (rank + 1), depth, crt.SHADE_PATH, seed, 0, 1,
+                                    accum.data_ptr())
+        else:
+            # the frame is fixed; ranks split its 32x32 tiles (bit-identical to the 1-GPU image)
+            ctx.render_accum_device(cam, nx, ny, 0, spp, depth, crt.SHADE_PATH, seed, rank, world, accum.data_ptr())
         if world > 1:
             with torch.cuda.stream(ext):
                 multi.combine_accum(accum, 0)
         if rank == 0:
-            ctx.resolve_device(accum.data_ptr(), nx * ny, spp, rgb.data_ptr())
+            ctx.resolve_device(accum.data_ptr(), nx * ny, spp * world if weak else spp, rgb.data_ptr())
 
     def e2e_step(seed):
         if world == 1:
@@ -304,15 +315,17 @@ def run_ours(args):
         tpath = os.path.join(ROOT, "profiles", "k_trace_queue_traffic.json")
         if os.path.exists(tpath):
             with open(tpath) as f:
-                traffic = json.load(f).get("dram_bytes_per_launch")
+                traffic = json.load(f).get("dram_bytes_per_launch") if (world == 1 or weak) else None
         line = {
             "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong",
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": args.scaling,
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "paths_per_s": paths / (ms * 1e-3),
             "config": {"workload": WORKLOAD, "triangles": int(info["n_prims"]), "lbvh_depth": info["max_depth"],
-                       "lbvh_build_ms": build_ms, "parallelism": "tiles%d" % world if world > 1 else "single",
-                       "combine": "ncclReduce(sum) of 32x32-tile-sharded accumulators" if world > 1 else "none",
+                       "lbvh_build_ms": build_ms, "parallelism": ("single" if world == 1 else
+                                       "samples%d: every rank renders 16 spp of every pixel (sample range [16r, 16r+16)), %d spp in the combined frame" % (world, spp * world)
+                                       if weak else "tiles%d: 32x32 tiles, index mod N" % world),
+                       "combine": "ncclReduce(sum) of the 24.9 MB accumulators onto rank 0" if world > 1 else "none",
                        "l2": "per-step working set (queues 4.2 GB + LBVH 0.12 GB) exceeds the 126 MB L2; no explicit flush",
                        "rays_per_path": rays / max(1.0, paths)},
             "clocks": clocks,
@@ -357,6 +370,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="N > 1: weak = every rank renders the full 16-spp frame's work on its own sample range "
+                         "(default); strong = the 16-spp frame is split by tiles")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":

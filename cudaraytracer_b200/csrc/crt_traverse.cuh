@@ -52,7 +52,7 @@ constexpr int TP_BLOCK = 128;    // threads per block of every traversal kernel
 constexpr int TP_CHUNK = 256;    // most rays a warp takes from the queue per atomic
 constexpr int TP_REFILL = 8;     // default: refill once this many lanes are idle
 
-struct TraceCounters { uint32_t nodes, tris, spheres; };
+struct TraceCounters { uint32_t nodes, tris, spheres, max_steps; };
 
 __device__ __forceinline__ float safe_rcp(float d)
 {
@@ -131,6 +131,7 @@ __device__ __forceinline__ void traverse_persistent(const AccelView& A, const ui
     int node = CRT_NODE_DONE;
     uint32_t sp = 0;                          // stack depth
     uint32_t ray_i = 0;
+    uint32_t ray_steps = 0;                   // COUNT only: loop iterations spent on the current ray
     v3 o = V(0.f, 0.f, 0.f), d = V(0.f, 0.f, 1.f);
     RaySlabs S = make_slabs(o, d);
     Hit best;
@@ -184,6 +185,7 @@ __device__ __forceinline__ void traverse_persistent(const AccelView& A, const ui
                         S = make_slabs(o, d);
                         best.t = t_max; best.k = 0xFFFFFFFFu; best.id = CRT_MISS_ID; best.u = best.v = 0.f;
                         sp = 0;
+                        ray_steps = 0;
                         node = A.root;
                         if (A.n_prims == 0u) { sink.store(ray_i, best); node = CRT_NODE_DONE; }
                     }
@@ -205,7 +207,7 @@ __device__ __forceinline__ void traverse_persistent(const AccelView& A, const ui
                 ldg256(np + 2, loy, hiy);
                 ldg256(np + 4, loz, hiz);
                 const int4 refs = __ldg(reinterpret_cast<const int4*>(np + 6));
-                if (COUNT) cnt.nodes++;
+                if (COUNT) { cnt.nodes++; ray_steps++; cnt.max_steps = max(cnt.max_steps, ray_steps); }
                 float key[4];
                 int ref[4] = {refs.x, refs.y, refs.z, refs.w};
                 const float plo_x[4] = {lox.x, lox.y, lox.z, lox.w}, phi_x[4] = {hix.x, hix.y, hix.z, hix.w};
@@ -246,6 +248,7 @@ __device__ __forceinline__ void traverse_persistent(const AccelView& A, const ui
             const uint32_t ref = ~(uint32_t)node;
             const uint32_t k = ref >> 3;
             const uint32_t rest = ref & 7u;
+            if (COUNT) { ray_steps++; cnt.max_steps = max(cnt.max_steps, ray_steps); }
             {
                 const float4* rp = A.recs + 4 * (size_t)k;
                 float4 r0, r1, r2, r3;

@@ -152,7 +152,7 @@ k_trace_queue(AccelView A, const float4* __restrict__ q, uint32_t cap, const uin
               uint32_t refill, uint32_t leaf_thresh)
 {
     __shared__ int s_stack[CRT_STACK_SMEM * TP_BLOCK];
-    TraceCounters cnt = {0u, 0u, 0u};
+    TraceCounters cnt = {0u, 0u, 0u, 0u};
     QueueSrc src = {q, cap};
     QueueSink sink = {hits};
     traverse_persistent<COUNT, HAS_SPH>(A, *n_ptr, work_ctr, 0.001f, FLT_MAX, src, sink, s_stack, cnt, refill, leaf_thresh);   // render.h:53
@@ -165,6 +165,7 @@ k_trace_queue(AccelView A, const float4* __restrict__ q, uint32_t cap, const uin
             atomicAdd(counters + CNT_TRIS, (unsigned long long)tris);
             atomicAdd(counters + CNT_SPHERES, (unsigned long long)sph);
         }
+        atomicMax(counters + CNT_MAX_STEPS, (unsigned long long)cnt.max_steps);
     }
 }
 
@@ -351,6 +352,13 @@ static void launch_bounce(crt_ctx* c, int b, int grid_trace, int grid_shade, con
     k_trace_queue<COUNT, HAS_SPH><<<grid_trace, TP_BLOCK, 0, c->stream>>>(A, q_in, P.cap, n_in, work_ctr, c->hitbuf.as<float4>(),
                                                                           c->counters.as<unsigned long long>(), (uint32_t)c->refill, (uint32_t)c->leaf_thresh);
     cudaEventRecord(c->ev_trace[2 * b + 1], c->stream);
+    if (COUNT && getenv("CRT_TRACE_TIMING")) {   // development aid: longest dependent chain of the launch
+        unsigned long long ms = 0;
+        cudaMemcpyAsync(&ms, c->counters.as<unsigned long long>() + CNT_MAX_STEPS, 8, cudaMemcpyDeviceToHost, c->stream);
+        cudaMemsetAsync(c->counters.as<unsigned long long>() + CNT_MAX_STEPS, 0, 8, c->stream);
+        cudaStreamSynchronize(c->stream);
+        fprintf(stderr, "[crt] bounce %d: longest ray took %llu traversal steps\n", b, ms);
+    }
     k_shade<COUNT, HAS_SPH><<<grid_shade, RB, 0, c->stream>>>(P, A, c->mats.as<DMat>(), q_in, c->hitbuf.as<float4>(), n_in, q_out,
                                                               n_out, c->rad.as<float4>(), c->counters.as<unsigned long long>());
 }
