@@ -5,7 +5,8 @@
 // and UpdateBVH<<<1,1>>> (createScene.h:46-58 -> hitable/bvh.h:135-158:
 // recursive refit on one thread) with data-parallel passes:
 //   1. k_scene_bounds : primitive boxes -> scene box (warp shuffles + float atomics)
-//   2. k_morton       : 63-bit Morton code of each box centre (21 bits per axis)
+//   2. k_morton       : 63-bit Morton code of each box centre (21 bits per axis);
+//                       bit 63 marks oversize primitives (see is_oversize)
 //   3. radix_sort_pairs (radix_sort.cu): (code, primitive) pairs
 //   4. k_hierarchy    : Karras 2012 binary radix tree, one thread per internal
 //                       node, ties between equal codes broken by position
@@ -69,19 +70,37 @@ __device__ __forceinline__ void atomic_max_f(float* a, float v)
     else atomicMin((unsigned int*)a, __float_as_uint(v));
 }
 
+// bounds[0..5]: box of all primitives; bounds[6..11]: box of the primitives that are not oversize.
 __global__ void k_init_bounds(float* bounds)
 {
-    if (threadIdx.x < 3) bounds[threadIdx.x] = INFINITY;
-    else if (threadIdx.x < 6) bounds[threadIdx.x] = -INFINITY;
+    if (threadIdx.x < 12) bounds[threadIdx.x] = (threadIdx.x % 6) < 3 ? INFINITY : -INFINITY;
+}
+
+// A primitive is OVERSIZE when its box is longer than 1/8 of the scene box along
+// the scene's longest axis (a ground quad under a finely tessellated mesh, the
+// ground sphere of the random-spheres scene). In a Morton-ordered tree such a
+// primitive sits as a leaf deep inside some spatial cell and inflates the box of
+// every ancestor up to the root, so every ray walks that chain first. Oversize
+// primitives get key bit 63 set: they sort behind everything else and form
+// their own subtree directly under the root, and the Morton grid is laid over
+// the remaining primitives only.
+__device__ __forceinline__ bool is_oversize(const Box& b, const float* __restrict__ bounds)
+{
+    const float scene = fmaxf(bounds[3] - bounds[0], fmaxf(bounds[4] - bounds[1], bounds[5] - bounds[2]));
+    const float prim = fmaxf(b.hx - b.lx, fmaxf(b.hy - b.ly, b.hz - b.lz));
+    return prim > 0.125f * scene;
 }
 
 __global__ void __launch_bounds__(256)
 k_scene_bounds(const float* __restrict__ tri_in, const float* __restrict__ sph_in, uint32_t n_tri, uint32_t n,
-               float* __restrict__ bounds)
+               const float* __restrict__ all_bounds, float* __restrict__ bounds)
 {
+    // all_bounds == nullptr: pass 1, every primitive; otherwise pass 2, only those that are not oversize
     Box b = {INFINITY, INFINITY, INFINITY, -INFINITY, -INFINITY, -INFINITY};
-    for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x)
-        b = box_union(b, prim_box(tri_in, sph_in, n_tri, p));
+    for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x) {
+        const Box pb = prim_box(tri_in, sph_in, n_tri, p);
+        if (all_bounds == nullptr || !is_oversize(pb, all_bounds)) b = box_union(b, pb);
+    }
     for (int o = 16; o > 0; o >>= 1) {
         b.lx = fminf(b.lx, __shfl_xor_sync(0xffffffffu, b.lx, o));
         b.ly = fminf(b.ly, __shfl_xor_sync(0xffffffffu, b.ly, o));
@@ -114,8 +133,11 @@ k_morton(const float* __restrict__ tri_in, const float* __restrict__ sph_in, uin
     const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n) return;
     const Box b = prim_box(tri_in, sph_in, n_tri, p);
-    const float lx = bounds[0], ly = bounds[1], lz = bounds[2];
-    const float ex = bounds[3] - lx, ey = bounds[4] - ly, ez = bounds[5] - lz;
+    const bool oversize = is_oversize(b, bounds);
+    // grid over the regular primitives; if every primitive is oversize, over all of them
+    const float* gb = bounds[6] <= bounds[9] ? bounds + 6 : bounds;
+    const float lx = gb[0], ly = gb[1], lz = gb[2];
+    const float ex = gb[3] - lx, ey = gb[4] - ly, ez = gb[5] - lz;
     const float scale = 2097152.0f;   // 2^21
     const float fx = ex > 0.0f ? (0.5f * (b.lx + b.hx) - lx) / ex : 0.0f;
     const float fy = ey > 0.0f ? (0.5f * (b.ly + b.hy) - ly) / ey : 0.0f;
@@ -123,7 +145,7 @@ k_morton(const float* __restrict__ tri_in, const float* __restrict__ sph_in, uin
     const uint64_t qx = (uint64_t)fminf(fmaxf(fx * scale, 0.0f), scale - 1.0f);
     const uint64_t qy = (uint64_t)fminf(fmaxf(fy * scale, 0.0f), scale - 1.0f);
     const uint64_t qz = (uint64_t)fminf(fmaxf(fz * scale, 0.0f), scale - 1.0f);
-    keys[p] = (expand21(qx) << 2) | (expand21(qy) << 1) | expand21(qz);
+    keys[p] = (expand21(qx) << 2) | (expand21(qy) << 1) | expand21(qz) | (oversize ? (1ull << 63) : 0ull);
     vals[p] = p;
 }
 
@@ -335,7 +357,7 @@ int lbvh_build(crt_ctx* c, bool refit_only)
         CRT_CUDA(c->keys[0].reserve(n * 8)); CRT_CUDA(c->keys[1].reserve(n * 8));
         CRT_CUDA(c->vals[0].reserve(n * 4)); CRT_CUDA(c->vals[1].reserve(n * 4));
         CRT_CUDA(c->hist.reserve(radix_sort_hist_bytes()));
-        CRT_CUDA(c->bounds.reserve(6 * sizeof(float)));
+        CRT_CUDA(c->bounds.reserve(12 * sizeof(float)));
         CRT_CUDA(c->recs.reserve(n * 64));
         CRT_CUDA(c->leaf_box.reserve(n * 32));
         CRT_CUDA(c->leaf_parent.reserve(n * 4));
@@ -350,7 +372,8 @@ int lbvh_build(crt_ctx* c, bool refit_only)
 
         k_init_bounds<<<1, 32, 0, st>>>(c->bounds.as<float>());
         const unsigned int gb = min(grid_for(n, 256), (unsigned int)(c->sm_count * 8));
-        k_scene_bounds<<<gb, 256, 0, st>>>(tri_in, sph_in, n_tri, un, c->bounds.as<float>());
+        k_scene_bounds<<<gb, 256, 0, st>>>(tri_in, sph_in, n_tri, un, nullptr, c->bounds.as<float>());
+        k_scene_bounds<<<gb, 256, 0, st>>>(tri_in, sph_in, n_tri, un, c->bounds.as<float>(), c->bounds.as<float>() + 6);
         k_morton<<<grid_for(n, 256), 256, 0, st>>>(tri_in, sph_in, n_tri, un, c->bounds.as<float>(),
                                                     c->keys[0].as<uint64_t>(), c->vals[0].as<uint32_t>());
         uint64_t* keys[2] = {c->keys[0].as<uint64_t>(), c->keys[1].as<uint64_t>()};
