@@ -346,11 +346,16 @@ def run_ours(args):
             lib, sh, kind = cpu_reference_setup(sc)
             cam_fn = lambda a, b: crt.camera_for(sc, a, b)
             snx, sny = cpu_sample_shape(sh, cam_fn, sc, 15.0)
-            sh.render(cam_fn(snx, sny), snx, sny, 1, depth, crt.SHADE_PATH, 1)
+            img_cpu = np.asarray(sh.render(cam_fn(snx, sny), snx, sny, 1, depth, crt.SHADE_PATH, 1), np.float32)
+            # the checker at full scene size: the same sub-frame through the GPU path (the oracle is only the referee here)
+            img_gpu = ctx.render(cam_fn(snx, sny), snx, sny, 1, depth, crt.SHADE_PATH, 1)
+            diff = img_gpu.astype(np.float64) - img_cpu.astype(np.float64)
             line["cpu_baseline"] = {
                 "value": sh.last_rays / sh.last_seconds / 1e6, "unit": "Mrays/s", "cores": lib.num_threads(), "kind": kind,
                 "sample": "%dx%d px x 1 spp of the 1920x1080x16 frame (same scene, camera, depth), %.1f s; list scan over %d triangles"
-                          % (snx, sny, sh.last_seconds, len(sc["tri"]))}
+                          % (snx, sny, sh.last_seconds, len(sc["tri"])),
+                "rmse_gpu_vs_reference": float(np.sqrt(np.mean(diff * diff))), "max_abs_diff": float(np.abs(diff).max()),
+                "pixels_differing": int((np.abs(diff).max(axis=-1) > 0).sum())}
         print(json.dumps(line), flush=True)
     # torch tensors that were used on the context's stream must go before the stream does
     barrier()
