@@ -144,6 +144,9 @@ int crt_set_option(crt_ctx* c, int option, int64_t value)
         if (value < 1 || value > 32) { set_error("CRT_OPT_LEAF_THRESH must be in [1, 32]"); return CRT_ERR_INVALID; }
         c->leaf_thresh = (int)value;
         return CRT_OK;
+    case CRT_OPT_PACKET_PRIMARY:
+        c->packet_primary = value != 0;
+        return CRT_OK;
     case CRT_OPT_BATCH_PATHS:
         if (value < 1) { set_error("CRT_OPT_BATCH_PATHS must be >= 1"); return CRT_ERR_INVALID; }
         c->batch_paths = value;

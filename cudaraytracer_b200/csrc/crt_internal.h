@@ -83,6 +83,7 @@ struct crt_ctx {
     int count_work = 0;
     int leaf_thresh = 8;                   // parked lanes that trigger the primitive-test phase
     int refill = 8;                        // idle lanes that trigger a refill in the persistent traversal
+    int packet_primary = 1;                // camera rays through the packet kernel
     int64_t batch_paths = 1ll << 25;
 
     crt_counters host_counters = {};

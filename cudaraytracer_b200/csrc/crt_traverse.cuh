@@ -77,6 +77,17 @@ __device__ __forceinline__ int lds32(uint32_t addr)
     return v;
 }
 
+// The same with a "memory" clobber, for the packet traversal where lane 0 writes
+// the warp's stack and every lane reads it after __syncwarp(): without the
+// clobber the compiler may move the load across the barrier.
+__device__ __forceinline__ void sts32_fenced(uint32_t addr, int v) { asm volatile("st.shared.b32 [%0], %1;" ::"r"(addr), "r"(v) : "memory"); }
+__device__ __forceinline__ int lds32_fenced(uint32_t addr)
+{
+    int v;
+    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+    return v;
+}
+
 // Per-ray constants of the slab test. For a plane at coordinate p the exact
 // distance is (p - o) / d. The kernel evaluates fma(p, inv, c) with
 // inv = rn(1 / d) and c = -(o * inv) moved by a slack s = 2^-22 * |o * inv|
@@ -271,6 +282,131 @@ __device__ __forceinline__ void traverse_persistent(const AccelView& A, const ui
             }
             if (rest != 0u) node = (int)~(((k + 1u) << 3) | (rest - 1u));
             else pop_or_finish();
+        }
+    }
+}
+
+
+// ---------------------------------------------------------------------------
+// Packet form for COHERENT rays (camera rays: with the sample-minor path order
+// of render.cu a warp holds all samples of one or two pixels, i.e. 32 nearly
+// identical rays). The warp walks ONE stack: a node is visited when any lane's
+// ray enters it, every lane tests the node's four boxes against its own ray and
+// keeps its own closest hit, children are ordered by the first entering lane's
+// distance. Control flow is warp-uniform, so there is no lane refill, no
+// node/leaf phase vote and no per-lane stack; node and record addresses are
+// uniform, so each load is one L1 wavefront for the whole warp.
+// Visiting a node another lane needed never changes a lane's result: the
+// primitive tests and the tie-break are the ones of traverse_persistent.
+// s_wstack: CRT_PACKET_STACK ints per warp.
+#define CRT_PACKET_STACK 160   // 3 pushes per wide level, <= 48 wide levels (95 binary levels)
+
+template <bool COUNT, bool HAS_SPH, class Src, class Sink>
+__device__ __forceinline__ void traverse_packets(const AccelView& A, const uint32_t n, uint32_t* work_ctr,
+                                                 const float t_min, const float t_max, const Src& src,
+                                                 const Sink& sink, int* s_wstack, TraceCounters& cnt)
+{
+    const uint32_t lane = threadIdx.x & 31u;
+    (void)s_wstack;
+    int wstack[CRT_PACKET_STACK];   // every lane keeps the same (warp-uniform) stack; slot X of 32 lanes is one 128-byte line of local memory
+    constexpr uint32_t FULL = 0xffffffffu;
+    // packets per grab
+    uint32_t chunk = (n / (gridDim.x * (TP_BLOCK / 32u) * 8u)) & ~31u;
+    chunk = chunk < 32u ? 32u : (chunk > 1024u ? 1024u : chunk);
+
+    for (;;) {
+        uint32_t begin = 0;
+        if (lane == 0) begin = atomicAdd(work_ctr, chunk);
+        begin = __shfl_sync(FULL, begin, 0);
+        if (begin >= n) break;
+        const uint32_t end = min(begin + chunk, n);
+        for (uint32_t first = begin; first < end; first += 32u) {
+            const uint32_t ray_i = first + lane;
+            const bool live = ray_i < end;
+            v3 o = V(0.f, 0.f, 0.f), d = V(0.f, 0.f, 1.f);
+            if (live) {
+                v3 dr;
+                src.load(ray_i, o, dr);
+                d = ray_dir_local(dr);
+            }
+            const RaySlabs S = make_slabs(o, d);
+            Hit best;
+            best.t = t_max; best.k = 0xFFFFFFFFu; best.id = CRT_MISS_ID; best.u = best.v = 0.f;
+            if (A.n_prims != 0u) {
+                int node = A.root;               // warp-uniform
+                uint32_t sp = 0;                 // warp-uniform
+                for (;;) {
+                    if (node >= 0) {
+                        const float4* np = A.nodes + 8 * (size_t)(uint32_t)node;
+                        float4 lox, hix, loy, hiy, loz, hiz;
+                        ldg256(np, lox, hix);
+                        ldg256(np + 2, loy, hiy);
+                        ldg256(np + 4, loz, hiz);
+                        const int4 refs = __ldg(reinterpret_cast<const int4*>(np + 6));
+                        if (COUNT && live) cnt.nodes++;
+                        float key[4];
+                        int ref[4] = {refs.x, refs.y, refs.z, refs.w};
+                        const float plo_x[4] = {lox.x, lox.y, lox.z, lox.w}, phi_x[4] = {hix.x, hix.y, hix.z, hix.w};
+                        const float plo_y[4] = {loy.x, loy.y, loy.z, loy.w}, phi_y[4] = {hiy.x, hiy.y, hiy.z, hiy.w};
+                        const float plo_z[4] = {loz.x, loz.y, loz.z, loz.w}, phi_z[4] = {hiz.x, hiz.y, hiz.z, hiz.w};
+                        int n_hit = 0;
+#pragma unroll
+                        for (int k = 0; k < 4; k++) {
+                            const float ax = fmaf(plo_x[k], S.ix, S.cx_lo), bx = fmaf(phi_x[k], S.ix, S.cx_hi);
+                            const float ay = fmaf(plo_y[k], S.iy, S.cy_lo), by = fmaf(phi_y[k], S.iy, S.cy_hi);
+                            const float az = fmaf(plo_z[k], S.iz, S.cz_lo), bz = fmaf(phi_z[k], S.iz, S.cz_hi);
+                            const float tn = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), t_min));
+                            const float tf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), best.t));
+                            const bool h = live && tn <= tf * 1.0000005f;
+                            const uint32_t m = ref[k] != CRT_SLOT_EMPTY ? __ballot_sync(FULL, h) : 0u;   // ref is uniform
+                            // entry distance of the first lane that enters the child; uniform
+                            key[k] = m ? __shfl_sync(FULL, tn, __ffs(m) - 1) : INFINITY;
+                            n_hit += m ? 1 : 0;
+                        }
+#define CRT_CSWAP(a, b)                                                                    \
+                        {                                                                  \
+                            const bool sw = key[b] < key[a];                               \
+                            const float ka = key[a], kb = key[b];                          \
+                            const int ra = ref[a], rb = ref[b];                            \
+                            key[a] = sw ? kb : ka; key[b] = sw ? ka : kb;                  \
+                            ref[a] = sw ? rb : ra; ref[b] = sw ? ra : rb;                  \
+                        }
+                        CRT_CSWAP(0, 1) CRT_CSWAP(2, 3) CRT_CSWAP(0, 2) CRT_CSWAP(1, 3) CRT_CSWAP(1, 2)
+#undef CRT_CSWAP
+                                                if (n_hit > 3) wstack[sp++] = ref[3];
+                        if (n_hit > 2) wstack[sp++] = ref[2];
+                        if (n_hit > 1) wstack[sp++] = ref[1];
+                        if (n_hit > 0) { node = ref[0]; continue; }
+                    } else {
+                        const uint32_t ref = ~(uint32_t)node;
+                        const uint32_t k0 = ref >> 3, count = (ref & 7u) + 1u;
+                        for (uint32_t j = 0; j < count; j++) {
+                            const uint32_t k = k0 + j;
+                            const float4* rp = A.recs + 4 * (size_t)k;
+                            float4 r0, r1, r2, r3;
+                            ldg256(rp, r0, r1);
+                            ldg256(rp + 2, r2, r3);
+                            const uint32_t pid = __float_as_uint(r3.x);
+                            float t, u = 0.0f, v = 0.0f;
+                            bool ok;
+                            if (HAS_SPH && (__float_as_uint(r3.y) & CRT_KIND_SPHERE)) {
+                                if (COUNT && live) cnt.spheres++;
+                                ok = sphere_test(vsub(o, V(r0.x, r0.y, r0.z)), d, r0.w, t_min, best.t, t);
+                            } else {
+                                if (COUNT && live) cnt.tris++;
+                                ok = triangle_test(o, d, V(r0.x, r0.y, r0.z), V(r1.x, r1.y, r1.z), V(r2.x, r2.y, r2.z),
+                                                   V(r0.w, r1.w, r2.w), t_min, best.t, t, u, v);
+                            }
+                            if (ok && t == best.t && (best.k == 0xFFFFFFFFu || pid >= best.id)) ok = false;
+                            if (ok && live) { best.t = t; best.k = k; best.id = pid; best.u = u; best.v = v; }
+                        }
+                    }
+                    if (sp == 0u) break;
+                    node = wstack[--sp];
+                }
+            }
+            if (live) sink.store(ray_i, best);
+            __syncwarp();
         }
     }
 }

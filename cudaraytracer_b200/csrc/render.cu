@@ -59,6 +59,31 @@ __device__ __forceinline__ bool slot_to_pixel(const RenderParams& P, uint32_t sl
     return x < P.nx && y < P.ny;
 }
 
+// Path id <-> (slot, sample of the batch). Sample-minor: the s_count samples of a
+// pixel are consecutive, so a warp of primary rays is 32 / s_count pixels x all
+// their samples - nearly identical rays that walk the same nodes.
+#ifndef CRT_SAMPLE_MINOR
+#define CRT_SAMPLE_MINOR 1
+#endif
+__device__ __forceinline__ void split_path_id(const RenderParams& P, uint32_t id, uint32_t& slot, uint32_t& s_local)
+{
+#if CRT_SAMPLE_MINOR
+    slot = id / (uint32_t)P.s_count;
+    s_local = id - slot * (uint32_t)P.s_count;
+#else
+    s_local = id / P.n_slots;
+    slot = id - s_local * P.n_slots;
+#endif
+}
+__device__ __forceinline__ size_t make_path_id(const RenderParams& P, uint32_t slot, uint32_t s_local)
+{
+#if CRT_SAMPLE_MINOR
+    return (size_t)slot * (uint32_t)P.s_count + s_local;
+#else
+    return (size_t)s_local * P.n_slots + slot;
+#endif
+}
+
 // Warp-aggregated append: every lane of the warp must call this.
 __device__ __forceinline__ uint32_t warp_append(bool want, uint32_t* counter)
 {
@@ -82,8 +107,8 @@ k_raygen(RenderParams P, float4* __restrict__ q, uint32_t* __restrict__ q_count)
         bool live = id < total;
         float4 w0 = make_float4(0, 0, 0, 0), w1 = w0;
         if (live) {
-            const uint32_t s_local = id / P.n_slots;
-            const uint32_t slot = id - s_local * P.n_slots;
+            uint32_t slot, s_local;
+            split_path_id(P, id, slot, s_local);
             int x, y;
             live = slot_to_pixel(P, slot, x, y);
             if (live) {
@@ -169,6 +194,29 @@ k_trace_queue(AccelView A, const float4* __restrict__ q, uint32_t cap, const uin
     }
 }
 
+// ---- closest hit for camera rays: one packet per warp (crt_traverse.cuh traverse_packets) ----
+template <bool COUNT, bool HAS_SPH>
+__global__ void __launch_bounds__(TP_BLOCK, CRT_TRACE_MIN_BLOCKS)
+k_trace_packet(AccelView A, const float4* __restrict__ q, uint32_t cap, const uint32_t* __restrict__ n_ptr,
+               uint32_t* __restrict__ work_ctr, float4* __restrict__ hits, unsigned long long* __restrict__ counters)
+{
+    __shared__ int s_wstack[(TP_BLOCK / 32) * CRT_PACKET_STACK];
+    TraceCounters cnt = {0u, 0u, 0u, 0u};
+    QueueSrc src = {q, cap};
+    QueueSink sink = {hits};
+    traverse_packets<COUNT, HAS_SPH>(A, *n_ptr, work_ctr, 0.001f, FLT_MAX, src, sink, s_wstack, cnt);   // render.h:53
+    if (COUNT) {
+        const uint32_t nodes = __reduce_add_sync(0xffffffffu, cnt.nodes);
+        const uint32_t tris = __reduce_add_sync(0xffffffffu, cnt.tris);
+        const uint32_t sph = __reduce_add_sync(0xffffffffu, cnt.spheres);
+        if ((threadIdx.x & 31u) == 0u) {
+            atomicAdd(counters + CNT_NODES, (unsigned long long)nodes);
+            atomicAdd(counters + CNT_TRIS, (unsigned long long)tris);
+            atomicAdd(counters + CNT_SPHERES, (unsigned long long)sph);
+        }
+    }
+}
+
 // ---- shade(): one thread per queue entry, fully converged ----
 template <bool COUNT, bool HAS_SPH>
 __global__ void __launch_bounds__(RB)
@@ -211,8 +259,8 @@ k_shade(RenderParams P, AccelView A, const DMat* __restrict__ mats, const float4
             } else {
                 Rng rng;
                 {
-                    const uint32_t s_local = path_id / P.n_slots;
-                    const uint32_t slot = path_id - s_local * P.n_slots;
+                    uint32_t slot, s_local;
+                    split_path_id(P, path_id, slot, s_local);
                     int px, py;
                     slot_to_pixel(P, slot, px, py);
                     rng.key = crt_rng_key(P.seed, (uint32_t)py * (uint32_t)P.nx + (uint32_t)px, (uint32_t)(P.s_begin + (int)s_local));
@@ -299,7 +347,7 @@ k_accumulate(RenderParams P, const float4* __restrict__ rad, float* __restrict__
     const size_t pixel = (size_t)y * P.nx + x;
     v3 col = V(accum[3 * pixel], accum[3 * pixel + 1], accum[3 * pixel + 2]);
     for (int s = 0; s < P.s_count; s++) {
-        const float4 r = rad[(size_t)s * P.n_slots + slot];
+        const float4 r = rad[make_path_id(P, slot, (uint32_t)s)];
         col = vadd(col, V(r.x, r.y, r.z));                                         // render.h:119-121
     }
     accum[3 * pixel] = col.x;
@@ -349,8 +397,12 @@ static void launch_bounce(crt_ctx* c, int b, int grid_trace, int grid_shade, con
                           const float4* q_in, const uint32_t* n_in, uint32_t* work_ctr, float4* q_out, uint32_t* n_out)
 {
     cudaEventRecord(c->ev_trace[2 * b], c->stream);
-    k_trace_queue<COUNT, HAS_SPH><<<grid_trace, TP_BLOCK, 0, c->stream>>>(A, q_in, P.cap, n_in, work_ctr, c->hitbuf.as<float4>(),
-                                                                          c->counters.as<unsigned long long>(), (uint32_t)c->refill, (uint32_t)c->leaf_thresh);
+    if (b == 0 && c->packet_primary)   // camera rays: a warp holds the samples of one or two pixels
+        k_trace_packet<COUNT, HAS_SPH><<<grid_trace, TP_BLOCK, 0, c->stream>>>(A, q_in, P.cap, n_in, work_ctr, c->hitbuf.as<float4>(),
+                                                                               c->counters.as<unsigned long long>());
+    else
+        k_trace_queue<COUNT, HAS_SPH><<<grid_trace, TP_BLOCK, 0, c->stream>>>(A, q_in, P.cap, n_in, work_ctr, c->hitbuf.as<float4>(),
+                                                                              c->counters.as<unsigned long long>(), (uint32_t)c->refill, (uint32_t)c->leaf_thresh);
     cudaEventRecord(c->ev_trace[2 * b + 1], c->stream);
     if (COUNT && getenv("CRT_TRACE_TIMING")) {   // development aid: longest dependent chain of the launch
         unsigned long long ms = 0;

@@ -96,6 +96,7 @@ typedef enum {
     CRT_OPT_COUNTERS = 2,   /* 1: run the instrumented kernels that count nodes/primitives visited */
     CRT_OPT_BATCH_PATHS = 3,/* max camera samples in flight per wavefront batch (default 1<<25) */
     CRT_OPT_LEAF_THRESH = 5,/* tuning: lanes parked on a leaf that trigger the primitive-test phase, 1..32 (default 8) */
+    CRT_OPT_PACKET_PRIMARY = 6, /* 1 (default): camera rays are traced as one packet per warp; 0: like every other bounce */
     CRT_OPT_REFILL = 4      /* tuning: idle lanes per warp that trigger a refill from the ray queue, 1..32 (default 8) */
 } crt_option;
 
