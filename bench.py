@@ -306,7 +306,7 @@ def run_ours(args):
     if rank == 0:
         peaks, peak_src = measured_peaks()
         n_r = work["rays"]
-        alg_bytes = 128 * work["nodes_visited"] + 48 * work["tris_tested"] + 16 * work["spheres_tested"] + 48 * n_r
+        alg_bytes = 128 * work["node_fetches"] + 48 * work["tri_fetches"] + 16 * work["sphere_fetches"] + 48 * n_r
         alg_flops = 96 * work["nodes_visited"] + 50 * work["tris_tested"] + 27 * work["spheres_tested"]
         bounce_launches = depth + 1
         per_launch_ms = bounce_ms / max(1, args.steps * bounce_launches)
@@ -333,13 +333,15 @@ def run_ours(args):
                     "h2d_bytes_per_step": int(host_verts.numel() * 4 + 88), "d2h_bytes_per_step": int(nx * ny * 12),
                     "what": "crt_scene_update_vertices + crt_accel_refit + crt_render per frame, host buffers, wall clock"},
             "gpu_launches": int(args.steps * (1 + 2 * bounce_launches + 1 + 1)),
-            "roofline": {"kernel": "k_trace_queue (persistent-warp LBVH closest hit, %d launches/step)" % bounce_launches,
+            "roofline": {"kernel": "closest hit over the 4-wide LBVH: k_trace_packet (camera rays) + k_trace_queue (bounces), %d launches/step" % bounce_launches,
                          "bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                          "frac": achieved / peaks["hbm_gbs"], "traffic": traffic, "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": alg_bytes / bounce_launches,
                          "algorithmic_flops_per_launch": alg_flops / bounce_launches,
                          "avg_launch_ms": per_launch_ms,
                          "nodes_per_ray": work["nodes_visited"] / max(1, n_r), "tris_per_ray": work["tris_tested"] / max(1, n_r),
+                         "node_fetches_per_ray": work["node_fetches"] / max(1, n_r), "tri_fetches_per_ray": work["tri_fetches"] / max(1, n_r),
+                         "accounting": "bytes = 128 B x node fetches + 48 B x triangle fetches + 48 B x rays; camera rays share one fetch per packet of <= 32 rays, every other bounce fetches per ray; flops = 96 x node tests + 50 x triangle tests (per ray)",
                          "fp32_tflops_achieved": alg_flops / bounce_launches / (per_launch_ms * 1e-3) / 1e12},
         }
         if world == 1 and not args.no_cpu_baseline:

@@ -45,7 +45,8 @@ class Counters(C.Structure):
     _fields_ = [("rays", C.c_uint64), ("nodes_visited", C.c_uint64), ("tris_tested", C.c_uint64),
                 ("spheres_tested", C.c_uint64), ("scatters", C.c_uint64), ("paths", C.c_uint64),
                 ("build_ms", C.c_float), ("refit_ms", C.c_float), ("render_ms", C.c_float), ("trace_ms", C.c_float),
-                ("bounce_ms", C.c_float), ("trace_queue_ms", C.c_float)]
+                ("bounce_ms", C.c_float), ("trace_queue_ms", C.c_float),
+                ("node_fetches", C.c_uint64), ("tri_fetches", C.c_uint64), ("sphere_fetches", C.c_uint64)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}

@@ -338,6 +338,9 @@ int crt_get_counters(crt_ctx* c, crt_counters* out)
     out->tris_tested = h[CNT_TRIS];
     out->spheres_tested = h[CNT_SPHERES];
     out->scatters = h[CNT_SCATTERS];
+    out->node_fetches = h[CNT_NODE_F];
+    out->tri_fetches = h[CNT_TRI_F];
+    out->sphere_fetches = h[CNT_SPH_F];
     return CRT_OK;
 }
 

@@ -43,7 +43,7 @@ struct DevBuf {
 };
 
 // Device-side work counters, one 64-bit word each.
-enum { CNT_RAYS = 0, CNT_NODES, CNT_TRIS, CNT_SPHERES, CNT_SCATTERS, CNT_PATHS, CNT_MAX_STEPS, CNT_COUNT };
+enum { CNT_RAYS = 0, CNT_NODES, CNT_TRIS, CNT_SPHERES, CNT_SCATTERS, CNT_PATHS, CNT_MAX_STEPS, CNT_NODE_F, CNT_TRI_F, CNT_SPH_F, CNT_COUNT };
 
 // Wavefront path state, 64 B = 4 x 128-bit words (SoA by word):
 //   w0 = {o.x, o.y, o.z, d.x}

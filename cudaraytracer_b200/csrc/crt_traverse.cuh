@@ -52,7 +52,9 @@ constexpr int TP_BLOCK = 128;    // threads per block of every traversal kernel
 constexpr int TP_CHUNK = 256;    // most rays a warp takes from the queue per atomic
 constexpr int TP_REFILL = 8;     // default: refill once this many lanes are idle
 
-struct TraceCounters { uint32_t nodes, tris, spheres, max_steps; };
+// nodes/tris/spheres: tests executed per ray (work, flops). *_f: records FETCHED - equal to the tests in the
+// per-ray kernels, one per packet visit in the packet kernel (a packet of <= 32 rays shares each fetch).
+struct TraceCounters { uint32_t nodes, tris, spheres, max_steps, node_f, tri_f, sph_f; };
 
 __device__ __forceinline__ float safe_rcp(float d)
 {
@@ -344,6 +346,7 @@ __device__ __forceinline__ void traverse_packets(const AccelView& A, const uint3
                         ldg256(np + 4, loz, hiz);
                         const int4 refs = __ldg(reinterpret_cast<const int4*>(np + 6));
                         if (COUNT && live) cnt.nodes++;
+                        if (COUNT && lane == 0) cnt.node_f++;
                         float key[4];
                         int ref[4] = {refs.x, refs.y, refs.z, refs.w};
                         const float plo_x[4] = {lox.x, lox.y, lox.z, lox.w}, phi_x[4] = {hix.x, hix.y, hix.z, hix.w};
@@ -391,9 +394,11 @@ __device__ __forceinline__ void traverse_packets(const AccelView& A, const uint3
                             bool ok;
                             if (HAS_SPH && (__float_as_uint(r3.y) & CRT_KIND_SPHERE)) {
                                 if (COUNT && live) cnt.spheres++;
+                                if (COUNT && lane == 0) cnt.sph_f++;
                                 ok = sphere_test(vsub(o, V(r0.x, r0.y, r0.z)), d, r0.w, t_min, best.t, t);
                             } else {
                                 if (COUNT && live) cnt.tris++;
+                                if (COUNT && lane == 0) cnt.tri_f++;
                                 ok = triangle_test(o, d, V(r0.x, r0.y, r0.z), V(r1.x, r1.y, r1.z), V(r2.x, r2.y, r2.z),
                                                    V(r0.w, r1.w, r2.w), t_min, best.t, t, u, v);
                             }

@@ -177,7 +177,7 @@ k_trace_queue(AccelView A, const float4* __restrict__ q, uint32_t cap, const uin
               uint32_t refill, uint32_t leaf_thresh)
 {
     __shared__ int s_stack[CRT_STACK_SMEM * TP_BLOCK];
-    TraceCounters cnt = {0u, 0u, 0u, 0u};
+    TraceCounters cnt = {0u, 0u, 0u, 0u, 0u, 0u, 0u};
     QueueSrc src = {q, cap};
     QueueSink sink = {hits};
     traverse_persistent<COUNT, HAS_SPH>(A, *n_ptr, work_ctr, 0.001f, FLT_MAX, src, sink, s_stack, cnt, refill, leaf_thresh);   // render.h:53
@@ -189,6 +189,9 @@ k_trace_queue(AccelView A, const float4* __restrict__ q, uint32_t cap, const uin
             atomicAdd(counters + CNT_NODES, (unsigned long long)nodes);
             atomicAdd(counters + CNT_TRIS, (unsigned long long)tris);
             atomicAdd(counters + CNT_SPHERES, (unsigned long long)sph);
+            atomicAdd(counters + CNT_NODE_F, (unsigned long long)nodes);
+            atomicAdd(counters + CNT_TRI_F, (unsigned long long)tris);
+            atomicAdd(counters + CNT_SPH_F, (unsigned long long)sph);
         }
         atomicMax(counters + CNT_MAX_STEPS, (unsigned long long)cnt.max_steps);
     }
@@ -201,7 +204,7 @@ k_trace_packet(AccelView A, const float4* __restrict__ q, uint32_t cap, const ui
                uint32_t* __restrict__ work_ctr, float4* __restrict__ hits, unsigned long long* __restrict__ counters)
 {
     __shared__ int s_wstack[(TP_BLOCK / 32) * CRT_PACKET_STACK];
-    TraceCounters cnt = {0u, 0u, 0u, 0u};
+    TraceCounters cnt = {0u, 0u, 0u, 0u, 0u, 0u, 0u};
     QueueSrc src = {q, cap};
     QueueSink sink = {hits};
     traverse_packets<COUNT, HAS_SPH>(A, *n_ptr, work_ctr, 0.001f, FLT_MAX, src, sink, s_wstack, cnt);   // render.h:53
@@ -213,6 +216,9 @@ k_trace_packet(AccelView A, const float4* __restrict__ q, uint32_t cap, const ui
             atomicAdd(counters + CNT_NODES, (unsigned long long)nodes);
             atomicAdd(counters + CNT_TRIS, (unsigned long long)tris);
             atomicAdd(counters + CNT_SPHERES, (unsigned long long)sph);
+            atomicAdd(counters + CNT_NODE_F, (unsigned long long)cnt.node_f);
+            atomicAdd(counters + CNT_TRI_F, (unsigned long long)cnt.tri_f);
+            atomicAdd(counters + CNT_SPH_F, (unsigned long long)cnt.sph_f);
         }
     }
 }

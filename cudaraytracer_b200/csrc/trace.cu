@@ -42,6 +42,9 @@ __device__ __forceinline__ void flush_counters(unsigned long long* counters, con
         atomicAdd(counters + CNT_NODES, (unsigned long long)nodes);
         atomicAdd(counters + CNT_TRIS, (unsigned long long)tris);
         atomicAdd(counters + CNT_SPHERES, (unsigned long long)sph);
+        atomicAdd(counters + CNT_NODE_F, (unsigned long long)nodes);
+        atomicAdd(counters + CNT_TRI_F, (unsigned long long)tris);
+        atomicAdd(counters + CNT_SPH_F, (unsigned long long)sph);
         atomicAdd(counters + CNT_RAYS, (unsigned long long)r);
     }
 }
@@ -66,7 +69,7 @@ k_trace_lbvh(AccelView A, const crt_ray* __restrict__ rays, uint32_t n, uint32_t
              float t_max, crt_hit* __restrict__ hits, unsigned long long* __restrict__ counters, uint32_t refill, uint32_t leaf_thresh)
 {
     __shared__ int s_stack[CRT_STACK_SMEM * TP_BLOCK];
-    TraceCounters cnt = {0u, 0u, 0u, 0u};
+    TraceCounters cnt = {0u, 0u, 0u, 0u, 0u, 0u, 0u};
     RaySrc src = {rays};
     HitSink sink = {hits};
     traverse_persistent<COUNT, HAS_SPH>(A, n, work_ctr, t_min, t_max, src, sink, s_stack, cnt, refill, leaf_thresh);
@@ -90,7 +93,7 @@ k_trace_brute(const float* __restrict__ tri_in, const uint32_t* __restrict__ tri
     if (live) { load_ray(rays, i, o, d); d = ray_dir_local(d); }
     float best_t = t_max, best_u = 0.f, best_v = 0.f;
     uint32_t best_id = CRT_MISS_ID;
-    TraceCounters cnt = {0u, 0u, 0u, 0u};
+    TraceCounters cnt = {0u, 0u, 0u, 0u, 0u, 0u, 0u};
 
     for (uint32_t base = 0; base < n_tri; base += BRUTE_TILE) {
         const uint32_t m = min((uint32_t)BRUTE_TILE, n_tri - base);

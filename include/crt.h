@@ -115,7 +115,13 @@ typedef struct {
     float    render_ms;       /* last crt_render* call, device time */
     float    trace_ms;        /* last crt_trace (host-buffer form), device time of the kernel */
     float    bounce_ms;       /* device time of all trace+shade launches since crt_reset_counters */
-    float    trace_queue_ms;  /* of which k_trace_queue (closest hit) alone */
+    float    trace_queue_ms;  /* of which the closest-hit kernels (k_trace_packet, k_trace_queue) alone */
+    /* records fetched, the memory side of the roofline: equal to the tests above where
+     * every ray walks its own stack; in the packet kernel (camera rays) one fetch serves
+     * the <= 32 rays of a packet, while each ray still executes the test */
+    uint64_t node_fetches;
+    uint64_t tri_fetches;
+    uint64_t sphere_fetches;
 } crt_counters;
 
 /* Image partition for one-process-per-GPU rendering. The image is cut into

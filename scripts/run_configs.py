@@ -42,7 +42,7 @@ def render_row(name, sc, mode=crt.SHADE_PATH, reps=3):
                nodes_per_ray=w["nodes_visited"] / max(1, w["rays"]), tris_per_ray=w["tris_tested"] / max(1, w["rays"]),
                spheres_per_ray=w["spheres_tested"] / max(1, w["rays"]), build_ms=build_ms,
                trace_ms=c["trace_queue_ms"] / reps,
-               alg_gbs=(128 * w["nodes_visited"] + 48 * w["tris_tested"] + 16 * w["spheres_tested"] + 48 * w["rays"]) / (c["trace_queue_ms"] / reps) / 1e6)
+               alg_gbs=(128 * w["node_fetches"] + 48 * w["tri_fetches"] + 16 * w["sphere_fetches"] + 48 * w["rays"]) / (c["trace_queue_ms"] / reps) / 1e6)
     ctx.close()
     del accum
     torch.cuda.empty_cache()
