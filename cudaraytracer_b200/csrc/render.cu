@@ -97,13 +97,34 @@ __device__ __forceinline__ uint32_t warp_append(bool want, uint32_t* counter)
     return base + (uint32_t)__popc(m & ((1u << lane) - 1u));
 }
 
+// Block-aggregated append: ONE atomic on the queue counter per block and iteration
+// instead of one per warp (a million same-address atomics per bounce serialise in L2).
+// Every thread of the block must call this the same number of times.
+template <int THREADS>
+__device__ __forceinline__ uint32_t block_append(bool want, uint32_t* counter, uint32_t* s_cnt /* THREADS/32 + 1 */)
+{
+    const uint32_t lane = threadIdx.x & 31u, w = threadIdx.x >> 5;
+    const uint32_t m = __ballot_sync(0xffffffffu, want);
+    __syncthreads();                                   // the previous call's readers are done with s_cnt
+    if (lane == 0) s_cnt[w] = (uint32_t)__popc(m);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t tot = 0;
+#pragma unroll
+        for (int i = 0; i < THREADS / 32; i++) { const uint32_t c = s_cnt[i]; s_cnt[i] = tot; tot += c; }
+        s_cnt[THREADS / 32] = tot ? atomicAdd(counter, tot) : 0u;
+    }
+    __syncthreads();
+    return s_cnt[THREADS / 32] + s_cnt[w] + (uint32_t)__popc(m & ((1u << lane) - 1u));
+}
+
 __global__ void __launch_bounds__(RB)
 k_raygen(RenderParams P, float4* __restrict__ q, uint32_t* __restrict__ q_count)
 {
+    __shared__ uint32_t s_cnt[RB / 32 + 1];
     const uint32_t total = P.n_slots * (uint32_t)P.s_count;
-    const uint32_t lane = threadIdx.x & 31u;
-    for (uint32_t base = (blockIdx.x * RB + (threadIdx.x & ~31u)); base < total; base += gridDim.x * RB) {
-        const uint32_t id = base + lane;
+    for (uint32_t bbase = blockIdx.x * RB; bbase < total; bbase += gridDim.x * RB) {   // block-uniform trip count
+        const uint32_t id = bbase + threadIdx.x;
         bool live = id < total;
         float4 w0 = make_float4(0, 0, 0, 0), w1 = w0;
         if (live) {
@@ -124,12 +145,10 @@ k_raygen(RenderParams P, float4* __restrict__ q, uint32_t* __restrict__ q_count)
                 w1 = make_float4(d.y, d.z, __uint_as_float(id), __uint_as_float(rng.ctr | ((uint32_t)P.max_depth << 24)));
             }
         }
-        const uint32_t pos = warp_append(live, q_count);
-        if (live) {
+        const uint32_t pos = block_append<RB>(live, q_count, s_cnt);
+        if (live) {   // the material-id words (2, 3) are first written by k_shade and never read at bounce 0
             q[pos] = w0;
             q[(size_t)P.cap + pos] = w1;
-            q[2 * (size_t)P.cap + pos] = make_float4(0, 0, 0, 0);
-            q[3 * (size_t)P.cap + pos] = make_float4(0, 0, 0, 0);
         }
     }
 }
@@ -230,12 +249,13 @@ k_shade(RenderParams P, AccelView A, const DMat* __restrict__ mats, const float4
         const float4* __restrict__ hits, const uint32_t* __restrict__ n_in_ptr, float4* __restrict__ q_out,
         uint32_t* __restrict__ n_out_ptr, float4* __restrict__ rad, unsigned long long* __restrict__ counters)
 {
+    __shared__ uint32_t s_cnt[RB / 32 + 1];
     const uint32_t n_in = *n_in_ptr;
     const uint32_t lane = threadIdx.x & 31u;
     uint32_t n_scatter = 0;
 
-    for (uint32_t base = (blockIdx.x * RB + (threadIdx.x & ~31u)); base < n_in; base += gridDim.x * RB) {
-        const uint32_t i = base + lane;
+    for (uint32_t bbase = blockIdx.x * RB; bbase < n_in; bbase += gridDim.x * RB) {   // block-uniform trip count
+        const uint32_t i = bbase + threadIdx.x;
         const bool live = i < n_in;
         bool next = false;
         float4 w0 = make_float4(0, 0, 0, 0), w1 = w0;
@@ -328,7 +348,7 @@ k_shade(RenderParams P, AccelView A, const DMat* __restrict__ mats, const float4
                 rad[path_id] = make_float4(L.x, L.y, L.z, 0.0f);
             }
         }
-        const uint32_t pos = warp_append(next, n_out_ptr);
+        const uint32_t pos = block_append<RB>(next, n_out_ptr, s_cnt);
         if (next) {
             q_out[pos] = w0;
             q_out[(size_t)P.cap + pos] = w1;
