@@ -75,9 +75,17 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append(line.strip())
+            self.rows.append((time.perf_counter(), line.strip()))
 
-    def stop(self):
+    def wait_first(self, timeout=5.0):
+        """nvidia-smi needs a few hundred ms to start: block until it has printed one row."""
+        t_end = time.perf_counter() + timeout
+        while self.proc and not self.rows and time.perf_counter() < t_end:
+            time.sleep(0.01)
+
+    def stop(self, t0=None, t1=None):
+        """Rows that arrived inside [t0, t1] (the timed region); when the region is shorter than three sampling
+        periods, every row since start() is used instead (warm-up + timed + e2e, all under the same load)."""
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
@@ -85,9 +93,16 @@ class ClockSampler:
             self.proc.wait(timeout=2)
         except Exception:
             self.proc.kill()
+        rows, window = [r for _, r in self.rows], "sampler lifetime"
+        if t0 is not None:
+            inside = [r for t, r in self.rows if t0 <= t <= t1]
+            if len(inside) >= 3:
+                rows, window = inside, "timed region"
+            else:
+                window = "warm-up + timed region + e2e loop (timed region shorter than 3 sampling periods)"
         sm, mx, reasons = [], None, set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
+        for r in rows:
             parts = [p.strip() for p in r.split(",")]
             if len(parts) < 7:
                 continue
@@ -100,7 +115,7 @@ class ClockSampler:
                 if v.lower().startswith("active"):
                     reasons.add(n)
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
-                "samples": len(sm)}
+                "samples": len(sm), "window": window}
 
 
 def build_ref_scene(lib, sc):
@@ -254,20 +269,22 @@ def run_ours(args):
     ctx.set_option(crt.OPT_COUNTERS, 0)
 
     # ---- device-resident timing ----
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+        sampler.wait_first()
     for i in range(args.warmup):
         step(1 + i)
     ctx.reset_counters()
     barrier()
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
+    t_wall0 = time.perf_counter()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(ext)
     for i in range(args.steps):
         step(100 + i)
     e1.record(ext)
     barrier()
-    clocks = sampler.stop() if rank == 0 else None
+    t_wall1 = time.perf_counter()
     ms = e0.elapsed_time(e1)
     c = ctx.counters()
     stats = torch.tensor([ms, float(c["rays"]), float(c["paths"]), c["trace_queue_ms"]], dtype=torch.float64, device=dev)
@@ -291,6 +308,7 @@ def run_ours(args):
         e2e_step(100 + i)
     barrier()
     e2e_s = time.perf_counter() - t0
+    clocks = sampler.stop(t_wall0, t_wall1) if rank == 0 else None
     ce = ctx.counters()
     e2e_stats = torch.tensor([e2e_s, float(ce["rays"])], dtype=torch.float64, device=dev)
     if world > 1:
