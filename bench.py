@@ -287,15 +287,26 @@ def run_ours(args):
     t_wall1 = time.perf_counter()
     ms = e0.elapsed_time(e1)
     c = ctx.counters()
-    stats = torch.tensor([ms, float(c["rays"]), float(c["paths"]), c["trace_queue_ms"]], dtype=torch.float64, device=dev)
+    lanes, launches = int(c["lanes"]), int(c["launches"])
+    # the roofline kernels timed alone: the same frames with one slice in flight (in the timed region above up to
+    # CRT_OPT_LANES slices overlap, so a launch's event pair also spans the other slices' kernels)
+    ctx.set_option(crt.OPT_LANES, 1)
+    step(50)
+    ctx.reset_counters()
+    for i in range(args.steps):
+        step(100 + i)
+    ctx.sync()
+    alone_ms = ctx.counters()["trace_queue_ms"]
+    ctx.set_option(crt.OPT_LANES, 4)
+    stats = torch.tensor([ms, float(c["rays"]), float(c["paths"]), alone_ms, float(launches)], dtype=torch.float64, device=dev)
     if world > 1:
         mx = stats.clone()
         dist.all_reduce(mx, op=dist.ReduceOp.MAX)
         sm = stats.clone()
         dist.all_reduce(sm, op=dist.ReduceOp.SUM)
-        ms, rays, paths, bounce_ms = float(mx[0]), float(sm[1]), float(sm[2]), float(mx[3])
+        ms, rays, paths, bounce_ms, launches = float(mx[0]), float(sm[1]), float(sm[2]), float(mx[3]), int(sm[4])
     else:
-        rays, paths, bounce_ms = float(c["rays"]), float(c["paths"]), c["trace_queue_ms"]
+        rays, paths, bounce_ms = float(c["rays"]), float(c["paths"]), alone_ms
     value = rays / (ms * 1e-3) / 1e6
 
     # ---- end to end through host buffers ----
@@ -340,7 +351,7 @@ def run_ours(args):
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "paths_per_s": paths / (ms * 1e-3),
             "config": {"workload": WORKLOAD, "triangles": int(info["n_prims"]), "lbvh_depth": info["max_depth"],
-                       "lbvh_build_ms": build_ms, "parallelism": ("single" if world == 1 else
+                       "lbvh_build_ms": build_ms, "lanes": lanes, "parallelism": ("single" if world == 1 else
                                        "samples%d: every rank renders 16 spp of every pixel (sample range [16r, 16r+16)), %d spp in the combined frame" % (world, spp * world)
                                        if weak else "tiles%d: 32x32 tiles, index mod N" % world),
                        "combine": "ncclReduce(sum) of the 24.9 MB accumulators onto rank 0" if world > 1 else "none",
@@ -350,13 +361,14 @@ def run_ours(args):
             "e2e": {"value": e2e_value, "unit": "Mrays/s", "ms_per_step": 1e3 * e2e_s / args.steps,
                     "h2d_bytes_per_step": int(host_verts.numel() * 4 + 88), "d2h_bytes_per_step": int(nx * ny * 12),
                     "what": "crt_scene_update_vertices + crt_accel_refit + crt_render per frame, host buffers, wall clock"},
-            "gpu_launches": int(args.steps * (1 + 2 * bounce_launches + 1 + 1)),
+            "gpu_launches": launches,
             "roofline": {"kernel": "closest hit over the 4-wide LBVH: k_trace_packet (camera rays) + k_trace_queue (bounces), %d launches/step" % bounce_launches,
                          "bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                          "frac": achieved / peaks["hbm_gbs"], "traffic": traffic, "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": alg_bytes / bounce_launches,
                          "algorithmic_flops_per_launch": alg_flops / bounce_launches,
                          "avg_launch_ms": per_launch_ms,
+                         "timing": "CUDA events around each closest-hit launch, on its stream, over %d frames rendered with one slice in flight (CRT_OPT_LANES=1); the timed region of `value` keeps %d slices in flight" % (args.steps, lanes),
                          "nodes_per_ray": work["nodes_visited"] / max(1, n_r), "tris_per_ray": work["tris_tested"] / max(1, n_r),
                          "node_fetches_per_ray": work["node_fetches"] / max(1, n_r), "tri_fetches_per_ray": work["tri_fetches"] / max(1, n_r),
                          "accounting": "bytes = 128 B x node fetches + 48 B x triangle fetches + 48 B x rays; camera rays share one fetch per packet of <= 32 rays, every other bounce fetches per ray; flops = 96 x node tests + 50 x triangle tests (per ray)",

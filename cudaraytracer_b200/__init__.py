@@ -16,7 +16,7 @@ LIB_PATH = os.path.join(_HERE, "libcrt_b200.so")
 MISS = 0xFFFFFFFF
 SHADE_PATH, SHADE_LAMBERT, SHADE_NORMAL = 0, 1, 2
 ACCEL_LBVH, ACCEL_BRUTE = 0, 1
-OPT_LEAF_MAX, OPT_COUNTERS, OPT_BATCH_PATHS, OPT_REFILL, OPT_LEAF_THRESH, OPT_PACKET_PRIMARY = 1, 2, 3, 4, 5, 6
+OPT_LEAF_MAX, OPT_COUNTERS, OPT_BATCH_PATHS, OPT_REFILL, OPT_LEAF_THRESH, OPT_PACKET_PRIMARY, OPT_LANES = 1, 2, 3, 4, 5, 6, 7
 TILE = 32
 
 # every symbol include/crt.h declares
@@ -46,7 +46,8 @@ class Counters(C.Structure):
                 ("spheres_tested", C.c_uint64), ("scatters", C.c_uint64), ("paths", C.c_uint64),
                 ("build_ms", C.c_float), ("refit_ms", C.c_float), ("render_ms", C.c_float), ("trace_ms", C.c_float),
                 ("bounce_ms", C.c_float), ("trace_queue_ms", C.c_float),
-                ("node_fetches", C.c_uint64), ("tri_fetches", C.c_uint64), ("sphere_fetches", C.c_uint64)]
+                ("node_fetches", C.c_uint64), ("tri_fetches", C.c_uint64), ("sphere_fetches", C.c_uint64),
+                ("launches", C.c_uint64), ("lanes", C.c_uint64)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}

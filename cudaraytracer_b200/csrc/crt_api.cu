@@ -95,9 +95,16 @@ int crt_create(int device, crt_ctx** out)
     CRT_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     CRT_CUDA(cudaEventCreate(&c->ev0));
     CRT_CUDA(cudaEventCreate(&c->ev1));
-    CRT_CUDA(cudaEventCreate(&c->ev2));
-    CRT_CUDA(cudaEventCreate(&c->ev3));
-    for (auto& e : c->ev_trace) CRT_CUDA(cudaEventCreate(&e));
+    CRT_CUDA(cudaEventCreate(&c->ev_fork));
+    for (int l = 0; l < CRT_MAX_LANES; l++) {
+        crt_lane& L = c->lane[l];
+        if (l == 0) L.stream = c->stream;
+        else CRT_CUDA(cudaStreamCreateWithFlags(&L.stream, cudaStreamNonBlocking));
+        CRT_CUDA(cudaEventCreate(&L.ev_begin));
+        CRT_CUDA(cudaEventCreate(&L.ev_end));
+        for (auto& e : L.ev_trace) CRT_CUDA(cudaEventCreate(&e));
+        CRT_CUDA(cudaMallocHost((void**)&L.h_counts, sizeof(uint32_t) * (CRT_MAX_DEPTH + 3)));
+    }
     CRT_CUDA(c->counters.reserve(sizeof(unsigned long long) * CNT_COUNT));
     CRT_CUDA(cudaMemsetAsync(c->counters.p, 0, sizeof(unsigned long long) * CNT_COUNT, c->stream));
     CRT_CUDA(cudaStreamSynchronize(c->stream));
@@ -113,14 +120,23 @@ void crt_destroy(crt_ctx* c)
     DevBuf* bufs[] = {&c->tri_in, &c->tri_mat, &c->tri_id, &c->sph_in, &c->sph_mat, &c->sph_id, &c->mats,
                       &c->keys[0], &c->keys[1], &c->vals[0], &c->vals[1], &c->hist, &c->nodes, &c->recs,
                       &c->child, &c->parent, &c->leaf_parent, &c->range, &c->node_box, &c->leaf_box, &c->flags,
-                      &c->bounds, &c->depth_out, &c->queue[0], &c->queue[1], &c->qcount, &c->work_ctr, &c->hitbuf, &c->rad, &c->accum, &c->rgb,
+                      &c->bounds, &c->depth_out, &c->work_ctr, &c->accum, &c->rgb,
                       &c->rays_tmp, &c->hits_tmp, &c->counters};
     for (DevBuf* b : bufs) b->release();
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
-    if (c->ev2) cudaEventDestroy(c->ev2);
-    if (c->ev3) cudaEventDestroy(c->ev3);
-    for (auto& e : c->ev_trace) if (e) cudaEventDestroy(e);
+    if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+    for (int l = 0; l < CRT_MAX_LANES; l++) {
+        crt_lane& L = c->lane[l];
+        if (L.stream) cudaStreamSynchronize(L.stream);
+        DevBuf* lb[] = {&L.queue[0], &L.queue[1], &L.qcount, &L.work_ctr, &L.hitbuf, &L.rad};
+        for (DevBuf* b : lb) b->release();
+        if (L.ev_begin) cudaEventDestroy(L.ev_begin);
+        if (L.ev_end) cudaEventDestroy(L.ev_end);
+        for (auto& e : L.ev_trace) if (e) cudaEventDestroy(e);
+        if (L.h_counts) cudaFreeHost(L.h_counts);
+        if (l > 0 && L.stream) cudaStreamDestroy(L.stream);
+    }
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -146,6 +162,10 @@ int crt_set_option(crt_ctx* c, int option, int64_t value)
         return CRT_OK;
     case CRT_OPT_PACKET_PRIMARY:
         c->packet_primary = value != 0;
+        return CRT_OK;
+    case CRT_OPT_LANES:
+        if (value < 1 || value > CRT_MAX_LANES) { set_error("CRT_OPT_LANES must be in [1, %d]", CRT_MAX_LANES); return CRT_ERR_INVALID; }
+        c->n_lanes = (int)value;
         return CRT_OK;
     case CRT_OPT_BATCH_PATHS:
         if (value < 1) { set_error("CRT_OPT_BATCH_PATHS must be >= 1"); return CRT_ERR_INVALID; }

@@ -53,12 +53,24 @@ constexpr int CRT_MAX_DEPTH = 16;
 
 }  // namespace crt
 
+// One slice of a frame in flight (render.cu): its own stream, wavefront
+// queues, hit and radiance buffers, queue counters and timing events.
+constexpr int CRT_MAX_LANES = 4;
+struct crt_lane {
+    cudaStream_t stream = nullptr;         // lane 0 uses the context's stream
+    crt::DevBuf queue[2], qcount, work_ctr, hitbuf, rad;
+    cudaEvent_t ev_begin = nullptr, ev_end = nullptr;   // bounces of the current job
+    cudaEvent_t ev_trace[2 * (crt::CRT_MAX_DEPTH + 1)] = {};
+    uint32_t* h_counts = nullptr;          // pinned copy of qcount
+};
+
 struct crt_ctx {
     int device = 0;
     int sm_count = 148;
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr, ev3 = nullptr;
-    cudaEvent_t ev_trace[2 * (crt::CRT_MAX_DEPTH + 1)] = {};
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_fork = nullptr;
+    crt_lane lane[CRT_MAX_LANES];
+    int n_lanes = 4;                       // CRT_OPT_LANES: most slices of a frame in flight
 
     // scene as uploaded (caller's order)
     crt::DevBuf tri_in, tri_mat, tri_id;   // n_tri x 12 floats, u32, u32
@@ -78,7 +90,7 @@ struct crt_ctx {
     int tree_depth = 0;
 
     // render
-    crt::DevBuf queue[2], qcount, work_ctr, hitbuf, rad, accum, rgb, rays_tmp, hits_tmp;
+    crt::DevBuf work_ctr, accum, rgb, rays_tmp, hits_tmp;
     crt::DevBuf counters;                  // CNT_COUNT x uint64
     int count_work = 0;
     int leaf_thresh = 8;                   // parked lanes that trigger the primitive-test phase

@@ -26,6 +26,7 @@
 #include "crt_traverse.cuh"
 #include <stdio.h>
 #include <stdlib.h>
+#include <algorithm>
 
 namespace crt {
 
@@ -35,8 +36,8 @@ struct RenderParams {
     DCamera cam;
     int nx, ny;
     int tiles_x;
-    int rank, world;
-    uint32_t n_slots;     // local tiles * CRT_TILE^2
+    int rank, world;      // the job renders tiles rank, rank + world, ... (a lane of a rank is a sub-rank: render_accum)
+    uint32_t n_slots;     // slots of this job: its tiles * CRT_TILE^2
     int s_begin;          // first sample index of this batch
     int s_count;          // samples in this batch
     int max_depth;
@@ -419,28 +420,39 @@ static DCamera to_dcamera(const crt_camera* c)
 }
 
 template <bool COUNT, bool HAS_SPH>
-static void launch_bounce(crt_ctx* c, int b, int grid_trace, int grid_shade, const RenderParams& P, const AccelView& A,
+static void launch_bounce(crt_ctx* c, crt_lane& L, int b, int grid_trace, int grid_shade, const RenderParams& P, const AccelView& A,
                           const float4* q_in, const uint32_t* n_in, uint32_t* work_ctr, float4* q_out, uint32_t* n_out)
 {
-    cudaEventRecord(c->ev_trace[2 * b], c->stream);
+    cudaEventRecord(L.ev_trace[2 * b], L.stream);
     if (b == 0 && c->packet_primary)   // camera rays: a warp holds the samples of one or two pixels
-        k_trace_packet<COUNT, HAS_SPH><<<grid_trace, TP_BLOCK, 0, c->stream>>>(A, q_in, P.cap, n_in, work_ctr, c->hitbuf.as<float4>(),
-                                                                               c->counters.as<unsigned long long>());
+        k_trace_packet<COUNT, HAS_SPH><<<grid_trace, TP_BLOCK, 0, L.stream>>>(A, q_in, P.cap, n_in, work_ctr, L.hitbuf.as<float4>(),
+                                                                              c->counters.as<unsigned long long>());
     else
-        k_trace_queue<COUNT, HAS_SPH><<<grid_trace, TP_BLOCK, 0, c->stream>>>(A, q_in, P.cap, n_in, work_ctr, c->hitbuf.as<float4>(),
-                                                                              c->counters.as<unsigned long long>(), (uint32_t)c->refill, (uint32_t)c->leaf_thresh);
-    cudaEventRecord(c->ev_trace[2 * b + 1], c->stream);
+        k_trace_queue<COUNT, HAS_SPH><<<grid_trace, TP_BLOCK, 0, L.stream>>>(A, q_in, P.cap, n_in, work_ctr, L.hitbuf.as<float4>(),
+                                                                             c->counters.as<unsigned long long>(), (uint32_t)c->refill, (uint32_t)c->leaf_thresh);
+    cudaEventRecord(L.ev_trace[2 * b + 1], L.stream);
     if (COUNT && getenv("CRT_TRACE_TIMING")) {   // development aid: longest dependent chain of the launch
         unsigned long long ms = 0;
-        cudaMemcpyAsync(&ms, c->counters.as<unsigned long long>() + CNT_MAX_STEPS, 8, cudaMemcpyDeviceToHost, c->stream);
-        cudaMemsetAsync(c->counters.as<unsigned long long>() + CNT_MAX_STEPS, 0, 8, c->stream);
-        cudaStreamSynchronize(c->stream);
+        cudaMemcpyAsync(&ms, c->counters.as<unsigned long long>() + CNT_MAX_STEPS, 8, cudaMemcpyDeviceToHost, L.stream);
+        cudaMemsetAsync(c->counters.as<unsigned long long>() + CNT_MAX_STEPS, 0, 8, L.stream);
+        cudaStreamSynchronize(L.stream);
         fprintf(stderr, "[crt] bounce %d: longest ray took %llu traversal steps\n", b, ms);
     }
-    k_shade<COUNT, HAS_SPH><<<grid_shade, RB, 0, c->stream>>>(P, A, c->mats.as<DMat>(), q_in, c->hitbuf.as<float4>(), n_in, q_out,
-                                                              n_out, c->rad.as<float4>(), c->counters.as<unsigned long long>());
+    k_shade<COUNT, HAS_SPH><<<grid_shade, RB, 0, L.stream>>>(P, A, c->mats.as<DMat>(), q_in, L.hitbuf.as<float4>(), n_in, q_out,
+                                                             n_out, L.rad.as<float4>(), c->counters.as<unsigned long long>());
 }
 
+// A frame is cut into jobs: sample batches (when all samples of the rank's
+// pixels do not fit CRT_OPT_BATCH_PATHS) x n_lanes slices of the rank's tiles.
+// The slices of one sample batch run concurrently, one per lane (stream): each
+// is the full wavefront loop raygen -> (trace, shade) x bounces -> accumulate
+// over its own queues; slices interleave tile by tile. A slice's last bounces trace a few hundred rays that
+// walk 200-700 dependent steps each - launches that leave the GPU idle when
+// they run alone - and every persistent launch ends with a tail of
+// half-empty SMs; with two slices in flight the other slice's wide launches
+// fill both. Slices own disjoint pixels and a pixel's sample batches stay on
+// one lane in order, so d_accum is summed in the same order for any lane
+// count and the image does not depend on it.
 int render_accum(crt_ctx* c, const crt_camera* cam, int nx, int ny, int s0, int s1, int max_depth, int mode,
                  uint64_t seed, int rank, int world, float* d_accum)
 {
@@ -461,7 +473,6 @@ int render_accum(crt_ctx* c, const crt_camera* cam, int nx, int ny, int s0, int 
     const long long local_tiles = tiles > rank ? (tiles - rank + world - 1) / world : 0;
     P.rank = rank; P.world = world;
     if (local_tiles * CRT_TILE * CRT_TILE >= (1ll << 31)) { set_error("crt_render: image too large"); return CRT_ERR_INVALID; }
-    P.n_slots = (uint32_t)(local_tiles * CRT_TILE * CRT_TILE);
     P.max_depth = max_depth; P.mode = mode; P.seed = seed;
 
     CRT_CUDA(cudaEventRecord(c->ev0, st));
@@ -469,21 +480,34 @@ int render_accum(crt_ctx* c, const crt_camera* cam, int nx, int ny, int s0, int 
     const int n_samples = s1 - s0;
     uint64_t total_rays = 0, total_paths = 0;
     float bounce_ms = 0.f, trace_q_ms = 0.f;
-    if (P.n_slots > 0 && n_samples > 0) {
-        long long per_batch = c->batch_paths / (long long)P.n_slots;
+    if (local_tiles > 0 && n_samples > 0) {
+        // lane l of rank r renders tiles r + world * (l + n_lanes * j): the slices interleave, so they are balanced
+        // at most CRT_OPT_LANES, at least 2^22 camera samples per slice: a small frame is launch-bound already
+        const long long want = (local_tiles * CRT_TILE * CRT_TILE * n_samples) >> 22;
+        const int n_lanes = (int)std::max(1ll, std::min((long long)c->n_lanes, std::min(local_tiles, want)));
+        c->host_counters.lanes = (uint64_t)n_lanes;
+        const int sub_world = world * n_lanes;
+        auto sub_tiles = [&](int l) {
+            const long long sr = (long long)l * world + rank;
+            return tiles > sr ? (tiles - sr + sub_world - 1) / sub_world : 0ll;
+        };
+        const long long lane_slots = sub_tiles(0) * CRT_TILE * CRT_TILE;               // lane 0 has the most tiles
+        long long per_batch = c->batch_paths / (lane_slots * n_lanes);
         if (per_batch < 1) per_batch = 1;
         if (per_batch > n_samples) per_batch = n_samples;
-        while ((long long)P.n_slots * per_batch >= (1ll << 31) && per_batch > 1) per_batch--;
-        const size_t cap = (size_t)P.n_slots * (size_t)per_batch;
+        while (lane_slots * per_batch >= (1ll << 31) && per_batch > 1) per_batch--;
+        const size_t cap = (size_t)lane_slots * (size_t)per_batch;
         P.cap = (uint32_t)cap;
-        CRT_CUDA(c->queue[0].reserve(cap * 64));
-        CRT_CUDA(c->queue[1].reserve(cap * 64));
-        CRT_CUDA(c->rad.reserve(cap * 16));
         const int n_levels = CRT_MAX_DEPTH + 3;
-        CRT_CUDA(c->qcount.reserve(sizeof(uint32_t) * n_levels));
-        CRT_CUDA(c->work_ctr.reserve(sizeof(uint32_t) * 64));
-        CRT_CUDA(c->hitbuf.reserve(cap * 16));
-        uint32_t h_counts[CRT_MAX_DEPTH + 3];
+        for (int l = 0; l < n_lanes; l++) {
+            crt_lane& L = c->lane[l];
+            CRT_CUDA(L.queue[0].reserve(cap * 64));
+            CRT_CUDA(L.queue[1].reserve(cap * 64));
+            CRT_CUDA(L.rad.reserve(cap * 16));
+            CRT_CUDA(L.qcount.reserve(sizeof(uint32_t) * n_levels));
+            CRT_CUDA(L.work_ctr.reserve(sizeof(uint32_t) * 64));
+            CRT_CUDA(L.hitbuf.reserve(cap * 16));
+        }
 
         int bps = 1, bps_shade = 1;
         // the instantiations have near-identical resource needs; size the persistent grids from one
@@ -496,47 +520,68 @@ int render_accum(crt_ctx* c, const crt_camera* cam, int nx, int ny, int s0, int 
         const AccelView A = accel_view(c);
         const bool sph = c->n_sph > 0;
         const int bounces = mode == CRT_SHADE_PATH ? max_depth + 1 : 1;
+        static const bool verbose = getenv("CRT_TRACE_TIMING") != nullptr;   // development aid
+
+        // lanes 1.. start after what the caller queued on the context's stream (uploads, refit, the memset above)
+        CRT_CUDA(cudaEventRecord(c->ev_fork, st));
+        for (int l = 1; l < n_lanes; l++) CRT_CUDA(cudaStreamWaitEvent(c->lane[l].stream, c->ev_fork, 0));
 
         for (int sb = s0; sb < s1; sb += (int)per_batch) {
             P.s_begin = sb;
             P.s_count = (s1 - sb) < per_batch ? (s1 - sb) : (int)per_batch;
-            CRT_CUDA(cudaMemsetAsync(c->qcount.p, 0, sizeof(uint32_t) * n_levels, st));
-            CRT_CUDA(cudaMemsetAsync(c->work_ctr.p, 0, sizeof(uint32_t) * 64, st));
-            const uint32_t total = P.n_slots * (uint32_t)P.s_count;
-            const unsigned int rg = (unsigned int)min((size_t)(total + RB - 1) / RB, (size_t)c->sm_count * 32);
-            k_raygen<<<rg, RB, 0, st>>>(P, c->queue[0].as<float4>(), c->qcount.as<uint32_t>());
-            CRT_CUDA(cudaEventRecord(c->ev2, st));
-            for (int b = 0; b < bounces; b++) {
-                const float4* qi = c->queue[b & 1].as<float4>();
-                float4* qo = c->queue[(b + 1) & 1].as<float4>();
-                const uint32_t* ni = c->qcount.as<uint32_t>() + b;
-                uint32_t* no = c->qcount.as<uint32_t>() + b + 1;
-                uint32_t* wc = c->work_ctr.as<uint32_t>() + b;
-                if (c->count_work) {
-                    if (sph) launch_bounce<true, true>(c, b, grid, grid_shade, P, A, qi, ni, wc, qo, no);
-                    else launch_bounce<true, false>(c, b, grid, grid_shade, P, A, qi, ni, wc, qo, no);
-                } else {
-                    if (sph) launch_bounce<false, true>(c, b, grid, grid_shade, P, A, qi, ni, wc, qo, no);
-                    else launch_bounce<false, false>(c, b, grid, grid_shade, P, A, qi, ni, wc, qo, no);
+            for (int l = 0; l < n_lanes; l++) {
+                crt_lane& L = c->lane[l];
+                L.h_counts[0] = 0;
+                if (sub_tiles(l) == 0) continue;
+                RenderParams PL = P;
+                PL.world = sub_world;
+                PL.rank = l * world + rank;
+                PL.n_slots = (uint32_t)(sub_tiles(l) * CRT_TILE * CRT_TILE);
+                CRT_CUDA(cudaMemsetAsync(L.qcount.p, 0, sizeof(uint32_t) * n_levels, L.stream));
+                CRT_CUDA(cudaMemsetAsync(L.work_ctr.p, 0, sizeof(uint32_t) * 64, L.stream));
+                const uint32_t total = PL.n_slots * (uint32_t)PL.s_count;
+                const unsigned int rg = (unsigned int)min((size_t)(total + RB - 1) / RB, (size_t)c->sm_count * 32);
+                k_raygen<<<rg, RB, 0, L.stream>>>(PL, L.queue[0].as<float4>(), L.qcount.as<uint32_t>());
+                c->host_counters.launches += 2 + 2 * (uint64_t)bounces;   // raygen, (trace, shade) per bounce, accumulate
+                CRT_CUDA(cudaEventRecord(L.ev_begin, L.stream));
+                for (int b = 0; b < bounces; b++) {
+                    const float4* qi = L.queue[b & 1].as<float4>();
+                    float4* qo = L.queue[(b + 1) & 1].as<float4>();
+                    const uint32_t* ni = L.qcount.as<uint32_t>() + b;
+                    uint32_t* no = L.qcount.as<uint32_t>() + b + 1;
+                    uint32_t* wc = L.work_ctr.as<uint32_t>() + b;
+                    if (c->count_work) {
+                        if (sph) launch_bounce<true, true>(c, L, b, grid, grid_shade, PL, A, qi, ni, wc, qo, no);
+                        else launch_bounce<true, false>(c, L, b, grid, grid_shade, PL, A, qi, ni, wc, qo, no);
+                    } else {
+                        if (sph) launch_bounce<false, true>(c, L, b, grid, grid_shade, PL, A, qi, ni, wc, qo, no);
+                        else launch_bounce<false, false>(c, L, b, grid, grid_shade, PL, A, qi, ni, wc, qo, no);
+                    }
                 }
+                CRT_CUDA(cudaEventRecord(L.ev_end, L.stream));
+                k_accumulate<<<(PL.n_slots + 255) / 256, 256, 0, L.stream>>>(PL, L.rad.as<float4>(), d_accum);
+                CRT_CUDA(cudaMemcpyAsync(L.h_counts, L.qcount.p, sizeof(uint32_t) * n_levels, cudaMemcpyDeviceToHost, L.stream));
             }
-            CRT_CUDA(cudaEventRecord(c->ev3, st));
-            k_accumulate<<<(P.n_slots + 255) / 256, 256, 0, st>>>(P, c->rad.as<float4>(), d_accum);
-            CRT_CUDA(cudaMemcpyAsync(h_counts, c->qcount.p, sizeof(uint32_t) * n_levels, cudaMemcpyDeviceToHost, st));
-            CRT_CUDA(cudaStreamSynchronize(st));
-            float bms = 0.f;
-            CRT_CUDA(cudaEventElapsedTime(&bms, c->ev2, c->ev3));
-            bounce_ms += bms;
-            static const bool verbose = getenv("CRT_TRACE_TIMING") != nullptr;   // development aid
-            for (int b = 0; b < bounces; b++) {
-                float tms = 0.f;
-                CRT_CUDA(cudaEventElapsedTime(&tms, c->ev_trace[2 * b], c->ev_trace[2 * b + 1]));
-                trace_q_ms += tms;
-                if (verbose) fprintf(stderr, "[crt] bounce %d: %u rays, trace %.3f ms\n", b, h_counts[b], tms);
+            // the queue counts size the statistics and the lanes' buffers are reused by the next sample batch
+            float batch_ms = 0.f;
+            for (int l = 0; l < n_lanes; l++) {
+                crt_lane& L = c->lane[l];
+                CRT_CUDA(cudaStreamSynchronize(L.stream));
+                if (L.h_counts[0] == 0) continue;
+                float bms = 0.f;
+                CRT_CUDA(cudaEventElapsedTime(&bms, L.ev_begin, L.ev_end));
+                batch_ms = bms > batch_ms ? bms : batch_ms;
+                for (int b = 0; b < bounces; b++) {
+                    float tms = 0.f;
+                    CRT_CUDA(cudaEventElapsedTime(&tms, L.ev_trace[2 * b], L.ev_trace[2 * b + 1]));
+                    trace_q_ms += tms;
+                    if (verbose) fprintf(stderr, "[crt] lane %d bounce %d: %u rays, trace %.3f ms\n", l, b, L.h_counts[b], tms);
+                }
+                if (verbose) fprintf(stderr, "[crt] lane %d: bounces %.3f ms\n", l, bms);
+                total_paths += L.h_counts[0];
+                for (int b = 0; b < bounces; b++) total_rays += L.h_counts[b];
             }
-            if (verbose) fprintf(stderr, "[crt] batch: raygen..accumulate %.3f ms, bounces %.3f ms\n", 0.f, bms);
-            total_paths += h_counts[0];
-            for (int b = 0; b < bounces; b++) total_rays += h_counts[b];
+            bounce_ms += batch_ms;
         }
     }
     CRT_CUDA(cudaEventRecord(c->ev1, st));
@@ -559,6 +604,7 @@ int launch_resolve(crt_ctx* c, const float* d_accum, size_t n_pixels, int spp, f
     if (nv == 0) return CRT_OK;
     const float inv_ns = 1.0f / (float)spp;   // float(1.0 / t), vec3.h:183 (correctly rounded either way)
     k_resolve<<<(unsigned int)((nv + 255) / 256), 256, 0, c->stream>>>(d_accum, nv, inv_ns, d_rgb);
+    c->host_counters.launches++;
     CRT_CUDA(cudaGetLastError());
     return CRT_OK;
 }
@@ -568,6 +614,7 @@ int launch_pack_rgba8(crt_ctx* c, const float* d_rgb, int nx, int ny, uint8_t* d
     const size_t n = (size_t)nx * ny;
     if (n == 0) return CRT_OK;
     k_pack_rgba8<<<(unsigned int)((n + 255) / 256), 256, 0, c->stream>>>(d_rgb, nx, ny, reinterpret_cast<uchar4*>(d_rgba8));
+    c->host_counters.launches++;
     CRT_CUDA(cudaGetLastError());
     return CRT_OK;
 }

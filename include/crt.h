@@ -97,6 +97,9 @@ typedef enum {
     CRT_OPT_BATCH_PATHS = 3,/* max camera samples in flight per wavefront batch (default 1<<25) */
     CRT_OPT_LEAF_THRESH = 5,/* tuning: lanes parked on a leaf that trigger the primitive-test phase, 1..32 (default 8) */
     CRT_OPT_PACKET_PRIMARY = 6, /* 1 (default): camera rays are traced as one packet per warp; 0: like every other bounce */
+    CRT_OPT_LANES = 7,      /* render: at most 1..4 slices of the frame in flight on their own streams (default 4; a slice is
+                             * never smaller than 2^22 camera samples), so one slice's
+                             * latency-bound last bounces overlap the other's wide launches; images do not depend on it */
     CRT_OPT_REFILL = 4      /* tuning: idle lanes per warp that trigger a refill from the ray queue, 1..32 (default 8) */
 } crt_option;
 
@@ -122,6 +125,8 @@ typedef struct {
     uint64_t node_fetches;
     uint64_t tri_fetches;
     uint64_t sphere_fetches;
+    uint64_t launches;        /* kernels launched by crt_render*, crt_resolve_device, crt_pack_rgba8_device since crt_reset_counters */
+    uint64_t lanes;           /* slices the last crt_render* call kept in flight (CRT_OPT_LANES, capped by the frame size) */
 } crt_counters;
 
 /* Image partition for one-process-per-GPU rendering. The image is cut into

@@ -1,6 +1,7 @@
 """Quick device-side throughput probe (development aid, not the bench):
 builds a scene, times crt_trace_device on primary + incoherent rays and one
 render, prints counters. Usage: python scripts/quick_perf.py [c3|c1|c2|c5:N] [leaf_max]"""
+import os
 import sys
 import time
 
@@ -31,6 +32,8 @@ def main():
     ctx.set_option(crt.OPT_LEAF_MAX, leaf_max)
     ctx.set_option(crt.OPT_REFILL, refill)
     ctx.set_option(crt.OPT_LEAF_THRESH, lthr)
+    if os.environ.get("CRT_LANES"):
+        ctx.set_option(crt.OPT_LANES, int(os.environ["CRT_LANES"]))
     t0 = time.time()
     ctx.set_scene(sc)
     print("upload %.3fs" % (time.time() - t0))
