@@ -249,8 +249,9 @@ k_fit(const float* __restrict__ tri_in, const uint32_t* __restrict__ tri_mat, co
 }
 
 // One 4-wide traversal node per binary node i that is not collapsed into a
-// leaf: its slots are i's grandchildren (a child that is a leaf, or a subtree
-// of <= leaf_max primitives, keeps its own slot). Every binary node gets its
+// leaf: its slots start as i's two children, and the inner slot with the
+// largest surface area is replaced by its own two children until four slots
+// are in use (a leaf, or a subtree of <= leaf_max primitives, stays a slot). Every binary node gets its
 // wide node at the same index, so no renumbering pass is needed; only the
 // nodes reachable from the root through slot references are ever fetched.
 struct Slot { int ref; Box box; };
@@ -286,18 +287,27 @@ k_emit_nodes(int n, int leaf_max, const int2* __restrict__ child, const int2* __
     if (rg.y - rg.x + 1 <= leaf_max) return;               // collapsed into a leaf of an ancestor
     const int2 ch = child[i];
     Slot slot[4];
-    int ns = 0;
-    const int cc[2] = {ch.x, ch.y};
-#pragma unroll
-    for (int s = 0; s < 2; s++) {
-        Slot c;
-        if (resolve_child(cc[s], leaf_max, range, leaf_box, node_box, c)) {
-            slot[ns++] = c;
-        } else {
-            const int2 gc = child[c.ref];
-            resolve_child(gc.x, leaf_max, range, leaf_box, node_box, slot[ns++]);
-            resolve_child(gc.y, leaf_max, range, leaf_box, node_box, slot[ns++]);
+    bool inner[4] = {false, false, false, false};
+    int ns = 2;
+    inner[0] = !resolve_child(ch.x, leaf_max, range, leaf_box, node_box, slot[0]);
+    inner[1] = !resolve_child(ch.y, leaf_max, range, leaf_box, node_box, slot[1]);
+    // open the inner slot with the largest surface area until the node is full: a large
+    // child is the one most rays enter anyway, so its two children take its place
+    while (ns < 4) {
+        int pick = -1;
+        float best = -1.0f;
+        for (int s = 0; s < ns; s++) {
+            if (!inner[s]) continue;
+            const Box& b = slot[s].box;
+            const float dx = b.hx - b.lx, dy = b.hy - b.ly, dz = b.hz - b.lz;
+            const float area = dx * dy + dy * dz + dz * dx;
+            if (area > best) { best = area; pick = s; }
         }
+        if (pick < 0) break;
+        const int2 gc = child[slot[pick].ref];
+        inner[pick] = !resolve_child(gc.x, leaf_max, range, leaf_box, node_box, slot[pick]);
+        inner[ns] = !resolve_child(gc.y, leaf_max, range, leaf_box, node_box, slot[ns]);
+        ns++;
     }
     for (int s = ns; s < 4; s++) {
         slot[s].ref = CRT_SLOT_EMPTY;
