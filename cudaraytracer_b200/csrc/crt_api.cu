@@ -1,5 +1,7 @@
 // crt_api.cu — the C ABI of include/crt.h: context, scene upload, dispatch.
 #include "crt_internal.h"
+#include <algorithm>
+#include <stdlib.h>
 
 #include <stdarg.h>
 #include <stdio.h>
@@ -92,6 +94,8 @@ int crt_create(int device, crt_ctx** out)
     cudaDeviceProp prop;
     CRT_CUDA(cudaGetDeviceProperties(&prop, device));
     c->sm_count = prop.multiProcessorCount;
+    if (const char* e = getenv("CRT_BUILDER")) c->builder = atoi(e) == CRT_BUILDER_PLOC ? CRT_BUILDER_PLOC : CRT_BUILDER_LBVH;   // development aids
+    if (const char* e = getenv("CRT_PLOC_RADIUS")) c->ploc_radius = std::max(1, std::min(32, atoi(e)));
     CRT_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     CRT_CUDA(cudaEventCreate(&c->ev0));
     CRT_CUDA(cudaEventCreate(&c->ev1));
@@ -120,7 +124,7 @@ void crt_destroy(crt_ctx* c)
     DevBuf* bufs[] = {&c->tri_in, &c->tri_mat, &c->tri_id, &c->sph_in, &c->sph_mat, &c->sph_id, &c->mats,
                       &c->keys[0], &c->keys[1], &c->vals[0], &c->vals[1], &c->hist, &c->nodes, &c->recs,
                       &c->child, &c->parent, &c->leaf_parent, &c->range, &c->node_box, &c->leaf_box, &c->flags,
-                      &c->bounds, &c->depth_out, &c->work_ctr, &c->accum, &c->rgb,
+                      &c->bounds, &c->depth_out, &c->ploc_box[0], &c->ploc_box[1], &c->ploc_nn, &c->ploc_tmp, &c->ploc_blk, &c->work_ctr, &c->accum, &c->rgb,
                       &c->rays_tmp, &c->hits_tmp, &c->counters};
     for (DevBuf* b : bufs) b->release();
     if (c->ev0) cudaEventDestroy(c->ev0);
@@ -162,6 +166,10 @@ int crt_set_option(crt_ctx* c, int option, int64_t value)
         return CRT_OK;
     case CRT_OPT_PACKET_PRIMARY:
         c->packet_primary = value != 0;
+        return CRT_OK;
+    case CRT_OPT_BUILDER:
+        if (value != CRT_BUILDER_LBVH && value != CRT_BUILDER_PLOC) { set_error("CRT_OPT_BUILDER must be CRT_BUILDER_LBVH or CRT_BUILDER_PLOC"); return CRT_ERR_INVALID; }
+        c->builder = (int)value;
         return CRT_OK;
     case CRT_OPT_LANES:
         if (value < 1 || value > CRT_MAX_LANES) { set_error("CRT_OPT_LANES must be in [1, %d]", CRT_MAX_LANES); return CRT_ERR_INVALID; }

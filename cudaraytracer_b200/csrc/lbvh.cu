@@ -337,7 +337,292 @@ k_depth(int n, const int* __restrict__ parent, const int* __restrict__ leaf_pare
     if ((threadIdx.x & 31) == (unsigned int)(__ffs(act) - 1)) atomicMax(out, d);
 }
 
+// ---------------------------------------------------------------------------
+// PLOC topology (Meister & Bittner, "Parallel Locally-Ordered Clustering for
+// BVH Construction", TVCG 2018) as the alternative to k_hierarchy: the
+// Morton-sorted primitives start as one cluster each; per round every cluster
+// looks PLOC_R positions to either side for the partner whose union with it has
+// the smallest surface area, mutual partners merge into a new node that takes
+// the left partner's place, and the array is compacted in order. Unlike the
+// radix tree, whose splits follow the bits of the code, a merge looks at the
+// boxes themselves, so large primitives stay unmerged until the clusters around
+// them have grown and the tree costs fewer node visits per ray.
+// Candidate order: (area, |i - j|, parity of min(i, j), min(i, j)) is a strict
+// total order on unordered pairs, so the smallest pair of a round is always
+// mutual (every round merges something) and n identical boxes pair up as
+// (0,1)(2,3).. instead of chaining.
+// Node ids are handed out from n-2 downwards, in array order inside a round:
+// the last merge is node 0, the root, as in the radix tree, and the nodes of a
+// level lie in Morton order. A final pass renumbers the leaves in depth-first
+// order so that every subtree covers a contiguous range of records again
+// (k_emit_nodes folds small subtrees into leaves by range).
+constexpr int PLOC_R = 32;   // largest search radius (shared-memory halo)
+constexpr int PLOC_B = 256;
+
+__global__ void __launch_bounds__(256)
+k_ploc_init(const float* __restrict__ tri_in, const float* __restrict__ sph_in, uint32_t n_tri, uint32_t n,
+            const uint32_t* __restrict__ perm, float4* __restrict__ lo, float4* __restrict__ hi)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const Box b = prim_box(tri_in, sph_in, n_tri, perm[i]);
+    lo[i] = make_float4(b.lx, b.ly, b.lz, __int_as_float(~(int)i));   // .w: reference of the cluster's subtree
+    hi[i] = make_float4(b.hx, b.hy, b.hz, __int_as_float(1));         // .w: primitives below it
+}
+
+__global__ void __launch_bounds__(PLOC_B)
+k_ploc_nn(int nc, int radius, const float4* __restrict__ lo, const float4* __restrict__ hi, int* __restrict__ nn)
+{
+    __shared__ float4 s_lo[PLOC_B + 2 * PLOC_R], s_hi[PLOC_B + 2 * PLOC_R];
+    const int base = (int)blockIdx.x * PLOC_B - PLOC_R;
+    for (int t = threadIdx.x; t < PLOC_B + 2 * PLOC_R; t += PLOC_B) {
+        const int g = base + t;
+        if (g >= 0 && g < nc) { s_lo[t] = lo[g]; s_hi[t] = hi[g]; }
+    }
+    __syncthreads();
+    const int i = (int)blockIdx.x * PLOC_B + (int)threadIdx.x;
+    if (i >= nc) return;
+    const float4 al = s_lo[threadIdx.x + PLOC_R], ah = s_hi[threadIdx.x + PLOC_R];
+    unsigned long long best = ~0ull;
+    int best_j = -1;
+#pragma unroll 4
+    for (int o = -radius; o <= radius; o++) {
+        const int j = i + o;
+        if (o == 0 || j < 0 || j >= nc) continue;
+        const float4 bl = s_lo[threadIdx.x + PLOC_R + o], bh = s_hi[threadIdx.x + PLOC_R + o];
+        const float dx = fmaxf(ah.x, bh.x) - fminf(al.x, bl.x);
+        const float dy = fmaxf(ah.y, bh.y) - fminf(al.y, bl.y);
+        const float dz = fmaxf(ah.z, bh.z) - fminf(al.z, bl.z);
+        const float area = dx * dy + dy * dz + dz * dx;            // >= 0: its bits order like the value
+        const uint32_t g = (uint32_t)(o < 0 ? -o : o);
+        const uint32_t m = (uint32_t)(o < 0 ? j : i);
+        const unsigned long long key = ((unsigned long long)__float_as_uint(area) << 32) |
+                                       (unsigned long long)((g << 2) | ((m & 1u) << 1) | (o > 0 ? 1u : 0u));
+        if (key < best) { best = key; best_j = j; }
+    }
+    nn[i] = best_j;
+}
+
+// exclusive scan of one int per thread over a PLOC_B-thread block; *total = block sum
+__device__ __forceinline__ int block_exscan(int v, int* s_warp, int* total)
+{
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    int x = v;
+    for (int o = 1; o < 32; o <<= 1) {
+        const int y = __shfl_up_sync(0xffffffffu, x, o);
+        if (lane >= o) x += y;
+    }
+    __syncthreads();
+    if (lane == 31) s_warp[w] = x;
+    __syncthreads();
+    if (w == 0) {
+        int t = lane < PLOC_B / 32 ? s_warp[lane] : 0;
+        for (int o = 1; o < 32; o <<= 1) {
+            const int y = __shfl_up_sync(0xffffffffu, t, o);
+            if (lane >= o) t += y;
+        }
+        if (lane < PLOC_B / 32) s_warp[lane] = t;                  // inclusive warp sums
+    }
+    __syncthreads();
+    *total = s_warp[PLOC_B / 32 - 1];
+    return x - v + (w > 0 ? s_warp[w - 1] : 0);
+}
+
+// role of cluster i in this round: 0 = stays, 1 = left partner (becomes the merged node), 2 = right partner (leaves)
+__device__ __forceinline__ int ploc_role(int nc, const int* __restrict__ nn, int i)
+{
+    if (i >= nc) return 2;
+    const int j = nn[i];
+    if (j < 0 || nn[j] != i) return 0;
+    return i < j ? 1 : 2;
+}
+
+__global__ void __launch_bounds__(PLOC_B)
+k_ploc_count(int nc, const int* __restrict__ nn, int2* __restrict__ blk)
+{
+    __shared__ int s_a[PLOC_B / 32], s_b[PLOC_B / 32];
+    const int i = (int)blockIdx.x * PLOC_B + (int)threadIdx.x;
+    const int role = ploc_role(nc, nn, i);
+    const unsigned int keep = __ballot_sync(0xffffffffu, role != 2), merge = __ballot_sync(0xffffffffu, role == 1);
+    if ((threadIdx.x & 31) == 0) { s_a[threadIdx.x >> 5] = __popc(keep); s_b[threadIdx.x >> 5] = __popc(merge); }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int a = 0, b = 0;
+        for (int w = 0; w < PLOC_B / 32; w++) { a += s_a[w]; b += s_b[w]; }
+        blk[blockIdx.x] = make_int2(a, b);
+    }
+}
+
+// one block: blk[] -> exclusive prefix sums in place, the totals to *total
+__global__ void __launch_bounds__(1024)
+k_ploc_scan(int nb, int2* __restrict__ blk, int2* __restrict__ total)
+{
+    __shared__ int2 s_w[32];
+    __shared__ int2 s_carry;
+    if (threadIdx.x == 0) s_carry = make_int2(0, 0);
+    __syncthreads();
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    for (int b0 = 0; b0 < nb; b0 += 1024) {
+        const int b = b0 + (int)threadIdx.x;
+        const int2 v = b < nb ? blk[b] : make_int2(0, 0);
+        int2 x = v;
+        for (int o = 1; o < 32; o <<= 1) {
+            const int yx = __shfl_up_sync(0xffffffffu, x.x, o), yy = __shfl_up_sync(0xffffffffu, x.y, o);
+            if (lane >= o) { x.x += yx; x.y += yy; }
+        }
+        if (lane == 31) s_w[w] = x;
+        __syncthreads();
+        if (w == 0) {
+            int2 t = s_w[lane];
+            for (int o = 1; o < 32; o <<= 1) {
+                const int yx = __shfl_up_sync(0xffffffffu, t.x, o), yy = __shfl_up_sync(0xffffffffu, t.y, o);
+                if (lane >= o) { t.x += yx; t.y += yy; }
+            }
+            s_w[lane] = t;
+        }
+        __syncthreads();
+        const int2 carry = s_carry;
+        const int2 wp = w > 0 ? s_w[w - 1] : make_int2(0, 0);
+        if (b < nb) blk[b] = make_int2(carry.x + wp.x + x.x - v.x, carry.y + wp.y + x.y - v.y);
+        __syncthreads();
+        if (threadIdx.x == 1023) s_carry = make_int2(carry.x + wp.x + x.x, carry.y + wp.y + x.y);
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *total = s_carry;
+}
+
+__global__ void __launch_bounds__(PLOC_B)
+k_ploc_merge(int nc, const int* __restrict__ nn, const float4* __restrict__ lo_in, const float4* __restrict__ hi_in,
+             float4* __restrict__ lo_out, float4* __restrict__ hi_out, const int2* __restrict__ blk, int id_top,
+             int2* __restrict__ child, int* __restrict__ parent, int* __restrict__ leaf_parent, int* __restrict__ size)
+{
+    __shared__ int s_warp[PLOC_B / 32];
+    const int i = (int)blockIdx.x * PLOC_B + (int)threadIdx.x;
+    const int role = ploc_role(nc, nn, i);
+    int tot;
+    const int k_keep = block_exscan(role != 2 ? 1 : 0, s_warp, &tot);
+    const int k_merge = block_exscan(role == 1 ? 1 : 0, s_warp, &tot);
+    if (role == 2) return;
+    const int2 off = blk[blockIdx.x];
+    const int pos = off.x + k_keep;
+    float4 l = lo_in[i], h = hi_in[i];
+    if (role == 1) {
+        const int j = nn[i];
+        const float4 bl = lo_in[j], bh = hi_in[j];
+        const int id = id_top - (off.y + k_merge);
+        const int ra = __float_as_int(l.w), rb = __float_as_int(bl.w);
+        child[id] = make_int2(ra, rb);
+        if (ra < 0) leaf_parent[~ra] = id; else parent[ra] = id;
+        if (rb < 0) leaf_parent[~rb] = id; else parent[rb] = id;
+        const int sz = __float_as_int(h.w) + __float_as_int(bh.w);
+        size[id] = sz;
+        l = make_float4(fminf(l.x, bl.x), fminf(l.y, bl.y), fminf(l.z, bl.z), __int_as_float(id));
+        h = make_float4(fmaxf(h.x, bh.x), fmaxf(h.y, bh.y), fmaxf(h.z, bh.z), __int_as_float(sz));
+    }
+    lo_out[pos] = l;
+    hi_out[pos] = h;
+}
+
+// Depth-first position of sorted primitive i: the primitives in the left
+// subtrees of the ancestors it reaches from the right. The same walk gives the
+// first position of an inner node.
+__device__ __forceinline__ int ploc_first_pos(int ref, int up, const int2* __restrict__ child,
+                                              const int* __restrict__ parent, const int* __restrict__ size)
+{
+    int off = 0;
+    for (int node = up; node >= 0; node = parent[node]) {
+        const int2 ch = child[node];
+        if (ch.y == ref) off += ch.x < 0 ? 1 : size[ch.x];
+        ref = node;
+    }
+    return off;
+}
+
+__global__ void __launch_bounds__(256)
+k_ploc_leaf_pos(int n, const int2* __restrict__ child, const int* __restrict__ parent, const int* __restrict__ leaf_parent,
+                const int* __restrict__ size, const uint32_t* __restrict__ perm_in, int* __restrict__ newpos,
+                uint32_t* __restrict__ perm_out, int* __restrict__ leaf_parent_out)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int p = ploc_first_pos(~i, leaf_parent[i], child, parent, size);
+    newpos[i] = p;
+    perm_out[p] = perm_in[i];
+    leaf_parent_out[p] = leaf_parent[i];
+}
+
+__global__ void __launch_bounds__(256)
+k_ploc_node_range(int n, int2* __restrict__ child, const int* __restrict__ parent, const int* __restrict__ size,
+                  const int* __restrict__ newpos, int2* __restrict__ range)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    const int first = ploc_first_pos(i, parent[i], child, parent, size);
+    range[i] = make_int2(first, first + size[i] - 1);
+}
+
+// after every walk is done: leaf references switch to the depth-first numbering
+__global__ void __launch_bounds__(256)
+k_ploc_relabel(int n, int2* __restrict__ child, const int* __restrict__ newpos)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    int2 ch = child[i];
+    if (ch.x < 0) ch.x = ~newpos[~ch.x];
+    if (ch.y < 0) ch.y = ~newpos[~ch.y];
+    child[i] = ch;
+}
+
 static inline unsigned int grid_for(size_t n, int block) { return (unsigned int)((n + block - 1) / block); }
+
+// PLOC rounds on the Morton-sorted primitives, then the depth-first renumbering.
+// Leaves child / parent / leaf_parent / range and the permutation in the state
+// k_hierarchy leaves them in (root = node 0, leaf references = record positions).
+static int ploc_topology(crt_ctx* c, const float* tri_in, const float* sph_in, uint32_t n_tri, uint32_t n)
+{
+    cudaStream_t st = c->stream;
+    CRT_CUDA(c->ploc_box[0].reserve((size_t)n * 32));
+    CRT_CUDA(c->ploc_box[1].reserve((size_t)n * 32));
+    CRT_CUDA(c->ploc_nn.reserve((size_t)n * 4));
+    CRT_CUDA(c->ploc_tmp.reserve((size_t)n * 4));
+    const unsigned int nb_max = grid_for(n, PLOC_B);
+    CRT_CUDA(c->ploc_blk.reserve((size_t)(nb_max + 1) * sizeof(int2)));
+    int2* blk = c->ploc_blk.as<int2>();
+    int2* d_total = blk + nb_max;
+    float4* lo[2] = {c->ploc_box[0].as<float4>(), c->ploc_box[1].as<float4>()};
+    float4* hi[2] = {lo[0] + n, lo[1] + n};
+    int* size = c->flags.as<int>();                         // free until k_fit: primitives below each inner node
+    k_ploc_init<<<grid_for(n, 256), 256, 0, st>>>(tri_in, sph_in, n_tri, n, c->vals[c->perm_buf].as<uint32_t>(), lo[0], hi[0]);
+    int nc = (int)n, created = 0, cur = 0;
+    while (nc > 1) {
+        const unsigned int nb = grid_for((size_t)nc, PLOC_B);
+        k_ploc_nn<<<nb, PLOC_B, 0, st>>>(nc, c->ploc_radius, lo[cur], hi[cur], c->ploc_nn.as<int>());
+        k_ploc_count<<<nb, PLOC_B, 0, st>>>(nc, c->ploc_nn.as<int>(), blk);
+        k_ploc_scan<<<1, 1024, 0, st>>>((int)nb, blk, d_total);
+        k_ploc_merge<<<nb, PLOC_B, 0, st>>>(nc, c->ploc_nn.as<int>(), lo[cur], hi[cur], lo[cur ^ 1], hi[cur ^ 1], blk,
+                                            (int)n - 2 - created, c->child.as<int2>(), c->parent.as<int>(),
+                                            c->leaf_parent.as<int>(), size);
+        int2 total = make_int2(0, 0);
+        CRT_CUDA(cudaMemcpyAsync(&total, d_total, sizeof(int2), cudaMemcpyDeviceToHost, st));
+        CRT_CUDA(cudaStreamSynchronize(st));
+        if (total.y <= 0 || total.x != nc - total.y) { set_error("PLOC build: round made no progress (%d clusters, %d merges)", nc, total.y); return CRT_ERR_CUDA; }
+        created += total.y;
+        nc = total.x;
+        cur ^= 1;
+    }
+    const int root_parent = -1;
+    CRT_CUDA(cudaMemcpyAsync(c->parent.p, &root_parent, sizeof(int), cudaMemcpyHostToDevice, st));
+    const int other = c->perm_buf ^ 1;
+    k_ploc_leaf_pos<<<grid_for(n, 256), 256, 0, st>>>((int)n, c->child.as<int2>(), c->parent.as<int>(), c->leaf_parent.as<int>(), size,
+                                                       c->vals[c->perm_buf].as<uint32_t>(), c->ploc_nn.as<int>(),
+                                                       c->vals[other].as<uint32_t>(), c->ploc_tmp.as<int>());
+    k_ploc_node_range<<<grid_for(n - 1, 256), 256, 0, st>>>((int)n, c->child.as<int2>(), c->parent.as<int>(), size,
+                                                             c->ploc_nn.as<int>(), c->range.as<int2>());
+    k_ploc_relabel<<<grid_for(n - 1, 256), 256, 0, st>>>((int)n, c->child.as<int2>(), c->ploc_nn.as<int>());
+    CRT_CUDA(cudaMemcpyAsync(c->leaf_parent.p, c->ploc_tmp.p, (size_t)n * 4, cudaMemcpyDeviceToDevice, st));
+    c->perm_buf = other;
+    return CRT_OK;
+}
 
 int lbvh_build(crt_ctx* c, bool refit_only)
 {
@@ -389,10 +674,14 @@ int lbvh_build(crt_ctx* c, bool refit_only)
         uint64_t* keys[2] = {c->keys[0].as<uint64_t>(), c->keys[1].as<uint64_t>()};
         uint32_t* vals[2] = {c->vals[0].as<uint32_t>(), c->vals[1].as<uint32_t>()};
         c->perm_buf = radix_sort_pairs(st, keys, vals, un, 0, 64, c->hist.as<uint32_t>());
-        if (n > 1)
+        if (n > 1 && c->builder == CRT_BUILDER_LBVH)
             k_hierarchy<<<grid_for(n - 1, 256), 256, 0, st>>>(keys[c->perm_buf], (int)n, c->child.as<int2>(),
                                                               c->range.as<int2>(), c->parent.as<int>(),
                                                               c->leaf_parent.as<int>());
+        if (n > 1 && c->builder == CRT_BUILDER_PLOC) {
+            const int r = ploc_topology(c, tri_in, sph_in, n_tri, un);
+            if (r != CRT_OK) return r;
+        }
     }
     if (n > 1) CRT_CUDA(cudaMemsetAsync(c->flags.p, 0, (n - 1) * 4, st));
     k_fit<<<grid_for(n, 256), 256, 0, st>>>(tri_in, c->tri_mat.as<uint32_t>(), c->tri_id.as<uint32_t>(), sph_in,

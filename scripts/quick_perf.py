@@ -32,6 +32,8 @@ def main():
     ctx.set_option(crt.OPT_LEAF_MAX, leaf_max)
     ctx.set_option(crt.OPT_REFILL, refill)
     ctx.set_option(crt.OPT_LEAF_THRESH, lthr)
+    if os.environ.get("CRT_BUILDER"):
+        ctx.set_option(crt.OPT_BUILDER, int(os.environ["CRT_BUILDER"]))
     if os.environ.get("CRT_LANES"):
         ctx.set_option(crt.OPT_LANES, int(os.environ["CRT_LANES"]))
     t0 = time.time()
