@@ -215,6 +215,7 @@ def run_ours(args):
     nx, ny, spp, depth = sc["nx"], sc["ny"], sc["spp"], sc["max_depth"]
     cam = crt.camera_for(sc)
     ctx = crt.Context(local)
+    ctx.set_option(crt.OPT_LANES, args.lanes)
     ctx.set_scene(sc)
     ctx.build()
     build_ms = ctx.counters()["build_ms"]
@@ -297,7 +298,7 @@ def run_ours(args):
         step(100 + i)
     ctx.sync()
     alone_ms = ctx.counters()["trace_queue_ms"]
-    ctx.set_option(crt.OPT_LANES, 4)
+    ctx.set_option(crt.OPT_LANES, args.lanes)
     stats = torch.tensor([ms, float(c["rays"]), float(c["paths"]), alone_ms, float(launches)], dtype=torch.float64, device=dev)
     if world > 1:
         mx = stats.clone()
@@ -407,6 +408,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--lanes", type=int, default=4, help="CRT_OPT_LANES of the timed region (1 for profiling: one slice, launches in bounce order)")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="N > 1: weak = every rank renders the full 16-spp frame's work on its own sample range "
                          "(default); strong = the 16-spp frame is split by tiles")

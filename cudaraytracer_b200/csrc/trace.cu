@@ -76,6 +76,31 @@ k_trace_lbvh(AccelView A, const crt_ray* __restrict__ rays, uint32_t n, uint32_t
     if (COUNT) flush_counters(counters, cnt, 0u);
 }
 
+template <bool COUNT, bool HAS_SPH>
+__global__ void __launch_bounds__(TP_BLOCK, CRT_TRACE_MIN_BLOCKS)
+k_trace_lbvh_packet(AccelView A, const crt_ray* __restrict__ rays, uint32_t n, uint32_t* __restrict__ work_ctr, float t_min,
+                    float t_max, crt_hit* __restrict__ hits, unsigned long long* __restrict__ counters)
+{
+    TraceCounters cnt = {0u, 0u, 0u, 0u, 0u, 0u, 0u};
+    RaySrc src = {rays};
+    HitSink sink = {hits};
+    traverse_packets<COUNT, HAS_SPH>(A, n, work_ctr, t_min, t_max, src, sink, nullptr, cnt);
+    if (COUNT) {   // tests per ray, fetches per packet (kept by lane 0)
+        const uint32_t nodes = __reduce_add_sync(0xffffffffu, cnt.nodes), tris = __reduce_add_sync(0xffffffffu, cnt.tris);
+        const uint32_t sph = __reduce_add_sync(0xffffffffu, cnt.spheres);
+        const uint32_t nf = __reduce_add_sync(0xffffffffu, cnt.node_f), tf = __reduce_add_sync(0xffffffffu, cnt.tri_f);
+        const uint32_t sf = __reduce_add_sync(0xffffffffu, cnt.sph_f);
+        if ((threadIdx.x & 31u) == 0u) {
+            atomicAdd(counters + CNT_NODES, (unsigned long long)nodes);
+            atomicAdd(counters + CNT_TRIS, (unsigned long long)tris);
+            atomicAdd(counters + CNT_SPHERES, (unsigned long long)sph);
+            atomicAdd(counters + CNT_NODE_F, (unsigned long long)nf);
+            atomicAdd(counters + CNT_TRI_F, (unsigned long long)tf);
+            atomicAdd(counters + CNT_SPH_F, (unsigned long long)sf);
+        }
+    }
+}
+
 constexpr int BRUTE_TILE = 64;
 
 template <bool COUNT>
@@ -153,7 +178,7 @@ int launch_trace(crt_ctx* c, const crt_ray* d_rays, size_t n, float t_min, float
             k_trace_brute<false><<<grid, TRACE_BLOCK, 0, st>>>(c->tri_in.as<float>(), c->tri_id.as<uint32_t>(), (uint32_t)c->n_tri,
                                                                c->sph_in.as<float>(), c->sph_id.as<uint32_t>(), (uint32_t)c->n_sph,
                                                                d_rays, n, t_min, t_max, d_hits, counters);
-    } else if (accel == CRT_ACCEL_LBVH) {
+    } else if (accel == CRT_ACCEL_LBVH || accel == CRT_ACCEL_LBVH_PACKET) {
         if (!c->accel_valid) { set_error("crt_trace: call crt_accel_build first"); return CRT_ERR_STATE; }
         if (n >= (1ull << 32) - TP_CHUNK * 4096ull) { set_error("crt_trace: at most 2^32 - 2^20 rays per call"); return CRT_ERR_INVALID; }
         const AccelView A = accel_view(c);
@@ -169,7 +194,15 @@ int launch_trace(crt_ctx* c, const crt_ray* d_rays, size_t n, float t_min, float
         const bool sph = c->n_sph > 0;
         uint32_t* wc = c->work_ctr.as<uint32_t>();
         const uint32_t un = (uint32_t)n;
-        if (c->count_work) {
+        if (accel == CRT_ACCEL_LBVH_PACKET) {
+            if (c->count_work) {
+                if (sph) k_trace_lbvh_packet<true, true><<<grid, TP_BLOCK, 0, st>>>(A, d_rays, un, wc, t_min, t_max, d_hits, counters);
+                else k_trace_lbvh_packet<true, false><<<grid, TP_BLOCK, 0, st>>>(A, d_rays, un, wc, t_min, t_max, d_hits, counters);
+            } else {
+                if (sph) k_trace_lbvh_packet<false, true><<<grid, TP_BLOCK, 0, st>>>(A, d_rays, un, wc, t_min, t_max, d_hits, counters);
+                else k_trace_lbvh_packet<false, false><<<grid, TP_BLOCK, 0, st>>>(A, d_rays, un, wc, t_min, t_max, d_hits, counters);
+            }
+        } else if (c->count_work) {
             if (sph) k_trace_lbvh<true, true><<<grid, TP_BLOCK, 0, st>>>(A, d_rays, un, wc, t_min, t_max, d_hits, counters, (uint32_t)c->refill, (uint32_t)c->leaf_thresh);
             else k_trace_lbvh<true, false><<<grid, TP_BLOCK, 0, st>>>(A, d_rays, un, wc, t_min, t_max, d_hits, counters, (uint32_t)c->refill, (uint32_t)c->leaf_thresh);
         } else {

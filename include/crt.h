@@ -88,7 +88,9 @@ typedef enum {
 
 typedef enum {
     CRT_ACCEL_LBVH = 0,     /* Morton LBVH traversal (replaces hitable/bvh.h:160-190) */
-    CRT_ACCEL_BRUTE = 1     /* linear scan over all primitives (hitable/hitable_list.h:76-91) */
+    CRT_ACCEL_BRUTE = 1,    /* linear scan over all primitives (hitable/hitable_list.h:76-91) */
+    CRT_ACCEL_LBVH_PACKET = 2 /* LBVH, every 32 consecutive rays walk the tree together: for batches whose neighbours are
+                             * nearly parallel (camera rays in pixel order); same hits as CRT_ACCEL_LBVH for any batch */
 } crt_accel_kind;
 
 typedef enum {

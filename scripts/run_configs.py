@@ -37,10 +37,18 @@ def render_row(name, sc, mode=crt.SHADE_PATH, reps=3):
     c = ctx.counters()
     t = float(np.median(ms))
     rays = c["rays"] / reps
+    lanes = int(c["lanes"])
+    # the closest-hit launches timed alone (one slice in flight), as bench.py does for the roofline
+    ctx.set_option(crt.OPT_LANES, 1)
+    ctx.render_accum_device(cam, nx, ny, 0, spp, depth, mode, 2, 0, 1, accum.data_ptr())
+    ctx.reset_counters()
+    for i in range(reps):
+        ctx.render_accum_device(cam, nx, ny, 0, spp, depth, mode, 3 + i, 0, 1, accum.data_ptr())
+    c = ctx.counters()
     row = dict(config=name, prims=len(sc["tri"]) + len(sc["sph"]), nx=nx, ny=ny, spp=spp, ms_per_frame=t,
                mrays_s=rays / t / 1e3, mpaths_s=nx * ny * spp / t / 1e3, rays_per_path=rays / (nx * ny * spp),
                nodes_per_ray=w["nodes_visited"] / max(1, w["rays"]), tris_per_ray=w["tris_tested"] / max(1, w["rays"]),
-               spheres_per_ray=w["spheres_tested"] / max(1, w["rays"]), build_ms=build_ms,
+               spheres_per_ray=w["spheres_tested"] / max(1, w["rays"]), build_ms=build_ms, lanes=lanes,
                trace_ms=c["trace_queue_ms"] / reps,
                alg_gbs=(128 * w["node_fetches"] + 48 * w["tri_fetches"] + 16 * w["sphere_fetches"] + 48 * w["rays"]) / (c["trace_queue_ms"] / reps) / 1e6)
     ctx.close()
@@ -61,24 +69,26 @@ def trace_rows(n_tri, reps=5):
     cam = crt.camera_for(sc)
     st = torch.cuda.ExternalStream(ctx.stream())
     rows = []
-    for kind, rays in (("coherent", scenes.primary_rays(cam, 1920, 1080)), ("incoherent", scenes.c5_incoherent_rays(1 << 21))):
+    prim = scenes.primary_rays(cam, 1920, 1080)
+    for kind, rays, accel in (("coherent", prim, crt.ACCEL_LBVH), ("coherent, packets", prim, crt.ACCEL_LBVH_PACKET),
+                              ("incoherent", scenes.c5_incoherent_rays(1 << 21), crt.ACCEL_LBVH)):
         # the launch is replicated 8x so that a persistent grid of 1184 blocks has work beyond its ramp-up
         rays = np.ascontiguousarray(np.tile(rays, (8, 1)))
         d_rays = torch.from_numpy(rays).cuda()
         d_hits = torch.empty(len(rays), 4, dtype=torch.float32, device="cuda")
         ctx.set_option(crt.OPT_COUNTERS, 1)
         ctx.reset_counters()
-        ctx.trace_device(d_rays.data_ptr(), len(rays), d_hits.data_ptr())
+        ctx.trace_device(d_rays.data_ptr(), len(rays), d_hits.data_ptr(), accel=accel)
         ctx.sync()
         w = ctx.counters()
         ctx.set_option(crt.OPT_COUNTERS, 0)
         for _ in range(2):
-            ctx.trace_device(d_rays.data_ptr(), len(rays), d_hits.data_ptr())
+            ctx.trace_device(d_rays.data_ptr(), len(rays), d_hits.data_ptr(), accel=accel)
         ctx.sync()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(st)
         for _ in range(reps):
-            ctx.trace_device(d_rays.data_ptr(), len(rays), d_hits.data_ptr())
+            ctx.trace_device(d_rays.data_ptr(), len(rays), d_hits.data_ptr(), accel=accel)
         e1.record(st)
         ctx.sync()
         ms = e0.elapsed_time(e1) / reps
@@ -86,7 +96,7 @@ def trace_rows(n_tri, reps=5):
         rows.append(dict(config="C5 %s" % kind, prims=n_tri, rays=n, ms=ms, mrays_s=n / ms / 1e3, build_ms=build_ms,
                          hit_rate=float((d_hits[:, 1].view(torch.int32) != -1).float().mean()),
                          nodes_per_ray=w["nodes_visited"] / n, tris_per_ray=w["tris_tested"] / n, scene_gen_s=gen,
-                         alg_gbs=(128 * w["nodes_visited"] + 48 * w["tris_tested"] + 48 * n) / ms / 1e6))
+                         alg_gbs=(128 * w["node_fetches"] + 48 * w["tri_fetches"] + 48 * n) / ms / 1e6))
         del d_rays, d_hits
     ctx.close()
     torch.cuda.empty_cache()
