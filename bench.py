@@ -130,6 +130,20 @@ def build_ref_scene(lib, sc):
     return s.finalize()
 
 
+def use_all_host_threads():
+    """torchrun exports OMP_NUM_THREADS=1 to its workers; the CPU reference is meant to run on every host core this
+    process may use, so the OpenMP runtime it shares with this process is told so explicitly."""
+    import ctypes
+    try:
+        n = len(os.sched_getaffinity(0))
+    except AttributeError:
+        n = os.cpu_count() or 1
+    try:
+        ctypes.CDLL("libgomp.so.1").omp_set_num_threads(int(n))
+    except OSError:
+        pass
+
+
 def cpu_reference_setup(sc):
     """The reference's CPU implementation of the path: oracle/_ref (unmodified
     headers) when the prebuilt library is there, else the C restatement."""
@@ -138,6 +152,7 @@ def cpu_reference_setup(sc):
     if not oracle.available(kind):
         oracle.build(ref=False, port=True)
     lib = oracle.load(kind)
+    use_all_host_threads()
     return lib, build_ref_scene(lib, sc), ("reference" if kind == "ref" else "port")
 
 

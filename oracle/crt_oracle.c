@@ -567,10 +567,13 @@ double oracle_render(void* h, const float* cam22, int nx, int ny, int ns, int ma
     if (y_step < 1) y_step = 1;
     uint64_t total_rays = 0;
     double t0 = now_s();
-#pragma omp parallel for schedule(dynamic, 1) reduction(+ : total_rays)
-    for (int y = y0; y < y1; y += y_step) {
+    /* one parallel loop over the pixels of the selected rows (a bounded sample may have fewer rows than cores) */
+    const long long n_rows = y1 > y0 ? (y1 - y0 + y_step - 1) / y_step : 0;
+#pragma omp parallel for schedule(dynamic, 4) reduction(+ : total_rays)
+    for (long long q = 0; q < n_rows * nx; q++) {
         uint64_t rays = 0;
-        for (int x = 0; x < nx; x++) {
+        {
+            const int y = y0 + (int)(q / nx) * y_step, x = (int)(q % nx);
             int pixel_index = y * nx + x;
             v3 col = V(0, 0, 0);
             for (int i = 0; i < ns; i++) {
