@@ -42,7 +42,10 @@
 namespace crt {
 
 #define CRT_STACK_SMEM 32     // levels kept in shared memory
-#define CRT_STACK_LOCAL 72    // spill levels (63 Morton bits + 32 index bits bound the depth)
+#define CRT_STACK_LOCAL 256   // spill levels. A descent pushes <= 3 references per inner node, so a tree of depth D needs
+                              // <= 3 (D - 1) entries; the radix tree has D <= 96 (63 Morton bits + 32 index bits + leaf),
+                              // and lbvh_build keeps any other topology within CRT_STACK_ENTRIES
+#define CRT_STACK_ENTRIES (CRT_STACK_SMEM + CRT_STACK_LOCAL)
 #define CRT_NODE_DONE ((int)0x80000000)
 
 constexpr int TP_BLOCK = 128;    // threads per block of every traversal kernel
@@ -300,16 +303,14 @@ __device__ __forceinline__ void traverse_persistent(const AccelView& A, const ui
 // uniform, so each load is one L1 wavefront for the whole warp.
 // Visiting a node another lane needed never changes a lane's result: the
 // primitive tests and the tie-break are the ones of traverse_persistent.
-// s_wstack: CRT_PACKET_STACK ints per warp.
-#define CRT_PACKET_STACK 160   // 3 pushes per wide level, <= 48 wide levels (95 binary levels)
+#define CRT_PACKET_STACK CRT_STACK_ENTRIES   // same bound as the per-ray stack
 
 template <bool COUNT, bool HAS_SPH, class Src, class Sink>
 __device__ __forceinline__ void traverse_packets(const AccelView& A, const uint32_t n, uint32_t* work_ctr,
                                                  const float t_min, const float t_max, const Src& src,
-                                                 const Sink& sink, int* s_wstack, TraceCounters& cnt)
+                                                 const Sink& sink, TraceCounters& cnt)
 {
     const uint32_t lane = threadIdx.x & 31u;
-    (void)s_wstack;
     int wstack[CRT_PACKET_STACK];   // every lane keeps the same (warp-uniform) stack; slot X of 32 lanes is one 128-byte line of local memory
     constexpr uint32_t FULL = 0xffffffffu;
     // packets per grab

@@ -19,6 +19,7 @@
 //                       node always covers a contiguous range of sorted primitives)
 // Refit = steps 5 and 6 on the existing topology.
 #include "crt_internal.h"
+#include "crt_traverse.cuh"
 
 namespace crt {
 
@@ -706,6 +707,14 @@ int lbvh_build(crt_ctx* c, bool refit_only)
         CRT_CUDA(cudaMemcpyAsync(&depth, c->depth_out.p, sizeof(int), cudaMemcpyDeviceToHost, st));
         CRT_CUDA(cudaStreamSynchronize(st));
         c->tree_depth = n > 1 ? depth : 1;
+        // the traversal stacks hold CRT_STACK_ENTRIES references (crt_traverse.cuh); a clustered tree is not bounded
+        // by the key length like the radix tree, so a pathologically deep one is replaced by the radix tree
+        if (c->builder == CRT_BUILDER_PLOC && 3 * (c->tree_depth - 1) > CRT_STACK_ENTRIES) {
+            c->builder = CRT_BUILDER_LBVH;
+            const int r = lbvh_build(c, false);
+            c->builder = CRT_BUILDER_PLOC;
+            return r;
+        }
     }
     CRT_CUDA(cudaEventSynchronize(c->ev1));
     CRT_CUDA(cudaGetLastError());

@@ -223,11 +223,10 @@ __global__ void __launch_bounds__(TP_BLOCK, CRT_TRACE_MIN_BLOCKS)
 k_trace_packet(AccelView A, const float4* __restrict__ q, uint32_t cap, const uint32_t* __restrict__ n_ptr,
                uint32_t* __restrict__ work_ctr, float4* __restrict__ hits, unsigned long long* __restrict__ counters)
 {
-    __shared__ int s_wstack[(TP_BLOCK / 32) * CRT_PACKET_STACK];
     TraceCounters cnt = {0u, 0u, 0u, 0u, 0u, 0u, 0u};
     QueueSrc src = {q, cap};
     QueueSink sink = {hits};
-    traverse_packets<COUNT, HAS_SPH>(A, *n_ptr, work_ctr, 0.001f, FLT_MAX, src, sink, s_wstack, cnt);   // render.h:53
+    traverse_packets<COUNT, HAS_SPH>(A, *n_ptr, work_ctr, 0.001f, FLT_MAX, src, sink, cnt);   // render.h:53
     if (COUNT) {
         const uint32_t nodes = __reduce_add_sync(0xffffffffu, cnt.nodes);
         const uint32_t tris = __reduce_add_sync(0xffffffffu, cnt.tris);

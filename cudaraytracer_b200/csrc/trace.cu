@@ -84,7 +84,7 @@ k_trace_lbvh_packet(AccelView A, const crt_ray* __restrict__ rays, uint32_t n, u
     TraceCounters cnt = {0u, 0u, 0u, 0u, 0u, 0u, 0u};
     RaySrc src = {rays};
     HitSink sink = {hits};
-    traverse_packets<COUNT, HAS_SPH>(A, n, work_ctr, t_min, t_max, src, sink, nullptr, cnt);
+    traverse_packets<COUNT, HAS_SPH>(A, n, work_ctr, t_min, t_max, src, sink, cnt);
     if (COUNT) {   // tests per ray, fetches per packet (kept by lane 0)
         const uint32_t nodes = __reduce_add_sync(0xffffffffu, cnt.nodes), tris = __reduce_add_sync(0xffffffffu, cnt.tris);
         const uint32_t sph = __reduce_add_sync(0xffffffffu, cnt.spheres);

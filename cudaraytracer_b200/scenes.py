@@ -340,3 +340,44 @@ def scene_bounds(scene):
         lo = np.minimum(lo, (s[:, :3] - np.abs(s[:, 3:4])).min(0))
         hi = np.maximum(hi, (s[:, :3] + np.abs(s[:, 3:4])).max(0))
     return lo, hi
+
+
+def light_panels(nx=160, ny=120, spp=8):
+    """Triangles only, for the DiffuseLight path (material/material.h:146-159, core/render.h:56-61): a Lambertian
+    wall and floor, a light panel in front of the wall (seen directly), a second one behind it, a metal and a glass
+    block, through a lens with a finite aperture. A reference triangle answers only rays that travel ALONG its
+    stored normal and scatters along that normal too, i.e. onwards through the surface: the paths that
+    reach the second panel are the ones scattered by the wall."""
+    def quad(a, b, c, d, n):
+        a, b, c, d, n = (np.asarray(v, np.float32) for v in (a, b, c, d, n))
+        return [np.concatenate([a, b, c, n]), np.concatenate([a, c, d, n])]
+
+    def block(lo, hi):
+        (x0, y0, z0), (x1, y1, z1) = lo, hi
+        f = []
+        f += quad((x0, y0, z0), (x0, y1, z0), (x1, y1, z0), (x1, y0, z0), (0, 0, 1))      # normals point into the block
+        f += quad((x0, y0, z1), (x1, y0, z1), (x1, y1, z1), (x0, y1, z1), (0, 0, -1))
+        f += quad((x0, y0, z0), (x0, y0, z1), (x0, y1, z1), (x0, y1, z0), (1, 0, 0))
+        f += quad((x1, y0, z0), (x1, y1, z0), (x1, y1, z1), (x1, y0, z1), (-1, 0, 0))
+        f += quad((x0, y0, z0), (x1, y0, z0), (x1, y0, z1), (x0, y0, z1), (0, 1, 0))
+        f += quad((x0, y1, z0), (x0, y1, z1), (x1, y1, z1), (x1, y1, z0), (0, -1, 0))
+        return f
+
+    mats = [(LAMBERTIAN, (0.73, 0.73, 0.73), 0.0), (LAMBERTIAN, (0.65, 0.05, 0.05), 0.0),
+            (DIFFUSE_LIGHT, (4.0, 3.5, 3.0), 0.0), (METAL, (0.8, 0.85, 0.88), 0.05), (DIELECTRIC, (1.0, 1.0, 1.0), 1.5)]
+    tris, tm = [], []
+
+    def add(faces, m):
+        tris.extend(faces)
+        tm.extend([m] * len(faces))
+
+    add(quad((-12, 0, 0), (-12, 20, 0), (12, 20, 0), (12, 0, 0), (0, 0, -1)), 0)           # wall, camera side is +z
+    add(quad((-12, 0, 0), (12, 0, 0), (12, 0, 14), (-12, 0, 14), (0, -1, 0)), 1)           # floor
+    add(quad((5, 13, 2), (5, 17, 2), (9, 17, 2), (9, 13, 2), (0, 0, -1)), 2)               # panel in front of the wall
+    add(quad((-6, 4, -5), (-6, 16, -5), (6, 16, -5), (6, 4, -5), (0, 0, -1)), 2)           # panel behind the wall
+    add(block((-7, 0, 3), (-3, 7, 7)), 3)
+    add(block((1, 0, 4), (5, 4, 8)), 4)
+    sph, sph_mat = _empty_sph()
+    return dict(name="light_panels", tri=np.ascontiguousarray(np.stack(tris), np.float32), tri_mat=np.asarray(tm, np.uint32),
+                sph=sph, sph_mat=sph_mat, mats=mats, camera=camera_dict((0, 9, 22), (0, 8, 0), 50, aperture=0.3, focus_dist=18.0),
+                nx=nx, ny=ny, spp=spp, max_depth=8)
