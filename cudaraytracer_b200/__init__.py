@@ -18,6 +18,7 @@ SHADE_PATH, SHADE_LAMBERT, SHADE_NORMAL = 0, 1, 2
 ACCEL_LBVH, ACCEL_BRUTE, ACCEL_LBVH_PACKET = 0, 1, 2
 OPT_LEAF_MAX, OPT_COUNTERS, OPT_BATCH_PATHS, OPT_REFILL, OPT_LEAF_THRESH, OPT_PACKET_PRIMARY, OPT_LANES, OPT_BUILDER = 1, 2, 3, 4, 5, 6, 7, 8
 BUILDER_LBVH, BUILDER_PLOC = 0, 1
+TEX_CONSTANT, TEX_CHECKER = 0, 1
 TILE = 32
 
 # every symbol include/crt.h declares
@@ -35,7 +36,8 @@ class CrtError(RuntimeError):
 
 
 class Material(C.Structure):
-    _fields_ = [("type", C.c_uint32), ("albedo", C.c_float * 3), ("param", C.c_float)]
+    _fields_ = [("type", C.c_uint32), ("albedo", C.c_float * 3), ("param", C.c_float),
+                ("texture", C.c_uint32), ("albedo2", C.c_float * 3)]
 
 
 class Camera(C.Structure):
@@ -181,10 +183,15 @@ class Context:
 
     def set_materials(self, mats):
         arr = (Material * max(len(mats), 1))()
-        for i, (t, alb, p) in enumerate(mats):
+        for i, m in enumerate(mats):          # (type, albedo, param) or, with a CheckerTexture, (type, even, param, odd)
+            t, alb, p = m[0], m[1], m[2]
             arr[i].type = int(t)
             arr[i].albedo[0], arr[i].albedo[1], arr[i].albedo[2] = (float(np.float32(v)) for v in alb)
             arr[i].param = float(np.float32(p))
+            arr[i].texture = TEX_CONSTANT
+            if len(m) > 3 and m[3] is not None:
+                arr[i].texture = TEX_CHECKER
+                arr[i].albedo2[0], arr[i].albedo2[1], arr[i].albedo2[2] = (float(np.float32(v)) for v in m[3])
         self._check(self.lib.crt_scene_set_materials(self._h, C.cast(arr, C.c_void_p), len(mats)))
 
     def set_triangles(self, tri, mat=None, ids=None):

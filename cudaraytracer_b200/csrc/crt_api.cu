@@ -197,14 +197,22 @@ int crt_scene_set_materials(crt_ctx* c, const crt_material* mats, size_t n)
 {
     CRT_CHECK_CTX(c);
     if (n > 0 && !mats) { set_error("crt_scene_set_materials: null table"); return CRT_ERR_INVALID; }
-    if (n > 65535) { set_error("crt_scene_set_materials: at most 65535 materials (got %zu)", n); return CRT_ERR_INVALID; }
+    if (n > 32768) { set_error("crt_scene_set_materials: at most 32768 materials (got %zu)", n); return CRT_ERR_INVALID; }
     std::vector<DMat> d(n);
     for (size_t i = 0; i < n; i++) {
         if (mats[i].type > CRT_MAT_DIFFUSE_LIGHT) { set_error("crt_scene_set_materials: material %zu has unknown type %u", i, mats[i].type); return CRT_ERR_INVALID; }
         d[i].r = mats[i].albedo[0]; d[i].g = mats[i].albedo[1]; d[i].b = mats[i].albedo[2];
         d[i].param = mats[i].param;
         d[i].type = mats[i].type;
-        d[i].pad0 = d[i].pad1 = d[i].pad2 = 0;
+        d[i].r2 = d[i].g2 = d[i].b2 = 0.0f;
+        if (mats[i].texture == CRT_TEX_CHECKER) {
+            if (mats[i].type != CRT_MAT_LAMBERTIAN && mats[i].type != CRT_MAT_DIFFUSE_LIGHT) { set_error("crt_scene_set_materials: material %zu: only Lambertian and DiffuseLight take a texture (material.h:59,148)", i); return CRT_ERR_INVALID; }
+            d[i].type = CRT_DMAT_CHECKER + mats[i].type;
+            d[i].r2 = mats[i].albedo2[0]; d[i].g2 = mats[i].albedo2[1]; d[i].b2 = mats[i].albedo2[2];
+        } else if (mats[i].texture != CRT_TEX_CONSTANT) {
+            set_error("crt_scene_set_materials: material %zu has unknown texture %u", i, mats[i].texture);
+            return CRT_ERR_INVALID;
+        }
     }
     int r = upload(c->mats, d.data(), n * sizeof(DMat), c->stream);
     if (r != CRT_OK) return r;

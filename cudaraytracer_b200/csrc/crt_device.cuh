@@ -29,7 +29,10 @@ namespace crt {
 #define CRT_SLOT_EMPTY ((int)0x80000000)
 #define CRT_KIND_SPHERE 0x80000000u
 
-struct DMat { float r, g, b, param; uint32_t type; uint32_t pad0, pad1, pad2; };  // 32 B
+// type: crt_material_type, or CRT_DMAT_CHECKER + it for a Lambertian / DiffuseLight whose texture is a
+// CheckerTexture(even = r g b, odd = r2 g2 b2)
+#define CRT_DMAT_CHECKER 4u
+struct DMat { float r, g, b, param; uint32_t type; float r2, g2, b2; };  // 32 B
 
 struct AccelView {
     const float4* nodes;
@@ -165,12 +168,22 @@ CRT_HD bool refract(v3 v, v3 n, float ni_over_nt, v3& refracted)
 // Material::scatter, material.h:57-155. in_d: direction of the incoming ray as
 // shade() holds it (not normalised). Returns the bool of scatter(); att and
 // out_d are written as the reference writes them.
-CRT_HD bool scatter(const DMat& m, v3 in_d, v3 p, v3 n, Rng& r, v3& att, v3& out_d)
+// CheckerTexture::value, material/texture.h:30-38: which of the two colours the hit point selects. Only the sign
+// of the product is used, so the last bits of sinf do not matter.
+CRT_HD bool checker_odd(const DMat& m, v3 p)
 {
-    if (m.type == 0u) {                                    // Lambertian, material.h:61-71
+    if (m.type < CRT_DMAT_CHECKER) return false;
+    const float sines = sinf(x::mul(10.0f, p.x)) * sinf(x::mul(10.0f, p.y)) * sinf(x::mul(10.0f, p.z));
+    return sines < 0.0f;
+}
+CRT_HD v3 texture_value(const DMat& m, bool odd) { return odd ? V(m.r2, m.g2, m.b2) : V(m.r, m.g, m.b); }
+
+CRT_HD bool scatter(const DMat& m, v3 in_d, v3 p, v3 n, Rng& r, v3& att, v3& out_d, bool odd = false)
+{
+    if (m.type == 0u || m.type == CRT_DMAT_CHECKER) {     // Lambertian, material.h:61-71
         v3 target = vadd(vadd(p, n), random_in_unit_sphere(r));
         out_d = vsub(target, p);
-        att = V(m.r, m.g, m.b);
+        att = texture_value(m, odd);
         return true;
     }
     if (m.type == 1u) {                                    // Metal, material.h:83-92 (fuzz clamp :80)
@@ -208,9 +221,9 @@ CRT_HD bool scatter(const DMat& m, v3 in_d, v3 p, v3 n, Rng& r, v3& att, v3& out
     return false;
 }
 
-CRT_HD v3 emitted(const DMat& m)                           // material.h:49-53,156-158
+CRT_HD v3 emitted(const DMat& m, bool odd = false)         // material.h:49-53,156-158
 {
-    return m.type == 3u ? V(m.r, m.g, m.b) : V(0.0f, 0.0f, 0.0f);
+    return (m.type == 3u || m.type == CRT_DMAT_CHECKER + 3u) ? texture_value(m, odd) : V(0.0f, 0.0f, 0.0f);
 }
 
 // core/render.h:41-46

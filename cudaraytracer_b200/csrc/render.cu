@@ -155,9 +155,9 @@ k_raygen(RenderParams P, float4* __restrict__ q, uint32_t* __restrict__ q_count)
 }
 
 // attenuation a finished bounce contributed, by material (material.h:69,90,111)
-__device__ __forceinline__ v3 bounce_attenuation(const DMat& m)
+__device__ __forceinline__ v3 bounce_attenuation(const DMat& m, bool odd)
 {
-    return m.type == 2u ? V(1.0f, 1.0f, 1.0f) : V(m.r, m.g, m.b);
+    return m.type == 2u ? V(1.0f, 1.0f, 1.0f) : texture_value(m, odd);
 }
 
 __device__ __forceinline__ DMat load_mat(const DMat* __restrict__ mats, uint32_t id)
@@ -166,7 +166,8 @@ __device__ __forceinline__ DMat load_mat(const DMat* __restrict__ mats, uint32_t
     const float4 a = __ldg(p);
     const uint4 b = __ldg(reinterpret_cast<const uint4*>(p + 1));
     DMat m;
-    m.r = a.x; m.g = a.y; m.b = a.z; m.param = a.w; m.type = b.x; m.pad0 = m.pad1 = m.pad2 = 0;
+    m.r = a.x; m.g = a.y; m.b = a.z; m.param = a.w; m.type = b.x;
+    m.r2 = __uint_as_float(b.y); m.g2 = __uint_as_float(b.z); m.b2 = __uint_as_float(b.w);
     return m;
 }
 
@@ -308,16 +309,18 @@ k_shade(RenderParams P, AccelView A, const DMat* __restrict__ mats, const float4
                 }
                 const uint32_t mat_id = inf_y & 0x7FFFFFFFu;
                 const DMat m = load_mat(mats, mat_id);
-                const v3 e = emitted(m);                                           // render.h:56
+                const bool odd = checker_odd(m, p);                                // texture.h:31
+                const v3 e = emitted(m, odd);                                      // render.h:56
                 if (P.mode == CRT_SHADE_PATH) {
                     v3 att, out_d;
                     if (COUNT && depth_left > 0) n_scatter++;
-                    if (depth_left > 0 && scatter(m, d, p, n, rng, att, out_d)) {  // render.h:57
+                    if (depth_left > 0 && scatter(m, d, p, n, rng, att, out_d, odd)) {  // render.h:57
                         next = true;
+                        const uint32_t hist = (mat_id & 0x7FFFu) | (odd ? 0x8000u : 0u);   // 15 bits of id + which checker colour
 #pragma unroll
                         for (int j = 0; j < 8; j++)
                             if (j == (bounces >> 1))
-                                ms[j] = (bounces & 1) ? ((ms[j] & 0xFFFFu) | (mat_id << 16)) : (mat_id & 0xFFFFu);
+                                ms[j] = (bounces & 1) ? ((ms[j] & 0xFFFFu) | (hist << 16)) : hist;
                         w0 = make_float4(p.x, p.y, p.z, out_d.x);
                         w1 = make_float4(out_d.y, out_d.z, __uint_as_float(path_id),
                                          __uint_as_float((rng.ctr & 0xFFFFFFu) | ((uint32_t)(depth_left - 1) << 24)));
@@ -327,7 +330,7 @@ k_shade(RenderParams P, AccelView A, const DMat* __restrict__ mats, const float4
                 } else if (P.mode == CRT_SHADE_LAMBERT) {                          // render.h:70-87
                     v3 att, out_d;
                     if (COUNT) n_scatter++;
-                    scatter(m, d, p, n, rng, att, out_d);
+                    scatter(m, d, p, n, rng, att, out_d, odd);
                     float c = vdot(d, n);
                     if (c < 0.0f) c = 0.0f;
                     L = vadd(vscale(0.2f, vmul(vscale(c, att), background_sky(d))), e);
@@ -341,8 +344,9 @@ k_shade(RenderParams P, AccelView A, const DMat* __restrict__ mats, const float4
                 for (int j = CRT_MAX_DEPTH - 1; j >= 0; j--) {
                     if (j < bounces) {
                         const uint32_t id = (ms[j >> 1] >> ((j & 1) * 16)) & 0xFFFFu;
-                        const DMat mj = load_mat(mats, id);
-                        L = vadd(emitted(mj), vmul(bounce_attenuation(mj), L));
+                        const DMat mj = load_mat(mats, id & 0x7FFFu);
+                        // a material that scattered is not a light (material.h:149-155): its emitted() is 0
+                        L = vadd(V(0.0f, 0.0f, 0.0f), vmul(bounce_attenuation(mj, (id & 0x8000u) != 0u), L));
                     }
                 }
                 rad[path_id] = make_float4(L.x, L.y, L.z, 0.0f);

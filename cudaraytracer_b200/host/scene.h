@@ -80,6 +80,19 @@ public:
     vec3 color;
 };
 
+class CheckerTexture : public Texture {                               // material/texture.h:25-42
+public:
+    CheckerTexture() : odd(nullptr), even(nullptr) {}
+    CheckerTexture(Texture* t0, Texture* t1) : odd(t1), even(t0) {}
+    vec3 value(float u, float v, const vec3& p) const override
+    {
+        float sines = std::sin(10 * p.x()) * std::sin(10 * p.y()) * std::sin(10 * p.z());
+        return sines < 0 ? odd->value(u, v, p) : even->value(u, v, p);
+    }
+    Texture* odd;
+    Texture* even;
+};
+
 class Material {                                                     // material/material.h:42-54
 public:
     virtual ~Material() {}
@@ -94,13 +107,27 @@ inline crt_material make_material(uint32_t type, const vec3& a, float param)
     m.type = type;
     m.albedo[0] = a[0]; m.albedo[1] = a[1]; m.albedo[2] = a[2];
     m.param = param;
+    m.texture = CRT_TEX_CONSTANT;
+    m.albedo2[0] = m.albedo2[1] = m.albedo2[2] = 0.f;
     return m;
 }
 inline vec3 constant_colour(const Texture* t, const char* who)
 {
     if (!t || !t->is_constant())
-        throw std::invalid_argument(std::string(who) + ": only ConstantTexture is supported on the render path (material/texture.h:12-22)");
+        throw std::invalid_argument(std::string(who) + ": only ConstantTexture, or a CheckerTexture of two of them, is supported on the render path (material/texture.h:12-42)");
     return t->value(0.f, 0.f, vec3(0.f));
+}
+// The record of a material whose texture is a ConstantTexture or a CheckerTexture of two ConstantTextures.
+inline crt_material textured_material(uint32_t type, const Texture* t, const char* who)
+{
+    if (const CheckerTexture* c = dynamic_cast<const CheckerTexture*>(t)) {
+        crt_material m = make_material(type, constant_colour(c->even, who), 0.f);
+        const vec3 o = constant_colour(c->odd, who);
+        m.texture = CRT_TEX_CHECKER;
+        m.albedo2[0] = o[0]; m.albedo2[1] = o[1]; m.albedo2[2] = o[2];
+        return m;
+    }
+    return make_material(type, constant_colour(t, who), 0.f);
 }
 }  // namespace crt_host
 
@@ -109,7 +136,7 @@ public:
     Lambertian(Texture* a) : albedo(a) {}
     crt_material describe() const override
     {
-        return crt_host::make_material(CRT_MAT_LAMBERTIAN, crt_host::constant_colour(albedo, "Lambertian"), 0.f);
+        return crt_host::textured_material(CRT_MAT_LAMBERTIAN, albedo, "Lambertian");
     }
     Texture* albedo;
 };
@@ -134,7 +161,7 @@ public:
     DiffuseLight(Texture* texture) : emit(texture) {}
     crt_material describe() const override
     {
-        return crt_host::make_material(CRT_MAT_DIFFUSE_LIGHT, crt_host::constant_colour(emit, "DiffuseLight"), 0.f);
+        return crt_host::textured_material(CRT_MAT_DIFFUSE_LIGHT, emit, "DiffuseLight");
     }
     Texture* emit;
 };

@@ -381,3 +381,23 @@ def light_panels(nx=160, ny=120, spp=8):
     return dict(name="light_panels", tri=np.ascontiguousarray(np.stack(tris), np.float32), tri_mat=np.asarray(tm, np.uint32),
                 sph=sph, sph_mat=sph_mat, mats=mats, camera=camera_dict((0, 9, 22), (0, 8, 0), 50, aperture=0.3, focus_dist=18.0),
                 nx=nx, ny=ny, spp=spp, max_depth=8)
+
+
+def checker_scene(nx=160, ny=100, spp=4):
+    """CheckerTexture (material/texture.h:25-42) under a Lambertian and under a DiffuseLight, on triangles and on
+    spheres: a checkered ground sphere in the manner of the reference's random scene, a checkered wall of triangles
+    (normals away from the camera), a checkered light, a metal and a glass sphere."""
+    mats = [(LAMBERTIAN, (0.2, 0.3, 0.1), 0.0, (0.9, 0.9, 0.9)), (LAMBERTIAN, (0.8, 0.1, 0.1), 0.0, (0.1, 0.1, 0.8)),
+            (DIFFUSE_LIGHT, (4.0, 4.0, 4.0), 0.0, (0.5, 2.0, 0.5)), (METAL, (0.7, 0.6, 0.5), 0.0), (DIELECTRIC, (1.0, 1.0, 1.0), 1.5),
+            (LAMBERTIAN, (0.4, 0.2, 0.1), 0.0)]
+    sph = np.asarray([[0, -1000, 0, 1000], [0, 1, 0, 1.0], [-4, 1, 0, 1.0], [4, 1, 0, 1.0], [0, 3.2, -1.0, 0.7]], np.float32)
+    sph_mat = np.asarray([0, 4, 5, 3, 2], np.uint32)
+
+    def quad(a, b, c, d, n):
+        a, b, c, d, n = (np.asarray(v, np.float32) for v in (a, b, c, d, n))
+        return [np.concatenate([a, b, c, n]), np.concatenate([a, c, d, n])]
+
+    tri = np.stack(quad((-8, 0, -4), (-8, 6, -4), (8, 6, -4), (8, 0, -4), (0.3, -0.1, -1.0)))
+    return dict(name="checker", tri=np.ascontiguousarray(tri, np.float32), tri_mat=np.asarray([1, 1], np.uint32), sph=sph, sph_mat=sph_mat,
+                mats=mats, camera=camera_dict((13, 2, 3), (0, 0, 0), 20, aperture=0.1, focus_dist=10.0),
+                nx=nx, ny=ny, spp=spp, max_depth=8)

@@ -56,8 +56,12 @@ typedef struct { float t; uint32_t prim_id; float u; float v; } crt_hit;
 
 /* material/material.h:57-161. param: Metal fuzz (clamped to 1 like
  * material.h:80), Dielectric ref_idx; unused otherwise. albedo: Lambertian
- * ConstantTexture colour (material/texture.h:12-22), Metal albedo,
- * DiffuseLight emission. */
+ * texture colour (material/texture.h:12-22), Metal albedo, DiffuseLight
+ * emission. texture (Lambertian and DiffuseLight only): CRT_TEX_CONSTANT uses
+ * albedo; CRT_TEX_CHECKER is CheckerTexture(even = albedo, odd = albedo2) of two
+ * ConstantTextures (material/texture.h:25-42): odd where
+ * sin(10 x) sin(10 y) sin(10 z) < 0 at the hit point. A table may hold 32768
+ * materials. */
 typedef enum {
     CRT_MAT_LAMBERTIAN = 0,
     CRT_MAT_METAL = 1,
@@ -65,7 +69,12 @@ typedef enum {
     CRT_MAT_DIFFUSE_LIGHT = 3
 } crt_material_type;
 
-typedef struct { uint32_t type; float albedo[3]; float param; } crt_material;
+typedef enum {
+    CRT_TEX_CONSTANT = 0,
+    CRT_TEX_CHECKER = 1
+} crt_texture_type;
+
+typedef struct { uint32_t type; float albedo[3]; float param; uint32_t texture; float albedo2[3]; } crt_material;
 
 /* The members of the reference Camera after its constructor ran
  * (core/camera.h:46-53), computed once on the host and passed by value so

@@ -64,8 +64,13 @@ class Scene:
         self.h = lib._fn("scene_create")(1 if d1 else 0)
         self.n_prims = 0
 
-    def add_material(self, mtype, albedo=(0, 0, 0), param=0.0):
+    def add_material(self, mtype, albedo=(0, 0, 0), param=0.0, odd=None):
+        """odd given: CheckerTexture(even = albedo, odd) under a Lambertian / DiffuseLight (material/texture.h:25-42)."""
         a = np.asarray(albedo, dtype=np.float32)
+        if odd is not None:
+            r = self.lib._fn("scene_add_checker_material")(self.h, int(mtype), a, np.asarray(odd, dtype=np.float32))
+            assert r >= 0
+            return r
         r = self.lib._fn("scene_add_material")(self.h, int(mtype), a, float(param))
         assert r >= 0
         return r
@@ -154,6 +159,8 @@ class OracleLib:
         f("scene_create").argtypes = [C.c_int]
         f("scene_add_material").restype = C.c_int
         f("scene_add_material").argtypes = [vp, C.c_uint32, _f32p, C.c_float]
+        f("scene_add_checker_material").restype = C.c_int
+        f("scene_add_checker_material").argtypes = [vp, C.c_uint32, _f32p, _f32p]
         f("scene_add_triangles").restype = None
         f("scene_add_triangles").argtypes = [vp, _f32p, vp, vp, C.c_size_t]
         f("scene_add_spheres").restype = None
@@ -190,6 +197,16 @@ class OracleLib:
 
     def scene(self, d1=True):
         return Scene(self, d1)
+
+    def checker_odd(self, points):
+        """CheckerTexture::value at n points: True where the odd texture is returned (material/texture.h:30-38)."""
+        pts = np.ascontiguousarray(points, np.float32).reshape(-1, 3)
+        out = np.zeros(len(pts), np.uint8)
+        fn = self._fn("checker_odd")
+        fn.restype = None
+        fn.argtypes = [_f32p, C.c_size_t, np.ctypeslib.ndpointer(np.uint8, flags="C_CONTIGUOUS")]
+        fn(pts, len(pts), out)
+        return out.astype(bool)
 
     def scatter(self, mtype, albedo, param, ray, p, normal, randoms):
         """One Material::scatter call with an injected (0,1] sequence.

@@ -91,7 +91,7 @@ typedef struct {
     uint32_t mat, id;
 } prim_t;
 
-typedef struct { uint32_t type; v3 albedo; float param; } mat_t;
+typedef struct { uint32_t type; v3 albedo; float param; int checker; v3 odd; } mat_t;
 
 struct oracle_scene {
     prim_t* prims; size_t n_prims, cap_prims;
@@ -241,6 +241,16 @@ static int refract(v3 v, v3 n, float ni_over_nt, v3* refracted)                 
 
 /* material.h:57-161. Returns scatter()'s bool; att/out always written the way
  * the reference writes them. */
+/* ConstantTexture::value / CheckerTexture::value, material/texture.h:17-19,30-38 */
+static v3 texture_value(const mat_t* m, v3 p)
+{
+    if (m->checker) {
+        float sines = sinf(10 * p.x) * sinf(10 * p.y) * sinf(10 * p.z);
+        if (sines < 0) return m->odd;
+    }
+    return m->albedo;
+}
+
 static int scatter(const mat_t* m, ray_t in, const hitrec_t* rec, v3* att, ray_t* out, rng_t* s)
 {
     switch (m->type) {
@@ -248,7 +258,7 @@ static int scatter(const mat_t* m, ray_t in, const hitrec_t* rec, v3* att, ray_t
         v3 target = vadd(vadd(rec->p, rec->normal), random_in_unit_sphere(s));
         out->o = rec->p;
         out->d = vsub(target, rec->p);
-        *att = m->albedo;
+        *att = texture_value(m, rec->p);                                            /* material.h:69 */
         return 1;
     }
     case 1: { /* Metal, material.h:83-92; fuzz clamped at construction (material.h:80) */
@@ -287,9 +297,9 @@ static int scatter(const mat_t* m, ray_t in, const hitrec_t* rec, v3* att, ray_t
     }
 }
 
-static v3 emitted(const mat_t* m)                                                  /* material.h:49-53,156-158 */
+static v3 emitted(const mat_t* m, v3 p)                                            /* material.h:49-53,156-158 */
 {
-    return m->type == 3 ? m->albedo : V(0, 0, 0);
+    return m->type == 3 ? texture_value(m, p) : V(0, 0, 0);
 }
 
 /* ---------------------------------------------------------------- camera */
@@ -340,7 +350,7 @@ static v3 shade_path(const struct oracle_scene* s, ray_t r, int depth, rng_t* st
         ray_t next;
         v3 att;
         const mat_t* m = &s->mats[rec.mat];
-        v3 e = emitted(m);
+        v3 e = emitted(m, rec.p);
         if (depth > 0 && scatter(m, r, &rec, &att, &next, st))
             return vadd(e, vmul(att, shade_path(s, next, depth - 1, st, rays)));
         return vadd(e, V(0.1f, 0.1f, 0.1f));
@@ -356,7 +366,7 @@ static v3 shade_lambert(const struct oracle_scene* s, ray_t r, rng_t* st, uint64
         ray_t next;
         v3 att = V(0, 0, 0);
         const mat_t* m = &s->mats[rec.mat];
-        v3 e = emitted(m);
+        v3 e = emitted(m, rec.p);
         scatter(m, r, &rec, &att, &next, st);
         float c = vdot(r.d, rec.normal);
         if (c < 0) c = 0;
@@ -419,7 +429,26 @@ int oracle_scene_add_material(void* h, uint32_t type, const float* albedo, float
     m->type = type;
     m->albedo = V(albedo[0], albedo[1], albedo[2]);
     m->param = param;
+    m->checker = 0;
+    m->odd = V(0, 0, 0);
     return (int)s->n_mats++;
+}
+
+void oracle_checker_odd(const float* p, size_t n, uint8_t* out)
+{
+    mat_t m = {0, V(0, 0, 0), 0.0f, 1, V(1, 1, 1)};
+    for (size_t i = 0; i < n; i++) out[i] = texture_value(&m, V(p[3 * i], p[3 * i + 1], p[3 * i + 2])).x > 0.5f ? 1 : 0;
+}
+
+int oracle_scene_add_checker_material(void* h, uint32_t type, const float* even, const float* odd)
+{
+    if (type != 0 && type != 3) return -1;
+    int id = oracle_scene_add_material(h, type, even, 0.0f);
+    if (id < 0) return id;
+    struct oracle_scene* s = (struct oracle_scene*)h;
+    s->mats[id].checker = 1;
+    s->mats[id].odd = V(odd[0], odd[1], odd[2]);
+    return id;
 }
 
 static prim_t* push_prims(struct oracle_scene* s, size_t n)
@@ -507,7 +536,7 @@ int oracle_scatter(uint32_t type, const float* albedo, float param, const float*
                    const float* randoms, int n_randoms, float* out, int* n_draws)
 {
     if (type > 3) return -1;
-    mat_t m = {type, V(albedo[0], albedo[1], albedo[2]), param};
+    mat_t m = {type, V(albedo[0], albedo[1], albedo[2]), param, 0, V(0, 0, 0)};
     rng_t st = {0, 0, randoms, n_randoms, 0};
     ray_t in = {V(ray[0], ray[1], ray[2]), V(ray[3], ray[4], ray[5])};
     hitrec_t rec;

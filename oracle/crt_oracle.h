@@ -13,6 +13,8 @@ int    oracle_num_threads(void);
 void*  oracle_scene_create(int d1);
 void   oracle_scene_destroy(void* scene);
 int    oracle_scene_add_material(void* scene, uint32_t type, const float* albedo, float param);
+void   oracle_checker_odd(const float* points, size_t n, uint8_t* out);
+int    oracle_scene_add_checker_material(void* scene, uint32_t type, const float* even, const float* odd);
 void   oracle_scene_add_triangles(void* scene, const float* tri, const uint32_t* mat, const uint32_t* ids, size_t n);
 void   oracle_scene_add_spheres(void* scene, const float* sph, const uint32_t* mat, const uint32_t* ids, size_t n);
 int    oracle_scene_finalize(void* scene);

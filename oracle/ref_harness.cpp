@@ -205,6 +205,26 @@ void* ref_scene_create(int d1)
     return s;
 }
 
+// CheckerTexture::value of n points x 3 floats: 1 where it returns the odd texture (material/texture.h:30-38)
+void ref_checker_odd(const float* p, size_t n, uint8_t* out)
+{
+    ConstantTexture even(vec3(0, 0, 0)), odd(vec3(1, 1, 1));
+    CheckerTexture c(&even, &odd);
+    for (size_t i = 0; i < n; i++) out[i] = c.value(0, 0, vec3(p[3 * i], p[3 * i + 1], p[3 * i + 2]))[0] > 0.5f ? 1 : 0;
+}
+
+// Lambertian / DiffuseLight over CheckerTexture(ConstantTexture(even), ConstantTexture(odd)), material/texture.h:25-42
+int ref_scene_add_checker_material(void* h, uint32_t type, const float* even, const float* odd)
+{
+    RefScene* s = (RefScene*)h;
+    Texture* t = new CheckerTexture(new ConstantTexture(vec3(even[0], even[1], even[2])),
+                                    new ConstantTexture(vec3(odd[0], odd[1], odd[2])));
+    Material* m = type == 0 ? (Material*)new Lambertian(t) : type == 3 ? (Material*)new DiffuseLight(t) : nullptr;
+    if (!m) return -1;
+    s->mats.push_back(m);
+    return int(s->mats.size()) - 1;
+}
+
 int ref_scene_add_material(void* h, uint32_t type, const float* albedo, float param)
 {
     RefScene* s = (RefScene*)h;

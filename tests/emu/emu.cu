@@ -16,7 +16,7 @@ int emu_scatter(uint32_t type, const float* albedo, float param, const float* ra
 {
     DMat m;
     m.r = albedo[0]; m.g = albedo[1]; m.b = albedo[2]; m.param = param; m.type = type;
-    m.pad0 = m.pad1 = m.pad2 = 0;
+    m.r2 = m.g2 = m.b2 = 0.0f;
     Rng r; r.key = key; r.ctr = ctr;
     v3 att, od;
     bool ok = scatter(m, V(ray[3], ray[4], ray[5]), V(recpn[0], recpn[1], recpn[2]), V(recpn[3], recpn[4], recpn[5]), r, att, od);
@@ -25,6 +25,14 @@ int emu_scatter(uint32_t type, const float* albedo, float param, const float* ra
     out[6] = od.x; out[7] = od.y; out[8] = od.z;
     *ctr_out = r.ctr;
     return ok ? 1 : 0;
+}
+
+// which colour of a CheckerTexture the points select (1 = odd), n points x 3 floats
+void emu_checker_odd(const float* p, size_t n, uint8_t* out)
+{
+    DMat m;
+    m.r = m.g = m.b = 0.0f; m.param = 0.0f; m.type = CRT_DMAT_CHECKER; m.r2 = m.g2 = m.b2 = 1.0f;
+    for (size_t i = 0; i < n; i++) out[i] = checker_odd(m, V(p[3 * i], p[3 * i + 1], p[3 * i + 2])) ? 1 : 0;
 }
 
 uint32_t emu_get_ray(const float* c, float s, float t, uint64_t seed, uint32_t pixel, uint32_t sample, uint32_t ctr,

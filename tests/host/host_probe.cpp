@@ -73,6 +73,10 @@ int main(int argc, char** argv)
                 HitableList* outer = new HitableList(arr, 1, new Transform(vec3(10, 20, 30), vec3(0.f), vec3(1.f)));
                 w.list.append(outer);
                 w.list.append(new Sphere(new Transform(), 2.0f, new Dielectric(1.5f)));
+                // CheckerTexture(t0 = even, t1 = odd), texture.h:28, under a Lambertian and under a light
+                Texture* chk = new CheckerTexture(new ConstantTexture(vec3(0.2f, 0.3f, 0.1f)), new ConstantTexture(vec3(0.9f, 0.9f, 0.9f)));
+                w.list.append(new Sphere(new Transform(vec3(0, -1000, 0), vec3(0.f), vec3(1.f)), 1000.0f, new Lambertian(chk)));
+                w.list.append(new Sphere(new Transform(vec3(0, 9, 0), vec3(0.f), vec3(1.f)), 1.0f, new DiffuseLight(chk)));
             } else return 64;
             dump_flat(flatten_scene(w.list), argv[3]);
             return 0;

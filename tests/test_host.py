@@ -97,6 +97,13 @@ def test_device_functions_on_host_match_oracle():
         ok = emu.emu_scatter(mt, alb, param, ray, np.concatenate([p, n]).astype(np.float32), key, 0, out, C.byref(co))
         assert bool(ok) == a[0] and co.value == a[4], i
         assert np.array_equal(out[0:3], a[1]) and np.array_equal(out[6:9], a[3], equal_nan=True), i
+    # CheckerTexture colour selection of the device code == the reference's
+    pts = np.concatenate([rng.normal(size=(20000, 3)) * 3, rng.normal(size=(20000, 3)) * 1000]).astype(np.float32)
+    emu.emu_checker_odd.argtypes = [f32p, C.c_size_t, np.ctypeslib.ndpointer(np.uint8, flags="C_CONTIGUOUS")]
+    emu.emu_checker_odd.restype = None
+    got = np.zeros(len(pts), np.uint8)
+    emu.emu_checker_odd(np.ascontiguousarray(pts), len(pts), got)
+    assert np.array_equal(got.astype(bool), o.checker_odd(pts))
     cam = crt.camera22((13, 2, 3), (0, 0, 0), (0, 1, 0), 20, 1.5, 0.1, 10)
     for i in range(500):
         s, t = rng.random(2)

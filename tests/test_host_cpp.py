@@ -46,7 +46,7 @@ def read_flat(path):
 
     out = dict(tri=take(np.float32, nt * 12).reshape(-1, 12), tri_mat=take(np.uint32, nt), tri_id=take(np.uint32, nt),
                sph=take(np.float32, ns * 4).reshape(-1, 4), sph_mat=take(np.uint32, ns), sph_id=take(np.uint32, ns))
-    m = np.frombuffer(b, dtype=np.dtype([("type", "<u4"), ("albedo", "<f4", 3), ("param", "<f4")]), count=nm, offset=off)
+    m = np.frombuffer(b, dtype=np.dtype([("type", "<u4"), ("albedo", "<f4", 3), ("param", "<f4"), ("texture", "<u4"), ("albedo2", "<f4", 3)]), count=nm, offset=off)
     out["mats"] = m
     assert off + m.nbytes == len(b)
     return out
@@ -149,16 +149,22 @@ def test_flatten_nested_lists_accumulate_offsets(probe, tmp_path):
     out = str(tmp_path / "f.bin")
     subprocess.run([probe, "flat", "nested", out], check=True)
     flat = read_flat(out)
-    assert np.array_equal(flat["sph"], np.asarray([[11, 22, 33, 0.5], [0, 0, 0, 2.0]], np.float32))
+    assert np.array_equal(flat["sph"], np.asarray([[11, 22, 33, 0.5], [0, 0, 0, 2.0], [0, -1000, 0, 1000.0], [0, 9, 0, 1.0]], np.float32))
     assert np.array_equal(flat["tri"][0, :9], np.asarray([10, 20, 30, 11, 20, 30, 10, 21, 30], np.float32))
     assert np.array_equal(flat["tri"][0, 9:], np.asarray([0, 0, 1], np.float32))
     # ids follow the depth-first list order: sphere, triangle, sphere
-    assert list(flat["sph_id"]) == [0, 2] and list(flat["tri_id"]) == [1]
+    assert list(flat["sph_id"]) == [0, 2, 3, 4] and list(flat["tri_id"]) == [1]
     m = flat["mats"]
     assert m["type"][flat["sph_mat"][0]] == scenes.METAL
     assert m["param"][flat["tri_mat"][0]] == 1.0          # Metal fuzz clamp, material.h:80
     assert flat["sph_mat"][0] == flat["tri_mat"][0]         # one Material object -> one table entry
     assert m["type"][flat["sph_mat"][1]] == scenes.DIELECTRIC and m["param"][flat["sph_mat"][1]] == 1.5
+    assert m["texture"][flat["sph_mat"][0]] == crt.TEX_CONSTANT
+    for k, t in ((2, scenes.LAMBERTIAN), (3, scenes.DIFFUSE_LIGHT)):       # CheckerTexture(even, odd), texture.h:25-42
+        c = m[flat["sph_mat"][k]]
+        assert c["type"] == t and c["texture"] == crt.TEX_CHECKER
+        assert np.array_equal(c["albedo"], np.asarray([0.2, 0.3, 0.1], np.float32))
+        assert np.array_equal(c["albedo2"], np.asarray([0.9, 0.9, 0.9], np.float32))
 
 
 @pytest.mark.parametrize("what", ["rotation", "scale", "texture", "nomat"])

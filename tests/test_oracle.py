@@ -182,6 +182,20 @@ def test_port_matches_reference_on_fresh_inputs():
     sa, sb = oracle_scene(ref, sc), oracle_scene(port, sc)
     for mode in (0, 1, 2):
         assert np.array_equal(sa.render(cam, 60, 40, 2, 8, mode, 9), sb.render(cam, 60, 40, 2, 8, mode, 9), equal_nan=True)
+    # CheckerTexture: which colour a point selects, then renders through checkered Lambertians and a checkered light
+    pts = np.concatenate([rng.normal(size=(20000, 3)) * 3, rng.normal(size=(20000, 3)) * 1000, np.zeros((1, 3)),
+                          np.asarray([[np.pi / 10, 1, 1], [1, -np.pi / 5, 2]])]).astype(np.float32)
+    odd = ref.checker_odd(pts)
+    assert np.array_equal(odd, port.checker_odd(pts)) and 0.4 < odd.mean() < 0.6 and not odd[40000]
+    sc = scenes.checker_scene()
+    cam = crt.camera_for(sc, 60, 40)
+    sa, sb = oracle_scene(ref, sc), oracle_scene(port, sc)
+    for mode in (0, 1):
+        ia = sa.render(cam, 60, 40, 2, 8, mode, 9)
+        assert np.array_equal(ia, sb.render(cam, 60, 40, 2, 8, mode, 9), equal_nan=True)
+    plain = dict(sc)
+    plain["mats"] = [m[:3] for m in sc["mats"]]
+    assert not np.array_equal(oracle_scene(ref, plain).render(cam, 60, 40, 2, 8, 0, 9), sa.render(cam, 60, 40, 2, 8, 0, 9))
     # triangle normals of the scene generator == Triangle constructor
     t = scenes.c1_bunny()["tri"]
     for k in range(0, len(t), 211):
