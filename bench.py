@@ -387,7 +387,7 @@ def run_ours(args):
                          "timing": "CUDA events around each closest-hit launch, on its stream, over %d frames rendered with one slice in flight (CRT_OPT_LANES=1); the timed region of `value` keeps %d slices in flight" % (args.steps, lanes),
                          "nodes_per_ray": work["nodes_visited"] / max(1, n_r), "tris_per_ray": work["tris_tested"] / max(1, n_r),
                          "node_fetches_per_ray": work["node_fetches"] / max(1, n_r), "tri_fetches_per_ray": work["tri_fetches"] / max(1, n_r),
-                         "accounting": "bytes = 128 B x node fetches + 48 B x triangle fetches + 48 B x rays; camera rays share one fetch per packet of <= 32 rays, every other bounce fetches per ray; flops = 96 x node tests + 50 x triangle tests (per ray)",
+                         "accounting": "bytes = 128 B x node fetches + 48 B x triangle fetches + 48 B x rays; camera rays share one fetch (and, with a common origin, one interval box test) per packet of <= 32 rays, every other bounce fetches and tests per ray; flops = 96 x node tests + 50 x triangle tests",
                          "fp32_tflops_achieved": alg_flops / bounce_launches / (per_launch_ms * 1e-3) / 1e12},
         }
         if world == 1 and not args.no_cpu_baseline:

@@ -165,7 +165,7 @@ int crt_set_option(crt_ctx* c, int option, int64_t value)
         c->leaf_thresh = (int)value;
         return CRT_OK;
     case CRT_OPT_PACKET_PRIMARY:
-        c->packet_primary = value != 0;
+        c->packet_primary = value == 2 ? 2 : (value != 0);   // 2: packets without the interval test (development aid)
         return CRT_OK;
     case CRT_OPT_BUILDER:
         if (value != CRT_BUILDER_LBVH && value != CRT_BUILDER_PLOC) { set_error("CRT_OPT_BUILDER must be CRT_BUILDER_LBVH or CRT_BUILDER_PLOC"); return CRT_ERR_INVALID; }

@@ -19,9 +19,9 @@ namespace crt {
 //   sphere:   r0 = {centre.xyz, radius}, r1 = r2 = 0
 //   both:     r3 = {prim_id, mat_id | kind << 31, 0, 0} as uint bits
 // 4-wide node, 128 B = 8 x float4 = one cache line, holds the boxes of up to
-// four children, one float4 per plane:
-//   n0 = lo.x[0..3]  n1 = hi.x[0..3]  n2 = lo.y[0..3]  n3 = hi.y[0..3]
-//   n4 = lo.z[0..3]  n5 = hi.z[0..3]
+// four children, child-major: floats 6k..6k+5 = {lo.x, hi.x, lo.y, hi.y, lo.z, hi.z}
+// of child k (n0..n5; a lane reads one child with three 64-bit loads, a ray
+// that tests all four reads the 96 bytes with three 256-bit loads)
 //   n6 = child[0..3] as int bits; child >= 0: node index, child < 0: leaf,
 //        ~child = (first sorted primitive << 3) | (count - 1);
 //        CRT_SLOT_EMPTY: unused slot (a node has 2..4 children)

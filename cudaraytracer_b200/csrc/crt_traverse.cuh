@@ -52,6 +52,9 @@ constexpr int TP_BLOCK = 128;    // threads per block of every traversal kernel
 #ifndef CRT_TRACE_MIN_BLOCKS
 #define CRT_TRACE_MIN_BLOCKS 8   // resident blocks per SM the register allocation must allow
 #endif
+#ifndef CRT_PACKET_MIN_BLOCKS
+#define CRT_PACKET_MIN_BLOCKS 8  // 10 and 12 resident blocks (51 and 40 registers) measured slower
+#endif
 constexpr int TP_CHUNK = 256;    // most rays a warp takes from the queue per atomic
 constexpr int TP_REFILL = 8;     // default: refill once this many lanes are idle
 
@@ -126,6 +129,32 @@ __device__ __forceinline__ RaySlabs make_slabs(v3 o, v3 d)
     slab_axis(o.z, d.z, s.iz, s.cz_lo, s.cz_hi);
     return s;
 }
+
+// The 24 box planes of a node, child-major: f[6k + {0..5}] = {lo.x, hi.x, lo.y, hi.y, lo.z, hi.z} of child k
+// (three 256-bit loads; the indices below are compile-time, so this is only a naming of registers).
+__device__ __forceinline__ void load_node_boxes(const float4* __restrict__ np, float (&f)[24])
+{
+    float4 a, b;
+    ldg256(np, a, b);
+    f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+    ldg256(np + 2, a, b);
+    f[8] = a.x; f[9] = a.y; f[10] = a.z; f[11] = a.w; f[12] = b.x; f[13] = b.y; f[14] = b.z; f[15] = b.w;
+    ldg256(np + 4, a, b);
+    f[16] = a.x; f[17] = a.y; f[18] = a.z; f[19] = a.w; f[20] = b.x; f[21] = b.y; f[22] = b.z; f[23] = b.w;
+}
+
+// order-preserving float <-> uint32 (for REDUX min/max over a warp)
+__device__ __forceinline__ uint32_t f2sortable(float f)
+{
+    const uint32_t u = __float_as_uint(f);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float sortable2f(uint32_t s)
+{
+    return __uint_as_float((s & 0x80000000u) ? (s & 0x7fffffffu) : ~s);
+}
+__device__ __forceinline__ float warp_min_f(float v) { return sortable2f(__reduce_min_sync(0xffffffffu, f2sortable(v))); }
+__device__ __forceinline__ float warp_max_f(float v) { return sortable2f(__reduce_max_sync(0xffffffffu, f2sortable(v))); }
 
 // Src: bool load(uint32_t i, v3& o, v3& d)  -> origin and raw direction of ray i
 // Sink: void store(uint32_t i, const Hit& h) -> h.k = sorted primitive position or ~0u, h.id = caller's id
@@ -218,23 +247,18 @@ __device__ __forceinline__ void traverse_persistent(const AccelView& A, const ui
         if (int_mask != 0u && (uint32_t)__popc(leaf_mask) < leaf_thresh) {
             if (node >= 0) {
                 const float4* np = A.nodes + 8 * (size_t)(uint32_t)node;
-                float4 lox, hix, loy, hiy, loz, hiz;
-                ldg256(np, lox, hix);
-                ldg256(np + 2, loy, hiy);
-                ldg256(np + 4, loz, hiz);
+                float f[24];
+                load_node_boxes(np, f);
                 const int4 refs = __ldg(reinterpret_cast<const int4*>(np + 6));
                 if (COUNT) { cnt.nodes++; ray_steps++; cnt.max_steps = max(cnt.max_steps, ray_steps); }
                 float key[4];
                 int ref[4] = {refs.x, refs.y, refs.z, refs.w};
-                const float plo_x[4] = {lox.x, lox.y, lox.z, lox.w}, phi_x[4] = {hix.x, hix.y, hix.z, hix.w};
-                const float plo_y[4] = {loy.x, loy.y, loy.z, loy.w}, phi_y[4] = {hiy.x, hiy.y, hiy.z, hiy.w};
-                const float plo_z[4] = {loz.x, loz.y, loz.z, loz.w}, phi_z[4] = {hiz.x, hiz.y, hiz.z, hiz.w};
                 int n_hit = 0;
 #pragma unroll
                 for (int k = 0; k < 4; k++) {
-                    const float ax = fmaf(plo_x[k], S.ix, S.cx_lo), bx = fmaf(phi_x[k], S.ix, S.cx_hi);
-                    const float ay = fmaf(plo_y[k], S.iy, S.cy_lo), by = fmaf(phi_y[k], S.iy, S.cy_hi);
-                    const float az = fmaf(plo_z[k], S.iz, S.cz_lo), bz = fmaf(phi_z[k], S.iz, S.cz_hi);
+                    const float ax = fmaf(f[6 * k], S.ix, S.cx_lo), bx = fmaf(f[6 * k + 1], S.ix, S.cx_hi);
+                    const float ay = fmaf(f[6 * k + 2], S.iy, S.cy_lo), by = fmaf(f[6 * k + 3], S.iy, S.cy_hi);
+                    const float az = fmaf(f[6 * k + 4], S.iz, S.cz_lo), bz = fmaf(f[6 * k + 5], S.iz, S.cz_hi);
                     const float tn = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), t_min));
                     const float tf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), best.t));
                     const bool h = tn <= tf * 1.0000005f && ref[k] != CRT_SLOT_EMPTY;
@@ -295,22 +319,34 @@ __device__ __forceinline__ void traverse_persistent(const AccelView& A, const ui
 // ---------------------------------------------------------------------------
 // Packet form for COHERENT rays (camera rays: with the sample-minor path order
 // of render.cu a warp holds all samples of one or two pixels, i.e. 32 nearly
-// identical rays). The warp walks ONE stack: a node is visited when any lane's
-// ray enters it, every lane tests the node's four boxes against its own ray and
-// keeps its own closest hit, children are ordered by the first entering lane's
-// distance. Control flow is warp-uniform, so there is no lane refill, no
-// node/leaf phase vote and no per-lane stack; node and record addresses are
-// uniform, so each load is one L1 wavefront for the whole warp.
-// Visiting a node another lane needed never changes a lane's result: the
-// primitive tests and the tie-break are the ones of traverse_persistent.
+// identical rays). The warp walks ONE stack; control flow is warp-uniform, so
+// there is no lane refill, no node/leaf phase vote and no per-lane stack, and
+// node and record addresses are uniform, so a load is one L1 wavefront for the
+// whole warp. Every lane tests the primitives of a visited leaf against its own
+// ray and keeps its own closest hit; visiting a node another lane needed never
+// changes a lane's result (same primitive tests and tie-break as
+// traverse_persistent), so the node test only has to be conservative for the
+// packet as a whole:
+//   - rays with one common origin (a pinhole camera): ONE interval test per
+//     child for the whole packet. With inv = 1/d in [imin, imax] over the lanes,
+//     a plane at p is crossed at (p - o) * inv in [min, max of the two products];
+//     lane k (k & 3) evaluates child k from three 64-bit loads of the child-major
+//     node, so the four children cost one pass of ~35 instructions instead of
+//     four per-lane slab tests, the entry bound of a child orders the descent
+//     and the farthest closest hit of the packet prunes it. The bounds are
+//     widened by 2^-21 relative, which covers the three roundings involved;
+//   - anything else (finite aperture, arbitrary crt_trace batches): every lane
+//     tests the four boxes against its own ray, a child is entered when any
+//     lane's ray enters it, children are ordered by the first entering lane.
 #define CRT_PACKET_STACK CRT_STACK_ENTRIES   // same bound as the per-ray stack
 
 template <bool COUNT, bool HAS_SPH, class Src, class Sink>
 __device__ __forceinline__ void traverse_packets(const AccelView& A, const uint32_t n, uint32_t* work_ctr,
                                                  const float t_min, const float t_max, const Src& src,
-                                                 const Sink& sink, TraceCounters& cnt)
+                                                 const Sink& sink, TraceCounters& cnt, const bool interval = true)
 {
     const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t kid = lane & 3u;
     int wstack[CRT_PACKET_STACK];   // every lane keeps the same (warp-uniform) stack; slot X of 32 lanes is one 128-byte line of local memory
     constexpr uint32_t FULL = 0xffffffffu;
     // packets per grab
@@ -333,6 +369,19 @@ __device__ __forceinline__ void traverse_packets(const AccelView& A, const uint3
                 d = ray_dir_local(dr);
             }
             const RaySlabs S = make_slabs(o, d);
+            // lane 0 is always live; a dead lane takes its ray so that it widens nothing
+            const float o0x = __shfl_sync(FULL, o.x, 0), o0y = __shfl_sync(FULL, o.y, 0), o0z = __shfl_sync(FULL, o.z, 0);
+            const float i0x = __shfl_sync(FULL, S.ix, 0), i0y = __shfl_sync(FULL, S.iy, 0), i0z = __shfl_sync(FULL, S.iz, 0);
+            const float l_ix = live ? S.ix : i0x, l_iy = live ? S.iy : i0y, l_iz = live ? S.iz : i0z;
+            const float ix_lo = warp_min_f(l_ix), ix_hi = warp_max_f(l_ix);
+            const float iy_lo = warp_min_f(l_iy), iy_hi = warp_max_f(l_iy);
+            const float iz_lo = warp_min_f(l_iz), iz_hi = warp_max_f(l_iz);
+            // the interval test is only as tight as the interval of 1/d: on an axis where the packet's directions
+            // change sign (or nearly do) it cannot cull, and the packet would walk a whole slab of the scene
+            auto narrow = [](float lo, float hi) { return lo > 0.0f ? hi <= 2.0f * lo : (hi < 0.0f && lo >= 2.0f * hi); };
+            const bool uni = interval && narrow(ix_lo, ix_hi) && narrow(iy_lo, iy_hi) && narrow(iz_lo, iz_hi) &&
+                             __all_sync(FULL, !live || (o.x == o0x && o.y == o0y && o.z == o0z));
+            float t_far = t_max;                 // warp-uniform: the largest closest-hit distance of the packet
             Hit best;
             best.t = t_max; best.k = 0xFFFFFFFFu; best.id = CRT_MISS_ID; best.u = best.v = 0.f;
             if (A.n_prims != 0u) {
@@ -341,31 +390,56 @@ __device__ __forceinline__ void traverse_packets(const AccelView& A, const uint3
                 for (;;) {
                     if (node >= 0) {
                         const float4* np = A.nodes + 8 * (size_t)(uint32_t)node;
-                        float4 lox, hix, loy, hiy, loz, hiz;
-                        ldg256(np, lox, hix);
-                        ldg256(np + 2, loy, hiy);
-                        ldg256(np + 4, loz, hiz);
                         const int4 refs = __ldg(reinterpret_cast<const int4*>(np + 6));
-                        if (COUNT && live) cnt.nodes++;
-                        if (COUNT && lane == 0) cnt.node_f++;
                         float key[4];
                         int ref[4] = {refs.x, refs.y, refs.z, refs.w};
-                        const float plo_x[4] = {lox.x, lox.y, lox.z, lox.w}, phi_x[4] = {hix.x, hix.y, hix.z, hix.w};
-                        const float plo_y[4] = {loy.x, loy.y, loy.z, loy.w}, phi_y[4] = {hiy.x, hiy.y, hiy.z, hiy.w};
-                        const float plo_z[4] = {loz.x, loz.y, loz.z, loz.w}, phi_z[4] = {hiz.x, hiz.y, hiz.z, hiz.w};
                         int n_hit = 0;
+                        if (COUNT && lane == 0) cnt.node_f++;
+                        if (uni) {
+                            if (COUNT && lane == 0) cnt.nodes++;       // one interval test serves the packet
+                            const float2* cp = reinterpret_cast<const float2*>(np) + 3u * kid;
+                            const float2 bx = __ldg(cp), by = __ldg(cp + 1), bz = __ldg(cp + 2);
+                            const float ax0 = bx.x - o0x, ax1 = bx.y - o0x;
+                            const float ay0 = by.x - o0y, ay1 = by.y - o0y;
+                            const float az0 = bz.x - o0z, az1 = bz.y - o0z;
+                            const float x00 = ax0 * ix_lo, x01 = ax0 * ix_hi, x10 = ax1 * ix_lo, x11 = ax1 * ix_hi;
+                            const float y00 = ay0 * iy_lo, y01 = ay0 * iy_hi, y10 = ay1 * iy_lo, y11 = ay1 * iy_hi;
+                            const float z00 = az0 * iz_lo, z01 = az0 * iz_hi, z10 = az1 * iz_lo, z11 = az1 * iz_hi;
+                            const float nx = fminf(fminf(x00, x01), fminf(x10, x11)), fx = fmaxf(fmaxf(x00, x01), fmaxf(x10, x11));
+                            const float ny = fminf(fminf(y00, y01), fminf(y10, y11)), fy = fmaxf(fmaxf(y00, y01), fmaxf(y10, y11));
+                            const float nz = fminf(fminf(z00, z01), fminf(z10, z11)), fz = fmaxf(fmaxf(z00, z01), fmaxf(z10, z11));
+                            float tn = fmaxf(fmaxf(nx, ny), nz), tf = fminf(fminf(fx, fy), fz);
+                            tn = fmaf(-fabsf(tn), 4.76837158203125e-7f, tn);       // 2^-21 towards "enters earlier"
+                            tf = fmaf(fabsf(tf), 4.76837158203125e-7f, tf);        // and "leaves later"
+                            tn = fmaxf(tn, t_min);
+                            tf = fminf(tf, t_far);
+                            const int my_ref = kid == 0u ? refs.x : kid == 1u ? refs.y : kid == 2u ? refs.z : refs.w;
+                            const bool enter = tn <= tf && my_ref != CRT_SLOT_EMPTY;
+                            const uint32_t m4 = __ballot_sync(FULL, enter) & 0xFu;
 #pragma unroll
-                        for (int k = 0; k < 4; k++) {
-                            const float ax = fmaf(plo_x[k], S.ix, S.cx_lo), bx = fmaf(phi_x[k], S.ix, S.cx_hi);
-                            const float ay = fmaf(plo_y[k], S.iy, S.cy_lo), by = fmaf(phi_y[k], S.iy, S.cy_hi);
-                            const float az = fmaf(plo_z[k], S.iz, S.cz_lo), bz = fmaf(phi_z[k], S.iz, S.cz_hi);
-                            const float tn = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), t_min));
-                            const float tf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), best.t));
-                            const bool h = live && tn <= tf * 1.0000005f;
-                            const uint32_t m = ref[k] != CRT_SLOT_EMPTY ? __ballot_sync(FULL, h) : 0u;   // ref is uniform
-                            // entry distance of the first lane that enters the child; uniform
-                            key[k] = m ? __shfl_sync(FULL, tn, __ffs(m) - 1) : INFINITY;
-                            n_hit += m ? 1 : 0;
+                            for (int k = 0; k < 4; k++) {
+                                const float tk = __shfl_sync(FULL, tn, k);
+                                const bool h = (m4 >> k) & 1u;
+                                key[k] = h ? tk : INFINITY;
+                                n_hit += h ? 1 : 0;
+                            }
+                        } else {
+                            float f[24];
+                            load_node_boxes(np, f);
+                            if (COUNT && live) cnt.nodes++;
+#pragma unroll
+                            for (int k = 0; k < 4; k++) {
+                                const float ax = fmaf(f[6 * k], S.ix, S.cx_lo), bx = fmaf(f[6 * k + 1], S.ix, S.cx_hi);
+                                const float ay = fmaf(f[6 * k + 2], S.iy, S.cy_lo), by = fmaf(f[6 * k + 3], S.iy, S.cy_hi);
+                                const float az = fmaf(f[6 * k + 4], S.iz, S.cz_lo), bz = fmaf(f[6 * k + 5], S.iz, S.cz_hi);
+                                const float tn = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), t_min));
+                                const float tf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), best.t));
+                                const bool h = live && tn <= tf * 1.0000005f;
+                                const uint32_t m = ref[k] != CRT_SLOT_EMPTY ? __ballot_sync(FULL, h) : 0u;   // ref is uniform
+                                // entry distance of the first lane that enters the child; uniform
+                                key[k] = m ? __shfl_sync(FULL, tn, __ffs(m) - 1) : INFINITY;
+                                n_hit += m ? 1 : 0;
+                            }
                         }
 #define CRT_CSWAP(a, b)                                                                    \
                         {                                                                  \
@@ -377,7 +451,7 @@ __device__ __forceinline__ void traverse_packets(const AccelView& A, const uint3
                         }
                         CRT_CSWAP(0, 1) CRT_CSWAP(2, 3) CRT_CSWAP(0, 2) CRT_CSWAP(1, 3) CRT_CSWAP(1, 2)
 #undef CRT_CSWAP
-                                                if (n_hit > 3) wstack[sp++] = ref[3];
+                        if (n_hit > 3) wstack[sp++] = ref[3];
                         if (n_hit > 2) wstack[sp++] = ref[2];
                         if (n_hit > 1) wstack[sp++] = ref[1];
                         if (n_hit > 0) { node = ref[0]; continue; }
@@ -406,6 +480,8 @@ __device__ __forceinline__ void traverse_packets(const AccelView& A, const uint3
                             if (ok && t == best.t && (best.k == 0xFFFFFFFFu || pid >= best.id)) ok = false;
                             if (ok && live) { best.t = t; best.k = k; best.id = pid; best.u = u; best.v = v; }
                         }
+                        // distances are positive, so their bit patterns order like the values
+                        if (uni) t_far = __uint_as_float(__reduce_max_sync(FULL, live ? __float_as_uint(best.t) : 0u));
                     }
                     if (sp == 0u) break;
                     node = wstack[--sp];

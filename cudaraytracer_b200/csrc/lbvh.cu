@@ -315,12 +315,13 @@ k_emit_nodes(int n, int leaf_max, const int2* __restrict__ child, const int2* __
         slot[s].box = Box{0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     }
     float4* np = nodes + 8 * (size_t)i;
-    np[0] = make_float4(slot[0].box.lx, slot[1].box.lx, slot[2].box.lx, slot[3].box.lx);
-    np[1] = make_float4(slot[0].box.hx, slot[1].box.hx, slot[2].box.hx, slot[3].box.hx);
-    np[2] = make_float4(slot[0].box.ly, slot[1].box.ly, slot[2].box.ly, slot[3].box.ly);
-    np[3] = make_float4(slot[0].box.hy, slot[1].box.hy, slot[2].box.hy, slot[3].box.hy);
-    np[4] = make_float4(slot[0].box.lz, slot[1].box.lz, slot[2].box.lz, slot[3].box.lz);
-    np[5] = make_float4(slot[0].box.hz, slot[1].box.hz, slot[2].box.hz, slot[3].box.hz);
+    float v[24];                                              // child-major: {lo.x, hi.x, lo.y, hi.y, lo.z, hi.z} per slot
+    for (int s = 0; s < 4; s++) {
+        v[6 * s] = slot[s].box.lx; v[6 * s + 1] = slot[s].box.hx;
+        v[6 * s + 2] = slot[s].box.ly; v[6 * s + 3] = slot[s].box.hy;
+        v[6 * s + 4] = slot[s].box.lz; v[6 * s + 5] = slot[s].box.hz;
+    }
+    for (int q = 0; q < 6; q++) np[q] = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
     np[6] = make_float4(__int_as_float(slot[0].ref), __int_as_float(slot[1].ref), __int_as_float(slot[2].ref),
                         __int_as_float(slot[3].ref));
     np[7] = make_float4(0.f, 0.f, 0.f, 0.f);

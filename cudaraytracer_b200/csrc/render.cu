@@ -220,14 +220,14 @@ k_trace_queue(AccelView A, const float4* __restrict__ q, uint32_t cap, const uin
 
 // ---- closest hit for camera rays: one packet per warp (crt_traverse.cuh traverse_packets) ----
 template <bool COUNT, bool HAS_SPH>
-__global__ void __launch_bounds__(TP_BLOCK, CRT_TRACE_MIN_BLOCKS)
+__global__ void __launch_bounds__(TP_BLOCK, CRT_PACKET_MIN_BLOCKS)
 k_trace_packet(AccelView A, const float4* __restrict__ q, uint32_t cap, const uint32_t* __restrict__ n_ptr,
-               uint32_t* __restrict__ work_ctr, float4* __restrict__ hits, unsigned long long* __restrict__ counters)
+               uint32_t* __restrict__ work_ctr, float4* __restrict__ hits, unsigned long long* __restrict__ counters, int interval)
 {
     TraceCounters cnt = {0u, 0u, 0u, 0u, 0u, 0u, 0u};
     QueueSrc src = {q, cap};
     QueueSink sink = {hits};
-    traverse_packets<COUNT, HAS_SPH>(A, *n_ptr, work_ctr, 0.001f, FLT_MAX, src, sink, cnt);   // render.h:53
+    traverse_packets<COUNT, HAS_SPH>(A, *n_ptr, work_ctr, 0.001f, FLT_MAX, src, sink, cnt, interval != 0);   // render.h:53
     if (COUNT) {
         const uint32_t nodes = __reduce_add_sync(0xffffffffu, cnt.nodes);
         const uint32_t tris = __reduce_add_sync(0xffffffffu, cnt.tris);
@@ -423,13 +423,13 @@ static DCamera to_dcamera(const crt_camera* c)
 }
 
 template <bool COUNT, bool HAS_SPH>
-static void launch_bounce(crt_ctx* c, crt_lane& L, int b, int grid_trace, int grid_shade, const RenderParams& P, const AccelView& A,
+static void launch_bounce(crt_ctx* c, crt_lane& L, int b, int grid_trace, int grid_packet, int grid_shade, const RenderParams& P, const AccelView& A,
                           const float4* q_in, const uint32_t* n_in, uint32_t* work_ctr, float4* q_out, uint32_t* n_out)
 {
     cudaEventRecord(L.ev_trace[2 * b], L.stream);
     if (b == 0 && c->packet_primary)   // camera rays: a warp holds the samples of one or two pixels
-        k_trace_packet<COUNT, HAS_SPH><<<grid_trace, TP_BLOCK, 0, L.stream>>>(A, q_in, P.cap, n_in, work_ctr, L.hitbuf.as<float4>(),
-                                                                              c->counters.as<unsigned long long>());
+        k_trace_packet<COUNT, HAS_SPH><<<grid_packet, TP_BLOCK, 0, L.stream>>>(A, q_in, P.cap, n_in, work_ctr, L.hitbuf.as<float4>(),
+                                                                              c->counters.as<unsigned long long>(), c->packet_primary == 1 ? 1 : 0);
     else
         k_trace_queue<COUNT, HAS_SPH><<<grid_trace, TP_BLOCK, 0, L.stream>>>(A, q_in, P.cap, n_in, work_ctr, L.hitbuf.as<float4>(),
                                                                              c->counters.as<unsigned long long>(), (uint32_t)c->refill, (uint32_t)c->leaf_thresh);
@@ -516,6 +516,10 @@ int render_accum(crt_ctx* c, const crt_camera* cam, int nx, int ny, int s0, int 
         // the instantiations have near-identical resource needs; size the persistent grids from one
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_trace_queue<false, false>, TP_BLOCK, 0);
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps_shade, k_shade<false, false>, RB, 0);
+        int bps_packet = 1;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps_packet, k_trace_packet<false, false>, TP_BLOCK, 0);
+        if (bps_packet < 1) bps_packet = 1;
+        const int grid_packet = c->sm_count * bps_packet;
         if (bps < 1) bps = 1;
         if (bps_shade < 1) bps_shade = 1;
         const int grid = c->sm_count * bps;
@@ -554,11 +558,11 @@ int render_accum(crt_ctx* c, const crt_camera* cam, int nx, int ny, int s0, int 
                     uint32_t* no = L.qcount.as<uint32_t>() + b + 1;
                     uint32_t* wc = L.work_ctr.as<uint32_t>() + b;
                     if (c->count_work) {
-                        if (sph) launch_bounce<true, true>(c, L, b, grid, grid_shade, PL, A, qi, ni, wc, qo, no);
-                        else launch_bounce<true, false>(c, L, b, grid, grid_shade, PL, A, qi, ni, wc, qo, no);
+                        if (sph) launch_bounce<true, true>(c, L, b, grid, grid_packet, grid_shade, PL, A, qi, ni, wc, qo, no);
+                        else launch_bounce<true, false>(c, L, b, grid, grid_packet, grid_shade, PL, A, qi, ni, wc, qo, no);
                     } else {
-                        if (sph) launch_bounce<false, true>(c, L, b, grid, grid_shade, PL, A, qi, ni, wc, qo, no);
-                        else launch_bounce<false, false>(c, L, b, grid, grid_shade, PL, A, qi, ni, wc, qo, no);
+                        if (sph) launch_bounce<false, true>(c, L, b, grid, grid_packet, grid_shade, PL, A, qi, ni, wc, qo, no);
+                        else launch_bounce<false, false>(c, L, b, grid, grid_packet, grid_shade, PL, A, qi, ni, wc, qo, no);
                     }
                 }
                 CRT_CUDA(cudaEventRecord(L.ev_end, L.stream));

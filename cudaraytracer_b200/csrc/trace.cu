@@ -77,7 +77,7 @@ k_trace_lbvh(AccelView A, const crt_ray* __restrict__ rays, uint32_t n, uint32_t
 }
 
 template <bool COUNT, bool HAS_SPH>
-__global__ void __launch_bounds__(TP_BLOCK, CRT_TRACE_MIN_BLOCKS)
+__global__ void __launch_bounds__(TP_BLOCK, CRT_PACKET_MIN_BLOCKS)
 k_trace_lbvh_packet(AccelView A, const crt_ray* __restrict__ rays, uint32_t n, uint32_t* __restrict__ work_ctr, float t_min,
                     float t_max, crt_hit* __restrict__ hits, unsigned long long* __restrict__ counters)
 {
@@ -195,6 +195,10 @@ int launch_trace(crt_ctx* c, const crt_ray* d_rays, size_t n, float t_min, float
         uint32_t* wc = c->work_ctr.as<uint32_t>();
         const uint32_t un = (uint32_t)n;
         if (accel == CRT_ACCEL_LBVH_PACKET) {
+            int bpp = 1;
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bpp, k_trace_lbvh_packet<false, false>, TP_BLOCK, 0);
+            const size_t capp = (size_t)c->sm_count * (bpp < 1 ? 1 : bpp);
+            const unsigned int grid = (unsigned int)(blocks < capp ? blocks : capp);
             if (c->count_work) {
                 if (sph) k_trace_lbvh_packet<true, true><<<grid, TP_BLOCK, 0, st>>>(A, d_rays, un, wc, t_min, t_max, d_hits, counters);
                 else k_trace_lbvh_packet<true, false><<<grid, TP_BLOCK, 0, st>>>(A, d_rays, un, wc, t_min, t_max, d_hits, counters);
