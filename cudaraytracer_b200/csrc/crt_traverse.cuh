@@ -416,6 +416,16 @@ __device__ __forceinline__ void traverse_packets(const AccelView& A, const uint3
                             const int my_ref = kid == 0u ? refs.x : kid == 1u ? refs.y : kid == 2u ? refs.z : refs.w;
                             const bool enter = tn <= tf && my_ref != CRT_SLOT_EMPTY;
                             const uint32_t m4 = __ballot_sync(FULL, enter) & 0xFu;
+                            if ((m4 & (m4 - 1u)) == 0u) {
+                                // none or one child entered (the common case): no ordering needed
+                                if (m4 == 0u) {
+                                    if (sp == 0u) break;
+                                    node = wstack[--sp];
+                                } else {
+                                    node = (m4 & 1u) ? refs.x : (m4 & 2u) ? refs.y : (m4 & 4u) ? refs.z : refs.w;
+                                }
+                                continue;
+                            }
 #pragma unroll
                             for (int k = 0; k < 4; k++) {
                                 const float tk = __shfl_sync(FULL, tn, k);

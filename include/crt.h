@@ -107,7 +107,8 @@ typedef enum {
     CRT_OPT_COUNTERS = 2,   /* 1: run the instrumented kernels that count nodes/primitives visited */
     CRT_OPT_BATCH_PATHS = 3,/* max camera samples in flight per wavefront batch (default 1<<25) */
     CRT_OPT_LEAF_THRESH = 5,/* tuning: lanes parked on a leaf that trigger the primitive-test phase, 1..32 (default 8) */
-    CRT_OPT_PACKET_PRIMARY = 6, /* 1 (default): camera rays are traced as one packet per warp; 0: like every other bounce */
+    CRT_OPT_PACKET_PRIMARY = 6, /* 1 (default): camera rays are traced as one packet per warp; 0: like every other bounce;
+                             * 2: packets without the shared interval box test (development aid) */
     CRT_OPT_LANES = 7,      /* render: at most 1..4 slices of the frame in flight on their own streams (default 4; a slice is
                              * never smaller than 2^22 camera samples), so one slice's
                              * latency-bound last bounces overlap the other's wide launches; images do not depend on it */
@@ -126,7 +127,8 @@ typedef enum {
  * counters other than rays are only maintained while CRT_OPT_COUNTERS is 1. */
 typedef struct {
     uint64_t rays;            /* closest-hit queries issued */
-    uint64_t nodes_visited;   /* BVH2 nodes fetched (two child boxes each) */
+    uint64_t nodes_visited;   /* 4-wide node tests executed: one per ray and visit, or one per PACKET and visit where a
+                               * packet of camera rays with a common origin takes one interval test (crt_traverse.cuh) */
     uint64_t tris_tested;
     uint64_t spheres_tested;
     uint64_t scatters;        /* material scatter evaluations */
