@@ -6,10 +6,12 @@
 //
 //   k_raygen      one thread per (pixel, sample): jitter + Camera::get_ray
 //                 (render.h:116-118, camera.h:40-44) -> path queue
-//   k_bounce      one launch per bounce over the live queue: LBVH closest hit
-//                 (crt_traverse.cuh), material scatter (material.h:57-143), and
-//                 either a new ray into the next queue (warp-ballot compaction,
-//                 one atomic per warp) or the path's radiance
+//   per bounce:
+//   k_trace_packet (camera rays) / k_trace_queue (every other bounce): LBVH
+//                 closest hit for every queue entry (crt_traverse.cuh) -> hit buffer
+//   k_shade       material scatter (material.h:57-143): either a new ray into
+//                 the next queue (ballot compaction, one atomic per block) or
+//                 the path's radiance
 //   k_accumulate  per pixel, adds the batch's samples IN SAMPLE ORDER, as the
 //                 reference's "col += shade(...)" loop does (render.h:115-122)
 //   k_resolve     col /= ns; sqrt; clip (render.h:123-128)
@@ -22,6 +24,9 @@
 //
 // Random numbers: include/crt_rng.h, keyed by (seed, pixel, sample); a path
 // carries only its draw counter.
+//
+// A frame is rendered as up to CRT_OPT_LANES interleaved slices, each running
+// this loop on its own stream and buffers (render_accum below).
 #include "crt_internal.h"
 #include "crt_traverse.cuh"
 #include <stdio.h>
