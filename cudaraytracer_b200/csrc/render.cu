@@ -490,8 +490,10 @@ int render_accum(crt_ctx* c, const crt_camera* cam, int nx, int ny, int s0, int 
     float bounce_ms = 0.f, trace_q_ms = 0.f;
     if (local_tiles > 0 && n_samples > 0) {
         // lane l of rank r renders tiles r + world * (l + n_lanes * j): the slices interleave, so they are balanced
-        // at most CRT_OPT_LANES, at least 2^22 camera samples per slice: a small frame is launch-bound already
-        const long long want = (local_tiles * CRT_TILE * CRT_TILE * n_samples) >> 22;
+        // at most CRT_OPT_LANES, at least 2 M camera samples per slice: below that a frame is launch bound and more
+        // launches cost more than the overlap gains (C1, 2.1 M samples in 0.8 ms: 1 slice 0.79 ms, 4 slices 0.91 ms;
+        // C3 at 960x540x16, 8.3 M samples: 3.91 ms -> 3.35 ms)
+        const long long want = (local_tiles * CRT_TILE * CRT_TILE * n_samples) / 2000000ll;
         const int n_lanes = (int)std::max(1ll, std::min((long long)c->n_lanes, std::min(local_tiles, want)));
         c->host_counters.lanes = (uint64_t)n_lanes;
         const int sub_world = world * n_lanes;

@@ -110,7 +110,7 @@ typedef enum {
     CRT_OPT_PACKET_PRIMARY = 6, /* 1 (default): camera rays are traced as one packet per warp; 0: like every other bounce;
                              * 2: packets without the shared interval box test (development aid) */
     CRT_OPT_LANES = 7,      /* render: at most 1..4 slices of the frame in flight on their own streams (default 4; a slice is
-                             * never smaller than 2^22 camera samples), so one slice's
+                             * never smaller than 2 M camera samples), so one slice's
                              * latency-bound last bounces overlap the other's wide launches; images do not depend on it */
     CRT_OPT_BUILDER = 8,    /* tree topology of crt_accel_build: CRT_BUILDER_LBVH (default) or CRT_BUILDER_PLOC; hits and images do not depend on it */
     CRT_OPT_REFILL = 4      /* tuning: idle lanes per warp that trigger a refill from the ray queue, 1..32 (default 8) */

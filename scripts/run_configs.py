@@ -120,6 +120,8 @@ def main():
         out.append(render_row("C4 10M-tri instanced, 1 GPU", scenes.c4_instanced(), reps=2))
     if "c5" in which:
         n = 1000
+        if "--min-tris" in sys.argv:
+            n = int(float(sys.argv[sys.argv.index("--min-tris") + 1]))
         while n <= max_tris:
             out.extend(trace_rows(n))
             n *= 10
