@@ -153,8 +153,8 @@ k_raygen(RenderParams P, float4* __restrict__ q, uint32_t* __restrict__ q_count)
         }
         const uint32_t pos = block_append<RB>(live, q_count, s_cnt);
         if (live) {   // the material-id words (2, 3) are first written by k_shade and never read at bounce 0
-            q[pos] = w0;
-            q[(size_t)P.cap + pos] = w1;
+            __stcs(q + pos, w0);
+            __stcs(q + (size_t)P.cap + pos, w1);
         }
     }
 }
@@ -182,8 +182,10 @@ struct QueueSrc {
     size_t cap;
     __device__ __forceinline__ void load(uint32_t i, v3& o, v3& d) const
     {
-        const float4 w0 = q[i];
-        const float4 w1 = q[cap + i];
+        // queue entries and hit records stream through once per launch (GB per bounce): evict-first loads and
+        // stores keep them from pushing the node and record working set (which does fit) out of the 126 MB L2
+        const float4 w0 = __ldcs(q + i);
+        const float4 w1 = __ldcs(q + cap + i);
         o = V(w0.x, w0.y, w0.z);
         d = V(w0.w, w1.x, w1.y);
     }
@@ -192,7 +194,7 @@ struct QueueSink {
     float4* hits;   // {t, sorted primitive position, u, v} per queue entry
     __device__ __forceinline__ void store(uint32_t i, const Hit& h) const
     {
-        hits[i] = make_float4(h.t, __uint_as_float(h.k), h.u, h.v);
+        __stcs(hits + i, make_float4(h.t, __uint_as_float(h.k), h.u, h.v));
     }
 };
 
@@ -267,19 +269,19 @@ k_shade(RenderParams P, AccelView A, const DMat* __restrict__ mats, const float4
         float4 w0 = make_float4(0, 0, 0, 0), w1 = w0;
         uint32_t ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};
         if (live) {
-            w0 = q_in[i];
-            w1 = q_in[(size_t)P.cap + i];
-            const float4 hr = hits[i];
+            w0 = __ldcs(q_in + i);
+            w1 = __ldcs(q_in + (size_t)P.cap + i);
+            const float4 hr = __ldcs(hits + i);
             const v3 o = V(w0.x, w0.y, w0.z), d = V(w0.w, w1.x, w1.y);
             const uint32_t path_id = __float_as_uint(w1.z);
             const uint32_t pack = __float_as_uint(w1.w);
             const int depth_left = (int)(pack >> 24);
             const int bounces = P.max_depth - depth_left;
             if (bounces > 0) {
-                const uint4 a2 = reinterpret_cast<const uint4*>(q_in)[2 * (size_t)P.cap + i];
+                const uint4 a2 = __ldcs(reinterpret_cast<const uint4*>(q_in) + 2 * (size_t)P.cap + i);
                 ms[0] = a2.x; ms[1] = a2.y; ms[2] = a2.z; ms[3] = a2.w;
                 if (bounces > 8) {
-                    const uint4 a3 = reinterpret_cast<const uint4*>(q_in)[3 * (size_t)P.cap + i];
+                    const uint4 a3 = __ldcs(reinterpret_cast<const uint4*>(q_in) + 3 * (size_t)P.cap + i);
                     ms[4] = a3.x; ms[5] = a3.y; ms[6] = a3.z; ms[7] = a3.w;
                 }
             }
@@ -354,16 +356,16 @@ k_shade(RenderParams P, AccelView A, const DMat* __restrict__ mats, const float4
                         L = vadd(V(0.0f, 0.0f, 0.0f), vmul(bounce_attenuation(mj, (id & 0x8000u) != 0u), L));
                     }
                 }
-                rad[path_id] = make_float4(L.x, L.y, L.z, 0.0f);
+                __stcs(rad + path_id, make_float4(L.x, L.y, L.z, 0.0f));
             }
         }
         const uint32_t pos = block_append<RB>(next, n_out_ptr, s_cnt);
         if (next) {
-            q_out[pos] = w0;
-            q_out[(size_t)P.cap + pos] = w1;
-            reinterpret_cast<uint4*>(q_out)[2 * (size_t)P.cap + pos] = make_uint4(ms[0], ms[1], ms[2], ms[3]);
+            __stcs(q_out + pos, w0);
+            __stcs(q_out + (size_t)P.cap + pos, w1);
+            __stcs(reinterpret_cast<uint4*>(q_out) + 2 * (size_t)P.cap + pos, make_uint4(ms[0], ms[1], ms[2], ms[3]));
             if (P.max_depth > 8)
-                reinterpret_cast<uint4*>(q_out)[3 * (size_t)P.cap + pos] = make_uint4(ms[4], ms[5], ms[6], ms[7]);
+                __stcs(reinterpret_cast<uint4*>(q_out) + 3 * (size_t)P.cap + pos, make_uint4(ms[4], ms[5], ms[6], ms[7]));
         }
     }
     if (COUNT) {
