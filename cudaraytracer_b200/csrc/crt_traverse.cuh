@@ -69,12 +69,22 @@ __device__ __forceinline__ float safe_rcp(float d)
 
 __device__ __forceinline__ float4 ldg4(const float4* p) { return __ldg(p); }
 
+// L2 policy for the node and record loads: evict-last, so that the GB of queue traffic that streams through
+// every launch (evict-first, render.cu) does not displace the tree, which fits the 126 MB L2.
+__device__ __forceinline__ uint64_t l2_keep_policy()
+{
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+
 // 32 bytes with one LDG.E.256 through the read-only path; p must be 32-byte aligned.
 __device__ __forceinline__ void ldg256(const float4* p, float4& a, float4& b)
 {
-    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+    const uint64_t pol = l2_keep_policy();       // a few uniform-datapath instructions, hoisted out of loops
+    asm volatile("ld.global.nc.L2::cache_hint.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8], %9;"
                  : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)
-                 : "l"(p));
+                 : "l"(p), "l"(pol));
 }
 
 __device__ __forceinline__ void sts32(uint32_t addr, int v) { asm volatile("st.shared.b32 [%0], %1;" ::"r"(addr), "r"(v)); }
