@@ -18,14 +18,15 @@ namespace crt {
 //             performs per test, done once; same float result)
 //   sphere:   r0 = {centre.xyz, radius}, r1 = r2 = 0
 //   both:     r3 = {prim_id, mat_id | kind << 31, 0, 0} as uint bits
-// 4-wide node, 128 B = 8 x float4 = one cache line, holds the boxes of up to
-// four children, child-major: floats 6k..6k+5 = {lo.x, hi.x, lo.y, hi.y, lo.z, hi.z}
-// of child k (n0..n5; a lane reads one child with three 64-bit loads, a ray
-// that tests all four reads the 96 bytes with three 256-bit loads)
-//   n6 = child[0..3] as int bits; child >= 0: node index, child < 0: leaf,
+// 4-wide node: 96 B of payload at a 128 B stride (one cache line), read with three 256-bit loads:
+//   words 5k..5k+4 = child k: {lo.x, lo.y, lo.z, half2(ext.x, ext.y), half2(ext.z, 0)}
+//        hi = lo + ext; ext is a half rounded up at build time until lo + ext >= hi in fp32, so the box only
+//        grows (by < 2^-10 of its own extent) and the child references fit the same three loads - a fourth
+//        load per node visit was a quarter of the L1 wavefronts of the incoherent bounces
+//   words 20..23  = child[0..3] as int bits; child >= 0: node index, child < 0: leaf,
 //        ~child = (first sorted primitive << 3) | (count - 1);
 //        CRT_SLOT_EMPTY: unused slot (a node has 2..4 children)
-//   n7 = padding
+//   words 24..31  = padding
 #define CRT_SLOT_EMPTY ((int)0x80000000)
 #define CRT_KIND_SPHERE 0x80000000u
 

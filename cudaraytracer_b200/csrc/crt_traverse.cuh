@@ -38,6 +38,7 @@
 //     in hitable_list.h:84.
 #pragma once
 #include "crt_device.cuh"
+#include <cuda_fp16.h>
 
 namespace crt {
 
@@ -140,17 +141,28 @@ __device__ __forceinline__ RaySlabs make_slabs(v3 o, v3 d)
     return s;
 }
 
-// The 24 box planes of a node, child-major: f[6k + {0..5}] = {lo.x, hi.x, lo.y, hi.y, lo.z, hi.z} of child k
-// (three 256-bit loads; the indices below are compile-time, so this is only a naming of registers).
-__device__ __forceinline__ void load_node_boxes(const float4* __restrict__ np, float (&f)[24])
+// A node's 24 words with three 256-bit loads (the whole record: boxes AND child references, crt_device.cuh):
+// w[5k..5k+4] = {lo.x, lo.y, lo.z, half2(ext.x, ext.y), half2(ext.z, 0)} of child k, w[20..23] = child references.
+__device__ __forceinline__ void load_node(const float4* __restrict__ np, float (&w)[24])
 {
     float4 a, b;
     ldg256(np, a, b);
-    f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+    w[0] = a.x; w[1] = a.y; w[2] = a.z; w[3] = a.w; w[4] = b.x; w[5] = b.y; w[6] = b.z; w[7] = b.w;
     ldg256(np + 2, a, b);
-    f[8] = a.x; f[9] = a.y; f[10] = a.z; f[11] = a.w; f[12] = b.x; f[13] = b.y; f[14] = b.z; f[15] = b.w;
+    w[8] = a.x; w[9] = a.y; w[10] = a.z; w[11] = a.w; w[12] = b.x; w[13] = b.y; w[14] = b.z; w[15] = b.w;
     ldg256(np + 4, a, b);
-    f[16] = a.x; f[17] = a.y; f[18] = a.z; f[19] = a.w; f[20] = b.x; f[21] = b.y; f[22] = b.z; f[23] = b.w;
+    w[16] = a.x; w[17] = a.y; w[18] = a.z; w[19] = a.w; w[20] = b.x; w[21] = b.y; w[22] = b.z; w[23] = b.w;
+}
+
+// hi = lo + ext with ext stored as a half rounded UP at build time so that this very addition gives a plane at
+// or beyond the true one (lbvh.cu:k_emit_nodes checks it with the same operation).
+__device__ __forceinline__ void child_box(const float lox, const float loy, const float loz, const float e_xy, const float e_z,
+                                          float& hix, float& hiy, float& hiz)
+{
+    const uint32_t u = __float_as_uint(e_xy), v = __float_as_uint(e_z);
+    hix = __fadd_rn(lox, __half2float(__ushort_as_half((unsigned short)(u & 0xFFFFu))));
+    hiy = __fadd_rn(loy, __half2float(__ushort_as_half((unsigned short)(u >> 16))));
+    hiz = __fadd_rn(loz, __half2float(__ushort_as_half((unsigned short)(v & 0xFFFFu))));
 }
 
 // order-preserving float <-> uint32 (for REDUX min/max over a warp)
@@ -258,17 +270,18 @@ __device__ __forceinline__ void traverse_persistent(const AccelView& A, const ui
             if (node >= 0) {
                 const float4* np = A.nodes + 8 * (size_t)(uint32_t)node;
                 float f[24];
-                load_node_boxes(np, f);
-                const int4 refs = __ldg(reinterpret_cast<const int4*>(np + 6));
+                load_node(np, f);
                 if (COUNT) { cnt.nodes++; ray_steps++; cnt.max_steps = max(cnt.max_steps, ray_steps); }
                 float key[4];
-                int ref[4] = {refs.x, refs.y, refs.z, refs.w};
+                int ref[4] = {__float_as_int(f[20]), __float_as_int(f[21]), __float_as_int(f[22]), __float_as_int(f[23])};
                 int n_hit = 0;
 #pragma unroll
                 for (int k = 0; k < 4; k++) {
-                    const float ax = fmaf(f[6 * k], S.ix, S.cx_lo), bx = fmaf(f[6 * k + 1], S.ix, S.cx_hi);
-                    const float ay = fmaf(f[6 * k + 2], S.iy, S.cy_lo), by = fmaf(f[6 * k + 3], S.iy, S.cy_hi);
-                    const float az = fmaf(f[6 * k + 4], S.iz, S.cz_lo), bz = fmaf(f[6 * k + 5], S.iz, S.cz_hi);
+                    float hx, hy, hz;
+                    child_box(f[5 * k], f[5 * k + 1], f[5 * k + 2], f[5 * k + 3], f[5 * k + 4], hx, hy, hz);
+                    const float ax = fmaf(f[5 * k], S.ix, S.cx_lo), bx = fmaf(hx, S.ix, S.cx_hi);
+                    const float ay = fmaf(f[5 * k + 1], S.iy, S.cy_lo), by = fmaf(hy, S.iy, S.cy_hi);
+                    const float az = fmaf(f[5 * k + 2], S.iz, S.cz_lo), bz = fmaf(hz, S.iz, S.cz_hi);
                     const float tn = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), t_min));
                     const float tf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), best.t));
                     const bool h = tn <= tf * 1.0000005f && ref[k] != CRT_SLOT_EMPTY;
@@ -400,18 +413,20 @@ __device__ __forceinline__ void traverse_packets(const AccelView& A, const uint3
                 for (;;) {
                     if (node >= 0) {
                         const float4* np = A.nodes + 8 * (size_t)(uint32_t)node;
-                        const int4 refs = __ldg(reinterpret_cast<const int4*>(np + 6));
+                        const int4 refs = __ldg(reinterpret_cast<const int4*>(np + 5));
                         float key[4];
                         int ref[4] = {refs.x, refs.y, refs.z, refs.w};
                         int n_hit = 0;
                         if (COUNT && lane == 0) cnt.node_f++;
                         if (uni) {
                             if (COUNT && lane == 0) cnt.nodes++;       // one interval test serves the packet
-                            const float2* cp = reinterpret_cast<const float2*>(np) + 3u * kid;
-                            const float2 bx = __ldg(cp), by = __ldg(cp + 1), bz = __ldg(cp + 2);
-                            const float ax0 = bx.x - o0x, ax1 = bx.y - o0x;
-                            const float ay0 = by.x - o0y, ay1 = by.y - o0y;
-                            const float az0 = bz.x - o0z, az1 = bz.y - o0z;
+                            const float* cp = reinterpret_cast<const float*>(np) + 5u * kid;
+                            const float clx = __ldg(cp), cly = __ldg(cp + 1), clz = __ldg(cp + 2);
+                            float chx, chy, chz;
+                            child_box(clx, cly, clz, __ldg(cp + 3), __ldg(cp + 4), chx, chy, chz);
+                            const float ax0 = clx - o0x, ax1 = chx - o0x;
+                            const float ay0 = cly - o0y, ay1 = chy - o0y;
+                            const float az0 = clz - o0z, az1 = chz - o0z;
                             const float x00 = ax0 * ix_lo, x01 = ax0 * ix_hi, x10 = ax1 * ix_lo, x11 = ax1 * ix_hi;
                             const float y00 = ay0 * iy_lo, y01 = ay0 * iy_hi, y10 = ay1 * iy_lo, y11 = ay1 * iy_hi;
                             const float z00 = az0 * iz_lo, z01 = az0 * iz_hi, z10 = az1 * iz_lo, z11 = az1 * iz_hi;
@@ -445,13 +460,15 @@ __device__ __forceinline__ void traverse_packets(const AccelView& A, const uint3
                             }
                         } else {
                             float f[24];
-                            load_node_boxes(np, f);
+                            load_node(np, f);
                             if (COUNT && live) cnt.nodes++;
 #pragma unroll
                             for (int k = 0; k < 4; k++) {
-                                const float ax = fmaf(f[6 * k], S.ix, S.cx_lo), bx = fmaf(f[6 * k + 1], S.ix, S.cx_hi);
-                                const float ay = fmaf(f[6 * k + 2], S.iy, S.cy_lo), by = fmaf(f[6 * k + 3], S.iy, S.cy_hi);
-                                const float az = fmaf(f[6 * k + 4], S.iz, S.cz_lo), bz = fmaf(f[6 * k + 5], S.iz, S.cz_hi);
+                                float hx, hy, hz;
+                                child_box(f[5 * k], f[5 * k + 1], f[5 * k + 2], f[5 * k + 3], f[5 * k + 4], hx, hy, hz);
+                                const float ax = fmaf(f[5 * k], S.ix, S.cx_lo), bx = fmaf(hx, S.ix, S.cx_hi);
+                                const float ay = fmaf(f[5 * k + 1], S.iy, S.cy_lo), by = fmaf(hy, S.iy, S.cy_hi);
+                                const float az = fmaf(f[5 * k + 2], S.iz, S.cz_lo), bz = fmaf(hz, S.iz, S.cz_hi);
                                 const float tn = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), t_min));
                                 const float tf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), best.t));
                                 const bool h = live && tn <= tf * 1.0000005f;

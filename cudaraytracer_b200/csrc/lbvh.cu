@@ -19,6 +19,7 @@
 //                       node always covers a contiguous range of sorted primitives)
 // Refit = steps 5 and 6 on the existing topology.
 #include "crt_internal.h"
+#include <cuda_fp16.h>
 #include "crt_traverse.cuh"
 
 namespace crt {
@@ -257,6 +258,16 @@ k_fit(const float* __restrict__ tri_in, const uint32_t* __restrict__ tri_mat, co
 // nodes reachable from the root through slot references are ever fetched.
 struct Slot { int ref; Box box; };
 
+// The extent hi - lo as a half, rounded up until the traversal's own reconstruction lo + half (one fp32 addition,
+// crt_traverse.cuh:child_box) reaches hi; +inf when the extent is beyond the half range (the box is then open
+// upwards, which is conservative).
+__device__ __forceinline__ uint32_t half_extent_up(float lo, float hi)
+{
+    unsigned short h = __half_as_ushort(__float2half_ru(hi - lo));
+    while (h < 0x7C00u && __fadd_rn(lo, __half2float(__ushort_as_half(h))) < hi) h++;
+    return (uint32_t)h;
+}
+
 __device__ __forceinline__ bool resolve_child(int c, int leaf_max, const int2* __restrict__ range,
                                               const float4* __restrict__ leaf_box, const float4* __restrict__ node_box,
                                               Slot& out)
@@ -315,16 +326,17 @@ k_emit_nodes(int n, int leaf_max, const int2* __restrict__ child, const int2* __
         slot[s].box = Box{0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     }
     float4* np = nodes + 8 * (size_t)i;
-    float v[24];                                              // child-major: {lo.x, hi.x, lo.y, hi.y, lo.z, hi.z} per slot
+    uint32_t w[24];                                           // layout: crt_device.cuh
     for (int s = 0; s < 4; s++) {
-        v[6 * s] = slot[s].box.lx; v[6 * s + 1] = slot[s].box.hx;
-        v[6 * s + 2] = slot[s].box.ly; v[6 * s + 3] = slot[s].box.hy;
-        v[6 * s + 4] = slot[s].box.lz; v[6 * s + 5] = slot[s].box.hz;
+        const Box& b = slot[s].box;
+        w[5 * s] = __float_as_uint(b.lx); w[5 * s + 1] = __float_as_uint(b.ly); w[5 * s + 2] = __float_as_uint(b.lz);
+        const uint32_t ex = half_extent_up(b.lx, b.hx), ey = half_extent_up(b.ly, b.hy), ez = half_extent_up(b.lz, b.hz);
+        w[5 * s + 3] = ex | (ey << 16);
+        w[5 * s + 4] = ez;
+        w[20 + s] = (uint32_t)slot[s].ref;
     }
-    for (int q = 0; q < 6; q++) np[q] = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
-    np[6] = make_float4(__int_as_float(slot[0].ref), __int_as_float(slot[1].ref), __int_as_float(slot[2].ref),
-                        __int_as_float(slot[3].ref));
-    np[7] = make_float4(0.f, 0.f, 0.f, 0.f);
+    uint4* nw = reinterpret_cast<uint4*>(np);
+    for (int q = 0; q < 6; q++) nw[q] = make_uint4(w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
 }
 
 __global__ void __launch_bounds__(256)
