@@ -263,7 +263,11 @@ def run_ours(args):
             ctx.resolve_device(accum.data_ptr(), nx * ny, spp * world if weak else spp, rgb.data_ptr())
 
     def e2e_step(seed):
-        if world == 1:
+        if world == 1 and args.e2e_api == "frame":
+            # the reference's loop body (render.h:206-233) as one call: upload + refit overlap ray generation,
+            # finished rows are read back while the rest of the frame renders
+            ctx.render_frame(host_verts.numpy(), cam, nx, ny, spp, depth, crt.SHADE_PATH, seed, out=host_rgb.numpy())
+        elif world == 1:
             ctx.update_vertices(host_verts.numpy())
             ctx.refit()
             ctx.render(cam, nx, ny, spp, depth, crt.SHADE_PATH, seed, out=host_rgb.numpy())
@@ -376,7 +380,9 @@ def run_ours(args):
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "Mrays/s", "ms_per_step": 1e3 * e2e_s / args.steps,
                     "h2d_bytes_per_step": int(host_verts.numel() * 4 + 88), "d2h_bytes_per_step": int(nx * ny * 12),
-                    "what": "crt_scene_update_vertices + crt_accel_refit + crt_render per frame, host buffers, wall clock"},
+                    "what": ("crt_render_frame (vertex upload + refit + render + read-back, overlapped) per frame, pinned host buffers, wall clock"
+                             if world == 1 and args.e2e_api == "frame" else
+                             "crt_scene_update_vertices + crt_accel_refit + crt_render per frame, host buffers, wall clock")},
             "gpu_launches": launches,
             "roofline": {"kernel": "closest hit over the 4-wide LBVH: k_trace_packet (camera rays) + k_trace_queue (bounces), %d launches/step" % bounce_launches,
                          "bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
@@ -424,6 +430,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--lanes", type=int, default=4, help="CRT_OPT_LANES of the timed region (1 for profiling: one slice, launches in bounce order)")
+    ap.add_argument("--e2e-api", default="frame", choices=["frame", "calls"],
+                    help="N = 1 end-to-end loop: crt_render_frame (one overlapped call per frame) or the three separate calls")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="N > 1: weak = every rank renders the full 16-spp frame's work on its own sample range "
                          "(default); strong = the 16-spp frame is split by tiles")

@@ -25,7 +25,7 @@ TILE = 32
 ABI_SYMBOLS = [
     "crt_abi_version", "crt_create", "crt_destroy", "crt_last_error", "crt_set_option", "crt_sync", "crt_stream",
     "crt_scene_set_materials", "crt_scene_set_triangles", "crt_scene_set_spheres", "crt_scene_update_vertices",
-    "crt_accel_build", "crt_accel_refit", "crt_trace", "crt_trace_device", "crt_render",
+    "crt_accel_build", "crt_accel_refit", "crt_trace", "crt_trace_device", "crt_render", "crt_render_frame",
     "crt_render_accum_device", "crt_resolve_device", "crt_pack_rgba8_device", "crt_get_counters",
     "crt_reset_counters", "crt_accel_info",
 ]
@@ -91,6 +91,7 @@ def load_library():
     lib.crt_trace.argtypes = [vp, vp, sz, C.c_float, C.c_float, C.c_int, vp]
     lib.crt_trace_device.argtypes = [vp, vp, sz, C.c_float, C.c_float, C.c_int, vp]
     lib.crt_render.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint64, vp]
+    lib.crt_render_frame.argtypes = [vp, vp, sz, sz, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint64, vp]
     lib.crt_render_accum_device.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                             C.c_uint64, C.c_int, C.c_int, vp]
     lib.crt_resolve_device.argtypes = [vp, vp, sz, C.c_int, vp]
@@ -247,6 +248,20 @@ class Context:
         assert cam.size == 22
         rgb = np.empty((ny, nx, 3), np.float32) if out is None else out
         self._check(self.lib.crt_render(self._h, _ptr(cam), nx, ny, spp, max_depth, int(mode), int(seed), _ptr(rgb)))
+        return rgb
+
+    def render_frame(self, verts, cam22, nx, ny, spp, max_depth=8, mode=SHADE_PATH, seed=1, out=None, first=0):
+        """One animation frame: new vertices for triangles [first, first+len(verts)), refit, render, read back
+        (crt_render_frame: the three steps overlap). verts may be None for a frame without a geometry change."""
+        cam = np.ascontiguousarray(cam22, np.float32)
+        assert cam.size == 22
+        n = 0
+        if verts is not None:
+            verts = np.ascontiguousarray(verts, np.float32).reshape(-1, 9)
+            n = verts.shape[0]
+        rgb = np.empty((ny, nx, 3), np.float32) if out is None else out
+        self._check(self.lib.crt_render_frame(self._h, _ptr(verts), int(first), n, _ptr(cam), nx, ny, spp, max_depth,
+                                              int(mode), int(seed), _ptr(rgb)))
         return rgb
 
     def render_accum_device(self, cam22, nx, ny, s0, s1, max_depth, mode, seed, rank, world, d_accum_ptr):

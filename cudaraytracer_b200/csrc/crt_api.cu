@@ -100,6 +100,10 @@ int crt_create(int device, crt_ctx** out)
     CRT_CUDA(cudaEventCreate(&c->ev0));
     CRT_CUDA(cudaEventCreate(&c->ev1));
     CRT_CUDA(cudaEventCreate(&c->ev_fork));
+    CRT_CUDA(cudaStreamCreateWithFlags(&c->up_stream, cudaStreamNonBlocking));
+    CRT_CUDA(cudaEventCreate(&c->ev_up0));
+    CRT_CUDA(cudaEventCreate(&c->ev_up1));
+    CRT_CUDA(cudaEventCreate(&c->ev_frame));
     for (int l = 0; l < CRT_MAX_LANES; l++) {
         crt_lane& L = c->lane[l];
         if (l == 0) L.stream = c->stream;
@@ -130,6 +134,10 @@ void crt_destroy(crt_ctx* c)
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+    if (c->up_stream) { cudaStreamSynchronize(c->up_stream); cudaStreamDestroy(c->up_stream); }
+    if (c->ev_up0) cudaEventDestroy(c->ev_up0);
+    if (c->ev_up1) cudaEventDestroy(c->ev_up1);
+    if (c->ev_frame) cudaEventDestroy(c->ev_frame);
     for (int l = 0; l < CRT_MAX_LANES; l++) {
         crt_lane& L = c->lane[l];
         if (L.stream) cudaStreamSynchronize(L.stream);
@@ -344,22 +352,67 @@ int crt_pack_rgba8_device(crt_ctx* c, const float* d_rgb, int nx, int ny, uint8_
     return launch_pack_rgba8(c, d_rgb, nx, ny, d_rgba8);
 }
 
+// render + resolve + read-back of one frame; `scene_ready`: event the closest-hit launches wait for (or null)
+static int render_to_host(crt_ctx* c, const crt_camera* cam, int nx, int ny, int spp, int max_depth, int shade_mode,
+                          uint64_t seed, float* rgb_out, cudaEvent_t scene_ready)
+{
+    const size_t npix = (size_t)nx * ny;
+    CRT_CUDA(c->accum.reserve(npix * 12));
+    CRT_CUDA(c->rgb.reserve(npix * 12));
+    // every slice of the frame resolves and returns its own rows as soon as they are final (render.cu)
+    RenderFinish fin = {c->rgb.as<float>(), rgb_out, spp, false};
+    int r = render_accum(c, cam, nx, ny, 0, spp, max_depth, shade_mode, seed, 0, 1, c->accum.as<float>(), &fin, scene_ready);
+    if (r != CRT_OK) return r;
+    if (!fin.done) {
+        if ((r = launch_resolve(c, c->accum.as<float>(), npix, spp, c->rgb.as<float>())) != CRT_OK) return r;
+        CRT_CUDA(cudaMemcpyAsync(rgb_out, c->rgb.p, npix * 12, cudaMemcpyDeviceToHost, c->stream));
+    }
+    CRT_CUDA(cudaStreamSynchronize(c->stream));
+    CRT_CUDA(cudaGetLastError());
+    return CRT_OK;
+}
+
 int crt_render(crt_ctx* c, const crt_camera* cam, int nx, int ny, int spp, int max_depth, int shade_mode,
                uint64_t seed, float* rgb_out)
 {
     CRT_CHECK_CTX(c);
     if (!rgb_out) { set_error("crt_render: rgb_out is null"); return CRT_ERR_INVALID; }
     if (nx <= 0 || ny <= 0 || spp < 1) { set_error("crt_render: nx, ny and spp must be positive"); return CRT_ERR_INVALID; }
-    const size_t npix = (size_t)nx * ny;
-    CRT_CUDA(c->accum.reserve(npix * 12));
-    CRT_CUDA(c->rgb.reserve(npix * 12));
-    int r = render_accum(c, cam, nx, ny, 0, spp, max_depth, shade_mode, seed, 0, 1, c->accum.as<float>());
-    if (r != CRT_OK) return r;
-    if ((r = launch_resolve(c, c->accum.as<float>(), npix, spp, c->rgb.as<float>())) != CRT_OK) return r;
-    CRT_CUDA(cudaMemcpyAsync(rgb_out, c->rgb.p, npix * 12, cudaMemcpyDeviceToHost, c->stream));
-    CRT_CUDA(cudaStreamSynchronize(c->stream));
-    CRT_CUDA(cudaGetLastError());
-    return CRT_OK;
+    return render_to_host(c, cam, nx, ny, spp, max_depth, shade_mode, seed, rgb_out, nullptr);
+}
+
+// One frame of the reference's animation loop (render.h:206-233: updateFBXObj, Update_BVH, render, copy back) as ONE
+// call, so that the steps can overlap: the vertex upload and the refit run on their own stream while the slices
+// generate their camera rays, and each slice's rows travel back while the others still render.
+int crt_render_frame(crt_ctx* c, const float* verts, size_t first, size_t n, const crt_camera* cam, int nx, int ny,
+                     int spp, int max_depth, int shade_mode, uint64_t seed, float* rgb_out)
+{
+    CRT_CHECK_CTX(c);
+    if (!rgb_out) { set_error("crt_render_frame: rgb_out is null"); return CRT_ERR_INVALID; }
+    if (nx <= 0 || ny <= 0 || spp < 1) { set_error("crt_render_frame: nx, ny and spp must be positive"); return CRT_ERR_INVALID; }
+    if (n > 0 && !verts) { set_error("crt_render_frame: null vertex array"); return CRT_ERR_INVALID; }
+    if (first + n > c->n_tri) { set_error("crt_render_frame: range [%zu, %zu) exceeds %zu triangles", first, first + n, c->n_tri); return CRT_ERR_INVALID; }
+    if (!c->accel_valid || c->n_prims != (uint32_t)(c->n_tri + c->n_sph)) {
+        set_error("crt_render_frame: call crt_accel_build first (a frame only refits)");
+        return CRT_ERR_STATE;
+    }
+    cudaStream_t up = c->up_stream;
+    if (n > 0) {
+        CRT_CUDA(c->rays_tmp.reserve(n * 36));
+        CRT_CUDA(cudaMemcpyAsync(c->rays_tmp.p, verts, n * 36, cudaMemcpyHostToDevice, up));
+        const size_t nv = n * 9;
+        k_update_vertices<<<(unsigned int)((nv + 255) / 256), 256, 0, up>>>(c->rays_tmp.as<float>(), nv, first, c->tri_in.as<float>());
+        CRT_CUDA(cudaGetLastError());
+        c->host_counters.launches++;
+    }
+    int r = lbvh_build(c, true, up);
+    if (r != CRT_OK) { cudaStreamSynchronize(up); return r; }
+    CRT_CUDA(cudaEventRecord(c->ev_frame, up));
+    r = render_to_host(c, cam, nx, ny, spp, max_depth, shade_mode, seed, rgb_out, c->ev_frame);
+    CRT_CUDA(cudaStreamSynchronize(up));
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, c->ev_up0, c->ev_up1) == cudaSuccess) c->host_counters.refit_ms = ms;
+    return r;
 }
 
 int crt_get_counters(crt_ctx* c, crt_counters* out)

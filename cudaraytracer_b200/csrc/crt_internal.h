@@ -69,6 +69,8 @@ struct crt_ctx {
     int sm_count = 148;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_fork = nullptr;
+    cudaStream_t up_stream = nullptr;      // crt_render_frame: vertex upload + refit, overlapped with ray generation
+    cudaEvent_t ev_up0 = nullptr, ev_up1 = nullptr, ev_frame = nullptr;
     crt_lane lane[CRT_MAX_LANES];
     int n_lanes = 4;                       // CRT_OPT_LANES: most slices of a frame in flight
 
@@ -112,15 +114,20 @@ int radix_sort_pairs(cudaStream_t stream, uint64_t* keys[2], uint32_t* vals[2], 
 size_t radix_sort_hist_bytes();
 
 // lbvh.cu
-int lbvh_build(crt_ctx* c, bool refit_only);
+int lbvh_build(crt_ctx* c, bool refit_only, cudaStream_t async = nullptr);
 
 // trace.cu
 int launch_trace(crt_ctx* c, const crt_ray* d_rays, size_t n, float t_min, float t_max, int accel, crt_hit* d_hits);
 AccelView accel_view(const crt_ctx* c);
 
 // render.cu
+// finish (world == 1 only): every slice resolves the rows it owns into d_rgb and copies them to h_rgb as soon as
+// its last sample batch is accumulated, on its own stream; *done says whether that happened.
+struct RenderFinish { float* d_rgb; float* h_rgb; int spp; bool done; };
+// scene_ready: the closest-hit launches (not ray generation) wait for this event
 int render_accum(crt_ctx* c, const crt_camera* cam, int nx, int ny, int s0, int s1, int max_depth, int mode,
-                 uint64_t seed, int rank, int world, float* d_accum);
+                 uint64_t seed, int rank, int world, float* d_accum, RenderFinish* finish = nullptr,
+                 cudaEvent_t scene_ready = nullptr);
 int launch_resolve(crt_ctx* c, const float* d_accum, size_t n_pixels, int spp, float* d_rgb);
 int launch_pack_rgba8(crt_ctx* c, const float* d_rgb, int nx, int ny, uint8_t* d_rgba8);
 

@@ -638,23 +638,27 @@ static int ploc_topology(crt_ctx* c, const float* tri_in, const float* sph_in, u
     return CRT_OK;
 }
 
-int lbvh_build(crt_ctx* c, bool refit_only)
+// `async` (refit only): enqueue on that stream and return without waiting; the caller orders its readers behind
+// c->ev_up1 and reads the duration from (ev_up0, ev_up1) once it has synchronised (crt_render_frame).
+int lbvh_build(crt_ctx* c, bool refit_only, cudaStream_t async)
 {
     const size_t n = c->n_tri + c->n_sph;
     if (n >= (1ull << 28)) { set_error("too many primitives (%zu), limit is 2^28", n); return CRT_ERR_INVALID; }
-    cudaStream_t st = c->stream;
+    if (async && !refit_only) { set_error("lbvh_build: only a refit can be queued without waiting"); return CRT_ERR_INVALID; }
+    cudaStream_t st = async ? async : c->stream;
+    cudaEvent_t ev_begin = async ? c->ev_up0 : c->ev0, ev_end = async ? c->ev_up1 : c->ev1;
     if (refit_only && (!c->accel_valid || c->n_prims != (uint32_t)n)) {
         set_error("crt_accel_refit: no acceleration structure for the current primitive count");
         return CRT_ERR_STATE;
     }
     c->n_prims = (uint32_t)n;
-    CRT_CUDA(cudaEventRecord(c->ev0, st));
+    CRT_CUDA(cudaEventRecord(ev_begin, st));
     if (n == 0) {
         c->accel_valid = true;
         c->root = -1;
         c->tree_depth = 0;
-        CRT_CUDA(cudaEventRecord(c->ev1, st));
-        CRT_CUDA(cudaEventSynchronize(c->ev1));
+        CRT_CUDA(cudaEventRecord(ev_end, st));
+        if (!async) CRT_CUDA(cudaEventSynchronize(ev_end));
         return CRT_OK;
     }
     const float* tri_in = c->tri_in.as<float>();
@@ -710,7 +714,8 @@ int lbvh_build(crt_ctx* c, bool refit_only)
                                                            c->leaf_box.as<float4>(), c->node_box.as<float4>(),
                                                            c->nodes.as<float4>());
     c->root = (n <= (size_t)leaf_max) ? ~(int)(n - 1) : 0;
-    CRT_CUDA(cudaEventRecord(c->ev1, st));
+    CRT_CUDA(cudaEventRecord(ev_end, st));
+    if (async) { CRT_CUDA(cudaGetLastError()); return CRT_OK; }
     if (!refit_only) {
         CRT_CUDA(cudaMemsetAsync(c->depth_out.p, 0, sizeof(int), st));
         if (n > 1)

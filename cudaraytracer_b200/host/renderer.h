@@ -10,6 +10,7 @@
 //   updateFBXObj                createScene.h:125      update_vertices(...)        crt_scene_update_vertices
 //   Update_BVH                  createScene.h:53       Update_BVH()                crt_accel_refit
 //   render<<<>>> + D2H copy     render.h:105,222-226   render(colorBuffer, ...)    crt_render
+//   the loop body as a whole    render.h:206-233       render_frame(...)           crt_render_frame (steps overlapped)
 //   WritePng                    render.h:135           WritePng (png_out.h)        -
 //   StopWatch + writeCSV        swatch.h, CSVWriter.h  counters(), write_csv()     crt_get_counters
 //
@@ -70,6 +71,17 @@ public:
         static_assert(sizeof(vec3) == 3 * sizeof(float), "vec3 must be three packed floats");
         const crt_camera cam = camera.to_crt();
         check(crt_render(ctx_, &cam, nx, ny, samples, max_depth, shade_mode, seed, &colorBuffer[0].e[0]), "crt_render");
+    }
+
+    // One iteration of the animation loop (render.h:206-233): new pose, refit, render, copy back - one call, so the
+    // upload and refit overlap ray generation and finished rows come back while the rest renders. Same image as
+    // update_vertices + Update_BVH + render.
+    void render_frame(const float* verts, size_t first, size_t n, vec3* colorBuffer, const Camera& camera, int nx, int ny,
+                      int samples, int max_depth, int shade_mode = CRT_SHADE_LAMBERT, uint64_t seed = 0)
+    {
+        const crt_camera cam = camera.to_crt();
+        check(crt_render_frame(ctx_, verts, first, n, &cam, nx, ny, samples, max_depth, shade_mode, seed, &colorBuffer[0].e[0]),
+              "crt_render_frame");
     }
 
     // (*world)->hit for a batch of rays (render.h:53).

@@ -207,6 +207,20 @@ int crt_trace_device(crt_ctx* ctx, const crt_ray* d_rays, size_t n, float t_min,
 int crt_render(crt_ctx* ctx, const crt_camera* cam, int nx, int ny, int spp, int max_depth,
                int shade_mode, uint64_t seed, float* rgb_out);
 
+/* One iteration of the reference's animation loop as a single call:
+ * updateFBXObj + Update_BVH + render<<<>>> + the D2H copy
+ * (core/render.h:206-233, createScene.h:46-58,125-140). Same results as
+ * crt_scene_update_vertices(verts, first, n) + crt_accel_refit + crt_render,
+ * but the steps overlap: upload and refit run on their own stream while the
+ * camera rays are generated, and finished rows are copied back while the rest
+ * of the frame still renders. n may be 0 (no geometry change). verts and
+ * rgb_out must stay untouched until the call returns (it returns when the frame
+ * is in rgb_out); page-locked buffers are what makes the copies overlap.
+ * Needs a built acceleration structure (crt_accel_build). */
+int crt_render_frame(crt_ctx* ctx, const float* verts, size_t first, size_t n,
+                     const crt_camera* cam, int nx, int ny, int spp, int max_depth,
+                     int shade_mode, uint64_t seed, float* rgb_out);
+
 /* Multi-GPU building blocks (device pointers, asynchronous on crt_stream()).
  * crt_render_accum_device adds nothing to d_accum: it overwrites it with, per
  * pixel this part owns, the sum over samples [sample_begin, sample_end) in

@@ -298,3 +298,10 @@ def test_cli_animation_loop_writes_every_frame(tmp_path):
     rows = [l.split(",") for l in open(csv).read().strip().split("\n")]
     assert rows[0] == ["frame", "rendering", "update", "build"] and len(rows) == 4
     assert float(rows[1][3]) > 0 and float(rows[2][3]) == 0 and float(rows[2][2]) > 0
+    # the same loop through Renderer::render_frame (crt_render_frame: one overlapped call per frame): same pictures
+    prefix2 = str(tmp_path / "g_")
+    r = subprocess.run([CLI, "--scene", "mesh", "--segments", "64", "--nx", "160", "--ny", "90", "--spp", "2", "--mode", "path",
+                        "--frames", "3", "--animate", "--overlap", "--out", prefix2, "--quiet"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    for i in range(3):
+        assert np.array_equal(decode_png(prefix2 + "%d.png" % i), imgs[i])
