@@ -438,7 +438,9 @@ __device__ __forceinline__ void traverse_packets(const AccelView& A, const uint3
                             tf = fmaf(fabsf(tf), 4.76837158203125e-7f, tf);        // and "leaves later"
                             tn = fmaxf(tn, t_min);
                             tf = fminf(tf, t_far);
-                            const int my_ref = kid == 0u ? refs.x : kid == 1u ? refs.y : kid == 2u ? refs.z : refs.w;
+                            // two-level select on the bits of kid (a chain of ?: compiles to divergent branches)
+                            const int ref_lo = (kid & 1u) ? refs.y : refs.x, ref_hi = (kid & 1u) ? refs.w : refs.z;
+                            const int my_ref = (kid & 2u) ? ref_hi : ref_lo;
                             const bool enter = tn <= tf && my_ref != CRT_SLOT_EMPTY;
                             const uint32_t m4 = __ballot_sync(FULL, enter) & 0xFu;
                             if ((m4 & (m4 - 1u)) == 0u) {
@@ -447,7 +449,8 @@ __device__ __forceinline__ void traverse_packets(const AccelView& A, const uint3
                                     if (sp == 0u) break;
                                     node = wstack[--sp];
                                 } else {
-                                    node = (m4 & 1u) ? refs.x : (m4 & 2u) ? refs.y : (m4 & 4u) ? refs.z : refs.w;
+                                    const int e_lo = (m4 & 1u) ? refs.x : refs.y, e_hi = (m4 & 4u) ? refs.z : refs.w;
+                                    node = (m4 & 3u) ? e_lo : e_hi;
                                 }
                                 continue;
                             }
