@@ -17,6 +17,7 @@ MISS = 0xFFFFFFFF
 SHADE_PATH, SHADE_LAMBERT, SHADE_NORMAL = 0, 1, 2
 ACCEL_LBVH, ACCEL_BRUTE, ACCEL_LBVH_PACKET = 0, 1, 2
 OPT_LEAF_MAX, OPT_COUNTERS, OPT_BATCH_PATHS, OPT_REFILL, OPT_LEAF_THRESH, OPT_PACKET_PRIMARY, OPT_LANES, OPT_BUILDER = 1, 2, 3, 4, 5, 6, 7, 8
+OPT_WIDE_BELOW = 9
 BUILDER_LBVH, BUILDER_PLOC = 0, 1
 TEX_CONSTANT, TEX_CHECKER = 0, 1
 TILE = 32

@@ -179,6 +179,10 @@ int crt_set_option(crt_ctx* c, int option, int64_t value)
         if (value != CRT_BUILDER_LBVH && value != CRT_BUILDER_PLOC) { set_error("CRT_OPT_BUILDER must be CRT_BUILDER_LBVH or CRT_BUILDER_PLOC"); return CRT_ERR_INVALID; }
         c->builder = (int)value;
         return CRT_OK;
+    case CRT_OPT_WIDE_BELOW:
+        if (value < 0 || value > (1ll << 31) - 1) { set_error("CRT_OPT_WIDE_BELOW must be in [0, 2^31)"); return CRT_ERR_INVALID; }
+        c->wide_below = (int64_t)value;
+        return CRT_OK;
     case CRT_OPT_LANES:
         if (value < 1 || value > CRT_MAX_LANES) { set_error("CRT_OPT_LANES must be in [1, %d]", CRT_MAX_LANES); return CRT_ERR_INVALID; }
         c->n_lanes = (int)value;

@@ -101,6 +101,7 @@ struct crt_ctx {
     int leaf_thresh = 8;                   // parked lanes that trigger the primitive-test phase
     int refill = 8;                        // idle lanes that trigger a refill in the persistent traversal
     int packet_primary = 1;                // camera rays through the packet kernel
+    int64_t wide_below = 32768;            // CRT_OPT_WIDE_BELOW: bounces with fewer rays run one warp per ray
     int64_t batch_paths = 1ll << 25;
 
     crt_counters host_counters = {};

@@ -533,4 +533,159 @@ __device__ __forceinline__ void traverse_packets(const AccelView& A, const uint3
     }
 }
 
+// ---------------------------------------------------------------------------
+// Wide form for launches with FEW rays (the last bounces of a frame: 20,000 rays
+// down to a handful). There the per-ray kernel is bound by its longest ray: a
+// grazing ray walks 200-700 DEPENDENT node visits while 99.9 % of the GPU idles
+// (bounces 3-8 of a C3 frame: 0.04 % of the rays, 7 % of the frame). Here a whole
+// warp works on ONE ray: the stack lives in shared memory and every round the 32
+// lanes pop up to 32 entries at once - each lane tests the four children of its
+// node (or the primitives of its leaf) against the same ray - and push what was
+// entered, so a ray's node visits are processed 32 abreast and only the depth of
+// the tree is left as a dependent chain. Closest hits are merged once per round
+// (minimum t, then lowest id). The primitive tests and the tie rule are those of
+// traverse_persistent, and the result of a closest-hit query does not depend on
+// the visiting order, so the hits are the same bit for bit.
+//
+// Stack bound: a round that pops p entries pushes <= 4 p. Wide rounds keep the
+// stack below CRT_WIDE_STACK - CRT_STACK_ENTRIES; past that the warp pops one
+// entry per round, which is a depth-first walk and adds <= CRT_STACK_ENTRIES
+// (3 per level, see above) to what was there.
+#define CRT_WIDE_STACK 1024   // entries {reference, entry distance} per warp: 8 KB
+
+template <bool COUNT, bool HAS_SPH, class Src, class Sink>
+__device__ __forceinline__ void traverse_wide(const AccelView& A, const uint32_t n, uint32_t* work_ctr,
+                                              const float t_min, const float t_max, const Src& src,
+                                              const Sink& sink, uint2* s_stack, TraceCounters& cnt)
+{
+    constexpr uint32_t FULL = 0xffffffffu;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    constexpr uint32_t WIDE_LIMIT = CRT_WIDE_STACK - CRT_STACK_ENTRIES;
+
+    for (;;) {
+        uint32_t ray_i = 0;
+        if (lane == 0) ray_i = atomicAdd(work_ctr, 1u);
+        ray_i = __shfl_sync(FULL, ray_i, 0);
+        if (ray_i >= n) break;
+        v3 o, dr;
+        src.load(ray_i, o, dr);                     // the same address in every lane: one broadcast load
+        const v3 d = ray_dir_local(dr);
+        const RaySlabs S = make_slabs(o, d);
+        Hit best;                                    // warp-uniform
+        best.t = t_max; best.k = 0xFFFFFFFFu; best.id = CRT_MISS_ID; best.u = best.v = 0.f;
+        uint32_t sp = 0;                             // warp-uniform
+        if (A.n_prims != 0u) {
+            if (lane == 0) s_stack[0] = make_uint2((uint32_t)A.root, __float_as_uint(t_min));
+            sp = 1;
+        }
+        __syncwarp();
+        while (sp > 0u) {
+            uint32_t p = sp < 32u ? sp : 32u;
+            if (sp + 3u * p > WIDE_LIMIT) p = sp + 3u <= WIDE_LIMIT ? (WIDE_LIMIT - sp) / 3u : 1u;
+            const bool have = lane < p;
+            uint2 e = make_uint2(0u, 0u);
+            if (have) e = s_stack[sp - 1u - lane];   // lane 0 takes the top (the nearest child pushed last)
+            __syncwarp();
+            sp -= p;
+            const int ref = (int)e.x;
+            // still entered before the current closest hit? (same slack as the test that pushed it)
+            const bool alive = have && __uint_as_float(e.y) <= best.t * 1.0000005f;
+
+            // ---- inner node: the four children against the ray ----
+            float key[4] = {INFINITY, INFINITY, INFINITY, INFINITY};
+            int cref[4] = {0, 0, 0, 0};
+            int n_hit = 0;
+            if (alive && ref >= 0) {
+                const float4* np = A.nodes + 8 * (size_t)(uint32_t)ref;
+                float f[24];
+                load_node(np, f);
+                if (COUNT) { cnt.nodes++; cnt.node_f++; }
+                cref[0] = __float_as_int(f[20]); cref[1] = __float_as_int(f[21]);
+                cref[2] = __float_as_int(f[22]); cref[3] = __float_as_int(f[23]);
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    float hx, hy, hz;
+                    child_box(f[5 * k], f[5 * k + 1], f[5 * k + 2], f[5 * k + 3], f[5 * k + 4], hx, hy, hz);
+                    const float ax = fmaf(f[5 * k], S.ix, S.cx_lo), bx = fmaf(hx, S.ix, S.cx_hi);
+                    const float ay = fmaf(f[5 * k + 1], S.iy, S.cy_lo), by = fmaf(hy, S.iy, S.cy_hi);
+                    const float az = fmaf(f[5 * k + 2], S.iz, S.cz_lo), bz = fmaf(hz, S.iz, S.cz_hi);
+                    const float tn = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), t_min));
+                    const float tf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), best.t));
+                    const bool h = tn <= tf * 1.0000005f && cref[k] != CRT_SLOT_EMPTY;
+                    key[k] = h ? tn : INFINITY;
+                    n_hit += h ? 1 : 0;
+                }
+#define CRT_CSWAP(a, b)                                                                    \
+                {                                                                          \
+                    const bool sw = key[b] < key[a];                                       \
+                    const float ka = key[a], kb = key[b];                                  \
+                    const int ra = cref[a], rb = cref[b];                                  \
+                    key[a] = sw ? kb : ka; key[b] = sw ? ka : kb;                          \
+                    cref[a] = sw ? rb : ra; cref[b] = sw ? ra : rb;                        \
+                }
+                CRT_CSWAP(0, 1) CRT_CSWAP(2, 3) CRT_CSWAP(0, 2) CRT_CSWAP(1, 3) CRT_CSWAP(1, 2)
+#undef CRT_CSWAP
+            }
+
+            // ---- leaf: its primitives against the ray, this lane's closest candidate ----
+            float ct = INFINITY, cu = 0.f, cv = 0.f;
+            uint32_t ck = 0xFFFFFFFFu, cid = CRT_MISS_ID;
+            if (alive && ref < 0) {
+                const uint32_t lr = ~(uint32_t)ref;
+                const uint32_t k0 = lr >> 3, count = (lr & 7u) + 1u;
+                float bound = best.t;
+                for (uint32_t j = 0; j < count; j++) {
+                    const uint32_t k = k0 + j;
+                    const float4* rp = A.recs + 4 * (size_t)k;
+                    float4 r0, r1, r2, r3;
+                    ldg256(rp, r0, r1);
+                    ldg256(rp + 2, r2, r3);
+                    const uint32_t pid = __float_as_uint(r3.x);
+                    float t, u = 0.0f, v = 0.0f;
+                    bool ok;
+                    if (HAS_SPH && (__float_as_uint(r3.y) & CRT_KIND_SPHERE)) {
+                        if (COUNT) { cnt.spheres++; cnt.sph_f++; }
+                        ok = sphere_test(vsub(o, V(r0.x, r0.y, r0.z)), d, r0.w, t_min, bound, t);
+                    } else {
+                        if (COUNT) { cnt.tris++; cnt.tri_f++; }
+                        ok = triangle_test(o, d, V(r0.x, r0.y, r0.z), V(r1.x, r1.y, r1.z), V(r2.x, r2.y, r2.z),
+                                           V(r0.w, r1.w, r2.w), t_min, bound, t, u, v);
+                    }
+                    // against this lane's candidate: nearer, or as near with a lower id
+                    if (ok && (t < ct || (t == ct && pid < cid))) { ct = t; ck = k; cid = pid; cu = u; cv = v; bound = t; }
+                }
+            }
+
+            // ---- push the entered children, farthest first: 4 passes, pass c holds every lane's c-th farthest ----
+#pragma unroll
+            for (int c = 3; c >= 0; c--) {
+                const bool has = n_hit > c;
+                const uint32_t m = __ballot_sync(FULL, has);
+                // within a pass the lane that popped the top of the stack writes last, so its children end on top
+                if (has) s_stack[sp + (uint32_t)__popc(m & ~lt_mask & ~(1u << lane))] = make_uint2((uint32_t)cref[c], __float_as_uint(key[c]));
+                sp += (uint32_t)__popc(m);
+            }
+
+            // ---- merge the round's candidates into the closest hit: minimum t, then lowest id ----
+            const uint32_t any = __ballot_sync(FULL, ck != 0xFFFFFFFFu);
+            if (any) {
+                const uint32_t tbits = __float_as_uint(ct);                   // t > 0: bit patterns order like values
+                const uint32_t tmin = __reduce_min_sync(FULL, ck != 0xFFFFFFFFu ? tbits : 0xFFFFFFFFu);
+                const bool at_min = ck != 0xFFFFFFFFu && tbits == tmin;
+                const uint32_t idmin = __reduce_min_sync(FULL, at_min ? cid : 0xFFFFFFFFu);
+                const uint32_t w = (uint32_t)__ffs(__ballot_sync(FULL, at_min && cid == idmin)) - 1u;
+                const float wt = __uint_as_float(tmin);
+                const uint32_t wk = __shfl_sync(FULL, ck, w);
+                const float wu = __shfl_sync(FULL, cu, w), wv = __shfl_sync(FULL, cv, w);
+                // the rule of traverse_persistent: t == t_max itself never counts, equal t keeps the lower id
+                bool take = wt < best.t || (wt == best.t && best.k != 0xFFFFFFFFu && idmin < best.id);
+                if (take) { best.t = wt; best.k = wk; best.id = idmin; best.u = wu; best.v = wv; }
+            }
+            __syncwarp();
+        }
+        if (lane == 0) sink.store(ray_i, best);
+    }
+}
+
 }  // namespace crt

@@ -212,13 +212,15 @@ template <bool COUNT, bool HAS_SPH>
 __global__ void __launch_bounds__(TP_BLOCK, CRT_TRACE_MIN_BLOCKS)
 k_trace_queue(AccelView A, const float4* __restrict__ q, uint32_t cap, const uint32_t* __restrict__ n_ptr,
               uint32_t* __restrict__ work_ctr, float4* __restrict__ hits, unsigned long long* __restrict__ counters,
-              uint32_t refill, uint32_t leaf_thresh)
+              uint32_t refill, uint32_t leaf_thresh, uint32_t wide_below)
 {
     __shared__ int s_stack[CRT_STACK_SMEM * TP_BLOCK];
+    const uint32_t n = *n_ptr;
+    if (n < wide_below) return;                     // a launch this small belongs to k_trace_wide (queued right behind)
     TraceCounters cnt = {0u, 0u, 0u, 0u, 0u, 0u, 0u};
     QueueSrc src = {q, cap};
     QueueSink sink = {hits};
-    traverse_persistent<COUNT, HAS_SPH>(A, *n_ptr, work_ctr, 0.001f, FLT_MAX, src, sink, s_stack, cnt, refill, leaf_thresh);   // render.h:53
+    traverse_persistent<COUNT, HAS_SPH>(A, n, work_ctr, 0.001f, FLT_MAX, src, sink, s_stack, cnt, refill, leaf_thresh);   // render.h:53
     if (COUNT) {
         const uint32_t nodes = __reduce_add_sync(0xffffffffu, cnt.nodes);
         const uint32_t tris = __reduce_add_sync(0xffffffffu, cnt.tris);
@@ -232,6 +234,35 @@ k_trace_queue(AccelView A, const float4* __restrict__ q, uint32_t cap, const uin
             atomicAdd(counters + CNT_SPH_F, (unsigned long long)sph);
         }
         atomicMax(counters + CNT_MAX_STEPS, (unsigned long long)cnt.max_steps);
+    }
+}
+
+// ---- closest hit for a queue of few rays: one warp per ray (crt_traverse.cuh traverse_wide) ----
+template <bool COUNT, bool HAS_SPH>
+__global__ void __launch_bounds__(TP_BLOCK)
+k_trace_wide(AccelView A, const float4* __restrict__ q, uint32_t cap, const uint32_t* __restrict__ n_ptr,
+             uint32_t* __restrict__ work_ctr, float4* __restrict__ hits, unsigned long long* __restrict__ counters,
+             uint32_t wide_below)
+{
+    __shared__ uint2 s_stack[(TP_BLOCK / 32) * CRT_WIDE_STACK];
+    const uint32_t n = *n_ptr;
+    if (n >= wide_below) return;                    // k_trace_queue took this launch
+    TraceCounters cnt = {0u, 0u, 0u, 0u, 0u, 0u, 0u};
+    QueueSrc src = {q, cap};
+    QueueSink sink = {hits};
+    traverse_wide<COUNT, HAS_SPH>(A, n, work_ctr, 0.001f, FLT_MAX, src, sink, s_stack + (threadIdx.x >> 5) * CRT_WIDE_STACK, cnt);   // render.h:53
+    if (COUNT) {
+        const uint32_t nodes = __reduce_add_sync(0xffffffffu, cnt.nodes);
+        const uint32_t tris = __reduce_add_sync(0xffffffffu, cnt.tris);
+        const uint32_t sph = __reduce_add_sync(0xffffffffu, cnt.spheres);
+        if ((threadIdx.x & 31u) == 0u) {
+            atomicAdd(counters + CNT_NODES, (unsigned long long)nodes);
+            atomicAdd(counters + CNT_TRIS, (unsigned long long)tris);
+            atomicAdd(counters + CNT_SPHERES, (unsigned long long)sph);
+            atomicAdd(counters + CNT_NODE_F, (unsigned long long)nodes);
+            atomicAdd(counters + CNT_TRI_F, (unsigned long long)tris);
+            atomicAdd(counters + CNT_SPH_F, (unsigned long long)sph);
+        }
     }
 }
 
@@ -455,16 +486,25 @@ static DCamera to_dcamera(const crt_camera* c)
 }
 
 template <bool COUNT, bool HAS_SPH>
-static void launch_bounce(crt_ctx* c, crt_lane& L, int b, int grid_trace, int grid_packet, int grid_shade, const RenderParams& P, const AccelView& A,
+static void launch_bounce(crt_ctx* c, crt_lane& L, int b, int grid_trace, int grid_packet, int grid_shade, int grid_wide, const RenderParams& P, const AccelView& A,
                           const float4* q_in, const uint32_t* n_in, uint32_t* work_ctr, float4* q_out, uint32_t* n_out)
 {
     cudaEventRecord(L.ev_trace[2 * b], L.stream);
     if (b == 0 && c->packet_primary)   // camera rays: a warp holds the samples of one or two pixels
         k_trace_packet<COUNT, HAS_SPH><<<grid_packet, TP_BLOCK, 0, L.stream>>>(A, q_in, P.cap, n_in, work_ctr, L.hitbuf.as<float4>(),
                                                                               c->counters.as<unsigned long long>(), c->packet_primary == 1 ? 1 : 0);
-    else
+    else {
+        // the queue length is only known on the device: both kernels are queued and the one the length does not
+        // belong to returns at once (a launch of fewer than wide_below rays is bound by its longest ray)
+        const uint32_t wide_below = (uint32_t)c->wide_below;
         k_trace_queue<COUNT, HAS_SPH><<<grid_trace, TP_BLOCK, 0, L.stream>>>(A, q_in, P.cap, n_in, work_ctr, L.hitbuf.as<float4>(),
-                                                                             c->counters.as<unsigned long long>(), (uint32_t)c->refill, (uint32_t)c->leaf_thresh);
+                                                                             c->counters.as<unsigned long long>(), (uint32_t)c->refill, (uint32_t)c->leaf_thresh, wide_below);
+        if (wide_below > 0u) {
+            k_trace_wide<COUNT, HAS_SPH><<<grid_wide, TP_BLOCK, 0, L.stream>>>(A, q_in, P.cap, n_in, work_ctr + 32, L.hitbuf.as<float4>(),
+                                                                              c->counters.as<unsigned long long>(), wide_below);
+            c->host_counters.launches++;
+        }
+    }
     cudaEventRecord(L.ev_trace[2 * b + 1], L.stream);
     if (COUNT && getenv("CRT_TRACE_TIMING")) {   // development aid: longest dependent chain of the launch
         unsigned long long ms = 0;
@@ -562,6 +602,9 @@ int render_accum(crt_ctx* c, const crt_camera* cam, int nx, int ny, int s0, int 
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps_packet, k_trace_packet<false, false>, TP_BLOCK, 0);
         if (bps_packet < 1) bps_packet = 1;
         const int grid_packet = c->sm_count * bps_packet;
+        int bps_wide = 1;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps_wide, k_trace_wide<false, false>, TP_BLOCK, 0);
+        const int grid_wide = c->sm_count * (bps_wide < 1 ? 1 : bps_wide);
         if (bps < 1) bps = 1;
         if (bps_shade < 1) bps_shade = 1;
         const int grid = c->sm_count * bps;
@@ -603,11 +646,11 @@ int render_accum(crt_ctx* c, const crt_camera* cam, int nx, int ny, int s0, int 
                     uint32_t* no = L.qcount.as<uint32_t>() + b + 1;
                     uint32_t* wc = L.work_ctr.as<uint32_t>() + b;
                     if (c->count_work) {
-                        if (sph) launch_bounce<true, true>(c, L, b, grid, grid_packet, grid_shade, PL, A, qi, ni, wc, qo, no);
-                        else launch_bounce<true, false>(c, L, b, grid, grid_packet, grid_shade, PL, A, qi, ni, wc, qo, no);
+                        if (sph) launch_bounce<true, true>(c, L, b, grid, grid_packet, grid_shade, grid_wide, PL, A, qi, ni, wc, qo, no);
+                        else launch_bounce<true, false>(c, L, b, grid, grid_packet, grid_shade, grid_wide, PL, A, qi, ni, wc, qo, no);
                     } else {
-                        if (sph) launch_bounce<false, true>(c, L, b, grid, grid_packet, grid_shade, PL, A, qi, ni, wc, qo, no);
-                        else launch_bounce<false, false>(c, L, b, grid, grid_packet, grid_shade, PL, A, qi, ni, wc, qo, no);
+                        if (sph) launch_bounce<false, true>(c, L, b, grid, grid_packet, grid_shade, grid_wide, PL, A, qi, ni, wc, qo, no);
+                        else launch_bounce<false, false>(c, L, b, grid, grid_packet, grid_shade, grid_wide, PL, A, qi, ni, wc, qo, no);
                     }
                 }
                 CRT_CUDA(cudaEventRecord(L.ev_end, L.stream));

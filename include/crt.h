@@ -112,6 +112,9 @@ typedef enum {
     CRT_OPT_LANES = 7,      /* render: at most 1..4 slices of the frame in flight on their own streams (default 4; a slice is
                              * never smaller than 2 M camera samples), so one slice's
                              * latency-bound last bounces overlap the other's wide launches; images do not depend on it */
+    CRT_OPT_WIDE_BELOW = 9, /* render: a bounce with fewer rays than this (default 32768) is traced one WARP per ray, the lanes
+                             * working through the ray's stack 32 entries abreast, because so small a launch is bound by
+                             * its longest ray; 0: always one ray per lane. Hits and images do not depend on it */
     CRT_OPT_BUILDER = 8,    /* tree topology of crt_accel_build: CRT_BUILDER_LBVH (default) or CRT_BUILDER_PLOC; hits and images do not depend on it */
     CRT_OPT_REFILL = 4      /* tuning: idle lanes per warp that trigger a refill from the ray queue, 1..32 (default 8) */
 } crt_option;
