@@ -15,8 +15,10 @@ A step is one full frame: 33,177,600 camera samples carried to termination.
           accumulators are summed with one NCCL reduce (16 N spp in the combined
           frame). --scaling strong splits the 16-spp frame by 32x32 tiles instead.
   e2e     the reference's per-frame loop (core/render.h:207-234) through the C
-          ABI with HOST buffers: vertex upload -> LBVH refit -> render -> image
-          download, wall clock around the synchronous calls.
+          ABI with HOST buffers: pose upload (the mesh's point array, as the
+          reference's updateFBXObj uploads it; --e2e-api frame uploads every
+          triangle's vertices instead) -> LBVH refit -> render -> image download,
+          wall clock around the synchronous calls.
   roofline  k_trace_queue (persistent-warp LBVH closest hit), algorithmic bytes of
           SURVEY §8d from an instrumented run of the same frame / the kernel's
           device time (CUDA events around each launch on the context's stream).
@@ -240,6 +242,8 @@ def run_ours(args):
     rgb = torch.zeros(ny, nx, 3, dtype=torch.float32, device=dev)
     host_rgb = torch.empty(ny, nx, 3, dtype=torch.float32).pin_memory()
     host_verts = torch.from_numpy(np.ascontiguousarray(sc["tri"][:, :9])).pin_memory()
+    host_points = torch.from_numpy(sc["points"]).pin_memory()
+    ctx.set_indices(sc["tri_idx"], len(sc["points"]))
 
     def barrier():
         if world > 1:
@@ -263,7 +267,12 @@ def run_ours(args):
             ctx.resolve_device(accum.data_ptr(), nx * ny, spp * world if weak else spp, rgb.data_ptr())
 
     def e2e_step(seed):
-        if world == 1 and args.e2e_api == "frame":
+        if world == 1 and args.e2e_api == "points":
+            # the reference's loop body (render.h:206-233) as one call, the pose in the form updateFBXObj uploads it:
+            # the point array (createScene.h:125-132); the face indices were set once
+            ctx.render_frame_pose(crt.POSE_POINTS, host_points.numpy(), cam, nx, ny, spp, depth, crt.SHADE_PATH, seed,
+                                  out=host_rgb.numpy())
+        elif world == 1 and args.e2e_api == "frame":
             # the reference's loop body (render.h:206-233) as one call: upload + refit overlap ray generation,
             # finished rows are read back while the rest of the frame renders
             ctx.render_frame(host_verts.numpy(), cam, nx, ny, spp, depth, crt.SHADE_PATH, seed, out=host_rgb.numpy())
@@ -272,7 +281,10 @@ def run_ours(args):
             ctx.refit()
             ctx.render(cam, nx, ny, spp, depth, crt.SHADE_PATH, seed, out=host_rgb.numpy())
         else:
-            ctx.update_vertices(host_verts.numpy())
+            if args.e2e_api == "points":
+                ctx.update_points(host_points.numpy())
+            else:
+                ctx.update_vertices(host_verts.numpy())
             ctx.refit()
             step(seed)
             if rank == 0:
@@ -379,10 +391,13 @@ def run_ours(args):
                        "rays_per_path": rays / max(1.0, paths)},
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "Mrays/s", "ms_per_step": 1e3 * e2e_s / args.steps,
-                    "h2d_bytes_per_step": int(host_verts.numel() * 4 + 88), "d2h_bytes_per_step": int(nx * ny * 12),
-                    "what": ("crt_render_frame (vertex upload + refit + render + read-back, overlapped) per frame, pinned host buffers, wall clock"
+                    "h2d_bytes_per_step": int((host_points.numel() if args.e2e_api == "points" else host_verts.numel()) * 4 + 88),
+                    "d2h_bytes_per_step": int(nx * ny * 12),
+                    "what": (("crt_render_frame_pose(CRT_POSE_POINTS): upload of the %d mesh points (the form the reference's updateFBXObj uploads, createScene.h:125-132) + gather into the triangles + refit + render + read-back, overlapped, per frame, pinned host buffers, wall clock" % (host_points.numel() // 3))
+                             if world == 1 and args.e2e_api == "points" else
+                             "crt_render_frame (upload of all triangle vertices + refit + render + read-back, overlapped) per frame, pinned host buffers, wall clock"
                              if world == 1 and args.e2e_api == "frame" else
-                             "crt_scene_update_vertices + crt_accel_refit + crt_render per frame, host buffers, wall clock")},
+                             "%s + crt_accel_refit + crt_render per frame, host buffers, wall clock" % ("crt_scene_update_points" if args.e2e_api == "points" else "crt_scene_update_vertices"))},
             "gpu_launches": launches,
             "roofline": {"kernel": "closest hit over the 4-wide LBVH: k_trace_packet (camera rays) + k_trace_queue (bounces), %d launches/step" % bounce_launches,
                          "bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
@@ -430,8 +445,10 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--lanes", type=int, default=4, help="CRT_OPT_LANES of the timed region (1 for profiling: one slice, launches in bounce order)")
-    ap.add_argument("--e2e-api", default="frame", choices=["frame", "calls"],
-                    help="N = 1 end-to-end loop: crt_render_frame (one overlapped call per frame) or the three separate calls")
+    ap.add_argument("--e2e-api", default="points", choices=["points", "frame", "calls"],
+                    help="end-to-end loop: points = the pose as the mesh's point array (crt_render_frame_pose, one overlapped "
+                         "call per frame at N = 1); frame = all triangle vertices (crt_render_frame); calls = vertices through "
+                         "the three separate calls")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="N > 1: weak = every rank renders the full 16-spp frame's work on its own sample range "
                          "(default); strong = the 16-spp frame is split by tiles")

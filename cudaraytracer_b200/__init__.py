@@ -20,12 +20,15 @@ OPT_LEAF_MAX, OPT_COUNTERS, OPT_BATCH_PATHS, OPT_REFILL, OPT_LEAF_THRESH, OPT_PA
 OPT_WIDE_BELOW = 9
 BUILDER_LBVH, BUILDER_PLOC = 0, 1
 TEX_CONSTANT, TEX_CHECKER = 0, 1
+POSE_VERTICES, POSE_POINTS, POSE_PARTS = 0, 1, 2
 TILE = 32
 
 # every symbol include/crt.h declares
 ABI_SYMBOLS = [
     "crt_abi_version", "crt_create", "crt_destroy", "crt_last_error", "crt_set_option", "crt_sync", "crt_stream",
     "crt_scene_set_materials", "crt_scene_set_triangles", "crt_scene_set_spheres", "crt_scene_update_vertices",
+    "crt_scene_set_indices", "crt_scene_update_points", "crt_scene_set_parts", "crt_scene_move_parts",
+    "crt_render_frame_pose",
     "crt_accel_build", "crt_accel_refit", "crt_trace", "crt_trace_device", "crt_render", "crt_render_frame",
     "crt_render_accum_device", "crt_resolve_device", "crt_pack_rgba8_device", "crt_get_counters",
     "crt_reset_counters", "crt_accel_info",
@@ -87,6 +90,11 @@ def load_library():
     lib.crt_scene_set_triangles.argtypes = [vp, vp, vp, vp, sz]
     lib.crt_scene_set_spheres.argtypes = [vp, vp, vp, vp, sz]
     lib.crt_scene_update_vertices.argtypes = [vp, vp, sz, sz]
+    lib.crt_scene_set_indices.argtypes = [vp, vp, sz, sz, sz]
+    lib.crt_scene_update_points.argtypes = [vp, vp, sz]
+    lib.crt_render_frame_pose.argtypes = [vp, C.c_int, vp, sz, sz, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint64, vp]
+    lib.crt_scene_set_parts.argtypes = [vp, vp, sz, sz]
+    lib.crt_scene_move_parts.argtypes = [vp, vp, sz]
     lib.crt_accel_build.argtypes = [vp]
     lib.crt_accel_refit.argtypes = [vp]
     lib.crt_trace.argtypes = [vp, vp, sz, C.c_float, C.c_float, C.c_int, vp]
@@ -218,6 +226,27 @@ class Context:
         verts = np.ascontiguousarray(verts, np.float32).reshape(-1, 9)
         self._check(self.lib.crt_scene_update_vertices(self._h, _ptr(verts), int(first), verts.shape[0]))
 
+    def set_indices(self, idx, n_points, first=0):
+        """Index buffer of an indexed mesh (createScene.h:99-109): triangle first + t stores
+        points[idx[t, 0]], points[idx[t, 1]], points[idx[t, 2]]."""
+        idx = np.ascontiguousarray(idx, np.uint32).reshape(-1, 3)
+        self._check(self.lib.crt_scene_set_indices(self._h, _ptr(idx), int(first), idx.shape[0], int(n_points)))
+
+    def update_points(self, points):
+        pts = np.ascontiguousarray(points, np.float32).reshape(-1, 3)
+        self._check(self.lib.crt_scene_update_points(self._h, _ptr(pts), pts.shape[0]))
+
+    def set_parts(self, part_of_tri, n_parts):
+        """Bone partition (createScene.h:221-307): the part every triangle moves with; the
+        current vertices become the rest pose."""
+        part = np.ascontiguousarray(part_of_tri, np.uint32).reshape(-1)
+        self._check(self.lib.crt_scene_set_parts(self._h, _ptr(part), part.shape[0], int(n_parts)))
+
+    def move_parts(self, translation):
+        """vertex = rest vertex + translation[part]; follow with refit()."""
+        t = np.ascontiguousarray(translation, np.float32).reshape(-1, 3)
+        self._check(self.lib.crt_scene_move_parts(self._h, _ptr(t), t.shape[0]))
+
     def build(self):
         self._check(self.lib.crt_accel_build(self._h))
 
@@ -263,6 +292,18 @@ class Context:
         rgb = np.empty((ny, nx, 3), np.float32) if out is None else out
         self._check(self.lib.crt_render_frame(self._h, _ptr(verts), int(first), n, _ptr(cam), nx, ny, spp, max_depth,
                                               int(mode), int(seed), _ptr(rgb)))
+        return rgb
+
+    def render_frame_pose(self, kind, pose, cam22, nx, ny, spp, max_depth=8, mode=SHADE_PATH, seed=1, out=None):
+        """crt_render_frame_pose: like render_frame with the pose given as points (POSE_POINTS, after set_indices)
+        or as one translation per part (POSE_PARTS, after set_parts)."""
+        cam = np.ascontiguousarray(cam22, np.float32)
+        assert cam.size == 22
+        width = 9 if kind == POSE_VERTICES else 3
+        pose = np.ascontiguousarray(pose, np.float32).reshape(-1, width)
+        rgb = np.empty((ny, nx, 3), np.float32) if out is None else out
+        self._check(self.lib.crt_render_frame_pose(self._h, int(kind), _ptr(pose), 0, pose.shape[0], _ptr(cam), nx, ny, spp,
+                                                   max_depth, int(mode), int(seed), _ptr(rgb)))
         return rgb
 
     def render_accum_device(self, cam22, nx, ny, s0, s1, max_depth, mode, seed, rank, world, d_accum_ptr):

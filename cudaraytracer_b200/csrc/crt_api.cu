@@ -58,6 +58,43 @@ k_update_vertices(const float* __restrict__ verts, size_t n_values, size_t first
     tri_in[(first + t) * 12 + k] = verts[i];
 }
 
+// A rigid part (bone) moved by a translation: vertex = rest vertex + T[part]. One
+// thread per vertex component; plain rounded adds so the host can predict every bit.
+// The reference keeps a BoneBVHNode per bone whose boxes live in the bone's frame
+// (hitable/BoneBVH.h:83-87,130-135) and still visits every node per frame, one
+// thread per bone (createScene.h:69-76); here the pose is one streaming kernel and
+// the ordinary refit follows.
+__global__ void __launch_bounds__(256)
+k_move_parts(const float* __restrict__ rest, const uint32_t* __restrict__ part, const float* __restrict__ T,
+             size_t n_values, float* __restrict__ tri_in)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_values) return;
+    const size_t t = i / 9, k = i - t * 9;
+    tri_in[t * 12 + k] = __fadd_rn(rest[i], T[(size_t)part[t] * 3 + k % 3]);
+}
+
+// update_pose (createScene.h:99-109) for an indexed mesh: vertex k of triangle
+// first + t = points[idx[3 t + k]]; pure copies, one thread per vertex component.
+__global__ void __launch_bounds__(256)
+k_gather_points(const float* __restrict__ points, const uint32_t* __restrict__ idx, size_t n_values, size_t first,
+                float* __restrict__ tri_in)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_values) return;
+    const size_t t = i / 9, k = i - t * 9;
+    tri_in[(first + t) * 12 + k] = points[(size_t)idx[t * 3 + k / 3] * 3 + k % 3];
+}
+
+__global__ void __launch_bounds__(256)
+k_capture_rest(const float* __restrict__ tri_in, size_t n_values, float* __restrict__ rest)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_values) return;
+    const size_t t = i / 9, k = i - t * 9;
+    rest[i] = tri_in[t * 12 + k];
+}
+
 }  // namespace crt
 
 using namespace crt;
@@ -129,7 +166,7 @@ void crt_destroy(crt_ctx* c)
                       &c->keys[0], &c->keys[1], &c->vals[0], &c->vals[1], &c->hist, &c->nodes, &c->recs,
                       &c->child, &c->parent, &c->leaf_parent, &c->range, &c->node_box, &c->leaf_box, &c->flags,
                       &c->bounds, &c->depth_out, &c->ploc_box[0], &c->ploc_box[1], &c->ploc_nn, &c->ploc_tmp, &c->ploc_blk, &c->work_ctr, &c->accum, &c->rgb,
-                      &c->rays_tmp, &c->hits_tmp, &c->counters};
+                      &c->rays_tmp, &c->hits_tmp, &c->counters, &c->rest, &c->part_id, &c->part_T, &c->tri_idx};
     for (DevBuf* b : bufs) b->release();
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
@@ -254,6 +291,9 @@ int crt_scene_set_triangles(crt_ctx* c, const float* tri, const uint32_t* mat_id
     if ((r = upload_ids(c->tri_id, prim_id, n, 0u, c->stream)) != CRT_OK) return r;
     CRT_CUDA(cudaStreamSynchronize(c->stream));
     c->n_tri = n;
+    c->n_parts = 0;
+    c->n_idx_tri = 0;
+    c->n_points = 0;
     c->accel_valid = false;
     // default sphere ids follow the triangles; renumber them if they were defaulted earlier
     return CRT_OK;
@@ -276,19 +316,110 @@ int crt_scene_set_spheres(crt_ctx* c, const float* sph, const uint32_t* mat_id, 
     return CRT_OK;
 }
 
+// Enqueue one pose update on `st` (no synchronisation): the H2D copy of the caller's array into the staging buffer and
+// the kernel that rewrites tri_in.
+static int enqueue_pose(crt_ctx* c, int kind, const float* data, size_t first, size_t n, cudaStream_t st, const char* who)
+{
+    if (n == 0) return CRT_OK;
+    if (!data) { set_error("%s: null array", who); return CRT_ERR_INVALID; }
+    size_t nv = 0;
+    switch (kind) {
+    case CRT_POSE_VERTICES:
+        if (first + n > c->n_tri) { set_error("%s: range [%zu, %zu) exceeds %zu triangles", who, first, first + n, c->n_tri); return CRT_ERR_INVALID; }
+        CRT_CUDA(c->rays_tmp.reserve(n * 36));
+        CRT_CUDA(cudaMemcpyAsync(c->rays_tmp.p, data, n * 36, cudaMemcpyHostToDevice, st));
+        nv = n * 9;
+        k_update_vertices<<<(unsigned int)((nv + 255) / 256), 256, 0, st>>>(c->rays_tmp.as<float>(), nv, first, c->tri_in.as<float>());
+        break;
+    case CRT_POSE_POINTS:
+        if (c->n_idx_tri == 0) { set_error("%s: no index buffer (crt_scene_set_indices)", who); return CRT_ERR_STATE; }
+        if (first != 0 || n != c->n_points) { set_error("%s: %zu points from %zu given, the index buffer addresses %zu from 0", who, n, first, c->n_points); return CRT_ERR_INVALID; }
+        CRT_CUDA(c->rays_tmp.reserve(n * 12));
+        CRT_CUDA(cudaMemcpyAsync(c->rays_tmp.p, data, n * 12, cudaMemcpyHostToDevice, st));
+        nv = c->n_idx_tri * 9;
+        k_gather_points<<<(unsigned int)((nv + 255) / 256), 256, 0, st>>>(c->rays_tmp.as<float>(), c->tri_idx.as<uint32_t>(), nv,
+                                                                          c->idx_first, c->tri_in.as<float>());
+        break;
+    case CRT_POSE_PARTS:
+        if (c->n_parts == 0) { set_error("%s: no parts set (crt_scene_set_parts)", who); return CRT_ERR_STATE; }
+        if (first != 0 || n != c->n_parts) { set_error("%s: %zu translations from %zu given, the scene has %zu parts", who, n, first, c->n_parts); return CRT_ERR_INVALID; }
+        CRT_CUDA(cudaMemcpyAsync(c->part_T.p, data, n * 12, cudaMemcpyHostToDevice, st));
+        nv = c->n_tri * 9;
+        k_move_parts<<<(unsigned int)((nv + 255) / 256), 256, 0, st>>>(c->rest.as<float>(), c->part_id.as<uint32_t>(),
+                                                                       c->part_T.as<float>(), nv, c->tri_in.as<float>());
+        break;
+    default:
+        set_error("%s: unknown pose kind %d", who, kind);
+        return CRT_ERR_INVALID;
+    }
+    CRT_CUDA(cudaGetLastError());
+    c->host_counters.launches++;
+    return CRT_OK;
+}
+
 int crt_scene_update_vertices(crt_ctx* c, const float* verts, size_t first, size_t n)
 {
     CRT_CHECK_CTX(c);
-    if (n == 0) return CRT_OK;
-    if (!verts) { set_error("crt_scene_update_vertices: null array"); return CRT_ERR_INVALID; }
-    if (first + n > c->n_tri) { set_error("crt_scene_update_vertices: range [%zu, %zu) exceeds %zu triangles", first, first + n, c->n_tri); return CRT_ERR_INVALID; }
     // staged through the (otherwise idle) ray upload buffer
-    CRT_CUDA(c->rays_tmp.reserve(n * 36));
-    CRT_CUDA(cudaMemcpyAsync(c->rays_tmp.p, verts, n * 36, cudaMemcpyHostToDevice, c->stream));
-    const size_t nv = n * 9;
-    k_update_vertices<<<(unsigned int)((nv + 255) / 256), 256, 0, c->stream>>>(c->rays_tmp.as<float>(), nv, first, c->tri_in.as<float>());
+    int r = enqueue_pose(c, CRT_POSE_VERTICES, verts, first, n, c->stream, "crt_scene_update_vertices");
+    if (r != CRT_OK) return r;
+    CRT_CUDA(cudaStreamSynchronize(c->stream));
+    return CRT_OK;
+}
+
+int crt_scene_set_indices(crt_ctx* c, const uint32_t* idx, size_t first, size_t n_tri, size_t n_points)
+{
+    CRT_CHECK_CTX(c);
+    if (n_tri == 0 || n_points == 0) { c->n_idx_tri = 0; c->n_points = 0; return CRT_OK; }
+    if (!idx) { set_error("crt_scene_set_indices: null array"); return CRT_ERR_INVALID; }
+    if (first + n_tri > c->n_tri) { set_error("crt_scene_set_indices: range [%zu, %zu) exceeds %zu triangles", first, first + n_tri, c->n_tri); return CRT_ERR_INVALID; }
+    if (n_points >= (1ull << 32)) { set_error("crt_scene_set_indices: too many points"); return CRT_ERR_INVALID; }
+    for (size_t i = 0; i < n_tri * 3; i++)
+        if (idx[i] >= n_points) { set_error("crt_scene_set_indices: triangle %zu names point %u of %zu", i / 3, idx[i], n_points); return CRT_ERR_INVALID; }
+    int r = upload(c->tri_idx, idx, n_tri * 12, c->stream);
+    if (r != CRT_OK) return r;
+    CRT_CUDA(cudaStreamSynchronize(c->stream));
+    c->idx_first = first;
+    c->n_idx_tri = n_tri;
+    c->n_points = n_points;
+    return CRT_OK;
+}
+
+int crt_scene_update_points(crt_ctx* c, const float* points, size_t n_points)
+{
+    CRT_CHECK_CTX(c);
+    int r = enqueue_pose(c, CRT_POSE_POINTS, points, 0, n_points, c->stream, "crt_scene_update_points");
+    if (r != CRT_OK) return r;
+    CRT_CUDA(cudaStreamSynchronize(c->stream));
+    return CRT_OK;
+}
+
+int crt_scene_set_parts(crt_ctx* c, const uint32_t* part_of_tri, size_t n_tri, size_t n_parts)
+{
+    CRT_CHECK_CTX(c);
+    if (n_tri != c->n_tri) { set_error("crt_scene_set_parts: %zu part ids for %zu triangles", n_tri, c->n_tri); return CRT_ERR_INVALID; }
+    if (n_tri == 0 || n_parts == 0) { c->n_parts = 0; return CRT_OK; }
+    if (!part_of_tri) { set_error("crt_scene_set_parts: null array"); return CRT_ERR_INVALID; }
+    for (size_t i = 0; i < n_tri; i++)
+        if (part_of_tri[i] >= n_parts) { set_error("crt_scene_set_parts: triangle %zu is in part %u of %zu", i, part_of_tri[i], n_parts); return CRT_ERR_INVALID; }
+    int r = upload(c->part_id, part_of_tri, n_tri * 4, c->stream);
+    if (r != CRT_OK) return r;
+    CRT_CUDA(c->rest.reserve(n_tri * 36));
+    CRT_CUDA(c->part_T.reserve(n_parts * 12));
+    const size_t nv = n_tri * 9;
+    k_capture_rest<<<(unsigned int)((nv + 255) / 256), 256, 0, c->stream>>>(c->tri_in.as<float>(), nv, c->rest.as<float>());
     CRT_CUDA(cudaGetLastError());
     CRT_CUDA(cudaStreamSynchronize(c->stream));
+    c->n_parts = n_parts;
+    return CRT_OK;
+}
+
+int crt_scene_move_parts(crt_ctx* c, const float* translation, size_t n_parts)
+{
+    CRT_CHECK_CTX(c);
+    int r = enqueue_pose(c, CRT_POSE_PARTS, translation, 0, n_parts, c->stream, "crt_scene_move_parts");
+    if (r != CRT_OK) return r;
+    CRT_CUDA(cudaStreamSynchronize(c->stream));   // the caller's array is free again
     return CRT_OK;
 }
 
@@ -388,28 +519,20 @@ int crt_render(crt_ctx* c, const crt_camera* cam, int nx, int ny, int spp, int m
 // One frame of the reference's animation loop (render.h:206-233: updateFBXObj, Update_BVH, render, copy back) as ONE
 // call, so that the steps can overlap: the vertex upload and the refit run on their own stream while the slices
 // generate their camera rays, and each slice's rows travel back while the others still render.
-int crt_render_frame(crt_ctx* c, const float* verts, size_t first, size_t n, const crt_camera* cam, int nx, int ny,
-                     int spp, int max_depth, int shade_mode, uint64_t seed, float* rgb_out)
+int crt_render_frame_pose(crt_ctx* c, int pose_kind, const float* pose, size_t first, size_t n, const crt_camera* cam,
+                          int nx, int ny, int spp, int max_depth, int shade_mode, uint64_t seed, float* rgb_out)
 {
     CRT_CHECK_CTX(c);
     if (!rgb_out) { set_error("crt_render_frame: rgb_out is null"); return CRT_ERR_INVALID; }
     if (nx <= 0 || ny <= 0 || spp < 1) { set_error("crt_render_frame: nx, ny and spp must be positive"); return CRT_ERR_INVALID; }
-    if (n > 0 && !verts) { set_error("crt_render_frame: null vertex array"); return CRT_ERR_INVALID; }
-    if (first + n > c->n_tri) { set_error("crt_render_frame: range [%zu, %zu) exceeds %zu triangles", first, first + n, c->n_tri); return CRT_ERR_INVALID; }
     if (!c->accel_valid || c->n_prims != (uint32_t)(c->n_tri + c->n_sph)) {
         set_error("crt_render_frame: call crt_accel_build first (a frame only refits)");
         return CRT_ERR_STATE;
     }
     cudaStream_t up = c->up_stream;
-    if (n > 0) {
-        CRT_CUDA(c->rays_tmp.reserve(n * 36));
-        CRT_CUDA(cudaMemcpyAsync(c->rays_tmp.p, verts, n * 36, cudaMemcpyHostToDevice, up));
-        const size_t nv = n * 9;
-        k_update_vertices<<<(unsigned int)((nv + 255) / 256), 256, 0, up>>>(c->rays_tmp.as<float>(), nv, first, c->tri_in.as<float>());
-        CRT_CUDA(cudaGetLastError());
-        c->host_counters.launches++;
-    }
-    int r = lbvh_build(c, true, up);
+    int r = enqueue_pose(c, pose_kind, pose, first, n, up, "crt_render_frame");
+    if (r != CRT_OK) return r;
+    r = lbvh_build(c, true, up);
     if (r != CRT_OK) { cudaStreamSynchronize(up); return r; }
     CRT_CUDA(cudaEventRecord(c->ev_frame, up));
     r = render_to_host(c, cam, nx, ny, spp, max_depth, shade_mode, seed, rgb_out, c->ev_frame);
@@ -417,6 +540,12 @@ int crt_render_frame(crt_ctx* c, const float* verts, size_t first, size_t n, con
     float ms = 0.f;
     if (cudaEventElapsedTime(&ms, c->ev_up0, c->ev_up1) == cudaSuccess) c->host_counters.refit_ms = ms;
     return r;
+}
+
+int crt_render_frame(crt_ctx* c, const float* verts, size_t first, size_t n, const crt_camera* cam, int nx, int ny,
+                     int spp, int max_depth, int shade_mode, uint64_t seed, float* rgb_out)
+{
+    return crt_render_frame_pose(c, CRT_POSE_VERTICES, verts, first, n, cam, nx, ny, spp, max_depth, shade_mode, seed, rgb_out);
 }
 
 int crt_get_counters(crt_ctx* c, crt_counters* out)

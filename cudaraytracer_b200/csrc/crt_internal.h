@@ -79,6 +79,12 @@ struct crt_ctx {
     crt::DevBuf sph_in, sph_mat, sph_id;   // n_sph x 4 floats
     crt::DevBuf mats;                      // DMat
     size_t n_tri = 0, n_sph = 0, n_mats = 0;
+    // rigid parts (bones): rest-pose vertices (n_tri x 9 floats), part of each triangle, the current translations
+    crt::DevBuf rest, part_id, part_T;
+    size_t n_parts = 0;
+    // indexed mesh: triangle idx_first + t has the vertices points[tri_idx[3 t + k]]
+    crt::DevBuf tri_idx;
+    size_t idx_first = 0, n_idx_tri = 0, n_points = 0;
 
     // LBVH
     crt::DevBuf keys[2], vals[2], hist;

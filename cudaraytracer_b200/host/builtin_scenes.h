@@ -105,6 +105,30 @@ inline void mesh_vertices(int n_theta, int n_phi, double phase, std::vector<floa
                  displaced_point(i, j + 1, n_theta, n_phi, phase), j);
 }
 
+// The same mesh in the indexed form the reference animates (mesh->points and
+// mesh->idxVertex, createScene.h:99-140): (n_phi+1) x (n_theta+1) points, row
+// major, and for every triangle of mesh_vertices() the three point numbers in
+// stored-vertex order. points[idx] reproduces mesh_vertices() exactly.
+inline void mesh_points(int n_theta, int n_phi, double phase, std::vector<float>& points)
+{
+    points.clear();
+    for (int j = 0; j <= n_phi; j++)
+        for (int i = 0; i <= n_theta; i++) {
+            const vec3 p = displaced_point(i, j, n_theta, n_phi, phase);
+            points.push_back(p[0]); points.push_back(p[1]); points.push_back(p[2]);
+        }
+}
+
+inline void mesh_indices(int n_theta, int n_phi, std::vector<uint32_t>& idx)
+{
+    idx.clear();
+    auto num = [&](int i, int j) { return (uint32_t)(j * (n_theta + 1) + i); };
+    for (int j = 1; j < n_phi; j++)
+        for (int i = 0; i < n_theta; i++) { idx.push_back(num(i, j)); idx.push_back(num(i + 1, j)); idx.push_back(num(i + 1, j + 1)); }
+    for (int j = 0; j < n_phi - 1; j++)
+        for (int i = 0; i < n_theta; i++) { idx.push_back(num(i, j)); idx.push_back(num(i + 1, j + 1)); idx.push_back(num(i, j + 1)); }
+}
+
 // C3: stored normals point INTO the sphere and the ground's DOWN, because the
 // reference triangle test only reports hits with dot(direction, normal) >= 0
 // (shapes/triangle.h:61).

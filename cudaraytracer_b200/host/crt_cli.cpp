@@ -34,6 +34,7 @@ struct Options {
     crt_host::SceneOptions sc;
     int nx = 1024, ny = 512, spp = 4, depth = 8, frames = 1, device = 0;
     bool animate = false, quiet = false, overlap = false;
+    std::string pose = "vertices";   // --pose vertices|points|bones: the form the per-frame geometry update takes
 };
 
 double now_s()
@@ -69,10 +70,12 @@ Options parse(int argc, char** argv)
         else if (a == "--seed") o.sc.seed = std::strtoull(val(), nullptr, 10);
         else if (a == "--animate") o.animate = true;
         else if (a == "--overlap") o.overlap = true;
+        else if (a == "--pose") o.pose = val();
         else if (a == "--quiet") o.quiet = true;
         else if (a == "--help" || a == "-h") {
             std::printf("usage: crt_cli [--scene bunny|spheres|mesh] [--obj FILE] [--camera framed|reference] [--nx N --ny N]\n"
-                        "               [--spp N] [--depth N] [--mode path|lambert|normal] [--seed S] [--frames N] [--animate [--overlap]]\n"
+                        "               [--spp N] [--depth N] [--mode path|lambert|normal] [--seed S] [--frames N]\n"
+                        "               [--animate [--overlap] [--pose vertices|points|bones]]\n"
                         "               [--segments N] [--out PREFIX] [--csv FILE] [--device D] [--quiet]\n");
             std::exit(0);
         } else die("unknown flag " + a);
@@ -109,24 +112,57 @@ int main(int argc, char** argv)
         std::vector<vec3> colorBuffer((size_t)o.nx * o.ny);
         std::vector<crt_host::FrameTiming> rows;
         std::vector<float> verts;
+        // --pose: how a frame's geometry reaches the device. vertices: 9 floats per triangle; points: the mesh's point
+        // array through the index buffer (what updateFBXObj uploads, createScene.h:125-140); bones: one translation
+        // per rigid part (Update_BVH over bones, createScene.h:80-97)
+        const bool moving = o.animate && o.scene == "mesh";
+        int pose_kind = CRT_POSE_VERTICES;
+        const size_t n_bones = 8;
+        std::vector<vec3> nowTransform(n_bones);
+        if (o.pose == "points") pose_kind = CRT_POSE_POINTS;
+        else if (o.pose == "bones") pose_kind = CRT_POSE_PARTS;
+        else if (o.pose != "vertices") die("unknown --pose " + o.pose);
+        if (moving && pose_kind == CRT_POSE_POINTS) {
+            std::vector<uint32_t> idx;
+            crt_host::mesh_indices(o.sc.n_theta, o.sc.n_phi, idx);
+            r.set_indices(idx.data(), 0, idx.size() / 3, (size_t)(o.sc.n_theta + 1) * (o.sc.n_phi + 1));
+        }
+        if (moving && pose_kind == CRT_POSE_PARTS) {                  // bones = groups of latitude bands; the ground is bone 0
+            std::vector<int> bands;
+            crt_host::mesh_vertices(o.sc.n_theta, o.sc.n_phi, 0.0, verts, &bands);
+            std::vector<uint32_t> part(r.flat().n_triangles(), 0u);
+            for (size_t t = 0; t < bands.size(); t++) part[t] = (uint32_t)((size_t)bands[t] * n_bones / (size_t)o.sc.n_phi);
+            r.createBoneBVH(part.data(), part.size(), n_bones);
+        }
+        auto make_pose = [&](int frame) -> size_t {                   // fills verts with the frame's pose, returns its rows
+            if (pose_kind == CRT_POSE_POINTS) { crt_host::mesh_points(o.sc.n_theta, o.sc.n_phi, 0.3 * frame, verts); return verts.size() / 3; }
+            if (pose_kind == CRT_POSE_PARTS) {
+                for (size_t b = 1; b < n_bones; b++) nowTransform[b] = vec3(0.f, 3.f * std::sin(0.3f * frame + (float)b), 0.f);
+                verts.assign(&nowTransform[0].e[0], &nowTransform[0].e[0] + 3 * n_bones);
+                return n_bones;
+            }
+            crt_host::mesh_vertices(o.sc.n_theta, o.sc.n_phi, 0.3 * frame, verts, nullptr);
+            return verts.size() / 9;
+        };
         for (int frame = 0; frame < o.frames; frame++) {
             double update_s = 0.0;
-            if (o.animate && o.overlap && o.scene == "mesh") {        // the whole loop body as one overlapped call
-                crt_host::mesh_vertices(o.sc.n_theta, o.sc.n_phi, 0.3 * frame, verts, nullptr);
+            if (moving && o.overlap) {                                // the whole loop body as one overlapped call
+                const size_t rows_n = make_pose(frame);
                 t0 = now_s();
-                r.render_frame(verts.data(), 0, verts.size() / 9, colorBuffer.data(), cam, o.nx, o.ny, o.spp, o.depth, mode,
-                               o.sc.seed + (uint64_t)frame);
+                r.render_frame_pose(pose_kind, verts.data(), rows_n, colorBuffer.data(), cam, o.nx, o.ny, o.spp, o.depth, mode,
+                                    o.sc.seed + (uint64_t)frame);
                 const double frame_s = now_s() - t0;
                 if (!WritePng(o.nx, o.ny, frame, colorBuffer.data(), o.out.c_str())) die("cannot write " + o.out + std::to_string(frame) + ".png");
                 rows.push_back({frame, frame_s, 0.0, frame == 0 ? build_s : 0.0});
                 if (!o.quiet) std::printf("frame %d: update + refit + rendering %g s (refit %g ms on the device)\n", frame, frame_s, r.counters().refit_ms);
                 continue;
             }
-            if (o.animate && o.scene == "mesh") {                     // render.h:207-217: new pose, then refit
+            if (moving) {                                             // render.h:207-217: new pose, then refit
                 t0 = now_s();
-                crt_host::mesh_vertices(o.sc.n_theta, o.sc.n_phi, 0.3 * frame, verts, nullptr);
-                r.update_vertices(verts.data(), 0, verts.size() / 9);
-                r.Update_BVH();
+                const size_t rows_n = make_pose(frame);
+                if (pose_kind == CRT_POSE_POINTS) { r.update_points(verts.data(), rows_n); r.Update_BVH(); }
+                else if (pose_kind == CRT_POSE_PARTS) r.Update_BVH(nowTransform.data(), n_bones);
+                else { r.update_vertices(verts.data(), 0, rows_n); r.Update_BVH(); }
                 update_s = now_s() - t0;
             }
             t0 = now_s();

@@ -8,6 +8,9 @@
 //   create_FBXMesh / init_List  createScene.h:167,192  set_world(list)             crt_scene_set_*
 //   create_BVHfromList          createScene.h:212      create_BVHfromList()        crt_accel_build
 //   updateFBXObj                createScene.h:125      update_vertices(...)        crt_scene_update_vertices
+//   update_pose(newPos, idx)    createScene.h:99,125   set_indices / update_points crt_scene_set_indices / _update_points
+//   createBoneBVH               createScene.h:256      createBoneBVH(part, n)      crt_scene_set_parts
+//   Update_BVH(boneBvh, obj)    createScene.h:80       Update_BVH(nowTransform, n) crt_scene_move_parts + crt_accel_refit
 //   Update_BVH                  createScene.h:53       Update_BVH()                crt_accel_refit
 //   render<<<>>> + D2H copy     render.h:105,222-226   render(colorBuffer, ...)    crt_render
 //   the loop body as a whole    render.h:206-233       render_frame(...)           crt_render_frame (steps overlapped)
@@ -63,6 +66,30 @@ public:
         check(crt_scene_update_vertices(ctx_, verts, first, n), "crt_scene_update_vertices");
     }
 
+    // Indexed pose, the form updateFBXObj / update_pose use (createScene.h:99-140): the face indices once
+    // (idx[3 t + k] = point of stored vertex k of triangle first + t), then one point array per frame.
+    void set_indices(const uint32_t* idx, size_t first, size_t n_tri, size_t n_points)
+    {
+        check(crt_scene_set_indices(ctx_, idx, first, n_tri, n_points), "crt_scene_set_indices");
+    }
+    void update_points(const float* points, size_t n_points)
+    {
+        check(crt_scene_update_points(ctx_, points, n_points), "crt_scene_update_points");
+    }
+
+    // Bones (createScene.h:256-307, hitable/BoneBVH.h): the part every triangle moves with; the current vertices
+    // become the rest pose. Update_BVH(nowTransform, n) is the reference's per-frame bone update: one translation per
+    // bone (BoneBVHNode::UpdateBVH(nowT), BoneBVH.h:113-137), then the refit.
+    void createBoneBVH(const uint32_t* part_of_tri, size_t n_tri, size_t n_parts)
+    {
+        check(crt_scene_set_parts(ctx_, part_of_tri, n_tri, n_parts), "crt_scene_set_parts");
+    }
+    void Update_BVH(const vec3* nowTransform, size_t n_parts)
+    {
+        check(crt_scene_move_parts(ctx_, &nowTransform[0].e[0], n_parts), "crt_scene_move_parts");
+        check(crt_accel_refit(ctx_), "crt_accel_refit");
+    }
+
     // render<<<>>> + cudaMemcpy D2H (render.h:222-226): colorBuffer is the
     // caller's nx*ny vec3 array, row 0 at the bottom, values after gamma and clip.
     void render(vec3* colorBuffer, const Camera& camera, int nx, int ny, int samples, int max_depth,
@@ -82,6 +109,15 @@ public:
         const crt_camera cam = camera.to_crt();
         check(crt_render_frame(ctx_, verts, first, n, &cam, nx, ny, samples, max_depth, shade_mode, seed, &colorBuffer[0].e[0]),
               "crt_render_frame");
+    }
+
+    // render_frame with the pose as points (CRT_POSE_POINTS) or bone translations (CRT_POSE_PARTS).
+    void render_frame_pose(int pose_kind, const float* pose, size_t n, vec3* colorBuffer, const Camera& camera, int nx, int ny,
+                           int samples, int max_depth, int shade_mode = CRT_SHADE_LAMBERT, uint64_t seed = 0)
+    {
+        const crt_camera cam = camera.to_crt();
+        check(crt_render_frame_pose(ctx_, pose_kind, pose, 0, n, &cam, nx, ny, samples, max_depth, shade_mode, seed,
+                                    &colorBuffer[0].e[0]), "crt_render_frame_pose");
     }
 
     // (*world)->hit for a batch of rays (render.h:53).

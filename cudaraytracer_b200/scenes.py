@@ -208,6 +208,29 @@ def displaced_sphere(n_theta, n_phi, radius=100.0, amp=5.0, centre=(0.0, 0.0, 0.
     return v0, v1, v2, bands
 
 
+def displaced_sphere_indexed(n_theta, n_phi, radius=100.0, amp=5.0, centre=(0.0, 0.0, 0.0)):
+    """The same mesh as displaced_sphere() in indexed form, the shape the reference
+    animates (a point array and a face index array, createScene.h:99-140): points
+    ((n_phi+1)*(n_theta+1), 3) float32 and idx (n_tri, 3) uint32 such that
+    points[idx[:, k]] equals v_k of displaced_sphere() triangle for triangle."""
+    th = (np.arange(n_theta + 1, dtype=np.float64) % n_theta) * (2.0 * np.pi / n_theta)
+    ph = np.arange(n_phi + 1, dtype=np.float64) * (np.pi / n_phi)
+    T, P = np.meshgrid(th, ph, indexing="xy")
+    R = radius + amp * np.sin(8.0 * T) * np.sin(6.0 * P)
+    X = R * np.sin(P) * np.cos(T) + centre[0]
+    Y = R * np.cos(P) + centre[1]
+    Z = R * np.sin(P) * np.sin(T) + centre[2]
+    points = np.stack([X, Y, Z], axis=-1).astype(np.float32).reshape(-1, 3)
+    num = np.arange((n_phi + 1) * (n_theta + 1), dtype=np.uint32).reshape(n_phi + 1, n_theta + 1)
+    a, b, c, d = num[:-1, :-1], num[:-1, 1:], num[1:, :-1], num[1:, 1:]
+    up = (slice(1, None), slice(None))
+    lo = (slice(0, n_phi - 1), slice(None))
+    i0 = np.concatenate([a[up].reshape(-1), a[lo].reshape(-1)])
+    i1 = np.concatenate([b[up].reshape(-1), d[lo].reshape(-1)])
+    i2 = np.concatenate([d[up].reshape(-1), c[lo].reshape(-1)])
+    return np.ascontiguousarray(points), np.ascontiguousarray(np.stack([i0, i1, i2], axis=1).astype(np.uint32))
+
+
 def ground_quad(y, half, normal_down=True):
     p = np.asarray([[-half, y, -half], [half, y, -half], [half, y, half], [-half, y, half]], np.float32)
     v0 = p[[0, 0]]
@@ -238,9 +261,12 @@ def c3_mesh(n_theta=1000, n_phi=500, nx=1920, ny=1080, spp=16, centre=(0.0, 0.0,
     tri_mat = np.concatenate([(bands % 2).astype(np.uint32), np.asarray([2, 2], np.uint32)])
     sph, sph_mat = _empty_sph()
     mats = [(LAMBERTIAN, (0.7, 0.3, 0.2), 0.0), (METAL, (0.8, 0.8, 0.8), 0.1), (LAMBERTIAN, (0.5, 0.5, 0.5), 0.0)]
+    # indexed form of the sphere (triangles [0, len(tri) - 2); the ground quad is not animated): the pose input of
+    # crt_scene_update_points, as the reference's update_pose takes it (createScene.h:99-109)
+    points, tri_idx = displaced_sphere_indexed(n_theta, n_phi, centre=centre)
     return dict(name="C3_mesh_%dk" % (len(tri) // 1000), tri=np.ascontiguousarray(tri), tri_mat=tri_mat, sph=sph,
                 sph_mat=sph_mat, mats=mats, camera=camera_dict((0, 60, 320), (0, 0, 0), 40),
-                nx=nx, ny=ny, spp=spp, max_depth=8)
+                nx=nx, ny=ny, spp=spp, max_depth=8, points=points, tri_idx=tri_idx)
 
 
 def c4_instanced(grid=10, pitch=250.0, n_theta=500, n_phi=101, nx=3840, ny=2160, spp=64):

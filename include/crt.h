@@ -189,6 +189,37 @@ int crt_scene_set_spheres(crt_ctx* ctx, const float* sph, const uint32_t* mat_id
  * Triangle::SetVertices (shapes/triangle.h:40-45) the stored normals stay. */
 int crt_scene_update_vertices(crt_ctx* ctx, const float* verts, size_t first, size_t n);
 
+/* Indexed mesh pose: the reference's per-frame update is a point array plus the
+ * face index array (updateFBXObj uploads newPos and idxVertices, update_pose
+ * writes tris[i]->SetVertices({newPos[idx[2]], newPos[idx[1]], newPos[idx[0]]}),
+ * createScene.h:99-140). crt_scene_set_indices stores, once, the three point
+ * numbers of triangles [first, first + n_tri) in the order the vertices are to be
+ * stored (the caller applies the reference's reversal); crt_scene_update_points
+ * uploads n_points x 3 floats (12 bytes per point instead of 36 per triangle:
+ * 6 MB instead of 36 MB for the 1 M-triangle mesh) and gathers them into the
+ * triangles on the device. Stored normals stay, as with SetVertices.
+ * crt_scene_set_triangles clears the index buffer. */
+int crt_scene_set_indices(crt_ctx* ctx, const uint32_t* idx, size_t first, size_t n_tri, size_t n_points);
+int crt_scene_update_points(crt_ctx* ctx, const float* points, size_t n_points);
+
+/* Bone-partitioned geometry: replaces createBoneBVH and Update_BVH(HitableList**,
+ * FBXObject*) (createScene.h:221-307, 69-97; hitable/BoneBVH.h:5-173). The reference
+ * gives every bone its own BoneBVHNode tree over the triangles skinned to it and
+ * a per-bone translation nowTransform, and refits all of them each frame with one
+ * thread per bone. Here a part is a set of triangles that moves rigidly:
+ * crt_scene_set_parts names the part of every triangle (n_tri must equal the
+ * uploaded triangle count) and records the current vertices as the rest pose;
+ * crt_scene_move_parts uploads one translation per part (n_parts x 3 floats,
+ * 12 bytes per bone instead of 36 bytes per triangle) and writes
+ * vertex = rest vertex + translation[part] in one device pass (single rounded
+ * FP32 adds; stored normals stay, a translation does not turn them). Follow it
+ * with crt_accel_refit, whose bottom-up fit is parallel over all primitives of all
+ * parts at once. Hits are those of the flat list over the moved triangles, which is
+ * also what the reference's bone trees return. crt_scene_set_triangles clears the
+ * parts. */
+int crt_scene_set_parts(crt_ctx* ctx, const uint32_t* part_of_tri, size_t n_tri, size_t n_parts);
+int crt_scene_move_parts(crt_ctx* ctx, const float* translation, size_t n_parts);
+
 /* ---- acceleration structure: replaces create_BVHfromList and Update_BVH
  *      (createScene.h:212-219, 46-58) ---- */
 int crt_accel_build(crt_ctx* ctx);
@@ -223,6 +254,16 @@ int crt_render(crt_ctx* ctx, const crt_camera* cam, int nx, int ny, int spp, int
 int crt_render_frame(crt_ctx* ctx, const float* verts, size_t first, size_t n,
                      const crt_camera* cam, int nx, int ny, int spp, int max_depth,
                      int shade_mode, uint64_t seed, float* rgb_out);
+
+/* crt_render_frame for any of the three pose forms. pose_kind says what `pose` holds:
+ *   CRT_POSE_VERTICES  n x 9 floats for triangles [first, first + n)      (crt_scene_update_vertices)
+ *   CRT_POSE_POINTS    n x 3 floats, n = n_points, first = 0              (crt_scene_update_points)
+ *   CRT_POSE_PARTS     n x 3 floats, n = n_parts, first = 0               (crt_scene_move_parts)
+ * crt_render_frame(verts, ...) is crt_render_frame_pose(CRT_POSE_VERTICES, verts, ...). */
+typedef enum { CRT_POSE_VERTICES = 0, CRT_POSE_POINTS = 1, CRT_POSE_PARTS = 2 } crt_pose_kind;
+int crt_render_frame_pose(crt_ctx* ctx, int pose_kind, const float* pose, size_t first, size_t n,
+                          const crt_camera* cam, int nx, int ny, int spp, int max_depth,
+                          int shade_mode, uint64_t seed, float* rgb_out);
 
 /* Multi-GPU building blocks (device pointers, asynchronous on crt_stream()).
  * crt_render_accum_device adds nothing to d_accum: it overwrites it with, per

@@ -305,3 +305,24 @@ def test_cli_animation_loop_writes_every_frame(tmp_path):
     assert r.returncode == 0, r.stdout + r.stderr
     for i in range(3):
         assert np.array_equal(decode_png(prefix2 + "%d.png" % i), imgs[i])
+    # the pose as the mesh's point array (Renderer::set_indices / update_points, the form update_pose takes,
+    # createScene.h:99-140): same pictures, separate calls and overlapped
+    for k, extra in enumerate((["--pose", "points"], ["--pose", "points", "--overlap"])):
+        prefix3 = str(tmp_path / ("p%d_" % k))
+        r = subprocess.run([CLI, "--scene", "mesh", "--segments", "64", "--nx", "160", "--ny", "90", "--spp", "2", "--mode", "path",
+                            "--frames", "3", "--animate", "--out", prefix3, "--quiet"] + extra, capture_output=True, text=True)
+        assert r.returncode == 0, r.stdout + r.stderr
+        for i in range(3):
+            assert np.array_equal(decode_png(prefix3 + "%d.png" % i), imgs[i])
+    # bones (Renderer::createBoneBVH / Update_BVH(nowTransform), createScene.h:80-97,256-307): rigid parts move
+    outs = []
+    for k, extra in enumerate(([], ["--overlap"])):
+        prefix4 = str(tmp_path / ("b%d_" % k))
+        r = subprocess.run([CLI, "--scene", "mesh", "--segments", "64", "--nx", "160", "--ny", "90", "--spp", "2", "--mode", "path",
+                            "--frames", "3", "--animate", "--pose", "bones", "--out", prefix4, "--quiet"] + extra,
+                           capture_output=True, text=True)
+        assert r.returncode == 0, r.stdout + r.stderr
+        outs.append([decode_png(prefix4 + "%d.png" % i) for i in range(3)])
+    assert not np.array_equal(outs[0][0], outs[0][1]) and not np.array_equal(outs[0][1], outs[0][2])
+    for i in range(3):
+        assert np.array_equal(outs[0][i], outs[1][i])
