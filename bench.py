@@ -40,6 +40,8 @@ sys.path.insert(0, ROOT)
 
 METRIC = "Mrays/s"
 WORKLOAD = "C3: 998,002-triangle displaced sphere + ground, 1920x1080, 16 spp, max_depth 8, shade() path tracer"
+# --workload c4: BASELINE.json configs[3], not the headline line (the driver never passes it)
+WORKLOAD_C4 = "C4: 10 x 10 instances of a 100,000-triangle displaced sphere + ground (10.0 M triangles, flattened), 3840x2160, 64 spp, max_depth 8, shade() path tracer"
 
 
 def log(*a):
@@ -228,7 +230,13 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     dev = torch.device("cuda", local)
 
-    sc = scenes.c3_mesh()
+    if args.workload == "c4":
+        sc = scenes.c4_instanced()
+        args.no_cpu_baseline = True      # a list scan over 10 M triangles manages about one ray per second
+        args.e2e_api = "frame" if args.e2e_api == "points" else args.e2e_api
+    else:
+        sc = scenes.c3_mesh()
+    workload = WORKLOAD_C4 if args.workload == "c4" else WORKLOAD
     nx, ny, spp, depth = sc["nx"], sc["ny"], sc["spp"], sc["max_depth"]
     cam = crt.camera_for(sc)
     ctx = crt.Context(local)
@@ -242,8 +250,10 @@ def run_ours(args):
     rgb = torch.zeros(ny, nx, 3, dtype=torch.float32, device=dev)
     host_rgb = torch.empty(ny, nx, 3, dtype=torch.float32).pin_memory()
     host_verts = torch.from_numpy(np.ascontiguousarray(sc["tri"][:, :9])).pin_memory()
-    host_points = torch.from_numpy(sc["points"]).pin_memory()
-    ctx.set_indices(sc["tri_idx"], len(sc["points"]))
+    host_points = None
+    if "points" in sc:
+        host_points = torch.from_numpy(sc["points"]).pin_memory()
+        ctx.set_indices(sc["tri_idx"], len(sc["points"]))
 
     def barrier():
         if world > 1:
@@ -382,12 +392,13 @@ def run_ours(args):
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": args.scaling,
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "paths_per_s": paths / (ms * 1e-3),
-            "config": {"workload": WORKLOAD, "triangles": int(info["n_prims"]), "lbvh_depth": info["max_depth"],
+            "config": {"workload": workload, "triangles": int(info["n_prims"]), "lbvh_depth": info["max_depth"],
                        "lbvh_build_ms": build_ms, "lanes": lanes, "parallelism": ("single" if world == 1 else
                                        "samples%d: every rank renders 16 spp of every pixel (sample range [16r, 16r+16)), %d spp in the combined frame" % (world, spp * world)
                                        if weak else "tiles%d: 32x32 tiles, index mod N" % world),
-                       "combine": "ncclReduce(sum) of the 24.9 MB accumulators onto rank 0" if world > 1 else "none",
-                       "l2": "per-step working set (queues 4.2 GB + LBVH 0.12 GB) exceeds the 126 MB L2; no explicit flush",
+                       "combine": ("ncclReduce(sum) of the %.1f MB accumulators onto rank 0" % (nx * ny * 12 / 1e6)) if world > 1 else "none",
+                       "l2": "per-step working set (queues %.1f GB + LBVH %.2f GB) exceeds the 126 MB L2; no explicit flush" % (
+                           min(nx * ny * spp, 1 << 25) * 128 / 1e9, info["bytes"] / 1e9),
                        "rays_per_path": rays / max(1.0, paths)},
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "Mrays/s", "ms_per_step": 1e3 * e2e_s / args.steps,
@@ -449,6 +460,9 @@ def main():
                     help="end-to-end loop: points = the pose as the mesh's point array (crt_render_frame_pose, one overlapped "
                          "call per frame at N = 1); frame = all triangle vertices (crt_render_frame); calls = vertices through "
                          "the three separate calls")
+    ap.add_argument("--workload", default="c3", choices=["c3", "c4"],
+                    help="c3 (default): the configuration the metric is quoted on; c4: the 10 M-triangle instanced scene at "
+                         "4K x 64 spp (BASELINE.json configs[3]; use --scaling strong for its tile partition + NCCL reduce)")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="N > 1: weak = every rank renders the full 16-spp frame's work on its own sample range "
                          "(default); strong = the 16-spp frame is split by tiles")
