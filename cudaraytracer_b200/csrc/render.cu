@@ -214,7 +214,7 @@ k_trace_queue(AccelView A, const float4* __restrict__ q, uint32_t cap, const uin
               uint32_t* __restrict__ work_ctr, float4* __restrict__ hits, unsigned long long* __restrict__ counters,
               uint32_t refill, uint32_t leaf_thresh, uint32_t wide_below)
 {
-    __shared__ int s_stack[CRT_STACK_SMEM * TP_BLOCK];
+    __shared__ int s_stack[CRT_STACK_WORDS * CRT_STACK_SMEM * TP_BLOCK];
     const uint32_t n = *n_ptr;
     if (n < wide_below) return;                     // a launch this small belongs to k_trace_wide (queued right behind)
     TraceCounters cnt = {0u, 0u, 0u, 0u, 0u, 0u, 0u};

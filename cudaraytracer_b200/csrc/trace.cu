@@ -68,7 +68,7 @@ __global__ void __launch_bounds__(TP_BLOCK, CRT_TRACE_MIN_BLOCKS)
 k_trace_lbvh(AccelView A, const crt_ray* __restrict__ rays, uint32_t n, uint32_t* __restrict__ work_ctr, float t_min,
              float t_max, crt_hit* __restrict__ hits, unsigned long long* __restrict__ counters, uint32_t refill, uint32_t leaf_thresh)
 {
-    __shared__ int s_stack[CRT_STACK_SMEM * TP_BLOCK];
+    __shared__ int s_stack[CRT_STACK_WORDS * CRT_STACK_SMEM * TP_BLOCK];
     TraceCounters cnt = {0u, 0u, 0u, 0u, 0u, 0u, 0u};
     RaySrc src = {rays};
     HitSink sink = {hits};

@@ -26,6 +26,10 @@ def main():
             ts.append(ctx.counters()["render_ms"])
         return float(np.median(ts[2:]))
 
+    if len(sys.argv) > 1 and sys.argv[1] == "one":      # just the default configuration
+        ctx.build()
+        print("defaults: %.3f ms" % frame_ms(9), flush=True)
+        return
     for leaf_max in (2, 3, 4):
         ctx.set_option(crt.OPT_LEAF_MAX, leaf_max)
         ctx.build()
