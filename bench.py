@@ -291,11 +291,15 @@ def run_ours(args):
             ctx.refit()
             ctx.render(cam, nx, ny, spp, depth, crt.SHADE_PATH, seed, out=host_rgb.numpy())
         else:
+            # one process per GPU: every rank queues its pose upload + refit (crt_scene_pose_async) and renders its
+            # share; the camera rays are generated while the pose lands
             if args.e2e_api == "points":
-                ctx.update_points(host_points.numpy())
+                ctx.pose_async(crt.POSE_POINTS, host_points.numpy())
+            elif args.e2e_api == "frame":
+                ctx.pose_async(crt.POSE_VERTICES, host_verts.numpy())
             else:
                 ctx.update_vertices(host_verts.numpy())
-            ctx.refit()
+                ctx.refit()
             step(seed)
             if rank == 0:
                 with torch.cuda.stream(ext):
@@ -408,7 +412,11 @@ def run_ours(args):
                              if world == 1 and args.e2e_api == "points" else
                              "crt_render_frame (upload of all triangle vertices + refit + render + read-back, overlapped) per frame, pinned host buffers, wall clock"
                              if world == 1 and args.e2e_api == "frame" else
-                             "%s + crt_accel_refit + crt_render per frame, host buffers, wall clock" % ("crt_scene_update_points" if args.e2e_api == "points" else "crt_scene_update_vertices"))},
+                             "crt_scene_update_vertices + crt_accel_refit + crt_render per frame, host buffers, wall clock"
+                             if world == 1 else
+                             "per rank: %s, render of the rank's share, ncclReduce; rank 0: resolve + read-back to a pinned host buffer; wall clock, max over ranks" % (
+                                 "crt_scene_update_vertices + crt_accel_refit" if args.e2e_api == "calls" else
+                                 "crt_scene_pose_async(%s) (upload + refit beside ray generation)" % ("points" if args.e2e_api == "points" else "vertices")))},
             "gpu_launches": launches,
             "roofline": {"kernel": "closest hit over the 4-wide LBVH: k_trace_packet (camera rays) + k_trace_queue (bounces), %d launches/step" % bounce_launches,
                          "bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",

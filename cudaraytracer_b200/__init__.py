@@ -28,7 +28,7 @@ ABI_SYMBOLS = [
     "crt_abi_version", "crt_create", "crt_destroy", "crt_last_error", "crt_set_option", "crt_sync", "crt_stream",
     "crt_scene_set_materials", "crt_scene_set_triangles", "crt_scene_set_spheres", "crt_scene_update_vertices",
     "crt_scene_set_indices", "crt_scene_update_points", "crt_scene_set_parts", "crt_scene_move_parts",
-    "crt_render_frame_pose",
+    "crt_render_frame_pose", "crt_scene_pose_async",
     "crt_accel_build", "crt_accel_refit", "crt_trace", "crt_trace_device", "crt_render", "crt_render_frame",
     "crt_render_accum_device", "crt_resolve_device", "crt_pack_rgba8_device", "crt_get_counters",
     "crt_reset_counters", "crt_accel_info",
@@ -93,6 +93,7 @@ def load_library():
     lib.crt_scene_set_indices.argtypes = [vp, vp, sz, sz, sz]
     lib.crt_scene_update_points.argtypes = [vp, vp, sz]
     lib.crt_render_frame_pose.argtypes = [vp, C.c_int, vp, sz, sz, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint64, vp]
+    lib.crt_scene_pose_async.argtypes = [vp, C.c_int, vp, sz, sz]
     lib.crt_scene_set_parts.argtypes = [vp, vp, sz, sz]
     lib.crt_scene_move_parts.argtypes = [vp, vp, sz]
     lib.crt_accel_build.argtypes = [vp]
@@ -246,6 +247,14 @@ class Context:
         """vertex = rest vertex + translation[part]; follow with refit()."""
         t = np.ascontiguousarray(translation, np.float32).reshape(-1, 3)
         self._check(self.lib.crt_scene_move_parts(self._h, _ptr(t), t.shape[0]))
+
+    def pose_async(self, kind, pose, first=0):
+        """crt_scene_pose_async: queue pose upload + refit; the next render_accum_device overlaps its ray generation
+        with them. `pose` must stay alive and untouched until the next call on this context returns."""
+        width = 9 if kind == POSE_VERTICES else 3
+        pose = np.ascontiguousarray(pose, np.float32).reshape(-1, width)
+        self._pose_keepalive = pose
+        self._check(self.lib.crt_scene_pose_async(self._h, int(kind), _ptr(pose), int(first), pose.shape[0]))
 
     def build(self):
         self._check(self.lib.crt_accel_build(self._h))

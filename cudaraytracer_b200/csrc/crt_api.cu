@@ -106,6 +106,25 @@ using namespace crt;
         if (e__ != cudaSuccess) return cuda_fail(e__, "cudaSetDevice", __FILE__, __LINE__); \
     } while (0)
 
+// A pose queued by crt_scene_pose_async is still in flight on the upload stream: wait for it before anything other
+// than a render touches the scene, the tree or the staging buffers.
+static int settle_pose(crt_ctx* c)
+{
+    if (!c->pose_pending) return CRT_OK;
+    c->pose_pending = false;
+    CRT_CUDA(cudaStreamSynchronize(c->up_stream));
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, c->ev_up0, c->ev_up1) == cudaSuccess) c->host_counters.refit_ms = ms;
+    return CRT_OK;
+}
+
+#define CRT_CHECK_SETTLED(c)                       \
+    do {                                           \
+        CRT_CHECK_CTX(c);                          \
+        int s__ = settle_pose(c);                  \
+        if (s__ != CRT_OK) return s__;             \
+    } while (0)
+
 extern "C" {
 
 int crt_abi_version(void) { return CRT_ABI_VERSION; }
@@ -192,7 +211,7 @@ void crt_destroy(crt_ctx* c)
 
 int crt_set_option(crt_ctx* c, int option, int64_t value)
 {
-    CRT_CHECK_CTX(c);
+    CRT_CHECK_SETTLED(c);
     switch (option) {
     case CRT_OPT_LEAF_MAX:
         if (value < 1 || value > 8) { set_error("CRT_OPT_LEAF_MAX must be in [1, 8]"); return CRT_ERR_INVALID; }
@@ -235,7 +254,7 @@ int crt_set_option(crt_ctx* c, int option, int64_t value)
 
 int crt_sync(crt_ctx* c)
 {
-    CRT_CHECK_CTX(c);
+    CRT_CHECK_SETTLED(c);
     CRT_CUDA(cudaStreamSynchronize(c->stream));
     return CRT_OK;
 }
@@ -244,7 +263,7 @@ void* crt_stream(crt_ctx* c) { return c ? (void*)c->stream : nullptr; }
 
 int crt_scene_set_materials(crt_ctx* c, const crt_material* mats, size_t n)
 {
-    CRT_CHECK_CTX(c);
+    CRT_CHECK_SETTLED(c);
     if (n > 0 && !mats) { set_error("crt_scene_set_materials: null table"); return CRT_ERR_INVALID; }
     if (n > 32768) { set_error("crt_scene_set_materials: at most 32768 materials (got %zu)", n); return CRT_ERR_INVALID; }
     std::vector<DMat> d(n);
@@ -280,7 +299,7 @@ static int check_mat_ids(const crt_ctx* c, const uint32_t* mat_id, size_t n, con
 
 int crt_scene_set_triangles(crt_ctx* c, const float* tri, const uint32_t* mat_id, const uint32_t* prim_id, size_t n)
 {
-    CRT_CHECK_CTX(c);
+    CRT_CHECK_SETTLED(c);
     if (n > 0 && !tri) { set_error("crt_scene_set_triangles: null vertex array"); return CRT_ERR_INVALID; }
     if (n >= (1ull << 28)) { set_error("crt_scene_set_triangles: too many triangles"); return CRT_ERR_INVALID; }
     int r = check_mat_ids(c, mat_id, n, "crt_scene_set_triangles");
@@ -301,7 +320,7 @@ int crt_scene_set_triangles(crt_ctx* c, const float* tri, const uint32_t* mat_id
 
 int crt_scene_set_spheres(crt_ctx* c, const float* sph, const uint32_t* mat_id, const uint32_t* prim_id, size_t n)
 {
-    CRT_CHECK_CTX(c);
+    CRT_CHECK_SETTLED(c);
     if (n > 0 && !sph) { set_error("crt_scene_set_spheres: null array"); return CRT_ERR_INVALID; }
     if (n >= (1ull << 28)) { set_error("crt_scene_set_spheres: too many spheres"); return CRT_ERR_INVALID; }
     int r = check_mat_ids(c, mat_id, n, "crt_scene_set_spheres");
@@ -359,7 +378,7 @@ static int enqueue_pose(crt_ctx* c, int kind, const float* data, size_t first, s
 
 int crt_scene_update_vertices(crt_ctx* c, const float* verts, size_t first, size_t n)
 {
-    CRT_CHECK_CTX(c);
+    CRT_CHECK_SETTLED(c);
     // staged through the (otherwise idle) ray upload buffer
     int r = enqueue_pose(c, CRT_POSE_VERTICES, verts, first, n, c->stream, "crt_scene_update_vertices");
     if (r != CRT_OK) return r;
@@ -369,7 +388,7 @@ int crt_scene_update_vertices(crt_ctx* c, const float* verts, size_t first, size
 
 int crt_scene_set_indices(crt_ctx* c, const uint32_t* idx, size_t first, size_t n_tri, size_t n_points)
 {
-    CRT_CHECK_CTX(c);
+    CRT_CHECK_SETTLED(c);
     if (n_tri == 0 || n_points == 0) { c->n_idx_tri = 0; c->n_points = 0; return CRT_OK; }
     if (!idx) { set_error("crt_scene_set_indices: null array"); return CRT_ERR_INVALID; }
     if (first + n_tri > c->n_tri) { set_error("crt_scene_set_indices: range [%zu, %zu) exceeds %zu triangles", first, first + n_tri, c->n_tri); return CRT_ERR_INVALID; }
@@ -387,16 +406,37 @@ int crt_scene_set_indices(crt_ctx* c, const uint32_t* idx, size_t first, size_t 
 
 int crt_scene_update_points(crt_ctx* c, const float* points, size_t n_points)
 {
-    CRT_CHECK_CTX(c);
+    CRT_CHECK_SETTLED(c);
     int r = enqueue_pose(c, CRT_POSE_POINTS, points, 0, n_points, c->stream, "crt_scene_update_points");
     if (r != CRT_OK) return r;
     CRT_CUDA(cudaStreamSynchronize(c->stream));
     return CRT_OK;
 }
 
+int crt_scene_pose_async(crt_ctx* c, int pose_kind, const float* pose, size_t first, size_t n)
+{
+    CRT_CHECK_SETTLED(c);
+    if (!c->accel_valid || c->n_prims != (uint32_t)(c->n_tri + c->n_sph)) {
+        set_error("crt_scene_pose_async: call crt_accel_build first (a pose only refits)");
+        return CRT_ERR_STATE;
+    }
+    cudaStream_t up = c->up_stream;
+    // behind whatever the context's stream still does with the scene (a render queued by a _device call has
+    // finished when that call returned; a crt_trace_device may not have)
+    CRT_CUDA(cudaEventRecord(c->ev_fork, c->stream));
+    CRT_CUDA(cudaStreamWaitEvent(up, c->ev_fork, 0));
+    int r = enqueue_pose(c, pose_kind, pose, first, n, up, "crt_scene_pose_async");
+    if (r != CRT_OK) return r;
+    r = lbvh_build(c, true, up);
+    if (r != CRT_OK) { cudaStreamSynchronize(up); return r; }
+    CRT_CUDA(cudaEventRecord(c->ev_frame, up));
+    c->pose_pending = true;
+    return CRT_OK;
+}
+
 int crt_scene_set_parts(crt_ctx* c, const uint32_t* part_of_tri, size_t n_tri, size_t n_parts)
 {
-    CRT_CHECK_CTX(c);
+    CRT_CHECK_SETTLED(c);
     if (n_tri != c->n_tri) { set_error("crt_scene_set_parts: %zu part ids for %zu triangles", n_tri, c->n_tri); return CRT_ERR_INVALID; }
     if (n_tri == 0 || n_parts == 0) { c->n_parts = 0; return CRT_OK; }
     if (!part_of_tri) { set_error("crt_scene_set_parts: null array"); return CRT_ERR_INVALID; }
@@ -416,7 +456,7 @@ int crt_scene_set_parts(crt_ctx* c, const uint32_t* part_of_tri, size_t n_tri, s
 
 int crt_scene_move_parts(crt_ctx* c, const float* translation, size_t n_parts)
 {
-    CRT_CHECK_CTX(c);
+    CRT_CHECK_SETTLED(c);
     int r = enqueue_pose(c, CRT_POSE_PARTS, translation, 0, n_parts, c->stream, "crt_scene_move_parts");
     if (r != CRT_OK) return r;
     CRT_CUDA(cudaStreamSynchronize(c->stream));   // the caller's array is free again
@@ -425,19 +465,19 @@ int crt_scene_move_parts(crt_ctx* c, const float* translation, size_t n_parts)
 
 int crt_accel_build(crt_ctx* c)
 {
-    CRT_CHECK_CTX(c);
+    CRT_CHECK_SETTLED(c);
     return lbvh_build(c, false);
 }
 
 int crt_accel_refit(crt_ctx* c)
 {
-    CRT_CHECK_CTX(c);
+    CRT_CHECK_SETTLED(c);
     return lbvh_build(c, true);
 }
 
 int crt_trace_device(crt_ctx* c, const crt_ray* d_rays, size_t n, float t_min, float t_max, int accel, crt_hit* d_hits)
 {
-    CRT_CHECK_CTX(c);
+    CRT_CHECK_SETTLED(c);
     if (n > 0 && (!d_rays || !d_hits)) { set_error("crt_trace_device: null buffer"); return CRT_ERR_INVALID; }
     int r = launch_trace(c, d_rays, n, t_min, t_max, accel, d_hits);
     if (r == CRT_OK) c->host_counters.rays += n;
@@ -446,7 +486,7 @@ int crt_trace_device(crt_ctx* c, const crt_ray* d_rays, size_t n, float t_min, f
 
 int crt_trace(crt_ctx* c, const crt_ray* rays, size_t n, float t_min, float t_max, int accel, crt_hit* hits)
 {
-    CRT_CHECK_CTX(c);
+    CRT_CHECK_SETTLED(c);
     if (n == 0) return CRT_OK;
     if (!rays || !hits) { set_error("crt_trace: null buffer"); return CRT_ERR_INVALID; }
     CRT_CUDA(c->rays_tmp.reserve(n * sizeof(crt_ray)));
@@ -470,7 +510,13 @@ int crt_render_accum_device(crt_ctx* c, const crt_camera* cam, int nx, int ny, i
                             int max_depth, int shade_mode, uint64_t seed, int rank, int world, float* d_accum)
 {
     CRT_CHECK_CTX(c);
-    return render_accum(c, cam, nx, ny, sample_begin, sample_end, max_depth, shade_mode, seed, rank, world, d_accum);
+    // a pose queued by crt_scene_pose_async: only the closest-hit launches wait for it (ray generation does not read
+    // the scene); render_accum returns after its last launch has finished, so the pose has landed by then
+    const bool pending = c->pose_pending;
+    const int r = render_accum(c, cam, nx, ny, sample_begin, sample_end, max_depth, shade_mode, seed, rank, world, d_accum,
+                               nullptr, pending ? c->ev_frame : nullptr);
+    const int s = settle_pose(c);
+    return r != CRT_OK ? r : s;
 }
 
 int crt_resolve_device(crt_ctx* c, const float* d_accum, size_t n_pixels, int spp, float* d_rgb)
@@ -510,7 +556,7 @@ static int render_to_host(crt_ctx* c, const crt_camera* cam, int nx, int ny, int
 int crt_render(crt_ctx* c, const crt_camera* cam, int nx, int ny, int spp, int max_depth, int shade_mode,
                uint64_t seed, float* rgb_out)
 {
-    CRT_CHECK_CTX(c);
+    CRT_CHECK_SETTLED(c);
     if (!rgb_out) { set_error("crt_render: rgb_out is null"); return CRT_ERR_INVALID; }
     if (nx <= 0 || ny <= 0 || spp < 1) { set_error("crt_render: nx, ny and spp must be positive"); return CRT_ERR_INVALID; }
     return render_to_host(c, cam, nx, ny, spp, max_depth, shade_mode, seed, rgb_out, nullptr);
@@ -522,7 +568,7 @@ int crt_render(crt_ctx* c, const crt_camera* cam, int nx, int ny, int spp, int m
 int crt_render_frame_pose(crt_ctx* c, int pose_kind, const float* pose, size_t first, size_t n, const crt_camera* cam,
                           int nx, int ny, int spp, int max_depth, int shade_mode, uint64_t seed, float* rgb_out)
 {
-    CRT_CHECK_CTX(c);
+    CRT_CHECK_SETTLED(c);
     if (!rgb_out) { set_error("crt_render_frame: rgb_out is null"); return CRT_ERR_INVALID; }
     if (nx <= 0 || ny <= 0 || spp < 1) { set_error("crt_render_frame: nx, ny and spp must be positive"); return CRT_ERR_INVALID; }
     if (!c->accel_valid || c->n_prims != (uint32_t)(c->n_tri + c->n_sph)) {
@@ -550,7 +596,7 @@ int crt_render_frame(crt_ctx* c, const float* verts, size_t first, size_t n, con
 
 int crt_get_counters(crt_ctx* c, crt_counters* out)
 {
-    CRT_CHECK_CTX(c);
+    CRT_CHECK_SETTLED(c);
     if (!out) { set_error("crt_get_counters: out is null"); return CRT_ERR_INVALID; }
     unsigned long long h[CNT_COUNT];
     CRT_CUDA(cudaMemcpyAsync(h, c->counters.p, sizeof h, cudaMemcpyDeviceToHost, c->stream));
@@ -568,7 +614,7 @@ int crt_get_counters(crt_ctx* c, crt_counters* out)
 
 int crt_reset_counters(crt_ctx* c)
 {
-    CRT_CHECK_CTX(c);
+    CRT_CHECK_SETTLED(c);
     CRT_CUDA(cudaMemsetAsync(c->counters.p, 0, sizeof(unsigned long long) * CNT_COUNT, c->stream));
     CRT_CUDA(cudaStreamSynchronize(c->stream));
     const float b = c->host_counters.build_ms, r = c->host_counters.refit_ms;
@@ -580,7 +626,7 @@ int crt_reset_counters(crt_ctx* c)
 
 int crt_accel_info(crt_ctx* c, uint64_t* n_prims, uint64_t* n_nodes, uint64_t* bytes, int* max_depth)
 {
-    CRT_CHECK_CTX(c);
+    CRT_CHECK_SETTLED(c);
     if (!c->accel_valid) { set_error("crt_accel_info: no acceleration structure"); return CRT_ERR_STATE; }
     const uint64_t n = c->n_prims;
     if (n_prims) *n_prims = n;

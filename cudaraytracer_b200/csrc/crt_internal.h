@@ -71,6 +71,7 @@ struct crt_ctx {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_fork = nullptr;
     cudaStream_t up_stream = nullptr;      // crt_render_frame: vertex upload + refit, overlapped with ray generation
     cudaEvent_t ev_up0 = nullptr, ev_up1 = nullptr, ev_frame = nullptr;
+    bool pose_pending = false;             // crt_scene_pose_async: upload + refit in flight on up_stream, ev_frame marks their end
     crt_lane lane[CRT_MAX_LANES];
     int n_lanes = 4;                       // CRT_OPT_LANES: most slices of a frame in flight
 

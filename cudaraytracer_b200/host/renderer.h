@@ -120,6 +120,13 @@ public:
                                     &colorBuffer[0].e[0]), "crt_render_frame_pose");
     }
 
+    // The pose + refit half of render_frame_pose alone (crt_scene_pose_async): returns at once; the next
+    // crt_render_accum_device on ctx() overlaps its ray generation with the upload and the refit.
+    void pose_async(int pose_kind, const float* pose, size_t first, size_t n)
+    {
+        check(crt_scene_pose_async(ctx_, pose_kind, pose, first, n), "crt_scene_pose_async");
+    }
+
     // (*world)->hit for a batch of rays (render.h:53).
     void trace(const std::vector<Ray>& rays, std::vector<crt_hit>& hits, float t_min = 0.001f, float t_max = 3.402823466e38f,
                int accel = CRT_ACCEL_LBVH)

@@ -265,6 +265,14 @@ int crt_render_frame_pose(crt_ctx* ctx, int pose_kind, const float* pose, size_t
                           const crt_camera* cam, int nx, int ny, int spp, int max_depth,
                           int shade_mode, uint64_t seed, float* rgb_out);
 
+/* The pose + refit half of crt_render_frame_pose on its own, for callers that render through the _device entry
+ * points (one process per GPU): queues the upload of `pose` (forms as above), the pose kernel and the refit on the
+ * context's upload stream and returns at once. The next crt_render_accum_device generates its camera rays meanwhile
+ * and only its closest-hit launches wait for the refit; every other entry point first waits for the queued pose.
+ * `pose` must stay untouched until the next call on this context returns (page-locked memory makes the copy
+ * asynchronous). Needs a built acceleration structure. */
+int crt_scene_pose_async(crt_ctx* ctx, int pose_kind, const float* pose, size_t first, size_t n);
+
 /* Multi-GPU building blocks (device pointers, asynchronous on crt_stream()).
  * crt_render_accum_device adds nothing to d_accum: it overwrites it with, per
  * pixel this part owns, the sum over samples [sample_begin, sample_end) in

@@ -1,7 +1,11 @@
 """Runs BASELINE.json's configs C1..C5 on one GPU through the C ABI and prints one
 table row per config. Development/report aid, not the bench.
-Usage: python scripts/run_configs.py [c1 c2 c3 c4 c5] [--max-tris N]"""
+Usage: python scripts/run_configs.py [c1 c2 c3 c4 c5] [--max-tris N]
+Under torchrun (N ranks) only c5 runs: every rank builds the same LBVH and traces its own 1/N of the rays (SURVEY 8e:
+"rays are split evenly across GPUs against a replicated BVH; no collective"); time = max over ranks, rate = all rays / it:
+  python -m torch.distributed.run --nproc-per-node N --master-addr 127.0.0.1 scripts/run_configs.py c5"""
 import json
+import os
 import sys
 import time
 
@@ -57,11 +61,16 @@ def render_row(name, sc, mode=crt.SHADE_PATH, reps=3):
     return row
 
 
+WORLD = int(os.environ.get("WORLD_SIZE", "1"))
+RANK = int(os.environ.get("RANK", "0"))
+LOCAL = int(os.environ.get("LOCAL_RANK", "0"))
+
+
 def trace_rows(n_tri, reps=5):
     t0 = time.time()
     sc = scenes.c5_triangles(n_tri)
     gen = time.time() - t0
-    ctx = crt.Context(0)
+    ctx = crt.Context(LOCAL)
     ctx.set_scene(sc)
     ctx.build()
     ctx.build()
@@ -74,8 +83,11 @@ def trace_rows(n_tri, reps=5):
                               ("incoherent", scenes.c5_incoherent_rays(1 << 21), crt.ACCEL_LBVH)):
         # the launch is replicated 8x so that a persistent grid of 1184 blocks has work beyond its ramp-up
         rays = np.ascontiguousarray(np.tile(rays, (8, 1)))
-        d_rays = torch.from_numpy(rays).cuda()
-        d_hits = torch.empty(len(rays), 4, dtype=torch.float32, device="cuda")
+        n_all = len(rays)
+        if WORLD > 1:      # this rank's contiguous share
+            rays = np.ascontiguousarray(rays[RANK * n_all // WORLD:(RANK + 1) * n_all // WORLD])
+        d_rays = torch.from_numpy(rays).cuda(LOCAL)
+        d_hits = torch.empty(len(rays), 4, dtype=torch.float32, device="cuda:%d" % LOCAL)
         ctx.set_option(crt.OPT_COUNTERS, 1)
         ctx.reset_counters()
         ctx.trace_device(d_rays.data_ptr(), len(rays), d_hits.data_ptr(), accel=accel)
@@ -93,6 +105,19 @@ def trace_rows(n_tri, reps=5):
         ctx.sync()
         ms = e0.elapsed_time(e1) / reps
         n = len(rays)
+        if WORLD > 1:
+            import torch.distributed as dist
+            tmax = torch.tensor([ms], dtype=torch.float64, device="cuda")
+            dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+            tot = torch.tensor([float(n), float(w["nodes_visited"]), float(w["tris_tested"]), float(w["node_fetches"]),
+                                float(w["tri_fetches"])], dtype=torch.float64, device="cuda")
+            dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+            rows.append(dict(config="C5 %s" % kind, gpus=WORLD, prims=n_tri, rays=int(tot[0]), ms=float(tmax[0]),
+                             mrays_s=float(tot[0]) / float(tmax[0]) / 1e3, build_ms=build_ms,
+                             nodes_per_ray=float(tot[1] / tot[0]), tris_per_ray=float(tot[2] / tot[0]),
+                             alg_gbs=float(128 * tot[3] + 48 * tot[4] + 48 * tot[0]) / float(tmax[0]) / 1e6))
+            del d_rays, d_hits
+            continue
         rows.append(dict(config="C5 %s" % kind, prims=n_tri, rays=n, ms=ms, mrays_s=n / ms / 1e3, build_ms=build_ms,
                          hit_rate=float((d_hits[:, 1].view(torch.int32) != -1).float().mean()),
                          nodes_per_ray=w["nodes_visited"] / n, tris_per_ray=w["tris_tested"] / n, scene_gen_s=gen,
@@ -109,6 +134,12 @@ def main():
     if "--max-tris" in sys.argv:
         max_tris = int(float(sys.argv[sys.argv.index("--max-tris") + 1]))
     out = []
+    if WORLD > 1:
+        import torch.distributed as dist
+        torch.cuda.set_device(LOCAL)
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", LOCAL))
+        which = [w for w in which if w == "c5"]
     if "c1" in which:
         out.append(render_row("C1 bunny LambertShade", scenes.c1_bunny(), crt.SHADE_LAMBERT, reps=10))
         out.append(render_row("C1 bunny shade()", scenes.c1_bunny(), crt.SHADE_PATH, reps=10))
@@ -125,8 +156,12 @@ def main():
         while n <= max_tris:
             out.extend(trace_rows(n))
             n *= 10
-    for r in out:
-        print(json.dumps(r), flush=True)
+    if RANK == 0:
+        for r in out:
+            print(json.dumps(r), flush=True)
+    if WORLD > 1:
+        dist.barrier()
+        dist.destroy_process_group()
 
 
 if __name__ == "__main__":
