@@ -115,6 +115,29 @@ int main(int argc, char** argv)
             if (raw.size() != (size_t)nx * ny * 12) return 65;
             return WritePng(nx, ny, 7, reinterpret_cast<const vec3*>(raw.data()), argv[5]) ? 0 : 1;
         }
+        if (cmd == "indexed" && argc == 5) {
+            // host_probe indexed SEGMENTS PHASE OUT: the indexed form of the C3 mesh (mesh_points + mesh_indices) must
+            // reproduce mesh_vertices() bit for bit; OUT gets {n_points, n_tri, points, idx}
+            const int nt = std::atoi(argv[2]), np = nt / 2;
+            const double phase = std::atof(argv[3]);
+            std::vector<float> verts, points;
+            std::vector<uint32_t> idx;
+            crt_host::mesh_vertices(nt, np, phase, verts, nullptr);
+            crt_host::mesh_points(nt, np, phase, points);
+            crt_host::mesh_indices(nt, np, idx);
+            if (idx.size() * 3 != verts.size()) return 2;
+            for (size_t i = 0; i < idx.size(); i++)
+                for (int k = 0; k < 3; k++)
+                    if (std::memcmp(&points[(size_t)idx[i] * 3 + k], &verts[i * 3 + k], 4) != 0) return 3;
+            FILE* f = std::fopen(argv[4], "wb");
+            if (!f) return 1;
+            const uint32_t hdr[2] = {(uint32_t)(points.size() / 3), (uint32_t)(idx.size() / 3)};
+            put(f, hdr, sizeof hdr);
+            put(f, points.data(), points.size() * 4);
+            put(f, idx.data(), idx.size() * 4);
+            std::fclose(f);
+            return 0;
+        }
         if (cmd == "reject" && argc == 3) {
             const std::string what = argv[2];
             HitableList l;

@@ -145,6 +145,29 @@ def test_flatten_mesh_matches_scenes_py(probe, tmp_path):
     assert np.array_equal(resolved_materials(flat, flat["tri_mat"]), scene_materials(sc, sc["tri_mat"]))
 
 
+def test_indexed_mesh_matches_scenes_py(probe, tmp_path):
+    """The indexed form of the C3 mesh (the pose input of crt_scene_update_points): the C++ generator's
+    points[idx] equals its own mesh_vertices() bit for bit (checked inside the probe), the index buffer equals
+    scenes.displaced_sphere_indexed's, and the rest-pose points agree to 1 ulp (libm vs numpy sin/cos)."""
+    out = str(tmp_path / "i.bin")
+    for phase in ("0", "0.6"):
+        r = subprocess.run([probe, "indexed", "40", phase, out])
+        assert r.returncode == 0
+    raw = open(out, "rb").read()
+    n_points, n_tri = np.frombuffer(raw[:8], np.uint32)
+    points = np.frombuffer(raw[8:8 + n_points * 12], np.float32).reshape(-1, 3)
+    idx = np.frombuffer(raw[8 + n_points * 12:], np.uint32).reshape(-1, 3)
+    assert len(idx) == n_tri
+    subprocess.run([probe, "indexed", "40", "0", out], check=True)
+    raw = open(out, "rb").read()
+    points = np.frombuffer(raw[8:8 + n_points * 12], np.float32).reshape(-1, 3)
+    p_py, i_py = scenes.displaced_sphere_indexed(40, 20)
+    assert np.array_equal(idx, i_py)
+    assert np.allclose(points, p_py, rtol=2e-7, atol=2e-5)
+    sc = scenes.c3_mesh(40, 20)
+    assert np.array_equal(sc["points"][sc["tri_idx"]].reshape(-1, 9), sc["tri"][:len(sc["tri_idx"]), :9])
+
+
 def test_flatten_nested_lists_accumulate_offsets(probe, tmp_path):
     out = str(tmp_path / "f.bin")
     subprocess.run([probe, "flat", "nested", out], check=True)
