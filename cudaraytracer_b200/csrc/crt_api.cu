@@ -152,18 +152,29 @@ int crt_create(int device, crt_ctx** out)
     c->sm_count = prop.multiProcessorCount;
     if (const char* e = getenv("CRT_BUILDER")) c->builder = atoi(e) == CRT_BUILDER_PLOC ? CRT_BUILDER_PLOC : CRT_BUILDER_LBVH;   // development aids
     if (const char* e = getenv("CRT_PLOC_RADIUS")) c->ploc_radius = std::max(1, std::min(32, atoi(e)));
-    CRT_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    // Stream priorities, measured at v9 (profiles/r01_v9_stream_priorities.txt). The upload + refit stream gets the
+    // highest priority: the closest-hit launches of every slice wait for it while ray generation fills the GPU, and
+    // with equal priorities its kernels queue behind the ray generation blocks (points frame 9.70 -> 9.56 ms).
+    // Giving the slices of a frame (lanes) descending priorities - so that they finish one after the other and each
+    // one's read-back overlaps the next one's rendering - serialises them and costs 0.7 ms per frame (8.95 -> 9.65):
+    // the slices stay equal. CRT_LANE_PRIO (development aid): 0 = no priorities, 1 = descending lanes too, 2 = default.
+    int prio_lo = 0, prio_hi = 0;
+    CRT_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));   // numerically lower = higher priority
+    const int prio_mode = getenv("CRT_LANE_PRIO") ? atoi(getenv("CRT_LANE_PRIO")) : 2;
+    const bool use_prio = prio_mode == 1;
+    auto lane_prio = [&](int l) { return use_prio ? std::max(prio_hi, std::min(prio_lo, prio_lo - (CRT_MAX_LANES - 1 - l))) : prio_lo; };
+    CRT_CUDA(cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, lane_prio(0)));
     CRT_CUDA(cudaEventCreate(&c->ev0));
     CRT_CUDA(cudaEventCreate(&c->ev1));
     CRT_CUDA(cudaEventCreate(&c->ev_fork));
-    CRT_CUDA(cudaStreamCreateWithFlags(&c->up_stream, cudaStreamNonBlocking));
+    CRT_CUDA(cudaStreamCreateWithPriority(&c->up_stream, cudaStreamNonBlocking, prio_mode != 0 ? prio_hi : prio_lo));
     CRT_CUDA(cudaEventCreate(&c->ev_up0));
     CRT_CUDA(cudaEventCreate(&c->ev_up1));
     CRT_CUDA(cudaEventCreate(&c->ev_frame));
     for (int l = 0; l < CRT_MAX_LANES; l++) {
         crt_lane& L = c->lane[l];
         if (l == 0) L.stream = c->stream;
-        else CRT_CUDA(cudaStreamCreateWithFlags(&L.stream, cudaStreamNonBlocking));
+        else CRT_CUDA(cudaStreamCreateWithPriority(&L.stream, cudaStreamNonBlocking, lane_prio(l)));
         CRT_CUDA(cudaEventCreate(&L.ev_begin));
         CRT_CUDA(cudaEventCreate(&L.ev_end));
         for (auto& e : L.ev_trace) CRT_CUDA(cudaEventCreate(&e));
