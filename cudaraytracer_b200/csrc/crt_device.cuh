@@ -19,7 +19,9 @@ namespace crt {
 //   sphere:   r0 = {centre.xyz, radius}, r1 = r2 = 0
 //   both:     r3 = {prim_id, mat_id | kind << 31, 0, 0} as uint bits
 // 4-wide node: 96 B of payload at a 128 B stride (one cache line), read with three 256-bit loads:
-//   words 5k..5k+4 = child k: {lo.x, lo.y, lo.z, half2(ext.x, ext.y), half2(ext.z, 0)}
+//   words 5k..5k+4 = child k: {lo.x, lo.y, lo.z, half2(ext.x, ext.y), half2(ext.z, A_k)}; A = (A_0, A_1, A_2) is the
+//        normal-cone vector of the NODE's own subtree (0 = none; lbvh.cu:cone_to_halves, crt_traverse.cuh:node_backfacing),
+//        the fourth child's spare half is 0
 //        hi = lo + ext; ext is a half rounded up at build time until lo + ext >= hi in fp32, so the box only
 //        grows (by < 2^-10 of its own extent) and the child references fit the same three loads - a fourth
 //        load per node visit was a quarter of the L1 wavefronts of the incoherent bounces

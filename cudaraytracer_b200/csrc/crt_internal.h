@@ -93,7 +93,7 @@ struct crt_ctx {
     crt::DevBuf ploc_box[2], ploc_nn, ploc_tmp, ploc_blk;   // PLOC rounds: cluster boxes (double-buffered), partners, scratch
     int builder = CRT_BUILDER_LBVH;
     int ploc_radius = 8;                   // positions searched to either side per PLOC round (<= 32)
-    crt::DevBuf child, parent, leaf_parent, range, node_box, leaf_box, flags, bounds, depth_out;
+    crt::DevBuf child, parent, leaf_parent, range, node_box, node_cone, leaf_box, flags, bounds, depth_out;
     bool accel_valid = false;
     int root = 0;
     int perm_buf = 0;                      // which vals[] holds the sorted permutation

@@ -179,6 +179,26 @@ __device__ __forceinline__ void child_box(const float lox, const float loy, cons
     hiz = __fadd_rn(loz, __half2float(__ushort_as_half((unsigned short)(v & 0xFFFFu))));
 }
 
+// Node-level version of the reference's `if (dot(direction, normal) < 0) return false` (shapes/triangle.h:61): the
+// spare halves of children 0-2 hold a vector A built from the normal cone of the node's whole subtree
+// (lbvh.cu:cone_to_halves) such that dot(d, A) < -1 for the unit direction d means every triangle below would fail
+// that test; such a node is left without testing its boxes. A = 0 (never true) for subtrees with spheres or normals
+// too spread out. CRT_NORMAL_CONES=0 compiles the test out (development switch).
+#ifndef CRT_NORMAL_CONES
+#define CRT_NORMAL_CONES 1
+#endif
+__device__ __forceinline__ bool node_backfacing(const float (&w)[24], const v3& d)
+{
+#if CRT_NORMAL_CONES
+    const float ax = __half2float(__ushort_as_half((unsigned short)(__float_as_uint(w[4]) >> 16)));
+    const float ay = __half2float(__ushort_as_half((unsigned short)(__float_as_uint(w[9]) >> 16)));
+    const float az = __half2float(__ushort_as_half((unsigned short)(__float_as_uint(w[14]) >> 16)));
+    return fmaf(d.x, ax, fmaf(d.y, ay, d.z * az)) < -1.0f;
+#else
+    return false;
+#endif
+}
+
 // order-preserving float <-> uint32 (for REDUX min/max over a warp)
 __device__ __forceinline__ uint32_t f2sortable(float f)
 {
@@ -330,6 +350,7 @@ __device__ __forceinline__ void traverse_persistent(const AccelView& A, const ui
                     key[k] = h ? tn : INFINITY;
                     n_hit += h ? 1 : 0;
                 }
+                if (node_backfacing(f, d)) n_hit = 0;   // every triangle below faces away from this ray (Q1)
                 // order the four slots by entry distance (misses last): 5 compare-exchanges
 #define CRT_CSWAP(a, b)                                                                    \
                 {                                                                          \
@@ -658,6 +679,7 @@ __device__ __forceinline__ void traverse_wide(const AccelView& A, const uint32_t
                     key[k] = h ? tn : INFINITY;
                     n_hit += h ? 1 : 0;
                 }
+                if (node_backfacing(f, d)) n_hit = 0;
 #define CRT_CSWAP(a, b)                                                                    \
                 {                                                                          \
                     const bool sw = key[b] < key[a];                                       \

@@ -207,12 +207,90 @@ __device__ __forceinline__ void store_box(float4* __restrict__ base, size_t idx,
     base[2 * idx + 1] = make_float4(b.hx, b.hy, b.hz, 0.0f);
 }
 
+// ---- normal cones -----------------------------------------------------------
+// The reference's triangle test starts with `if (dot(direction, normal) < 0) return false` (shapes/triangle.h:61,
+// SURVEY 9 Q1): a triangle whose STORED normal points against the ray is never hit. Every subtree therefore gets a
+// cone {unit axis, cos of the half-angle} that contains the stored normals of all its triangles (a sphere anywhere
+// below makes it "none": c = -2), merged bottom-up beside the boxes; k_emit_nodes turns the cone of a wide node's own
+// subtree into a vector A with  dot(unit direction, A) < -1  =>  dot(direction, n) < 0 for every normal n below, and
+// the per-ray traversals drop such a node before testing its children (crt_traverse.cuh:node_backfacing). The cones
+// depend on the stored normals only, which no pose update changes (Triangle::SetVertices keeps them).
+struct Cone { float x, y, z, c; };
+__device__ __forceinline__ Cone cone_none() { return Cone{0.f, 0.f, 0.f, -2.f}; }
+
+__device__ __forceinline__ Cone cone_of_normal(float nx, float ny, float nz)
+{
+    const float l2 = nx * nx + ny * ny + nz * nz;
+    if (!(l2 > 1e-30f) || !(l2 < 1e30f)) return cone_none();    // zero, huge or NaN: never culled
+    const float r = rsqrtf(l2);
+    return Cone{nx * r, ny * r, nz * r, 1.0f};
+}
+
+// Smallest cone that contains both cones: the wider one if it already contains the other, else half-angle
+// (theta + da + db) / 2 around the axis of a turned towards the axis of b by (half-angle - da); inflated by 5e-4 rad
+// per merge for the rounding of the construction; "none" beyond a half-angle of 1.5 rad (nothing can be culled by a
+// cone that wide).
+__device__ __forceinline__ Cone cone_merge(const Cone& a, const Cone& b)
+{
+    if (a.c < -1.5f || b.c < -1.5f) return cone_none();
+    // angle between the axes from the cross product (acos of a dot near 1 loses half the bits)
+    const float cx = a.y * b.z - a.z * b.y, cy = a.z * b.x - a.x * b.z, cz = a.x * b.y - a.y * b.x;
+    const float sin_t = sqrtf(cx * cx + cy * cy + cz * cz), cos_t = a.x * b.x + a.y * b.y + a.z * b.z;
+    const float theta = atan2f(sin_t, cos_t);
+    const float da = acosf(fminf(a.c, 1.0f)), db = acosf(fminf(b.c, 1.0f));
+    if (theta + db <= da) return Cone{a.x, a.y, a.z, cosf(fminf(da + 5e-4f, 3.0f))};
+    if (theta + da <= db) return Cone{b.x, b.y, b.z, cosf(fminf(db + 5e-4f, 3.0f))};
+    if (!(sin_t > 1e-6f)) {                                     // parallel axes (antiparallel ones give theta = pi below)
+        if (cos_t < 0.0f) return cone_none();
+        return Cone{a.x, a.y, a.z, cosf(fminf(fmaxf(da, db) + theta + 5e-4f, 3.0f))};
+    }
+    const float delta = 0.5f * (theta + da + db) + 5e-4f;
+    if (!(delta < 1.5f)) return cone_none();
+    // spherical interpolation from a towards b by phi = delta - da (0 <= phi <= theta)
+    const float phi = fminf(fmaxf(delta - da, 0.0f), theta);
+    const float wa = sinf(theta - phi) / sin_t, wb = sinf(phi) / sin_t;
+    float mx = wa * a.x + wb * b.x, my = wa * a.y + wb * b.y, mz = wa * a.z + wb * b.z;
+    const float r = rsqrtf(mx * mx + my * my + mz * mz);
+    return Cone{mx * r, my * r, mz * r, cosf(delta)};
+}
+
+// Cone of the sorted primitive at position k, from its record (written by the thread that owns the leaf).
+__device__ __forceinline__ Cone leaf_cone(const float4* __restrict__ recs, size_t k)
+{
+    const float4 r0 = __ldcg(recs + 4 * k), r1 = __ldcg(recs + 4 * k + 1), r2 = __ldcg(recs + 4 * k + 2), r3 = __ldcg(recs + 4 * k + 3);
+    if (__float_as_uint(r3.y) & CRT_KIND_SPHERE) return cone_none();
+    return cone_of_normal(r0.w, r1.w, r2.w);
+}
+
+__device__ __forceinline__ Cone load_cone(const float4* __restrict__ base, size_t idx)
+{
+    const float4 v = __ldcg(base + idx);
+    return Cone{v.x, v.y, v.z, v.w};
+}
+
+// The cone as the vector the traversal tests, three halves: A = axis / (sin(half-angle) + 0.01). For a unit direction d,
+// dot(d, A) < -1 puts d within 90 deg - half-angle - 0.5 deg of -axis, so dot(d, n) < -0.008 for every unit normal n in
+// the cone: far below the few 1e-7 by which the reference's float evaluation of dot(direction, normal) can differ
+// from the true value, and the 0.01 also covers the rounding of A to halves (direction 7e-4 rad, length 5e-4
+// relative) and of the traversal's three FMAs. All zero = never culled.
+__device__ __forceinline__ void cone_to_halves(const Cone& c, uint32_t& hx, uint32_t& hy, uint32_t& hz)
+{
+    hx = hy = hz = 0u;
+    if (c.c < -1.5f || !(c.c > 0.0707f)) return;                // none, or wider than 1.5 rad
+    const float s = sqrtf(fmaxf(0.0f, 1.0f - c.c * c.c));
+    const float L = 1.0f / (s + 0.01f);
+    hx = (uint32_t)__half_as_ushort(__float2half_rn(c.x * L));
+    hy = (uint32_t)__half_as_ushort(__float2half_rn(c.y * L));
+    hz = (uint32_t)__half_as_ushort(__float2half_rn(c.z * L));
+}
+
 __global__ void __launch_bounds__(256)
 k_fit(const float* __restrict__ tri_in, const uint32_t* __restrict__ tri_mat, const uint32_t* __restrict__ tri_id,
       const float* __restrict__ sph_in, const uint32_t* __restrict__ sph_mat, const uint32_t* __restrict__ sph_id,
       uint32_t n_tri, uint32_t n, const uint32_t* __restrict__ perm, const int2* __restrict__ child,
       const int* __restrict__ parent, const int* __restrict__ leaf_parent, int* __restrict__ flags,
-      float4* __restrict__ recs, float4* __restrict__ leaf_box, float4* __restrict__ node_box)
+      float4* __restrict__ recs, float4* __restrict__ leaf_box, float4* __restrict__ node_box,
+      float4* __restrict__ node_cone)
 {
     const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= n) return;
@@ -245,6 +323,10 @@ k_fit(const float* __restrict__ tri_in, const uint32_t* __restrict__ tri_mat, co
         const Box a = ch.x < 0 ? load_box(leaf_box, (size_t)(~ch.x)) : load_box(node_box, (size_t)ch.x);
         const Box b = ch.y < 0 ? load_box(leaf_box, (size_t)(~ch.y)) : load_box(node_box, (size_t)ch.y);
         store_box(node_box, (size_t)node, box_union(a, b));
+        const Cone ca = ch.x < 0 ? leaf_cone(recs, (size_t)(~ch.x)) : load_cone(node_cone, (size_t)ch.x);
+        const Cone cb = ch.y < 0 ? leaf_cone(recs, (size_t)(~ch.y)) : load_cone(node_cone, (size_t)ch.y);
+        const Cone cm = cone_merge(ca, cb);
+        node_cone[node] = make_float4(cm.x, cm.y, cm.z, cm.c);
         __threadfence();
         node = parent[node];
     }
@@ -291,7 +373,8 @@ __device__ __forceinline__ bool resolve_child(int c, int leaf_max, const int2* _
 
 __global__ void __launch_bounds__(256)
 k_emit_nodes(int n, int leaf_max, const int2* __restrict__ child, const int2* __restrict__ range,
-             const float4* __restrict__ leaf_box, const float4* __restrict__ node_box, float4* __restrict__ nodes)
+             const float4* __restrict__ leaf_box, const float4* __restrict__ node_box,
+             const float4* __restrict__ node_cone, float4* __restrict__ nodes)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n - 1) return;
@@ -335,6 +418,10 @@ k_emit_nodes(int n, int leaf_max, const int2* __restrict__ child, const int2* __
         w[5 * s + 4] = ez;
         w[20 + s] = (uint32_t)slot[s].ref;
     }
+    // the normal cone of this node's own subtree rides in the spare halves of children 0-2 (layout: crt_device.cuh)
+    uint32_t ax, ay, az;
+    cone_to_halves(load_cone(node_cone, (size_t)i), ax, ay, az);
+    w[4] |= ax << 16; w[9] |= ay << 16; w[14] |= az << 16;
     uint4* nw = reinterpret_cast<uint4*>(np);
     for (int q = 0; q < 6; q++) nw[q] = make_uint4(w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
 }
@@ -681,6 +768,7 @@ int lbvh_build(crt_ctx* c, bool refit_only, cudaStream_t async)
         CRT_CUDA(c->range.reserve(ni * 8));
         CRT_CUDA(c->parent.reserve(ni * 4));
         CRT_CUDA(c->node_box.reserve(ni * 32));
+        CRT_CUDA(c->node_cone.reserve(ni * 16));
         CRT_CUDA(c->flags.reserve(ni * 4));
 
         k_init_bounds<<<1, 32, 0, st>>>(c->bounds.as<float>());
@@ -707,12 +795,12 @@ int lbvh_build(crt_ctx* c, bool refit_only, cudaStream_t async)
                                             c->vals[c->perm_buf].as<uint32_t>(), c->child.as<int2>(),
                                             c->parent.as<int>(), c->leaf_parent.as<int>(), c->flags.as<int>(),
                                             c->recs.as<float4>(), c->leaf_box.as<float4>(),
-                                            c->node_box.as<float4>());
+                                            c->node_box.as<float4>(), c->node_cone.as<float4>());
     const int leaf_max = c->leaf_max;
     if (n > 1)
         k_emit_nodes<<<grid_for(n - 1, 256), 256, 0, st>>>((int)n, leaf_max, c->child.as<int2>(), c->range.as<int2>(),
                                                            c->leaf_box.as<float4>(), c->node_box.as<float4>(),
-                                                           c->nodes.as<float4>());
+                                                           c->node_cone.as<float4>(), c->nodes.as<float4>());
     c->root = (n <= (size_t)leaf_max) ? ~(int)(n - 1) : 0;
     CRT_CUDA(cudaEventRecord(ev_end, st));
     if (async) { CRT_CUDA(cudaGetLastError()); return CRT_OK; }
