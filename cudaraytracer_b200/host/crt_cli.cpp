@@ -118,7 +118,7 @@ int main(int argc, char** argv)
         const bool moving = o.animate && o.scene == "mesh";
         int pose_kind = CRT_POSE_VERTICES;
         const size_t n_bones = 8;
-        std::vector<vec3> nowTransform(n_bones);
+        std::vector<vec3> nowTransform(n_bones, vec3(0.f, 0.f, 0.f));   // vec3() leaves its members unset, like the reference's (core/vec3.h:9)
         if (o.pose == "points") pose_kind = CRT_POSE_POINTS;
         else if (o.pose == "bones") pose_kind = CRT_POSE_PARTS;
         else if (o.pose != "vertices") die("unknown --pose " + o.pose);
