@@ -284,6 +284,8 @@ __device__ __forceinline__ void cone_to_halves(const Cone& c, uint32_t& hx, uint
     hz = (uint32_t)__half_as_ushort(__float2half_rn(c.z * L));
 }
 
+// CONES: also merge the normal cones (a build; a refit leaves them alone: no pose update changes a stored normal)
+template <bool CONES>
 __global__ void __launch_bounds__(256)
 k_fit(const float* __restrict__ tri_in, const uint32_t* __restrict__ tri_mat, const uint32_t* __restrict__ tri_id,
       const float* __restrict__ sph_in, const uint32_t* __restrict__ sph_mat, const uint32_t* __restrict__ sph_id,
@@ -323,10 +325,12 @@ k_fit(const float* __restrict__ tri_in, const uint32_t* __restrict__ tri_mat, co
         const Box a = ch.x < 0 ? load_box(leaf_box, (size_t)(~ch.x)) : load_box(node_box, (size_t)ch.x);
         const Box b = ch.y < 0 ? load_box(leaf_box, (size_t)(~ch.y)) : load_box(node_box, (size_t)ch.y);
         store_box(node_box, (size_t)node, box_union(a, b));
-        const Cone ca = ch.x < 0 ? leaf_cone(recs, (size_t)(~ch.x)) : load_cone(node_cone, (size_t)ch.x);
-        const Cone cb = ch.y < 0 ? leaf_cone(recs, (size_t)(~ch.y)) : load_cone(node_cone, (size_t)ch.y);
-        const Cone cm = cone_merge(ca, cb);
-        node_cone[node] = make_float4(cm.x, cm.y, cm.z, cm.c);
+        if (CONES) {
+            const Cone ca = ch.x < 0 ? leaf_cone(recs, (size_t)(~ch.x)) : load_cone(node_cone, (size_t)ch.x);
+            const Cone cb = ch.y < 0 ? leaf_cone(recs, (size_t)(~ch.y)) : load_cone(node_cone, (size_t)ch.y);
+            const Cone cm = cone_merge(ca, cb);
+            node_cone[node] = make_float4(cm.x, cm.y, cm.z, cm.c);
+        }
         __threadfence();
         node = parent[node];
     }
@@ -790,7 +794,15 @@ int lbvh_build(crt_ctx* c, bool refit_only, cudaStream_t async)
         }
     }
     if (n > 1) CRT_CUDA(cudaMemsetAsync(c->flags.p, 0, (n - 1) * 4, st));
-    k_fit<<<grid_for(n, 256), 256, 0, st>>>(tri_in, c->tri_mat.as<uint32_t>(), c->tri_id.as<uint32_t>(), sph_in,
+    if (refit_only)
+        k_fit<false><<<grid_for(n, 256), 256, 0, st>>>(tri_in, c->tri_mat.as<uint32_t>(), c->tri_id.as<uint32_t>(), sph_in,
+                                            c->sph_mat.as<uint32_t>(), c->sph_id.as<uint32_t>(), n_tri, un,
+                                            c->vals[c->perm_buf].as<uint32_t>(), c->child.as<int2>(),
+                                            c->parent.as<int>(), c->leaf_parent.as<int>(), c->flags.as<int>(),
+                                            c->recs.as<float4>(), c->leaf_box.as<float4>(),
+                                            c->node_box.as<float4>(), c->node_cone.as<float4>());
+    else
+        k_fit<true><<<grid_for(n, 256), 256, 0, st>>>(tri_in, c->tri_mat.as<uint32_t>(), c->tri_id.as<uint32_t>(), sph_in,
                                             c->sph_mat.as<uint32_t>(), c->sph_id.as<uint32_t>(), n_tri, un,
                                             c->vals[c->perm_buf].as<uint32_t>(), c->child.as<int2>(),
                                             c->parent.as<int>(), c->leaf_parent.as<int>(), c->flags.as<int>(),
