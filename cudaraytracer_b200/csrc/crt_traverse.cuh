@@ -433,6 +433,13 @@ __device__ __forceinline__ void traverse_packets(const AccelView& A, const uint3
 {
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t kid = lane & 3u;
+#ifndef CRT_PACKET_STACK_T
+#define CRT_PACKET_STACK_T 1
+#endif
+#if CRT_PACKET_STACK_T
+    float wstack_t[CRT_PACKET_STACK];   // entry distance of each stacked child (interval test only): an entry beyond the
+                                        // packet's farthest closest hit is dropped when popped, without fetching its node
+#endif
     int wstack[CRT_PACKET_STACK];   // every lane keeps the same (warp-uniform) stack; slot X of 32 lanes is one 128-byte line of local memory
     constexpr uint32_t FULL = 0xffffffffu;
     // packets per grab
@@ -509,8 +516,16 @@ __device__ __forceinline__ void traverse_packets(const AccelView& A, const uint3
                             if ((m4 & (m4 - 1u)) == 0u) {
                                 // none or one child entered (the common case): no ordering needed
                                 if (m4 == 0u) {
-                                    if (sp == 0u) break;
-                                    node = wstack[--sp];
+                                    bool got = false;
+                                    while (sp > 0u) {
+                                        node = wstack[--sp];
+#if CRT_PACKET_STACK_T
+                                        if (wstack_t[sp] > t_far) continue;
+#endif
+                                        got = true;
+                                        break;
+                                    }
+                                    if (!got) break;
                                 } else {
                                     const int e_lo = (m4 & 1u) ? refs.x : refs.y, e_hi = (m4 & 4u) ? refs.z : refs.w;
                                     node = (m4 & 3u) ? e_lo : e_hi;
@@ -554,9 +569,16 @@ __device__ __forceinline__ void traverse_packets(const AccelView& A, const uint3
                         }
                         CRT_CSWAP(0, 1) CRT_CSWAP(2, 3) CRT_CSWAP(0, 2) CRT_CSWAP(1, 3) CRT_CSWAP(1, 2)
 #undef CRT_CSWAP
+#if CRT_PACKET_STACK_T
+                        // the per-lane test orders children by the first entering lane: not a bound for the packet
+                        if (n_hit > 3) { wstack_t[sp] = uni ? key[3] : 0.0f; wstack[sp++] = ref[3]; }
+                        if (n_hit > 2) { wstack_t[sp] = uni ? key[2] : 0.0f; wstack[sp++] = ref[2]; }
+                        if (n_hit > 1) { wstack_t[sp] = uni ? key[1] : 0.0f; wstack[sp++] = ref[1]; }
+#else
                         if (n_hit > 3) wstack[sp++] = ref[3];
                         if (n_hit > 2) wstack[sp++] = ref[2];
                         if (n_hit > 1) wstack[sp++] = ref[1];
+#endif
                         if (n_hit > 0) { node = ref[0]; continue; }
                     } else {
                         const uint32_t ref = ~(uint32_t)node;
@@ -586,8 +608,16 @@ __device__ __forceinline__ void traverse_packets(const AccelView& A, const uint3
                         // distances are positive, so their bit patterns order like the values
                         if (uni) t_far = __uint_as_float(__reduce_max_sync(FULL, live ? __float_as_uint(best.t) : 0u));
                     }
-                    if (sp == 0u) break;
-                    node = wstack[--sp];
+                    bool got = false;
+                    while (sp > 0u) {
+                        node = wstack[--sp];
+#if CRT_PACKET_STACK_T
+                        if (wstack_t[sp] > t_far) continue;
+#endif
+                        got = true;
+                        break;
+                    }
+                    if (!got) break;
                 }
             }
             if (live) sink.store(ray_i, best);
