@@ -106,7 +106,7 @@ struct crt_ctx {
     crt::DevBuf counters;                  // CNT_COUNT x uint64
     int count_work = 0;
     int leaf_thresh = 8;                   // parked lanes that trigger the primitive-test phase
-    int refill = 8;                        // idle lanes that trigger a refill in the persistent traversal
+    int refill = 12;                       // idle lanes that trigger a refill in the persistent traversal
     int packet_primary = 1;                // camera rays through the packet kernel
     int64_t wide_below = 32768;            // CRT_OPT_WIDE_BELOW: bounces with fewer rays run one warp per ray
     int64_t batch_paths = 1ll << 25;

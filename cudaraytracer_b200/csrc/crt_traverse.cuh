@@ -71,7 +71,7 @@ constexpr int TP_BLOCK = 128;    // threads per block of every traversal kernel
 #define CRT_PACKET_MIN_BLOCKS 8  // 10 and 12 resident blocks (51 and 40 registers) measured slower
 #endif
 constexpr int TP_CHUNK = 256;    // most rays a warp takes from the queue per atomic
-constexpr int TP_REFILL = 8;     // default: refill once this many lanes are idle
+constexpr int TP_REFILL = 12;    // default: refill once this many lanes are idle (sweeps at v9 and v11: 12 <= 8 < 4, 16)
 
 // nodes/tris/spheres: tests executed per ray (work, flops). *_f: records FETCHED - equal to the tests in the
 // per-ray kernels, one per packet visit in the packet kernel (a packet of <= 32 rays shares each fetch).

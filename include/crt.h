@@ -116,7 +116,7 @@ typedef enum {
                              * working through the ray's stack 32 entries abreast, because so small a launch is bound by
                              * its longest ray; 0: always one ray per lane. Hits and images do not depend on it */
     CRT_OPT_BUILDER = 8,    /* tree topology of crt_accel_build: CRT_BUILDER_LBVH (default) or CRT_BUILDER_PLOC; hits and images do not depend on it */
-    CRT_OPT_REFILL = 4      /* tuning: idle lanes per warp that trigger a refill from the ray queue, 1..32 (default 8) */
+    CRT_OPT_REFILL = 4      /* tuning: idle lanes per warp that trigger a refill from the ray queue, 1..32 (default 12) */
 } crt_option;
 
 typedef enum {
