@@ -205,3 +205,22 @@ def test_bench_reference_arm_contract(tmp_path):
     assert line["impl"] == "reference" and line["metric"] == "Mrays/s" and line["value"] > 0
     assert line["cpu_baseline"]["kind"] in ("reference", "port") and line["cpu_baseline"]["cores"] >= 1
     assert line["e2e"]["h2d_bytes_per_step"] == 0
+
+
+def test_bench_reference_arm_other_workloads_say_unavailable():
+    """The reference arm is measured on C3 only: for --workload c4 it prints the `unavailable` line and exits 0."""
+    import json
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--workload", "c4"],
+                         capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stderr[-2000:]
+    line = json.loads(out.stdout.strip().splitlines()[-1])
+    assert line["impl"] == "reference" and "unavailable" in line
+
+
+def test_bench_without_a_gpu_fails_loudly():
+    """bench.py's own arm has no CPU path: without a CUDA device it exits non-zero with a message."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--steps", "1"], capture_output=True, text=True, timeout=300)
+    assert out.returncode != 0 and "CUDA" in (out.stdout + out.stderr)
