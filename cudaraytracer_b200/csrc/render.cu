@@ -50,6 +50,7 @@ struct RenderParams {
     int max_depth;
     int mode;
     uint64_t seed;
+    uint32_t seed_key;    // crt_rng_seed_key(seed): the seed's share of every stream key, mixed once on the host
     uint32_t cap;         // queue capacity (entries per SoA word)
 };
 
@@ -162,7 +163,7 @@ k_raygen(RenderParams P, float4* __restrict__ q, uint32_t* __restrict__ q_count)
             if (live) {
                 const uint32_t pixel = (uint32_t)y * (uint32_t)P.nx + (uint32_t)x;
                 Rng rng;
-                rng.key = crt_rng_key(P.seed, pixel, (uint32_t)(P.s_begin + (int)s_local));
+                rng.key = crt_rng_key_from(P.seed_key, pixel, (uint32_t)(P.s_begin + (int)s_local));
                 rng.ctr = 0;
                 const float u = x::div(x::add((float)x, rnd(rng)), (float)P.nx);   // render.h:116
                 const float v = x::div(x::add((float)y, rnd(rng)), (float)P.ny);   // render.h:117
@@ -350,7 +351,7 @@ k_shade(RenderParams P, AccelView A, const DMat* __restrict__ mats, const float4
                     split_path_id(P, path_id, slot, s_local);
                     int px, py;
                     slot_to_pixel(P, slot, px, py);
-                    rng.key = crt_rng_key(P.seed, (uint32_t)py * (uint32_t)P.nx + (uint32_t)px, (uint32_t)(P.s_begin + (int)s_local));
+                    rng.key = crt_rng_key_from(P.seed_key, (uint32_t)py * (uint32_t)P.nx + (uint32_t)px, (uint32_t)(P.s_begin + (int)s_local));
                     rng.ctr = pack & 0xFFFFFFu;
                 }
                 const v3 dl = ray_dir_local(d);
@@ -567,7 +568,7 @@ int render_accum(crt_ctx* c, const crt_camera* cam, int nx, int ny, int s0, int 
     const long long local_tiles = units > rank ? (units - rank + world - 1) / world * unit_tiles : 0;
     P.rank = rank; P.world = world;
     if (local_tiles * CRT_TILE * CRT_TILE >= (1ll << 31)) { set_error("crt_render: image too large"); return CRT_ERR_INVALID; }
-    P.max_depth = max_depth; P.mode = mode; P.seed = seed;
+    P.max_depth = max_depth; P.mode = mode; P.seed = seed; P.seed_key = crt_rng_seed_key(seed);
 
     CRT_CUDA(cudaEventRecord(c->ev0, st));
     CRT_CUDA(cudaMemsetAsync(d_accum, 0, (size_t)nx * ny * 3 * sizeof(float), st));

@@ -37,14 +37,24 @@ CRT_HD uint32_t crt_mix32(uint32_t x)
     return x;
 }
 
+/* The seed's share of a stream key: the same for every sample of a frame, so a renderer computes it once. */
+CRT_HD uint32_t crt_rng_seed_key(uint64_t seed)
+{
+    uint32_t k = crt_mix32((uint32_t)seed ^ 0x9e3779b9U);
+    return crt_mix32(k + (uint32_t)(seed >> 32));
+}
+
+/* Stream key of one camera sample from the seed's share. */
+CRT_HD uint32_t crt_rng_key_from(uint32_t seed_key, uint32_t pixel, uint32_t sample)
+{
+    uint32_t k = crt_mix32(seed_key ^ crt_mix32(sample + 0x85ebca6bU));
+    return crt_mix32(k + pixel);
+}
+
 /* Stream key of one camera sample. */
 CRT_HD uint32_t crt_rng_key(uint64_t seed, uint32_t pixel, uint32_t sample)
 {
-    uint32_t k = crt_mix32((uint32_t)seed ^ 0x9e3779b9U);
-    k = crt_mix32(k + (uint32_t)(seed >> 32));
-    k = crt_mix32(k ^ crt_mix32(sample + 0x85ebca6bU));
-    k = crt_mix32(k + pixel);
-    return k;
+    return crt_rng_key_from(crt_rng_seed_key(seed), pixel, sample);
 }
 
 /* Raw 32-bit draw number `ctr` of stream `key`. */
