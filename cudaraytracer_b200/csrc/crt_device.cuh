@@ -105,7 +105,7 @@ CRT_HD bool sphere_test(v3 oc, v3 d, float radius, float t_min, float t_best, fl
 }
 
 // ---- camera ----------------------------------------------------------------
-struct Rng { uint32_t key, ctr; };
+struct Rng { uint64_t key; uint32_t ctr; };
 CRT_HD float rnd(Rng& r) { return crt_rng_uniform(r.key, r.ctr++); }
 
 // core/camera.h:6-13. C++ leaves the evaluation order of the two constructor

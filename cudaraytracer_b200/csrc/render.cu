@@ -50,7 +50,7 @@ struct RenderParams {
     int max_depth;
     int mode;
     uint64_t seed;
-    uint32_t seed_key;    // crt_rng_seed_key(seed): the seed's share of every stream key, mixed once on the host
+    uint64_t seed_key;    // crt_rng_seed_key(seed): the seed's share of every stream key, mixed once on the host
     uint32_t cap;         // queue capacity (entries per SoA word)
 };
 

@@ -22,7 +22,7 @@ struct SceneOptions {
 // Sequential (0,1] draws from the hash of include/crt_rng.h, the same stream
 // cudaraytracer_b200/scenes.py uses for its synthetic scenes.
 struct Stream {
-    uint32_t key, ctr = 0;
+    uint64_t key; uint32_t ctr = 0;
     Stream(uint64_t seed, uint32_t stream) : key(crt_rng_key(seed, stream, 0xC0FFEEu)) {}
     double draw() { return (double)crt_rng_uniform(key, ctr++); }
 };

@@ -41,18 +41,20 @@ def rng_key(seed, pixel, sample):
     """include/crt_rng.h crt_rng_key."""
     seed = int(seed) & 0xFFFFFFFFFFFFFFFF
     with np.errstate(over="ignore"):
-        k = mix32(np.uint32((seed & 0xFFFFFFFF) ^ 0x9E3779B9))
-        k = mix32(k + np.uint32(seed >> 32))
-        k = mix32(k ^ mix32(np.asarray(sample, np.uint32) + np.uint32(0x85EBCA6B)))
-        k = mix32(k + np.asarray(pixel, np.uint32))
-    return k
+        a = mix32(np.uint32((seed & 0xFFFFFFFF) ^ 0x9E3779B9))
+        b = mix32(np.uint32(seed >> 32) + a)
+        k0 = mix32(np.asarray(pixel, np.uint32) ^ a)
+        k1 = mix32(np.asarray(sample, np.uint32) ^ b) + k0
+    return (k1.astype(np.uint64) << np.uint64(32)) | k0.astype(np.uint64)
 
 
 def rng_uniform(key, ctr):
     """include/crt_rng.h crt_rng_uniform: float32 in (0, 1]."""
     with np.errstate(over="ignore"):
         c = np.asarray(ctr, np.uint32) * np.uint32(0x9E3779B1) + np.uint32(0x7F4A7C15)
-        bits = mix32(np.asarray(key, np.uint32) ^ mix32(c))
+        key = np.asarray(key, np.uint64)
+        k0, k1 = (key & np.uint64(0xFFFFFFFF)).astype(np.uint32), (key >> np.uint64(32)).astype(np.uint32)
+        bits = mix32(k0 ^ mix32(k1 ^ c))
     return ((bits >> np.uint32(8)) + np.uint32(1)).astype(np.float32) * np.float32(1.0 / 16777216.0)
 
 

@@ -37,34 +37,44 @@ CRT_HD uint32_t crt_mix32(uint32_t x)
     return x;
 }
 
+/* Stream keys are 64 bits wide, held as one uint64 = (k1 << 32) | k0, and the map
+ * (seed, pixel, sample) -> key is INJECTIVE for a fixed seed: k0 = mix(pixel ^ a) and
+ * k1 - k0 = mix(sample ^ b) are bijections of the pixel and of the sample number, so no two camera samples of a
+ * frame share a stream, whatever the frame size (a 32-bit key made whole sample planes of a 4K x 64 spp frame
+ * shifted copies of each other). (a, b) is a bijection of the 64-bit seed, so two seeds never give the same
+ * frame either.
+ */
+
 /* The seed's share of a stream key: the same for every sample of a frame, so a renderer computes it once. */
-CRT_HD uint32_t crt_rng_seed_key(uint64_t seed)
+CRT_HD uint64_t crt_rng_seed_key(uint64_t seed)
 {
-    uint32_t k = crt_mix32((uint32_t)seed ^ 0x9e3779b9U);
-    return crt_mix32(k + (uint32_t)(seed >> 32));
+    const uint32_t a = crt_mix32((uint32_t)seed ^ 0x9e3779b9U);
+    const uint32_t b = crt_mix32((uint32_t)(seed >> 32) + a);
+    return ((uint64_t)b << 32) | a;
 }
 
 /* Stream key of one camera sample from the seed's share. */
-CRT_HD uint32_t crt_rng_key_from(uint32_t seed_key, uint32_t pixel, uint32_t sample)
+CRT_HD uint64_t crt_rng_key_from(uint64_t seed_key, uint32_t pixel, uint32_t sample)
 {
-    uint32_t k = crt_mix32(seed_key ^ crt_mix32(sample + 0x85ebca6bU));
-    return crt_mix32(k + pixel);
+    const uint32_t k0 = crt_mix32(pixel ^ (uint32_t)seed_key);
+    const uint32_t k1 = crt_mix32(sample ^ (uint32_t)(seed_key >> 32)) + k0;
+    return ((uint64_t)k1 << 32) | k0;
 }
 
 /* Stream key of one camera sample. */
-CRT_HD uint32_t crt_rng_key(uint64_t seed, uint32_t pixel, uint32_t sample)
+CRT_HD uint64_t crt_rng_key(uint64_t seed, uint32_t pixel, uint32_t sample)
 {
     return crt_rng_key_from(crt_rng_seed_key(seed), pixel, sample);
 }
 
-/* Raw 32-bit draw number `ctr` of stream `key`. */
-CRT_HD uint32_t crt_rng_bits(uint32_t key, uint32_t ctr)
+/* Raw 32-bit draw number `ctr` of stream `key`: both key words enter, one per mixing round. */
+CRT_HD uint32_t crt_rng_bits(uint64_t key, uint32_t ctr)
 {
-    return crt_mix32(key ^ crt_mix32(ctr * 0x9e3779b1U + 0x7f4a7c15U));
+    return crt_mix32((uint32_t)key ^ crt_mix32((uint32_t)(key >> 32) ^ (ctr * 0x9e3779b1U + 0x7f4a7c15U)));
 }
 
 /* Uniform float in (0, 1]: 24 random bits, never 0, may be exactly 1. */
-CRT_HD float crt_rng_uniform(uint32_t key, uint32_t ctr)
+CRT_HD float crt_rng_uniform(uint64_t key, uint32_t ctr)
 {
     return (float)((crt_rng_bits(key, ctr) >> 8) + 1U) * (1.0f / 16777216.0f);
 }

@@ -101,7 +101,7 @@ struct oracle_scene {
     xform_t world_xf;
 };
 
-typedef struct { uint32_t key, ctr; const float* inject; int inject_n, inject_pos; } rng_t;
+typedef struct { uint64_t key; uint32_t ctr; const float* inject; int inject_n, inject_pos; } rng_t;
 
 static inline float rnd(rng_t* s)
 {

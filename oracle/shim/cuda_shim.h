@@ -29,7 +29,7 @@ using std::max;
 #include "crt_rng.h"
 
 struct curandState {
-    uint32_t key = 0;
+    uint64_t key = 0;
     uint32_t ctr = 0;
     const float* inject = nullptr;  // when set, values are served from here
     int inject_n = 0;

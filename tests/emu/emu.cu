@@ -12,7 +12,7 @@ extern "C" {
 
 // same contract as oracle_scatter / ref_scatter but with the counter stream
 int emu_scatter(uint32_t type, const float* albedo, float param, const float* ray, const float* recpn,
-                uint32_t key, uint32_t ctr, float* out, uint32_t* ctr_out)
+                uint64_t key, uint32_t ctr, float* out, uint32_t* ctr_out)
 {
     DMat m;
     m.r = albedo[0]; m.g = albedo[1]; m.b = albedo[2]; m.param = param; m.type = type;
@@ -87,7 +87,7 @@ void emu_sky(const float* d, float* out)
     out[0] = s.x; out[1] = s.y; out[2] = s.z;
 }
 
-float emu_uniform(uint32_t key, uint32_t ctr) { return crt_rng_uniform(key, ctr); }
-uint32_t emu_key(uint64_t seed, uint32_t pixel, uint32_t sample) { return crt_rng_key(seed, pixel, sample); }
+float emu_uniform(uint64_t key, uint32_t ctr) { return crt_rng_uniform(key, ctr); }
+uint64_t emu_key(uint64_t seed, uint32_t pixel, uint32_t sample) { return crt_rng_key(seed, pixel, sample); }
 
 }  // extern "C"

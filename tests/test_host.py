@@ -56,8 +56,8 @@ def test_product_never_touches_the_oracle():
 def test_rng_numpy_matches_c():
     emu = C.CDLL(EMU)
     emu.emu_uniform.restype = C.c_float
-    emu.emu_uniform.argtypes = [C.c_uint32, C.c_uint32]
-    emu.emu_key.restype = C.c_uint32
+    emu.emu_uniform.argtypes = [C.c_uint64, C.c_uint32]
+    emu.emu_key.restype = C.c_uint64
     emu.emu_key.argtypes = [C.c_uint64, C.c_uint32, C.c_uint32]
     rng = np.random.default_rng(0)
     for _ in range(500):
@@ -65,17 +65,48 @@ def test_rng_numpy_matches_c():
         k = emu.emu_key(seed, px, s)
         assert k == int(scenes.rng_key(seed, np.uint32(px), np.uint32(s)))
         u = emu.emu_uniform(k, ctr)
-        assert u == float(scenes.rng_uniform(np.uint32(k), np.uint32(ctr)))
+        assert u == float(scenes.rng_uniform(np.uint64(k), np.uint32(ctr)))
         assert 0.0 < u <= 1.0
-    u = scenes.rng_uniform(np.uint32(12345), np.arange(1 << 16, dtype=np.uint32))
+    u = scenes.rng_uniform(np.uint64(12345 | (777 << 32)), np.arange(1 << 16, dtype=np.uint32))
     assert abs(float(u.mean()) - 0.5) < 0.01 and u.min() > 0 and u.max() <= 1.0
+
+
+def test_rng_keys_never_collide_within_a_frame():
+    """include/crt_rng.h: (pixel, sample) -> 64-bit stream key is injective for a fixed seed (a 32-bit key made
+    whole sample planes of a C4-sized frame shifted copies of each other). Structure: the low word is a bijection of
+    the pixel, the difference of the words a bijection of the sample; checked at C4's size (3840 x 2160 pixels, 64
+    spp) word by word and by brute force on a 2^16-pixel x 16-sample block."""
+    for seed in (1, 100, 2**63 + 12345):
+        pix = np.arange(3840 * 2160 if seed == 1 else 1 << 20, dtype=np.uint32)
+        k = scenes.rng_key(seed, pix, np.uint32(0))
+        k0 = (k & np.uint64(0xFFFFFFFF)).astype(np.uint32)
+        assert np.unique(k0).size == pix.size                       # distinct pixels -> distinct low words
+        smp = np.arange(4096, dtype=np.uint32)
+        with np.errstate(over="ignore"):
+            for p in (0, 12345, 3840 * 2160 - 1):
+                ks = scenes.rng_key(seed, np.uint32(p), smp)
+                diff = (ks >> np.uint64(32)).astype(np.uint32) - (ks & np.uint64(0xFFFFFFFF)).astype(np.uint32)
+                ref = scenes.rng_key(seed, np.uint32(0), smp)
+                diff0 = (ref >> np.uint64(32)).astype(np.uint32) - (ref & np.uint64(0xFFFFFFFF)).astype(np.uint32)
+                assert np.array_equal(diff, diff0)                  # high - low depends on the sample only
+                assert np.unique(diff).size == smp.size             # distinct samples -> distinct differences
+        px, sm = np.meshgrid(np.arange(1 << 16, dtype=np.uint32), np.arange(16, dtype=np.uint32), indexing="ij")
+        allk = scenes.rng_key(seed, px.ravel(), sm.ravel())
+        assert np.unique(allk).size == allk.size
+    # and two seeds never share the seed's part of the key
+    a = {int(scenes.rng_key(s, np.uint32(7), np.uint32(3))) for s in range(2000)}
+    assert len(a) == 2000
+    # first draws of neighbouring streams are uncorrelated
+    u0 = scenes.rng_uniform(scenes.rng_key(1, np.arange(1 << 16, dtype=np.uint32), np.uint32(0)), np.uint32(0)).astype(np.float64)
+    u1 = scenes.rng_uniform(scenes.rng_key(1, np.arange(1 << 16, dtype=np.uint32), np.uint32(1)), np.uint32(0)).astype(np.float64)
+    assert abs(np.corrcoef(u0, u1)[0, 1]) < 0.02 and abs(np.corrcoef(u0[:-1], u0[1:])[0, 1]) < 0.02
 
 
 def test_device_functions_on_host_match_oracle():
     """crt_device.cuh (the code the kernels inline) compiled for the host:
     scatter, camera rays and the primitive tests bit-exact against the oracle."""
     emu = C.CDLL(EMU)
-    emu.emu_scatter.argtypes = [C.c_uint32, f32p, C.c_float, f32p, f32p, C.c_uint32, C.c_uint32, f32p, C.POINTER(C.c_uint32)]
+    emu.emu_scatter.argtypes = [C.c_uint32, f32p, C.c_float, f32p, f32p, C.c_uint64, C.c_uint32, f32p, C.POINTER(C.c_uint32)]
     emu.emu_trace.argtypes = [f32p, u32p, C.c_uint32, f32p, u32p, C.c_uint32, f32p, C.c_size_t, C.c_float, C.c_float, f32p, u32p]
     emu.emu_get_ray.argtypes = [f32p, C.c_float, C.c_float, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, f32p]
     emu.emu_get_ray.restype = C.c_uint32
@@ -89,8 +120,8 @@ def test_device_functions_on_host_match_oracle():
         n = rng.normal(size=3)
         n = (n / np.linalg.norm(n)).astype(np.float32)
         p = (rng.normal(size=3) * 10).astype(np.float32)
-        key = int(rng.integers(0, 2**32))
-        rnds = scenes.rng_uniform(np.uint32(key), np.arange(96, dtype=np.uint32))
+        key = int(rng.integers(0, 2**63))
+        rnds = scenes.rng_uniform(np.uint64(key), np.arange(96, dtype=np.uint32))
         a = o.scatter(mt, alb, param, ray, p, n, rnds)
         out = np.zeros(9, np.float32)
         co = C.c_uint32(0)
