@@ -2,28 +2,30 @@
 """bench.py — headline benchmark of the render hot path (contract: see the task brief).
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
-    torchrun ... bench.py --gpus N ...      (one rank per GPU, NCCL)
+    torchrun ... bench.py --gpus N ...      (one rank per GPU; the exchange step is the library's own NCCL communicator)
 
 Workload (BASELINE.json configs[2], "C3"): synthetic 998,002-triangle mesh,
 1920x1080, 16 spp, depth 8, diffuse+metal, the reference's shade() path tracer.
 A step is one full frame: 33,177,600 camera samples carried to termination.
 
   value   Mrays/s with the scene, LBVH and framebuffers resident in HBM
-          (crt_render_accum_device + resolve), CUDA events, max over ranks.
-          N > 1 (--scaling weak, the default): every rank renders the frame's
-          full work, 16 samples of every pixel on its own sample range, and the
-          accumulators are summed with one NCCL reduce (16 N spp in the combined
-          frame). --scaling strong splits the 16-spp frame by 32x32 tiles instead.
+          (crt_render_accum_device + crt_reduce_accum_device + resolve), CUDA
+          events on the context's stream, max over ranks.
+          N > 1, --scaling strong (the default: BASELINE.json's "1920x1080 at 16 spp ... 1/2/4/8 B200"): the SAME
+          16-spp frame, its 32x32 tiles dealt to the ranks, one ncclReduce of the accumulators onto rank 0; the
+          reduced frame is compared bit for bit with rank 0's own one-GPU render of the same seed (`parity_n`).
+          --scaling weak: every rank renders 16 samples of every pixel on its own sample range (16 N spp combined).
   e2e     the reference's per-frame loop (core/render.h:207-234) through the C
           ABI with HOST buffers: pose upload (the mesh's point array, as the
           reference's updateFBXObj uploads it; --e2e-api frame uploads every
           triangle's vertices instead) -> LBVH refit -> render -> image download,
-          wall clock around the synchronous calls.
-  roofline  k_trace_queue (persistent-warp LBVH closest hit), algorithmic bytes of
-          SURVEY §8d from an instrumented run of the same frame / the kernel's
-          device time (CUDA events around each launch on the context's stream).
-  cpu_baseline  the reference's own hit/scatter code (oracle/_ref, unmodified
-          headers, OpenMP over rows) on a bounded sample of the same workload.
+          wall clock around the calls.
+  roofline  the closest-hit launches (k_trace_packet + k_trace_queue): bytes their own load/store instructions move
+          (96 B per node visit, 64 B per primitive record, 48 B per ray; fetch counts from an instrumented run of the
+          same frame) / the launches' device time (CUDA events around each launch, one slice in flight).
+  cpu_baseline  the reference's own hit/scatter code (oracle/_ref, unmodified headers, OpenMP) through its shipping
+          accelerator, BVHNode (hitable/bvh.h:76-190, what kernel.cu:24-39 renders through), built host-side (build
+          time reported separately), on a bounded sample of the same frame.
 """
 import argparse
 import json
@@ -43,6 +45,13 @@ WORKLOAD = "C3: 998,002-triangle displaced sphere + ground, 1920x1080, 16 spp, m
 # --workload c4: BASELINE.json configs[3], not the headline line (the driver never passes it)
 WORKLOAD_C4 = "C4: 10 x 10 instances of a 100,000-triangle displaced sphere + ground (10.0 M triangles, flattened), 3840x2160, 64 spp, max_depth 8, shade() path tracer"
 
+# Bytes the closest-hit kernels move per unit of work: what their own load/store instructions read and
+# write, not the stride of the records.
+BYTES_NODE = 96     # crt_traverse.cuh:load_node, three 256-bit loads of a 4-wide node (128 B stride)
+BYTES_REC = 64      # two 256-bit loads of a primitive record (triangle or sphere)
+BYTES_RAY = 48      # queue words 0-1 in (32 B) + hit record out (16 B)
+FLOPS_NODE, FLOPS_TRI, FLOPS_SPH = 96, 50, 27     # SURVEY §8d, 4 boxes per node
+
 
 def log(*a):
     print(*a, file=sys.stderr, flush=True)
@@ -54,6 +63,14 @@ def measured_peaks():
         with open(path) as f:
             return json.load(f), "measured (MEASURED_PEAKS.json)"
     return {"hbm_gbs": 6650.0}, "fallback (B200_PROFILING.md)"
+
+
+def alg_bytes(w):
+    return (BYTES_NODE * w["node_fetches"] + BYTES_REC * (w["tri_fetches"] + w["sphere_fetches"]) + BYTES_RAY * w["rays"])
+
+
+def alg_flops(w):
+    return FLOPS_NODE * w["nodes_visited"] + FLOPS_TRI * w["tris_tested"] + FLOPS_SPH * w["spheres_tested"]
 
 
 class ClockSampler:
@@ -150,46 +167,57 @@ def use_all_host_threads():
         pass
 
 
-def cpu_reference_setup(sc):
-    """The reference's CPU implementation of the path: oracle/_ref (unmodified
-    headers) when the prebuilt library is there, else the C restatement."""
+def cpu_reference_setup(sc, want_bvh=True):
+    """The reference's CPU implementation of the path: oracle/_ref (unmodified headers) when the prebuilt library is
+    there, else the C restatement. With oracle/_ref the reference's own accelerator (BVHNode, hitable/bvh.h:76-125,
+    one thread as create_BVH<<<1,1>>> is) is built; `accel` says what ref_render then walks."""
     import oracle
     kind = "ref" if oracle.available("ref") else "port"
     if not oracle.available(kind):
         oracle.build(ref=False, port=True)
     lib = oracle.load(kind)
     use_all_host_threads()
-    return lib, build_ref_scene(lib, sc), ("reference" if kind == "ref" else "port")
+    sh = build_ref_scene(lib, sc)
+    info = {"kind": "reference" if kind == "ref" else "port", "accel": "HitableList scan", "bvh_build_s": None}
+    max_build = float(os.environ.get("CRT_BENCH_REF_BVH", "1"))
+    if kind == "ref" and want_bvh and max_build > 0:
+        info["bvh_build_s"] = sh.bvh_build(1)
+        info["accel"] = "BVHNode (hitable/bvh.h:76-190, median split on a random axis, both children always visited)"
+    else:
+        info["accel_reason"] = ("the C restatement has no BVHNode" if kind != "ref" else "BVHNode switched off (CRT_BENCH_REF_BVH=0)")
+    return lib, sh, info
 
 
-def cpu_sample_shape(scene_h, cam_fn, sc, budget_s):
+def cpu_sample_shape(scene_h, cam_fn, sc, budget_s, max_nx=None):
     """Pick a reduced frame (same scene, same camera, same aspect, 1 spp) whose
-    list-scan render takes about budget_s on this host."""
+    render through the current accelerator takes about budget_s on this host."""
     import cudaraytracer_b200 as crt
     nx0, ny0 = 16, 9
     scene_h.render(cam_fn(nx0, ny0), nx0, ny0, 1, sc["max_depth"], crt.SHADE_PATH, 1)
-    per_px = max(scene_h.last_seconds / (nx0 * ny0), 1e-6)
+    per_px = max(scene_h.last_seconds / (nx0 * ny0), 1e-7)
     k = max(1.0, (budget_s / per_px / (nx0 * ny0)) ** 0.5)
-    k = min(k, sc["nx"] / nx0)
+    k = min(k, (max_nx or sc["nx"]) / nx0)
     return max(nx0, int(nx0 * k)), max(ny0, int(ny0 * k))
 
 
 def run_reference(args):
-    """--impl reference: the reference's own CPU hit/scatter code on the host
-    cores; every step renders a bounded sample of the workload."""
+    """--impl reference: the reference's own CPU hit/scatter code on the host cores through its shipping
+    accelerator (BVHNode), every step a bounded sample of the workload."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     import cudaraytracer_b200 as crt
     from cudaraytracer_b200 import scenes
     if args.workload != "c3":
-        print(json.dumps({"impl": "reference", "unavailable": "the reference's list scan over 10 M triangles manages about one ray per second; the reference arm is measured on C3 only"}), flush=True)
+        print(json.dumps({"impl": "reference", "unavailable": "the reference's single-thread BVHNode build over 10 M triangles takes minutes and its list scan manages about one ray per second; the reference arm is measured on C3 only"}), flush=True)
         return
-    sc = scenes.c3_mesh()
-    lib, sh, kind = cpu_reference_setup(sc)
+    seg = int(os.environ.get("CRT_BENCH_C3_SEGMENTS", "0"))          # tests shrink the mesh (and say so in the line)
+    sc = scenes.c3_mesh(n_theta=seg, n_phi=seg // 2) if seg else scenes.c3_mesh()
+    lib, sh, info = cpu_reference_setup(sc)
+    bvh = sh.use_bvh(True) if info["bvh_build_s"] is not None else False
     cam_fn = lambda nx, ny: crt.camera_for(sc, nx, ny)
     steps, warm = args.steps, args.warmup
-    budget = max(2.0, min(20.0, 150.0 / max(1, steps + warm)))
+    budget = max(2.0, min(20.0, 120.0 / max(1, steps + warm)))
     budget = float(os.environ.get("CRT_BENCH_REF_BUDGET", budget))   # tests shorten it
     nx, ny = cpu_sample_shape(sh, cam_fn, sc, budget)
     cam = cam_fn(nx, ny)
@@ -202,19 +230,121 @@ def run_reference(args):
         rays += sh.last_rays
         paths += nx * ny
     value = rays / secs / 1e6
-    sample = "%dx%d px x 1 spp of the 1920x1080x16 frame per step (same scene, camera, depth); list scan over %d triangles" % (
-        nx, ny, len(sc["tri"]))
+    sample = "%dx%d px x 1 spp of the 1920x1080x16 frame per step (same scene, camera, depth); %s over %d triangles" % (
+        nx, ny, "the reference's BVHNode" if bvh else "list scan", len(sc["tri"]))
+    cb = {"value": value, "unit": "Mrays/s", "cores": lib.num_threads(), "kind": info["kind"], "sample": sample,
+          "accel": info["accel"], "bvh_build_s": info["bvh_build_s"]}
+    if bvh:
+        npr, ppr = sh.bvh_stats(scenes.primary_rays(cam_fn(192, 108), 192, 108))
+        cb["box_tests_per_camera_ray"], cb["prims_scanned_per_camera_ray"] = npr, ppr
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": args.gpus,
         "steps": steps, "warmup": warm, "ms_per_step": 1e3 * secs / max(1, steps), "higher_is_better": True,
-        "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "scaling": args.scaling or "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "paths_per_s": paths / secs,
-        "config": {"workload": WORKLOAD, "sample": sample},
-        "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": lib.num_threads(), "kind": kind, "sample": sample},
+        "config": {"workload": WORKLOAD if not seg else "TEST MESH of %d triangles (CRT_BENCH_C3_SEGMENTS)" % len(sc["tri"]),
+                   "sample": sample, "accelerator": info["accel"], "bvh_build_s": info["bvh_build_s"]},
+        "cpu_baseline": cb,
         "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)
+
+
+def other_configs(crt, scenes, torch, dev, local, peaks):
+    """BASELINE.json's other single-GPU configurations, a few frames each, so that they carry a driver-run number:
+    C1 (the reference's main(): bunny, 1024x512, 4 spp, LambertShade and shade()), C2 (spheres 1200x800x64),
+    C5 at 1e6 triangles (coherent camera rays x8 and 16.8 M incoherent rays through crt_trace_device)."""
+    out = {}
+
+    def render_cfg(name, sc, mode, reps):
+        ctx = crt.Context(local)
+        try:
+            ctx.set_scene(sc)
+            ctx.build()
+            nx, ny, spp, depth = sc["nx"], sc["ny"], sc["spp"], sc["max_depth"]
+            cam = crt.camera_for(sc)
+            accum = torch.zeros(ny, nx, 3, dtype=torch.float32, device=dev)
+            ext = torch.cuda.ExternalStream(ctx.stream(), device=dev)
+            ctx.set_option(crt.OPT_COUNTERS, 1)
+            ctx.reset_counters()
+            ctx.render_accum_device(cam, nx, ny, 0, spp, depth, mode, 1, 0, 1, accum.data_ptr())
+            w = ctx.counters()
+            ctx.set_option(crt.OPT_COUNTERS, 0)
+            for i in range(3):
+                ctx.render_accum_device(cam, nx, ny, 0, spp, depth, mode, 2 + i, 0, 1, accum.data_ptr())
+            ctx.sync()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(ext)
+            for i in range(reps):
+                ctx.render_accum_device(cam, nx, ny, 0, spp, depth, mode, 10 + i, 0, 1, accum.data_ptr())
+            e1.record(ext)
+            ctx.sync()
+            ms = e0.elapsed_time(e1) / reps
+            ctx.set_option(crt.OPT_LANES, 1)
+            ctx.set_option(crt.OPT_TIMING, 1)
+            ctx.render_accum_device(cam, nx, ny, 0, spp, depth, mode, 2, 0, 1, accum.data_ptr())
+            ctx.reset_counters()
+            for i in range(reps):
+                ctx.render_accum_device(cam, nx, ny, 0, spp, depth, mode, 10 + i, 0, 1, accum.data_ptr())
+            tq = ctx.counters()["trace_queue_ms"] / reps
+            out[name] = {"ms_per_frame": ms, "mrays_per_s": w["rays"] / ms / 1e3, "paths_per_s": nx * ny * spp / ms * 1e3,
+                         "prims": len(sc["tri"]) + len(sc["sph"]), "nx": nx, "ny": ny, "spp": spp,
+                         "rays_per_path": w["rays"] / (nx * ny * spp),
+                         "roofline_frac": alg_bytes(w) / (tq * 1e-3) / 1e9 / peaks["hbm_gbs"] if tq > 0 else None,
+                         "closest_hit_ms": tq}
+            del accum, e0, e1, ext
+        finally:
+            ctx.close()
+
+    def trace_cfg(n_tri, reps=5):
+        sc = scenes.c5_triangles(n_tri)
+        ctx = crt.Context(local)
+        try:
+            ctx.set_scene(sc)
+            ctx.build()
+            ctx.build()
+            build_ms = ctx.counters()["build_ms"]
+            cam = crt.camera_for(sc)
+            ext = torch.cuda.ExternalStream(ctx.stream(), device=dev)
+            prim = scenes.primary_rays(cam, 1920, 1080)
+            for kind, rays in (("coherent", prim), ("incoherent", scenes.c5_incoherent_rays(1 << 21))):
+                rays = np.ascontiguousarray(np.tile(rays, (8, 1)))     # 8 x so that the persistent grid has work beyond its ramp-up
+                d_rays = torch.from_numpy(rays).to(dev)
+                d_hits = torch.empty(len(rays), 4, dtype=torch.float32, device=dev)
+                ctx.set_option(crt.OPT_COUNTERS, 1)
+                ctx.reset_counters()
+                ctx.trace_device(d_rays.data_ptr(), len(rays), d_hits.data_ptr())
+                ctx.sync()
+                w = ctx.counters()
+                ctx.set_option(crt.OPT_COUNTERS, 0)
+                for _ in range(2):
+                    ctx.trace_device(d_rays.data_ptr(), len(rays), d_hits.data_ptr())
+                ctx.sync()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(ext)
+                for _ in range(reps):
+                    ctx.trace_device(d_rays.data_ptr(), len(rays), d_hits.data_ptr())
+                e1.record(ext)
+                ctx.sync()
+                ms = e0.elapsed_time(e1) / reps
+                n = len(rays)
+                w["rays"] = n
+                out["C5_%.0e_%s" % (n_tri, kind)] = {
+                    "ms_per_launch": ms, "mrays_per_s": n / ms / 1e3, "rays": n, "prims": n_tri, "lbvh_build_ms": build_ms,
+                    "nodes_per_ray": w["nodes_visited"] / n, "tris_per_ray": w["tris_tested"] / n,
+                    "roofline_frac": alg_bytes(w) / (ms * 1e-3) / 1e9 / peaks["hbm_gbs"]}
+                del d_rays, d_hits, e0, e1
+            del ext
+        finally:
+            ctx.close()
+
+    render_cfg("C1_bunny_1024x512x4_LambertShade", scenes.c1_bunny(), crt.SHADE_LAMBERT, 20)
+    render_cfg("C1_bunny_1024x512x4_shade", scenes.c1_bunny(), crt.SHADE_PATH, 20)
+    render_cfg("C2_spheres_1200x800x64", scenes.c2_spheres(), crt.SHADE_PATH, 5)
+    trace_cfg(10 ** 6)
+    torch.cuda.empty_cache()
+    return out
 
 
 def run_ours(args):
@@ -234,10 +364,13 @@ def run_ours(args):
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # keep stdout to the one JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     dev = torch.device("cuda", local)
+    scaling = args.scaling or "strong"      # the configured frame is fixed as N grows (total work fixed)
+    weak = scaling == "weak"
 
     if args.workload == "c4":
         sc = scenes.c4_instanced()
-        args.no_cpu_baseline = True      # a list scan over 10 M triangles manages about one ray per second
+        args.no_cpu_baseline = True      # the reference's single-thread BVH build over 10 M triangles takes minutes
+        args.no_configs = True
         args.e2e_api = "frame" if args.e2e_api == "points" else args.e2e_api
     else:
         sc = scenes.c3_mesh()
@@ -246,10 +379,18 @@ def run_ours(args):
     cam = crt.camera_for(sc)
     ctx = crt.Context(local)
     ctx.set_option(crt.OPT_LANES, args.lanes)
+    if args.slice_min:
+        ctx.set_option(crt.OPT_SLICE_MIN, args.slice_min)
     ctx.set_scene(sc)
     ctx.build()
-    build_ms = ctx.counters()["build_ms"]
+    build_cold_ms = ctx.counters()["build_ms"]      # first build: includes every allocation
+    ctx.build()
+    build_ms = ctx.counters()["build_ms"]           # the reference's "build" column, warm
+    ctx.refit()
+    refit_ms = ctx.counters()["refit_ms"]           # the reference's "update" column (Update_BVH), warm
     info = ctx.accel_info()
+    if world > 1:
+        multi.init_comm(ctx)                        # the library's own NCCL communicator (csrc/comm.cu)
     ext = torch.cuda.ExternalStream(ctx.stream(), device=dev)
     accum = torch.zeros(ny, nx, 3, dtype=torch.float32, device=dev)
     rgb = torch.zeros(ny, nx, 3, dtype=torch.float32, device=dev)
@@ -265,8 +406,6 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    weak = args.scaling == "weak"
-
     def step(seed):
         if weak:
             # every rank renders the named frame's full work: its own range of 16 samples of every pixel
@@ -276,8 +415,7 @@ def run_ours(args):
             # the frame is fixed; ranks split its 32x32 tiles (bit-identical to the 1-GPU image)
             ctx.render_accum_device(cam, nx, ny, 0, spp, depth, crt.SHADE_PATH, seed, rank, world, accum.data_ptr())
         if world > 1:
-            with torch.cuda.stream(ext):
-                multi.combine_accum(accum, 0)
+            ctx.reduce_accum_device(accum.data_ptr(), nx * ny * 3, 0)
         if rank == 0:
             ctx.resolve_device(accum.data_ptr(), nx * ny, spp * world if weak else spp, rgb.data_ptr())
 
@@ -326,6 +464,7 @@ def run_ours(args):
         sampler.wait_first()
     for i in range(args.warmup):
         step(1 + i)
+    ctx.sync()
     ctx.reset_counters()
     barrier()
     t_wall0 = time.perf_counter()
@@ -339,15 +478,19 @@ def run_ours(args):
     ms = e0.elapsed_time(e1)
     c = ctx.counters()
     lanes, launches = int(c["lanes"]), int(c["launches"])
-    # the roofline kernels timed alone: the same frames with one slice in flight (in the timed region above up to
-    # CRT_OPT_LANES slices overlap, so a launch's event pair also spans the other slices' kernels)
+    # the roofline kernels timed alone: the same frames with one slice in flight and an event pair around each
+    # closest-hit launch (in the timed region above up to CRT_OPT_LANES slices overlap, so an event pair would also
+    # span the other slices' kernels)
     ctx.set_option(crt.OPT_LANES, 1)
+    ctx.set_option(crt.OPT_TIMING, 1)
     step(50)
+    ctx.sync()
     ctx.reset_counters()
     for i in range(args.steps):
         step(100 + i)
     ctx.sync()
     alone_ms = ctx.counters()["trace_queue_ms"]
+    ctx.set_option(crt.OPT_TIMING, 0)
     ctx.set_option(crt.OPT_LANES, args.lanes)
     stats = torch.tensor([ms, float(c["rays"]), float(c["paths"]), alone_ms, float(launches)], dtype=torch.float64, device=dev)
     if world > 1:
@@ -359,6 +502,24 @@ def run_ours(args):
     else:
         rays, paths, bounce_ms = float(c["rays"]), float(c["paths"]), alone_ms
     value = rays / (ms * 1e-3) / 1e6
+
+    # ---- N > 1: is the combined frame the right image? ----
+    parity_n = None
+    if world > 1:
+        step(7)
+        ctx.sync()
+        barrier()
+        if rank == 0:
+            combined = accum.clone()
+            ctx.render_accum_device(cam, nx, ny, 0, spp * world if weak else spp, depth, crt.SHADE_PATH, 7, 0, 1, accum.data_ptr())
+            ctx.sync()
+            d = (combined.double() - accum.double()).abs()
+            parity_n = {"against": "rank 0's own one-GPU render of the same frame and seed (%d spp), accumulators before resolve" % (spp * world if weak else spp),
+                        "pixels_differing": int((d.amax(dim=-1) > 0).sum().item()), "max_abs_diff": float(d.max().item()),
+                        "expected": "bit-identical (each pixel is non-zero on one rank; adding zeros is exact)" if not weak else
+                                    "equal up to the order of float additions (the sum over ranks adds sample groups)"}
+            del combined
+        barrier()
 
     # ---- end to end through host buffers ----
     for i in range(args.warmup):
@@ -386,26 +547,32 @@ def run_ours(args):
     if rank == 0:
         peaks, peak_src = measured_peaks()
         n_r = work["rays"]
-        alg_bytes = 128 * work["node_fetches"] + 48 * work["tri_fetches"] + 16 * work["sphere_fetches"] + 48 * n_r
-        alg_flops = 96 * work["nodes_visited"] + 50 * work["tris_tested"] + 27 * work["spheres_tested"]
+        bytes_frame = alg_bytes(work)
+        flops_frame = alg_flops(work)
         bounce_launches = depth + 1
         per_launch_ms = bounce_ms / max(1, args.steps * bounce_launches)
-        achieved = alg_bytes / bounce_launches / (per_launch_ms * 1e-3) / 1e9
-        traffic = None
-        tpath = os.path.join(ROOT, "profiles", "k_trace_queue_traffic.json")
-        if os.path.exists(tpath):
+        achieved = bytes_frame / bounce_launches / (per_launch_ms * 1e-3) / 1e9
+        traffic, traffic_source, limiter = None, None, None
+        tpath = os.path.join(ROOT, "profiles", "closest_hit_ncu.json")
+        if os.path.exists(tpath) and args.workload == "c3":
             with open(tpath) as f:
-                traffic = json.load(f).get("dram_bytes_per_launch") if (world == 1 or weak) else None
+                prof = json.load(f)
+            if world == 1 or weak:
+                traffic = prof.get("dram_bytes_per_launch")
+            traffic_source = prof.get("source")
+            limiter = prof.get("limiter")
         line = {
             "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": args.scaling,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": scaling,
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "paths_per_s": paths / (ms * 1e-3),
             "config": {"workload": workload, "triangles": int(info["n_prims"]), "lbvh_depth": info["max_depth"],
-                       "lbvh_build_ms": build_ms, "lanes": lanes, "parallelism": ("single" if world == 1 else
+                       "lbvh_build_ms": build_ms, "lbvh_build_cold_ms": build_cold_ms, "lbvh_refit_ms": refit_ms,
+                       "reference_csv_columns": "rendering = ms_per_step, update = lbvh_refit_ms (+ the pose upload, inside e2e), build = lbvh_build_ms (kernel.cu:61, core/render.h:212-230)",
+                       "lanes": lanes, "parallelism": ("single" if world == 1 else
                                        "samples%d: every rank renders 16 spp of every pixel (sample range [16r, 16r+16)), %d spp in the combined frame" % (world, spp * world)
-                                       if weak else "tiles%d: 32x32 tiles, index mod N" % world),
-                       "combine": ("ncclReduce(sum) of the %.1f MB accumulators onto rank 0" % (nx * ny * 12 / 1e6)) if world > 1 else "none",
+                                       if weak else "tiles%d: the fixed %d-spp frame, 32x32 tiles, tile index mod N" % (world, spp)),
+                       "combine": ("crt_reduce_accum_device: ncclReduce(sum) of the %.1f MB accumulators onto rank 0, issued by libcrt_b200.so on its own communicator" % (nx * ny * 12 / 1e6)) if world > 1 else "none",
                        "l2": "per-step working set (queues %.1f GB + LBVH %.2f GB) exceeds the 126 MB L2; no explicit flush" % (
                            min(nx * ny * spp, 1 << 25) * 128 / 1e9, info["bytes"] / 1e9),
                        "rays_per_path": rays / max(1.0, paths)},
@@ -419,36 +586,66 @@ def run_ours(args):
                              if world == 1 and args.e2e_api == "frame" else
                              "crt_scene_update_vertices + crt_accel_refit + crt_render per frame, host buffers, wall clock"
                              if world == 1 else
-                             "per rank: %s, render of the rank's share, ncclReduce; rank 0: resolve + read-back to a pinned host buffer; wall clock, max over ranks" % (
+                             "per rank: %s, render of the rank's share, crt_reduce_accum_device; rank 0: resolve + read-back to a pinned host buffer; wall clock, max over ranks" % (
                                  "crt_scene_update_vertices + crt_accel_refit" if args.e2e_api == "calls" else
                                  "crt_scene_pose_async(%s) (upload + refit beside ray generation)" % ("points" if args.e2e_api == "points" else "vertices")))},
             "gpu_launches": launches,
             "roofline": {"kernel": "closest hit over the 4-wide LBVH: k_trace_packet (camera rays) + k_trace_queue (bounces), %d launches/step" % bounce_launches,
                          "bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                         "frac": achieved / peaks["hbm_gbs"], "traffic": traffic, "peak_source": peak_src,
-                         "algorithmic_bytes_per_launch": alg_bytes / bounce_launches,
-                         "algorithmic_flops_per_launch": alg_flops / bounce_launches,
+                         "frac": achieved / peaks["hbm_gbs"], "traffic": traffic, "traffic_source": traffic_source,
+                         "peak_source": peak_src,
+                         "algorithmic_bytes_per_launch": bytes_frame / bounce_launches,
+                         "algorithmic_flops_per_launch": flops_frame / bounce_launches,
                          "avg_launch_ms": per_launch_ms,
-                         "timing": "CUDA events around each closest-hit launch, on its stream, over %d frames rendered with one slice in flight (CRT_OPT_LANES=1); the timed region of `value` keeps %d slices in flight" % (args.steps, lanes),
+                         "timing": "CUDA events around each closest-hit launch, on its stream, over %d frames rendered with one slice in flight (CRT_OPT_LANES=1, CRT_OPT_TIMING=1); the timed region of `value` keeps %d slices in flight" % (args.steps, lanes),
                          "nodes_per_ray": work["nodes_visited"] / max(1, n_r), "tris_per_ray": work["tris_tested"] / max(1, n_r),
                          "node_fetches_per_ray": work["node_fetches"] / max(1, n_r), "tri_fetches_per_ray": work["tri_fetches"] / max(1, n_r),
-                         "accounting": "bytes = 128 B x node fetches + 48 B x triangle fetches + 48 B x rays; camera rays share one fetch (and, with a common origin, one interval box test) per packet of <= 32 rays, every other bounce fetches and tests per ray; flops = 96 x node tests + 50 x triangle tests",
-                         "fp32_tflops_achieved": alg_flops / bounce_launches / (per_launch_ms * 1e-3) / 1e12},
+                         "rays_per_launch": n_r / bounce_launches,
+                         "accounting": "bytes = %d B x node fetches (the three 256-bit loads of load_node) + %d B x primitive-record fetches (two 256-bit loads) + %d B x rays (32 B queue entry in, 16 B hit out); camera rays share one fetch (and, with a common origin, one interval box test) per packet of <= 32 rays, every other bounce fetches and tests per ray; flops = 96 x node tests + 50 x triangle tests" % (BYTES_NODE, BYTES_REC, BYTES_RAY),
+                         "limiter": limiter,
+                         "fp32_tflops_achieved": flops_frame / bounce_launches / (per_launch_ms * 1e-3) / 1e12},
         }
+        if parity_n is not None:
+            line["parity_n"] = parity_n
+        if world == 1 and not args.no_configs:
+            try:
+                line["configs"] = other_configs(crt, scenes, torch, dev, local, peaks)
+            except Exception as e:                       # the headline line must survive a failure here
+                line["configs"] = {"error": repr(e)}
         if world == 1 and not args.no_cpu_baseline:
-            lib, sh, kind = cpu_reference_setup(sc)
+            lib, sh, cinfo = cpu_reference_setup(sc)
             cam_fn = lambda a, b: crt.camera_for(sc, a, b)
-            snx, sny = cpu_sample_shape(sh, cam_fn, sc, 15.0)
-            img_cpu = np.asarray(sh.render(cam_fn(snx, sny), snx, sny, 1, depth, crt.SHADE_PATH, 1), np.float32)
-            # the checker at full scene size: the same sub-frame through the GPU path (the oracle is only the referee here)
-            img_gpu = ctx.render(cam_fn(snx, sny), snx, sny, 1, depth, crt.SHADE_PATH, 1)
+            # (1) parity at full scene size: a sub-frame through the reference's list scan (the parity oracle: the
+            #     GPU path reproduces its hits bit for bit) and through the GPU path
+            pnx, pny = cpu_sample_shape(sh, cam_fn, sc, 6.0)
+            img_cpu = np.asarray(sh.render(cam_fn(pnx, pny), pnx, pny, 1, depth, crt.SHADE_PATH, 1), np.float32)
+            list_rate = sh.last_rays / sh.last_seconds / 1e6
+            img_gpu = ctx.render(cam_fn(pnx, pny), pnx, pny, 1, depth, crt.SHADE_PATH, 1)
             diff = img_gpu.astype(np.float64) - img_cpu.astype(np.float64)
-            line["cpu_baseline"] = {
-                "value": sh.last_rays / sh.last_seconds / 1e6, "unit": "Mrays/s", "cores": lib.num_threads(), "kind": kind,
-                "sample": "%dx%d px x 1 spp of the 1920x1080x16 frame (same scene, camera, depth), %.1f s; list scan over %d triangles"
-                          % (snx, sny, sh.last_seconds, len(sc["tri"])),
-                "rmse_gpu_vs_reference": float(np.sqrt(np.mean(diff * diff))), "max_abs_diff": float(np.abs(diff).max()),
-                "pixels_differing": int((np.abs(diff).max(axis=-1) > 0).sum())}
+            cb = {"rmse_gpu_vs_reference": float(np.sqrt(np.mean(diff * diff))), "max_abs_diff": float(np.abs(diff).max()),
+                  "pixels_differing": int((np.abs(diff).max(axis=-1) > 0).sum()),
+                  "parity_sample": "%dx%d px x 1 spp, the reference's HitableList scan over %d triangles (%.1f s, %.6f Mrays/s)" % (
+                      pnx, pny, len(sc["tri"]), sh.last_seconds, list_rate)}
+            # (2) the timed baseline: the reference's shipping accelerator
+            if cinfo["bvh_build_s"] is not None and sh.use_bvh(True):
+                snx, sny = cpu_sample_shape(sh, cam_fn, sc, 12.0)
+                img_bvh = np.asarray(sh.render(cam_fn(snx, sny), snx, sny, 1, depth, crt.SHADE_PATH, 1), np.float32)
+                cb.update({"value": sh.last_rays / sh.last_seconds / 1e6, "unit": "Mrays/s", "cores": lib.num_threads(),
+                           "kind": cinfo["kind"], "accel": cinfo["accel"], "bvh_build_s": cinfo["bvh_build_s"],
+                           "sample": "%dx%d px x 1 spp of the 1920x1080x16 frame (same scene, camera, depth), %.1f s, through the reference's BVHNode over %d triangles"
+                                     % (snx, sny, sh.last_seconds, len(sc["tri"]))})
+                npr, ppr = sh.bvh_stats(scenes.primary_rays(cam_fn(192, 108), 192, 108))
+                cb["box_tests_per_camera_ray"], cb["prims_scanned_per_camera_ray"] = npr, ppr
+                # how far the reference's two accelerators are apart on the parity sub-frame (its AABB::hit rejects a
+                # box of zero thickness, core/aabb.h:38, so axis-aligned flat triangles such as the ground quad are
+                # invisible to its BVH)
+                img_b2 = np.asarray(sh.render(cam_fn(pnx, pny), pnx, pny, 1, depth, crt.SHADE_PATH, 1), np.float32)
+                cb["reference_bvh_vs_its_list_scan_pixels_differing"] = int((np.abs(img_b2 - img_cpu).max(axis=-1) > 0).sum())
+                del img_bvh
+            else:
+                cb.update({"value": list_rate, "unit": "Mrays/s", "cores": lib.num_threads(), "kind": cinfo["kind"],
+                           "accel": cinfo["accel"], "accel_reason": cinfo.get("accel_reason"), "sample": cb["parity_sample"]})
+            line["cpu_baseline"] = cb
         print(json.dumps(line), flush=True)
     # torch tensors that were used on the context's stream must go before the stream does
     barrier()
@@ -456,6 +653,7 @@ def run_ours(args):
     torch.cuda.synchronize()
     torch.cuda.empty_cache()
     if world > 1:
+        ctx.comm_destroy()
         dist.destroy_process_group()
     del ext
     ctx.close()
@@ -468,17 +666,19 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-configs", action="store_true", help="skip the C1 / C2 / C5 sub-records of the N = 1 line")
     ap.add_argument("--lanes", type=int, default=4, help="CRT_OPT_LANES of the timed region (1 for profiling: one slice, launches in bounce order)")
+    ap.add_argument("--slice-min", type=int, default=0, help="CRT_OPT_SLICE_MIN (tuning)")
     ap.add_argument("--e2e-api", default="points", choices=["points", "frame", "calls"],
                     help="end-to-end loop: points = the pose as the mesh's point array (crt_render_frame_pose, one overlapped "
                          "call per frame at N = 1); frame = all triangle vertices (crt_render_frame); calls = vertices through "
                          "the three separate calls")
     ap.add_argument("--workload", default="c3", choices=["c3", "c4"],
                     help="c3 (default): the configuration the metric is quoted on; c4: the 10 M-triangle instanced scene at "
-                         "4K x 64 spp (BASELINE.json configs[3]; use --scaling strong for its tile partition + NCCL reduce)")
-    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
-                    help="N > 1: weak = every rank renders the full 16-spp frame's work on its own sample range "
-                         "(default); strong = the 16-spp frame is split by tiles")
+                         "4K x 64 spp (BASELINE.json configs[3], tile partition + NCCL reduce under torchrun)")
+    ap.add_argument("--scaling", default=None, choices=["weak", "strong"],
+                    help="N > 1: strong (default) = the configured 16-spp frame split by tiles; weak = every rank renders the "
+                         "full 16-spp frame's work on its own sample range")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":

@@ -18,6 +18,8 @@ SHADE_PATH, SHADE_LAMBERT, SHADE_NORMAL = 0, 1, 2
 ACCEL_LBVH, ACCEL_BRUTE, ACCEL_LBVH_PACKET = 0, 1, 2
 OPT_LEAF_MAX, OPT_COUNTERS, OPT_BATCH_PATHS, OPT_REFILL, OPT_LEAF_THRESH, OPT_PACKET_PRIMARY, OPT_LANES, OPT_BUILDER = 1, 2, 3, 4, 5, 6, 7, 8
 OPT_WIDE_BELOW = 9
+OPT_TIMING, OPT_SLICE_MIN = 10, 11
+COMM_ID_BYTES = 128
 BUILDER_LBVH, BUILDER_PLOC = 0, 1
 TEX_CONSTANT, TEX_CHECKER = 0, 1
 POSE_VERTICES, POSE_POINTS, POSE_PARTS = 0, 1, 2
@@ -32,6 +34,8 @@ ABI_SYMBOLS = [
     "crt_accel_build", "crt_accel_refit", "crt_trace", "crt_trace_device", "crt_render", "crt_render_frame",
     "crt_render_accum_device", "crt_resolve_device", "crt_pack_rgba8_device", "crt_get_counters",
     "crt_reset_counters", "crt_accel_info",
+    "crt_comm_unique_id", "crt_comm_init", "crt_comm_destroy", "crt_comm_info", "crt_scene_broadcast",
+    "crt_reduce_accum_device", "crt_gather_device", "crt_render_dist",
 ]
 
 
@@ -110,11 +114,29 @@ def load_library():
     lib.crt_reset_counters.argtypes = [vp]
     lib.crt_accel_info.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64),
                                    C.POINTER(C.c_int)]
+    lib.crt_comm_unique_id.argtypes = [vp]
+    lib.crt_comm_init.argtypes = [vp, vp, C.c_int, C.c_int]
+    lib.crt_comm_destroy.argtypes = [vp]
+    lib.crt_comm_info.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    lib.crt_scene_broadcast.argtypes = [vp, C.c_int]
+    lib.crt_reduce_accum_device.argtypes = [vp, vp, sz, C.c_int]
+    lib.crt_gather_device.argtypes = [vp, vp, sz, vp, C.c_int]
+    lib.crt_render_dist.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint64, vp]
     for name in ABI_SYMBOLS:
         if name not in ("crt_destroy", "crt_last_error", "crt_stream"):
             getattr(lib, name).restype = C.c_int
     _lib = lib
     return lib
+
+
+def comm_unique_id():
+    """crt_comm_unique_id: the 128-byte id rank 0 hands to every rank before comm_init."""
+    lib = load_library()
+    buf = C.create_string_buffer(COMM_ID_BYTES)
+    rc = lib.crt_comm_unique_id(C.cast(buf, C.c_void_p))
+    if rc != 0:
+        raise CrtError("crt error %d: %s" % (rc, lib.crt_last_error().decode()))
+    return buf.raw
 
 
 def _ptr(a):
@@ -326,6 +348,41 @@ class Context:
 
     def pack_rgba8_device(self, d_rgb_ptr, nx, ny, d_rgba_ptr):
         self._check(self.lib.crt_pack_rgba8_device(self._h, C.c_void_p(d_rgb_ptr), nx, ny, C.c_void_p(d_rgba_ptr)))
+
+    # ---- several GPUs (comm.cu) ----
+    def comm_init(self, comm_id, rank, world):
+        """Collective: join the communicator `comm_id` (bytes from comm_unique_id() on rank 0) as `rank` of `world`."""
+        buf = C.create_string_buffer(bytes(comm_id), COMM_ID_BYTES)
+        self._check(self.lib.crt_comm_init(self._h, C.cast(buf, C.c_void_p), int(rank), int(world)))
+
+    def comm_destroy(self):
+        self._check(self.lib.crt_comm_destroy(self._h))
+
+    def comm_info(self):
+        r, w, v = C.c_int(), C.c_int(), C.c_int()
+        self._check(self.lib.crt_comm_info(self._h, C.byref(r), C.byref(w), C.byref(v)))
+        return dict(rank=r.value, world=w.value, nccl_version=v.value)
+
+    def scene_broadcast(self, root=0):
+        self._check(self.lib.crt_scene_broadcast(self._h, int(root)))
+
+    def reduce_accum_device(self, d_accum_ptr, n_floats, root=0):
+        self._check(self.lib.crt_reduce_accum_device(self._h, C.c_void_p(d_accum_ptr), int(n_floats), int(root)))
+
+    def gather_device(self, d_send_ptr, nbytes, d_recv_ptr, root=0):
+        self._check(self.lib.crt_gather_device(self._h, C.c_void_p(d_send_ptr), int(nbytes),
+                                               C.c_void_p(d_recv_ptr) if d_recv_ptr else None, int(root)))
+
+    def render_dist(self, cam22, nx, ny, spp, max_depth=8, mode=SHADE_PATH, seed=1, out=None):
+        """crt_render_dist (collective): the frame split by tiles over the communicator's GPUs; rank 0 gets the image."""
+        cam = np.ascontiguousarray(cam22, np.float32)
+        rank = self.comm_info()["rank"]
+        rgb = out
+        if rank == 0 and rgb is None:
+            rgb = np.empty((ny, nx, 3), np.float32)
+        self._check(self.lib.crt_render_dist(self._h, _ptr(cam), nx, ny, spp, max_depth, int(mode), int(seed),
+                                             _ptr(rgb) if rank == 0 else None))
+        return rgb if rank == 0 else None
 
     def sync(self):
         self._check(self.lib.crt_sync(self._h))

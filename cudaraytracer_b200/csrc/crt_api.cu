@@ -166,6 +166,8 @@ int crt_create(int device, crt_ctx** out)
     CRT_CUDA(cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, lane_prio(0)));
     CRT_CUDA(cudaEventCreate(&c->ev0));
     CRT_CUDA(cudaEventCreate(&c->ev1));
+    CRT_CUDA(cudaEventCreate(&c->ev_r0));
+    CRT_CUDA(cudaEventCreate(&c->ev_r1));
     CRT_CUDA(cudaEventCreate(&c->ev_fork));
     CRT_CUDA(cudaStreamCreateWithPriority(&c->up_stream, cudaStreamNonBlocking, prio_mode != 0 ? prio_hi : prio_lo));
     CRT_CUDA(cudaEventCreate(&c->ev_up0));
@@ -177,6 +179,7 @@ int crt_create(int device, crt_ctx** out)
         else CRT_CUDA(cudaStreamCreateWithPriority(&L.stream, cudaStreamNonBlocking, lane_prio(l)));
         CRT_CUDA(cudaEventCreate(&L.ev_begin));
         CRT_CUDA(cudaEventCreate(&L.ev_end));
+        CRT_CUDA(cudaEventCreateWithFlags(&L.ev_join, cudaEventDisableTiming));
         for (auto& e : L.ev_trace) CRT_CUDA(cudaEventCreate(&e));
         CRT_CUDA(cudaMallocHost((void**)&L.h_counts, sizeof(uint32_t) * (CRT_MAX_DEPTH + 3)));
     }
@@ -192,14 +195,17 @@ void crt_destroy(crt_ctx* c)
     if (!c) return;
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
+    if (c->comm) crt_comm_destroy(c);
     DevBuf* bufs[] = {&c->tri_in, &c->tri_mat, &c->tri_id, &c->sph_in, &c->sph_mat, &c->sph_id, &c->mats,
                       &c->keys[0], &c->keys[1], &c->vals[0], &c->vals[1], &c->hist, &c->nodes, &c->recs,
                       &c->child, &c->parent, &c->leaf_parent, &c->range, &c->node_box, &c->leaf_box, &c->flags,
                       &c->bounds, &c->depth_out, &c->ploc_box[0], &c->ploc_box[1], &c->ploc_nn, &c->ploc_tmp, &c->ploc_blk, &c->work_ctr, &c->accum, &c->rgb,
-                      &c->rays_tmp, &c->hits_tmp, &c->counters, &c->rest, &c->part_id, &c->part_T, &c->tri_idx, &c->node_cone};
+                      &c->rays_tmp, &c->hits_tmp, &c->counters, &c->rest, &c->part_id, &c->part_T, &c->tri_idx, &c->node_cone, &c->frames, &c->tri_frame, &c->sph_frame};
     for (DevBuf* b : bufs) b->release();
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
+    if (c->ev_r0) cudaEventDestroy(c->ev_r0);
+    if (c->ev_r1) cudaEventDestroy(c->ev_r1);
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
     if (c->up_stream) { cudaStreamSynchronize(c->up_stream); cudaStreamDestroy(c->up_stream); }
     if (c->ev_up0) cudaEventDestroy(c->ev_up0);
@@ -212,6 +218,7 @@ void crt_destroy(crt_ctx* c)
         for (DevBuf* b : lb) b->release();
         if (L.ev_begin) cudaEventDestroy(L.ev_begin);
         if (L.ev_end) cudaEventDestroy(L.ev_end);
+        if (L.ev_join) cudaEventDestroy(L.ev_join);
         for (auto& e : L.ev_trace) if (e) cudaEventDestroy(e);
         if (L.h_counts) cudaFreeHost(L.h_counts);
         if (l > 0 && L.stream) cudaStreamDestroy(L.stream);
@@ -253,6 +260,13 @@ int crt_set_option(crt_ctx* c, int option, int64_t value)
     case CRT_OPT_LANES:
         if (value < 1 || value > CRT_MAX_LANES) { set_error("CRT_OPT_LANES must be in [1, %d]", CRT_MAX_LANES); return CRT_ERR_INVALID; }
         c->n_lanes = (int)value;
+        return CRT_OK;
+    case CRT_OPT_TIMING:
+        c->timing = value != 0;
+        return CRT_OK;
+    case CRT_OPT_SLICE_MIN:
+        if (value < 1) { set_error("CRT_OPT_SLICE_MIN must be >= 1"); return CRT_ERR_INVALID; }
+        c->slice_min_samples = value;
         return CRT_OK;
     case CRT_OPT_BATCH_PATHS:
         if (value < 1) { set_error("CRT_OPT_BATCH_PATHS must be >= 1"); return CRT_ERR_INVALID; }
@@ -325,7 +339,12 @@ int crt_scene_set_triangles(crt_ctx* c, const float* tri, const uint32_t* mat_id
     c->n_idx_tri = 0;
     c->n_points = 0;
     c->accel_valid = false;
-    // default sphere ids follow the triangles; renumber them if they were defaulted earlier
+    // default sphere ids follow the triangles: renumber them if they were defaulted against another triangle count
+    if (c->sph_id_default && c->n_sph > 0 && c->sph_id_first != (uint32_t)n) {
+        if ((r = upload_ids(c->sph_id, nullptr, c->n_sph, (uint32_t)n, c->stream)) != CRT_OK) return r;
+        CRT_CUDA(cudaStreamSynchronize(c->stream));
+        c->sph_id_first = (uint32_t)n;
+    }
     return CRT_OK;
 }
 
@@ -342,6 +361,8 @@ int crt_scene_set_spheres(crt_ctx* c, const float* sph, const uint32_t* mat_id, 
     if ((r = upload_ids(c->sph_id, prim_id, n, (uint32_t)c->n_tri, c->stream)) != CRT_OK) return r;
     CRT_CUDA(cudaStreamSynchronize(c->stream));
     c->n_sph = n;
+    c->sph_id_default = prim_id == nullptr;
+    c->sph_id_first = (uint32_t)c->n_tri;
     c->accel_valid = false;
     return CRT_OK;
 }
@@ -587,6 +608,10 @@ int crt_render_frame_pose(crt_ctx* c, int pose_kind, const float* pose, size_t f
         return CRT_ERR_STATE;
     }
     cudaStream_t up = c->up_stream;
+    // behind whatever the context's stream still does with the scene or the staging buffers (an asynchronous
+    // crt_trace_device, a render queued by a _device call)
+    CRT_CUDA(cudaEventRecord(c->ev_fork, c->stream));
+    CRT_CUDA(cudaStreamWaitEvent(up, c->ev_fork, 0));
     int r = enqueue_pose(c, pose_kind, pose, first, n, up, "crt_render_frame");
     if (r != CRT_OK) return r;
     r = lbvh_build(c, true, up);
@@ -612,7 +637,15 @@ int crt_get_counters(crt_ctx* c, crt_counters* out)
     unsigned long long h[CNT_COUNT];
     CRT_CUDA(cudaMemcpyAsync(h, c->counters.p, sizeof h, cudaMemcpyDeviceToHost, c->stream));
     CRT_CUDA(cudaStreamSynchronize(c->stream));
+    if (c->render_ms_pending) {
+        c->render_ms_pending = false;
+        float ms = 0.f;
+        if (cudaEventSynchronize(c->ev_r1) == cudaSuccess && cudaEventElapsedTime(&ms, c->ev_r0, c->ev_r1) == cudaSuccess) c->host_counters.render_ms = ms;
+        else (void)cudaGetLastError();
+    }
     *out = c->host_counters;
+    out->rays += h[CNT_RENDER_RAYS];
+    out->paths += h[CNT_RENDER_PATHS];
     out->nodes_visited = h[CNT_NODES];
     out->tris_tested = h[CNT_TRIS];
     out->spheres_tested = h[CNT_SPHERES];

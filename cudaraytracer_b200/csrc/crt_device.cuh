@@ -37,6 +37,10 @@ namespace crt {
 #define CRT_DMAT_CHECKER 4u
 struct DMat { float r, g, b, param; uint32_t type; float r2, g2, b2; };  // 32 B
 
+// One level of a primitive's chain of enclosing Transforms (hitable/transform.h:7-14): the rows of the matrix
+// rotate() builds from the Euler angles (core/vec3.h:200-217), computed on the host, and the position. 64 B.
+struct DFrame { float m[9]; float px, py, pz; uint32_t has_rot; uint32_t pad[3]; };
+
 struct AccelView {
     const float4* nodes;
     const float4* recs;

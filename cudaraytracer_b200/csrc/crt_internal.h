@@ -43,7 +43,7 @@ struct DevBuf {
 };
 
 // Device-side work counters, one 64-bit word each.
-enum { CNT_RAYS = 0, CNT_NODES, CNT_TRIS, CNT_SPHERES, CNT_SCATTERS, CNT_PATHS, CNT_MAX_STEPS, CNT_NODE_F, CNT_TRI_F, CNT_SPH_F, CNT_COUNT };
+enum { CNT_RAYS = 0, CNT_NODES, CNT_TRIS, CNT_SPHERES, CNT_SCATTERS, CNT_PATHS, CNT_MAX_STEPS, CNT_NODE_F, CNT_TRI_F, CNT_SPH_F, CNT_RENDER_RAYS, CNT_RENDER_PATHS, CNT_COUNT };
 
 // Wavefront path state, 64 B = 4 x 128-bit words (SoA by word):
 //   w0 = {o.x, o.y, o.z, d.x}
@@ -59,7 +59,8 @@ constexpr int CRT_MAX_LANES = 4;
 struct crt_lane {
     cudaStream_t stream = nullptr;         // lane 0 uses the context's stream
     crt::DevBuf queue[2], qcount, work_ctr, hitbuf, rad;
-    cudaEvent_t ev_begin = nullptr, ev_end = nullptr;   // bounces of the current job
+    cudaEvent_t ev_begin = nullptr, ev_end = nullptr;   // bounces of the current job (CRT_OPT_TIMING)
+    cudaEvent_t ev_join = nullptr;         // end of the lane's share of a render call, joined into the context's stream
     cudaEvent_t ev_trace[2 * (crt::CRT_MAX_DEPTH + 1)] = {};
     uint32_t* h_counts = nullptr;          // pinned copy of qcount
 };
@@ -69,6 +70,7 @@ struct crt_ctx {
     int sm_count = 148;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_fork = nullptr;
+    cudaEvent_t ev_r0 = nullptr, ev_r1 = nullptr;   // begin and end of the last render call on the context's stream
     cudaStream_t up_stream = nullptr;      // crt_render_frame: vertex upload + refit, overlapped with ray generation
     cudaEvent_t ev_up0 = nullptr, ev_up1 = nullptr, ev_frame = nullptr;
     bool pose_pending = false;             // crt_scene_pose_async: upload + refit in flight on up_stream, ev_frame marks their end
@@ -80,6 +82,14 @@ struct crt_ctx {
     crt::DevBuf sph_in, sph_mat, sph_id;   // n_sph x 4 floats
     crt::DevBuf mats;                      // DMat
     size_t n_tri = 0, n_sph = 0, n_mats = 0;
+    bool sph_id_default = false;           // sphere ids were numbered by the library, from sph_id_first on
+    uint32_t sph_id_first = 0;
+    // chains of enclosing Transforms (rotation): the table and, per primitive, (first << 8) | count, 0 = none
+    crt::DevBuf frames, tri_frame, sph_frame;
+    size_t n_frames = 0;
+    // multi-GPU (comm.cu): NCCL communicator of this context's rank
+    void* comm = nullptr;
+    int comm_rank = 0, comm_world = 1;
     // rigid parts (bones): rest-pose vertices (n_tri x 9 floats), part of each triangle, the current translations
     crt::DevBuf rest, part_id, part_T;
     size_t n_parts = 0;
@@ -110,6 +120,10 @@ struct crt_ctx {
     int packet_primary = 1;                // camera rays through the packet kernel
     int64_t wide_below = 32768;            // CRT_OPT_WIDE_BELOW: bounces with fewer rays run one warp per ray
     int64_t batch_paths = 1ll << 25;
+    int64_t slice_min_samples = 2000000;   // CRT_OPT_SLICE_MIN: a slice (lane) of a frame holds at least this many camera samples
+    int timing = 0;                        // CRT_OPT_TIMING: per-launch events, render calls wait for the device
+    int grid_trace = 0, grid_shade = 0, grid_packet = 0, grid_tail = 0;   // persistent grids (render.cu:size_grids)
+    bool render_ms_pending = false;        // ev0/ev1 of the last render call not read yet
 
     crt_counters host_counters = {};
 };

@@ -646,24 +646,16 @@ __device__ __forceinline__ void traverse_packets(const AccelView& A, const uint3
 // (3 per level, see above) to what was there.
 #define CRT_WIDE_STACK 1024   // entries {reference, entry distance} per warp: 8 KB
 
-template <bool COUNT, bool HAS_SPH, class Src, class Sink>
-__device__ __forceinline__ void traverse_wide(const AccelView& A, const uint32_t n, uint32_t* work_ctr,
-                                              const float t_min, const float t_max, const Src& src,
-                                              const Sink& sink, uint2* s_stack, TraceCounters& cnt)
+// One ray, the whole warp: o and d (= ray_dir_local of the raw direction) are warp-uniform, and so is the result.
+template <bool COUNT, bool HAS_SPH>
+__device__ __forceinline__ Hit trace_wide_one(const AccelView& A, const v3 o, const v3 d, const float t_min, const float t_max,
+                                              uint2* s_stack, TraceCounters& cnt)
 {
     constexpr uint32_t FULL = 0xffffffffu;
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t lt_mask = (1u << lane) - 1u;
     constexpr uint32_t WIDE_LIMIT = CRT_WIDE_STACK - CRT_STACK_ENTRIES;
-
-    for (;;) {
-        uint32_t ray_i = 0;
-        if (lane == 0) ray_i = atomicAdd(work_ctr, 1u);
-        ray_i = __shfl_sync(FULL, ray_i, 0);
-        if (ray_i >= n) break;
-        v3 o, dr;
-        src.load(ray_i, o, dr);                     // the same address in every lane: one broadcast load
-        const v3 d = ray_dir_local(dr);
+    {
         const RaySlabs S = make_slabs(o, d);
         Hit best;                                    // warp-uniform
         best.t = t_max; best.k = 0xFFFFFFFFu; best.id = CRT_MISS_ID; best.u = best.v = 0.f;
@@ -778,6 +770,24 @@ __device__ __forceinline__ void traverse_wide(const AccelView& A, const uint32_t
             }
             __syncwarp();
         }
+        return best;
+    }
+}
+
+template <bool COUNT, bool HAS_SPH, class Src, class Sink>
+__device__ __forceinline__ void traverse_wide(const AccelView& A, const uint32_t n, uint32_t* work_ctr,
+                                              const float t_min, const float t_max, const Src& src,
+                                              const Sink& sink, uint2* s_stack, TraceCounters& cnt)
+{
+    const uint32_t lane = threadIdx.x & 31u;
+    for (;;) {
+        uint32_t ray_i = 0;
+        if (lane == 0) ray_i = atomicAdd(work_ctr, 1u);
+        ray_i = __shfl_sync(0xffffffffu, ray_i, 0);
+        if (ray_i >= n) break;
+        v3 o, dr;
+        src.load(ray_i, o, dr);                     // the same address in every lane: one broadcast load
+        const Hit best = trace_wide_one<COUNT, HAS_SPH>(A, o, ray_dir_local(dr), t_min, t_max, s_stack, cnt);
         if (lane == 0) sink.store(ray_i, best);
     }
 }

@@ -249,35 +249,6 @@ k_trace_queue(AccelView A, const float4* __restrict__ q, uint32_t cap, const uin
     }
 }
 
-// ---- closest hit for a queue of few rays: one warp per ray (crt_traverse.cuh traverse_wide) ----
-template <bool COUNT, bool HAS_SPH>
-__global__ void __launch_bounds__(TP_BLOCK)
-k_trace_wide(AccelView A, const float4* __restrict__ q, uint32_t cap, const uint32_t* __restrict__ n_ptr,
-             uint32_t* __restrict__ work_ctr, float4* __restrict__ hits, unsigned long long* __restrict__ counters,
-             uint32_t wide_below)
-{
-    __shared__ uint2 s_stack[(TP_BLOCK / 32) * CRT_WIDE_STACK];
-    const uint32_t n = *n_ptr;
-    if (n >= wide_below) return;                    // k_trace_queue took this launch
-    TraceCounters cnt = {0u, 0u, 0u, 0u, 0u, 0u, 0u};
-    QueueSrc src = {q, cap};
-    QueueSink sink = {hits};
-    traverse_wide<COUNT, HAS_SPH>(A, n, work_ctr, 0.001f, FLT_MAX, src, sink, s_stack + (threadIdx.x >> 5) * CRT_WIDE_STACK, cnt);   // render.h:53
-    if (COUNT) {
-        const uint32_t nodes = __reduce_add_sync(0xffffffffu, cnt.nodes);
-        const uint32_t tris = __reduce_add_sync(0xffffffffu, cnt.tris);
-        const uint32_t sph = __reduce_add_sync(0xffffffffu, cnt.spheres);
-        if ((threadIdx.x & 31u) == 0u) {
-            atomicAdd(counters + CNT_NODES, (unsigned long long)nodes);
-            atomicAdd(counters + CNT_TRIS, (unsigned long long)tris);
-            atomicAdd(counters + CNT_SPHERES, (unsigned long long)sph);
-            atomicAdd(counters + CNT_NODE_F, (unsigned long long)nodes);
-            atomicAdd(counters + CNT_TRI_F, (unsigned long long)tris);
-            atomicAdd(counters + CNT_SPH_F, (unsigned long long)sph);
-        }
-    }
-}
-
 // ---- closest hit for camera rays: one packet per warp (crt_traverse.cuh traverse_packets) ----
 template <bool COUNT, bool HAS_SPH>
 __global__ void __launch_bounds__(TP_BLOCK, CRT_PACKET_MIN_BLOCKS)
@@ -303,15 +274,130 @@ k_trace_packet(AccelView A, const float4* __restrict__ q, uint32_t cap, const ui
     }
 }
 
-// ---- shade(): one thread per queue entry, fully converged ----
+// ---- shade(): the body of the reference's recursion for one path segment ----
+struct PathState {
+    v3 o, d;              // the ray that was traced (d as shade() holds it: not normalised)
+    uint32_t path_id;     // slot * s_count + sample of the batch
+    uint32_t pack;        // draw counter | depth_left << 24
+    uint32_t ms[8];       // material ids of the bounces so far, 16 bits each
+};
+
+// One evaluation of shade()'s body (render.h:48-67) for a path whose ray has the closest hit (ht, hk = sorted
+// primitive position or ~0u). Returns true when the path goes on: S then holds the scattered ray, the bounce's
+// material id, the new draw counter and depth. Otherwise L is the path's radiance, unwound through every recorded
+// bounce innermost first.
+template <bool COUNT, bool HAS_SPH>
+__device__ __forceinline__ bool shade_step(const RenderParams& P, const AccelView& A, const DMat* __restrict__ mats,
+                                           PathState& S, const float ht, const uint32_t hk, v3& L, uint32_t& n_scatter)
+{
+    const v3 o = S.o, d = S.d;
+    const int depth_left = (int)(S.pack >> 24);
+    const int bounces = P.max_depth - depth_left;
+    bool next = false;
+    if (hk == 0xFFFFFFFFu) {
+        L = background_sky(d);                                             // render.h:65
+    } else {
+        Rng rng;
+        {
+            uint32_t slot, s_local;
+            split_path_id(P, S.path_id, slot, s_local);
+            int px, py;
+            slot_to_pixel(P, slot, px, py);
+            rng.key = crt_rng_key_from(P.seed_key, (uint32_t)py * (uint32_t)P.nx + (uint32_t)px, (uint32_t)(P.s_begin + (int)s_local));
+            rng.ctr = S.pack & 0xFFFFFFu;
+        }
+        const v3 dl = ray_dir_local(d);
+        float4 r0, r1, r2, r3;
+        ldg256(A.recs + 4 * (size_t)hk, r0, r1);
+        ldg256(A.recs + 4 * (size_t)hk + 2, r2, r3);
+        const uint32_t inf_y = __float_as_uint(r3.y);
+        v3 p, n;
+        if (HAS_SPH && (inf_y & CRT_KIND_SPHERE)) {
+            p = vadd(vsub(o, V(r0.x, r0.y, r0.z)), vscale(ht, dl));        // sphere.h:40 (local frame)
+            n = vdivf(p, r0.w);                                            // sphere.h:41
+        } else {
+            p = vadd(o, vscale(ht, dl));                                   // triangle.h:95
+            n = V(r0.w, r1.w, r2.w);                                       // triangle.h:96
+        }
+        const uint32_t mat_id = inf_y & 0x7FFFFFFFu;
+        const DMat m = load_mat(mats, mat_id);
+        const bool odd = checker_odd(m, p);                                // texture.h:31
+        const v3 e = emitted(m, odd);                                      // render.h:56
+        if (P.mode == CRT_SHADE_PATH) {
+            v3 att, out_d;
+            if (COUNT && depth_left > 0) n_scatter++;
+            if (depth_left > 0 && scatter(m, d, p, n, rng, att, out_d, odd)) {  // render.h:57
+                next = true;
+                const uint32_t hist = (mat_id & 0x7FFFu) | (odd ? 0x8000u : 0u);   // 15 bits of id + which checker colour
+#pragma unroll
+                for (int j = 0; j < 8; j++)
+                    if (j == (bounces >> 1))
+                        S.ms[j] = (bounces & 1) ? ((S.ms[j] & 0xFFFFu) | (hist << 16)) : hist;
+                S.o = p;
+                S.d = out_d;
+                S.pack = (rng.ctr & 0xFFFFFFu) | ((uint32_t)(depth_left - 1) << 24);
+            } else {
+                L = vadd(e, V(0.1f, 0.1f, 0.1f));                          // render.h:61
+            }
+        } else if (P.mode == CRT_SHADE_LAMBERT) {                          // render.h:70-87
+            v3 att, out_d;
+            if (COUNT) n_scatter++;
+            scatter(m, d, p, n, rng, att, out_d, odd);
+            float c = vdot(d, n);
+            if (c < 0.0f) c = 0.0f;
+            L = vadd(vscale(0.2f, vmul(vscale(c, att), background_sky(d))), e);
+        } else {                                                           // render.h:90-103
+            L = n;
+        }
+    }
+    if (!next) {
+        // unwind "emitted + attenuation * shade(next)" (render.h:58), innermost first
+#pragma unroll
+        for (int j = CRT_MAX_DEPTH - 1; j >= 0; j--) {
+            if (j < bounces) {
+                const uint32_t id = (S.ms[j >> 1] >> ((j & 1) * 16)) & 0xFFFFu;
+                const DMat mj = load_mat(mats, id & 0x7FFFu);
+                // a material that scattered is not a light (material.h:149-155): its emitted() is 0
+                L = vadd(V(0.0f, 0.0f, 0.0f), vmul(bounce_attenuation(mj, (id & 0x8000u) != 0u), L));
+            }
+        }
+    }
+    return next;
+}
+
+// path state of queue entry i; the material-id words exist once a bounce has been recorded
+__device__ __forceinline__ void load_path(const RenderParams& P, const float4* __restrict__ q, uint32_t i, PathState& S)
+{
+    const float4 w0 = __ldcs(q + i);
+    const float4 w1 = __ldcs(q + (size_t)P.cap + i);
+    S.o = V(w0.x, w0.y, w0.z);
+    S.d = V(w0.w, w1.x, w1.y);
+    S.path_id = __float_as_uint(w1.z);
+    S.pack = __float_as_uint(w1.w);
+#pragma unroll
+    for (int j = 0; j < 8; j++) S.ms[j] = 0u;
+    const int bounces = P.max_depth - (int)(S.pack >> 24);
+    if (bounces > 0) {
+        const uint4 a2 = __ldcs(reinterpret_cast<const uint4*>(q) + 2 * (size_t)P.cap + i);
+        S.ms[0] = a2.x; S.ms[1] = a2.y; S.ms[2] = a2.z; S.ms[3] = a2.w;
+        if (bounces > 8) {
+            const uint4 a3 = __ldcs(reinterpret_cast<const uint4*>(q) + 3 * (size_t)P.cap + i);
+            S.ms[4] = a3.x; S.ms[5] = a3.y; S.ms[6] = a3.z; S.ms[7] = a3.w;
+        }
+    }
+}
+
+// one thread per queue entry, fully converged. A queue of fewer than `tail_below` entries belongs to k_tail.
 template <bool COUNT, bool HAS_SPH>
 __global__ void __launch_bounds__(RB)
 k_shade(RenderParams P, AccelView A, const DMat* __restrict__ mats, const float4* __restrict__ q_in,
         const float4* __restrict__ hits, const uint32_t* __restrict__ n_in_ptr, float4* __restrict__ q_out,
-        uint32_t* __restrict__ n_out_ptr, float4* __restrict__ rad, unsigned long long* __restrict__ counters)
+        uint32_t* __restrict__ n_out_ptr, float4* __restrict__ rad, unsigned long long* __restrict__ counters,
+        uint32_t tail_below)
 {
     __shared__ uint32_t s_cnt[2 * (RB / 32 + 1)];
     const uint32_t n_in = *n_in_ptr;
+    if (n_in < tail_below) return;
     const uint32_t lane = threadIdx.x & 31u;
     uint32_t n_scatter = 0;
 
@@ -320,106 +406,21 @@ k_shade(RenderParams P, AccelView A, const DMat* __restrict__ mats, const float4
         const uint32_t i = bbase + threadIdx.x;
         const bool live = i < n_in;
         bool next = false;
-        float4 w0 = make_float4(0, 0, 0, 0), w1 = w0;
-        uint32_t ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        PathState S;
         if (live) {
-            w0 = __ldcs(q_in + i);
-            w1 = __ldcs(q_in + (size_t)P.cap + i);
+            load_path(P, q_in, i, S);
             const float4 hr = __ldcs(hits + i);
-            const v3 o = V(w0.x, w0.y, w0.z), d = V(w0.w, w1.x, w1.y);
-            const uint32_t path_id = __float_as_uint(w1.z);
-            const uint32_t pack = __float_as_uint(w1.w);
-            const int depth_left = (int)(pack >> 24);
-            const int bounces = P.max_depth - depth_left;
-            if (bounces > 0) {
-                const uint4 a2 = __ldcs(reinterpret_cast<const uint4*>(q_in) + 2 * (size_t)P.cap + i);
-                ms[0] = a2.x; ms[1] = a2.y; ms[2] = a2.z; ms[3] = a2.w;
-                if (bounces > 8) {
-                    const uint4 a3 = __ldcs(reinterpret_cast<const uint4*>(q_in) + 3 * (size_t)P.cap + i);
-                    ms[4] = a3.x; ms[5] = a3.y; ms[6] = a3.z; ms[7] = a3.w;
-                }
-            }
-            const uint32_t hk = __float_as_uint(hr.y);
-
             v3 L;
-            if (hk == 0xFFFFFFFFu) {
-                L = background_sky(d);                                             // render.h:65
-            } else {
-                Rng rng;
-                {
-                    uint32_t slot, s_local;
-                    split_path_id(P, path_id, slot, s_local);
-                    int px, py;
-                    slot_to_pixel(P, slot, px, py);
-                    rng.key = crt_rng_key_from(P.seed_key, (uint32_t)py * (uint32_t)P.nx + (uint32_t)px, (uint32_t)(P.s_begin + (int)s_local));
-                    rng.ctr = pack & 0xFFFFFFu;
-                }
-                const v3 dl = ray_dir_local(d);
-                const float ht = hr.x;
-                float4 r0, r1, r2, r3;
-                ldg256(A.recs + 4 * (size_t)hk, r0, r1);
-                ldg256(A.recs + 4 * (size_t)hk + 2, r2, r3);
-                const uint32_t inf_y = __float_as_uint(r3.y);
-                v3 p, n;
-                if (HAS_SPH && (inf_y & CRT_KIND_SPHERE)) {
-                    p = vadd(vsub(o, V(r0.x, r0.y, r0.z)), vscale(ht, dl));        // sphere.h:40 (local frame)
-                    n = vdivf(p, r0.w);                                            // sphere.h:41
-                } else {
-                    p = vadd(o, vscale(ht, dl));                                   // triangle.h:95
-                    n = V(r0.w, r1.w, r2.w);                                       // triangle.h:96
-                }
-                const uint32_t mat_id = inf_y & 0x7FFFFFFFu;
-                const DMat m = load_mat(mats, mat_id);
-                const bool odd = checker_odd(m, p);                                // texture.h:31
-                const v3 e = emitted(m, odd);                                      // render.h:56
-                if (P.mode == CRT_SHADE_PATH) {
-                    v3 att, out_d;
-                    if (COUNT && depth_left > 0) n_scatter++;
-                    if (depth_left > 0 && scatter(m, d, p, n, rng, att, out_d, odd)) {  // render.h:57
-                        next = true;
-                        const uint32_t hist = (mat_id & 0x7FFFu) | (odd ? 0x8000u : 0u);   // 15 bits of id + which checker colour
-#pragma unroll
-                        for (int j = 0; j < 8; j++)
-                            if (j == (bounces >> 1))
-                                ms[j] = (bounces & 1) ? ((ms[j] & 0xFFFFu) | (hist << 16)) : hist;
-                        w0 = make_float4(p.x, p.y, p.z, out_d.x);
-                        w1 = make_float4(out_d.y, out_d.z, __uint_as_float(path_id),
-                                         __uint_as_float((rng.ctr & 0xFFFFFFu) | ((uint32_t)(depth_left - 1) << 24)));
-                    } else {
-                        L = vadd(e, V(0.1f, 0.1f, 0.1f));                          // render.h:61
-                    }
-                } else if (P.mode == CRT_SHADE_LAMBERT) {                          // render.h:70-87
-                    v3 att, out_d;
-                    if (COUNT) n_scatter++;
-                    scatter(m, d, p, n, rng, att, out_d, odd);
-                    float c = vdot(d, n);
-                    if (c < 0.0f) c = 0.0f;
-                    L = vadd(vscale(0.2f, vmul(vscale(c, att), background_sky(d))), e);
-                } else {                                                           // render.h:90-103
-                    L = n;
-                }
-            }
-            if (!next) {
-                // unwind "emitted + attenuation * shade(next)" (render.h:58), innermost first
-#pragma unroll
-                for (int j = CRT_MAX_DEPTH - 1; j >= 0; j--) {
-                    if (j < bounces) {
-                        const uint32_t id = (ms[j >> 1] >> ((j & 1) * 16)) & 0xFFFFu;
-                        const DMat mj = load_mat(mats, id & 0x7FFFu);
-                        // a material that scattered is not a light (material.h:149-155): its emitted() is 0
-                        L = vadd(V(0.0f, 0.0f, 0.0f), vmul(bounce_attenuation(mj, (id & 0x8000u) != 0u), L));
-                    }
-                }
-                __stcs(rad + path_id, make_float4(L.x, L.y, L.z, 0.0f));
-            }
+            next = shade_step<COUNT, HAS_SPH>(P, A, mats, S, hr.x, __float_as_uint(hr.y), L, n_scatter);
+            if (!next) __stcs(rad + S.path_id, make_float4(L.x, L.y, L.z, 0.0f));
         }
         const uint32_t pos = block_append<RB>(next, n_out_ptr, s_cnt, it);
         if (next) {
-            __stcs(q_out + pos, w0);
-            __stcs(q_out + (size_t)P.cap + pos, w1);
-            __stcs(reinterpret_cast<uint4*>(q_out) + 2 * (size_t)P.cap + pos, make_uint4(ms[0], ms[1], ms[2], ms[3]));
+            __stcs(q_out + pos, make_float4(S.o.x, S.o.y, S.o.z, S.d.x));
+            __stcs(q_out + (size_t)P.cap + pos, make_float4(S.d.y, S.d.z, __uint_as_float(S.path_id), __uint_as_float(S.pack)));
+            __stcs(reinterpret_cast<uint4*>(q_out) + 2 * (size_t)P.cap + pos, make_uint4(S.ms[0], S.ms[1], S.ms[2], S.ms[3]));
             if (P.max_depth > 8)
-                __stcs(reinterpret_cast<uint4*>(q_out) + 3 * (size_t)P.cap + pos, make_uint4(ms[4], ms[5], ms[6], ms[7]));
+                __stcs(reinterpret_cast<uint4*>(q_out) + 3 * (size_t)P.cap + pos, make_uint4(S.ms[4], S.ms[5], S.ms[6], S.ms[7]));
         }
     }
     if (COUNT) {
@@ -428,9 +429,72 @@ k_shade(RenderParams P, AccelView A, const DMat* __restrict__ mats, const float4
     }
 }
 
-__global__ void __launch_bounds__(256)
-k_accumulate(RenderParams P, const float4* __restrict__ rad, float* __restrict__ accum)
+// ---- the tail of a slice: a queue of FEW paths is carried to termination by one launch ----
+// The last bounces of a frame hold 20,000 paths down to a handful; as wavefront launches each of them is bound by
+// its longest ray and by launch latency (bounces 3-8 of a C3 slice: 18 launches for 0.04 % of the rays). Here one
+// WARP takes a path of the queue and runs shade()'s whole remaining recursion: closest hit with the 32 lanes
+// working through the ray's stack abreast (crt_traverse.cuh trace_wide_one), then the material evaluation, which is
+// warp-uniform (every lane computes the same values from the same draw counter), then the next ray, until the path
+// ends. Nothing goes back to a queue. The arithmetic per path segment is shade_step and the primitive tests of the
+// wavefront kernels, so radiance values are the same bit for bit.
+template <bool COUNT, bool HAS_SPH>
+__global__ void __launch_bounds__(TP_BLOCK)
+k_tail(RenderParams P, AccelView A, const DMat* __restrict__ mats, const float4* __restrict__ q_in,
+       const uint32_t* __restrict__ n_in_ptr, uint32_t* __restrict__ work_ctr, float4* __restrict__ rad,
+       unsigned long long* __restrict__ counters, uint32_t tail_below)
 {
+    __shared__ uint2 s_stack[(TP_BLOCK / 32) * CRT_WIDE_STACK];
+    const uint32_t n = *n_in_ptr;
+    if (n == 0u || n >= tail_below) return;         // the wavefront kernels took (or take) this queue
+    const uint32_t lane = threadIdx.x & 31u;
+    uint2* stack = s_stack + (threadIdx.x >> 5) * CRT_WIDE_STACK;
+    TraceCounters cnt = {0u, 0u, 0u, 0u, 0u, 0u, 0u};
+    uint32_t n_scatter = 0, n_more = 0;             // warp-uniform: scatter evaluations, rays beyond each path's queued one
+    for (;;) {
+        uint32_t i = 0;
+        if (lane == 0) i = atomicAdd(work_ctr, 1u);
+        i = __shfl_sync(0xffffffffu, i, 0);
+        if (i >= n) break;
+        PathState S;
+        load_path(P, q_in, i, S);                   // one address for the warp: broadcast loads
+        for (;;) {
+            const Hit h = trace_wide_one<COUNT, HAS_SPH>(A, S.o, ray_dir_local(S.d), 0.001f, FLT_MAX, stack, cnt);   // render.h:53
+            v3 L;
+            if (!shade_step<COUNT, HAS_SPH>(P, A, mats, S, h.t, h.k, L, n_scatter)) {
+                if (lane == 0) __stcs(rad + S.path_id, make_float4(L.x, L.y, L.z, 0.0f));
+                break;
+            }
+            n_more++;
+        }
+    }
+    if (lane == 0 && n_more) atomicAdd(counters + CNT_RENDER_RAYS, (unsigned long long)n_more);
+    if (COUNT) {
+        const uint32_t nodes = __reduce_add_sync(0xffffffffu, cnt.nodes);
+        const uint32_t tris = __reduce_add_sync(0xffffffffu, cnt.tris);
+        const uint32_t sph = __reduce_add_sync(0xffffffffu, cnt.spheres);
+        if (lane == 0) {
+            atomicAdd(counters + CNT_NODES, (unsigned long long)nodes);
+            atomicAdd(counters + CNT_TRIS, (unsigned long long)tris);
+            atomicAdd(counters + CNT_SPHERES, (unsigned long long)sph);
+            atomicAdd(counters + CNT_NODE_F, (unsigned long long)nodes);
+            atomicAdd(counters + CNT_TRI_F, (unsigned long long)tris);
+            atomicAdd(counters + CNT_SPH_F, (unsigned long long)sph);
+            atomicAdd(counters + CNT_SCATTERS, (unsigned long long)n_scatter);
+        }
+    }
+}
+
+// Also the slice's tally: every queue entry was one closest-hit query, queue 0 holds the camera samples (the host
+// never reads the queue lengths, so a render call does not have to wait for its launches).
+__global__ void __launch_bounds__(256)
+k_accumulate(RenderParams P, const float4* __restrict__ rad, float* __restrict__ accum, const uint32_t* __restrict__ qcount,
+             int bounces, unsigned long long* __restrict__ counters)
+{
+    if (blockIdx.x == 0 && (int)threadIdx.x < bounces) {
+        const uint32_t q = qcount[threadIdx.x];
+        if (q) atomicAdd(counters + CNT_RENDER_RAYS, (unsigned long long)q);
+        if (threadIdx.x == 0 && q) atomicAdd(counters + CNT_RENDER_PATHS, (unsigned long long)q);
+    }
     const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
     if (slot >= P.n_slots) return;
     int x, y;
@@ -498,49 +562,70 @@ static DCamera to_dcamera(const crt_camera* c)
     return d;
 }
 
+// persistent grid sizes, from the occupancy of one instantiation each (they have near-identical resource needs)
+static void size_grids(crt_ctx* c)
+{
+    if (c->grid_trace) return;
+    int bps = 1, bps_shade = 1, bps_packet = 1, bps_tail = 1;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_trace_queue<false, false>, TP_BLOCK, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps_shade, k_shade<false, false>, RB, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps_packet, k_trace_packet<false, false>, TP_BLOCK, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps_tail, k_tail<false, false>, TP_BLOCK, 0);
+    c->grid_trace = c->sm_count * std::max(1, bps);
+    c->grid_shade = c->sm_count * std::max(1, bps_shade);
+    c->grid_packet = c->sm_count * std::max(1, bps_packet);
+    c->grid_tail = c->sm_count * std::max(1, bps_tail);
+}
+
 template <bool COUNT, bool HAS_SPH>
-static void launch_bounce(crt_ctx* c, crt_lane& L, int b, int grid_trace, int grid_packet, int grid_shade, int grid_wide, const RenderParams& P, const AccelView& A,
+static void launch_bounce(crt_ctx* c, crt_lane& L, int b, const RenderParams& P, const AccelView& A,
                           const float4* q_in, const uint32_t* n_in, uint32_t* work_ctr, float4* q_out, uint32_t* n_out)
 {
-    cudaEventRecord(L.ev_trace[2 * b], L.stream);
-    if (b == 0 && c->packet_primary)   // camera rays: a warp holds the samples of one or two pixels
-        k_trace_packet<COUNT, HAS_SPH><<<grid_packet, TP_BLOCK, 0, L.stream>>>(A, q_in, P.cap, n_in, work_ctr, L.hitbuf.as<float4>(),
-                                                                              c->counters.as<unsigned long long>(), c->packet_primary == 1 ? 1 : 0);
-    else {
-        // the queue length is only known on the device: both kernels are queued and the one the length does not
-        // belong to returns at once (a launch of fewer than wide_below rays is bound by its longest ray)
-        const uint32_t wide_below = (uint32_t)c->wide_below;
-        k_trace_queue<COUNT, HAS_SPH><<<grid_trace, TP_BLOCK, 0, L.stream>>>(A, q_in, P.cap, n_in, work_ctr, L.hitbuf.as<float4>(),
-                                                                             c->counters.as<unsigned long long>(), (uint32_t)c->refill, (uint32_t)c->leaf_thresh, wide_below);
-        if (wide_below > 0u) {
-            k_trace_wide<COUNT, HAS_SPH><<<grid_wide, TP_BLOCK, 0, L.stream>>>(A, q_in, P.cap, n_in, work_ctr + 32, L.hitbuf.as<float4>(),
-                                                                              c->counters.as<unsigned long long>(), wide_below);
-            c->host_counters.launches++;
-        }
-    }
-    cudaEventRecord(L.ev_trace[2 * b + 1], L.stream);
-    if (COUNT && getenv("CRT_TRACE_TIMING")) {   // development aid: longest dependent chain of the launch
+    unsigned long long* counters = c->counters.as<unsigned long long>();
+    const bool packet = b == 0 && c->packet_primary;
+    // the queue length is only known on the device: from the second bounce on, a queue of fewer than tail_below
+    // paths is left alone by the wavefront kernels (they return at once) and finished by k_tail
+    const uint32_t tail_below = b == 0 ? 0u : (uint32_t)c->wide_below;
+    if (c->timing) cudaEventRecord(L.ev_trace[2 * b], L.stream);
+    if (packet)   // camera rays: a warp holds the samples of one or two pixels
+        k_trace_packet<COUNT, HAS_SPH><<<c->grid_packet, TP_BLOCK, 0, L.stream>>>(A, q_in, P.cap, n_in, work_ctr, L.hitbuf.as<float4>(),
+                                                                                 counters, c->packet_primary == 1 ? 1 : 0);
+    else
+        k_trace_queue<COUNT, HAS_SPH><<<c->grid_trace, TP_BLOCK, 0, L.stream>>>(A, q_in, P.cap, n_in, work_ctr, L.hitbuf.as<float4>(),
+                                                                                counters, (uint32_t)c->refill, (uint32_t)c->leaf_thresh, tail_below);
+    if (c->timing) cudaEventRecord(L.ev_trace[2 * b + 1], L.stream);
+    if (COUNT && c->timing && getenv("CRT_TRACE_TIMING")) {   // development aid: longest dependent chain of the launch
         unsigned long long ms = 0;
-        cudaMemcpyAsync(&ms, c->counters.as<unsigned long long>() + CNT_MAX_STEPS, 8, cudaMemcpyDeviceToHost, L.stream);
-        cudaMemsetAsync(c->counters.as<unsigned long long>() + CNT_MAX_STEPS, 0, 8, L.stream);
+        cudaMemcpyAsync(&ms, counters + CNT_MAX_STEPS, 8, cudaMemcpyDeviceToHost, L.stream);
+        cudaMemsetAsync(counters + CNT_MAX_STEPS, 0, 8, L.stream);
         cudaStreamSynchronize(L.stream);
         fprintf(stderr, "[crt] bounce %d: longest ray took %llu traversal steps\n", b, ms);
     }
-    k_shade<COUNT, HAS_SPH><<<grid_shade, RB, 0, L.stream>>>(P, A, c->mats.as<DMat>(), q_in, L.hitbuf.as<float4>(), n_in, q_out,
-                                                             n_out, L.rad.as<float4>(), c->counters.as<unsigned long long>());
+    k_shade<COUNT, HAS_SPH><<<c->grid_shade, RB, 0, L.stream>>>(P, A, c->mats.as<DMat>(), q_in, L.hitbuf.as<float4>(), n_in, q_out,
+                                                                n_out, L.rad.as<float4>(), counters, tail_below);
+    if (tail_below > 0u) {
+        k_tail<COUNT, HAS_SPH><<<c->grid_tail, TP_BLOCK, 0, L.stream>>>(P, A, c->mats.as<DMat>(), q_in, n_in, work_ctr + 32,
+                                                                        L.rad.as<float4>(), counters, tail_below);
+        c->host_counters.launches++;
+    }
 }
 
 // A frame is cut into jobs: sample batches (when all samples of the rank's
 // pixels do not fit CRT_OPT_BATCH_PATHS) x n_lanes slices of the rank's tiles.
 // The slices of one sample batch run concurrently, one per lane (stream): each
 // is the full wavefront loop raygen -> (trace, shade) x bounces -> accumulate
-// over its own queues; slices interleave tile by tile. A slice's last bounces trace a few hundred rays that
-// walk 200-700 dependent steps each - launches that leave the GPU idle when
-// they run alone - and every persistent launch ends with a tail of
-// half-empty SMs; with two slices in flight the other slice's wide launches
-// fill both. Slices own disjoint pixels and a pixel's sample batches stay on
-// one lane in order, so d_accum is summed in the same order for any lane
-// count and the image does not depend on it.
+// over its own queues; slices interleave tile by tile, so one slice's
+// latency-bound last bounces and the drain phase of every persistent launch
+// overlap the other slices' wide launches. Slices own disjoint pixels and a
+// pixel's sample batches stay on one lane in order, so d_accum is summed in
+// the same order for any lane count and the image does not depend on it.
+//
+// Nothing here waits for the device: queue lengths stay on the device (every
+// kernel reads its own), the ray and path totals are tallied by k_accumulate,
+// and the lanes' streams are joined into the context's stream with events, so
+// the call returns as soon as its launches are queued and d_accum is valid in
+// stream order on crt_stream(). Only CRT_OPT_TIMING (per-launch events for the
+// roofline) makes it wait.
 int render_accum(crt_ctx* c, const crt_camera* cam, int nx, int ny, int s0, int s1, int max_depth, int mode,
                  uint64_t seed, int rank, int world, float* d_accum, RenderFinish* finish, cudaEvent_t scene_ready)
 {
@@ -570,17 +655,16 @@ int render_accum(crt_ctx* c, const crt_camera* cam, int nx, int ny, int s0, int 
     if (local_tiles * CRT_TILE * CRT_TILE >= (1ll << 31)) { set_error("crt_render: image too large"); return CRT_ERR_INVALID; }
     P.max_depth = max_depth; P.mode = mode; P.seed = seed; P.seed_key = crt_rng_seed_key(seed);
 
-    CRT_CUDA(cudaEventRecord(c->ev0, st));
+    CRT_CUDA(cudaEventRecord(c->ev_r0, st));
     CRT_CUDA(cudaMemsetAsync(d_accum, 0, (size_t)nx * ny * 3 * sizeof(float), st));
     const int n_samples = s1 - s0;
-    uint64_t total_rays = 0, total_paths = 0;
     float bounce_ms = 0.f, trace_q_ms = 0.f;
     if (local_tiles > 0 && n_samples > 0) {
         // lane l of rank r renders tiles r + world * (l + n_lanes * j): the slices interleave, so they are balanced
         // at most CRT_OPT_LANES, at least 2 M camera samples per slice: below that a frame is launch bound and more
         // launches cost more than the overlap gains (C1, 2.1 M samples in 0.8 ms: 1 slice 0.79 ms, 4 slices 0.91 ms;
         // C3 at 960x540x16, 8.3 M samples: 3.91 ms -> 3.35 ms)
-        const long long want = (local_tiles * CRT_TILE * CRT_TILE * n_samples) / 2000000ll;
+        const long long want = (local_tiles * CRT_TILE * CRT_TILE * n_samples) / c->slice_min_samples;
         const int n_lanes = (int)std::max(1ll, std::min((long long)c->n_lanes, std::min(local_tiles / unit_tiles, want)));
         c->host_counters.lanes = (uint64_t)n_lanes;
         const int sub_world = world * n_lanes;
@@ -606,22 +690,7 @@ int render_accum(crt_ctx* c, const crt_camera* cam, int nx, int ny, int s0, int 
             CRT_CUDA(L.work_ctr.reserve(sizeof(uint32_t) * 64));
             CRT_CUDA(L.hitbuf.reserve(cap * 16));
         }
-
-        int bps = 1, bps_shade = 1;
-        // the instantiations have near-identical resource needs; size the persistent grids from one
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_trace_queue<false, false>, TP_BLOCK, 0);
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps_shade, k_shade<false, false>, RB, 0);
-        int bps_packet = 1;
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps_packet, k_trace_packet<false, false>, TP_BLOCK, 0);
-        if (bps_packet < 1) bps_packet = 1;
-        const int grid_packet = c->sm_count * bps_packet;
-        int bps_wide = 1;
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps_wide, k_trace_wide<false, false>, TP_BLOCK, 0);
-        const int grid_wide = c->sm_count * (bps_wide < 1 ? 1 : bps_wide);
-        if (bps < 1) bps = 1;
-        if (bps_shade < 1) bps_shade = 1;
-        const int grid = c->sm_count * bps;
-        const int grid_shade = c->sm_count * bps_shade;
+        size_grids(c);
         const AccelView A = accel_view(c);
         const bool sph = c->n_sph > 0;
         const int bounces = mode == CRT_SHADE_PATH ? max_depth + 1 : 1;
@@ -648,7 +717,7 @@ int render_accum(crt_ctx* c, const crt_camera* cam, int nx, int ny, int s0, int 
                 const unsigned int rg = (unsigned int)min((size_t)(total + RB - 1) / RB, (size_t)c->sm_count * 32);
                 k_raygen<<<rg, RB, 0, L.stream>>>(PL, L.queue[0].as<float4>(), L.qcount.as<uint32_t>());
                 c->host_counters.launches += 2 + 2 * (uint64_t)bounces;   // raygen, (trace, shade) per bounce, accumulate
-                CRT_CUDA(cudaEventRecord(L.ev_begin, L.stream));
+                if (c->timing) CRT_CUDA(cudaEventRecord(L.ev_begin, L.stream));
                 // ray generation does not read the scene: only the closest-hit launches wait for an upload and refit
                 // queued on another stream (crt_render_frame)
                 if (scene_ready && sb == s0) CRT_CUDA(cudaStreamWaitEvent(L.stream, scene_ready, 0));
@@ -659,15 +728,16 @@ int render_accum(crt_ctx* c, const crt_camera* cam, int nx, int ny, int s0, int 
                     uint32_t* no = L.qcount.as<uint32_t>() + b + 1;
                     uint32_t* wc = L.work_ctr.as<uint32_t>() + b;
                     if (c->count_work) {
-                        if (sph) launch_bounce<true, true>(c, L, b, grid, grid_packet, grid_shade, grid_wide, PL, A, qi, ni, wc, qo, no);
-                        else launch_bounce<true, false>(c, L, b, grid, grid_packet, grid_shade, grid_wide, PL, A, qi, ni, wc, qo, no);
+                        if (sph) launch_bounce<true, true>(c, L, b, PL, A, qi, ni, wc, qo, no);
+                        else launch_bounce<true, false>(c, L, b, PL, A, qi, ni, wc, qo, no);
                     } else {
-                        if (sph) launch_bounce<false, true>(c, L, b, grid, grid_packet, grid_shade, grid_wide, PL, A, qi, ni, wc, qo, no);
-                        else launch_bounce<false, false>(c, L, b, grid, grid_packet, grid_shade, grid_wide, PL, A, qi, ni, wc, qo, no);
+                        if (sph) launch_bounce<false, true>(c, L, b, PL, A, qi, ni, wc, qo, no);
+                        else launch_bounce<false, false>(c, L, b, PL, A, qi, ni, wc, qo, no);
                     }
                 }
-                CRT_CUDA(cudaEventRecord(L.ev_end, L.stream));
-                k_accumulate<<<(PL.n_slots + 255) / 256, 256, 0, L.stream>>>(PL, L.rad.as<float4>(), d_accum);
+                if (c->timing) CRT_CUDA(cudaEventRecord(L.ev_end, L.stream));
+                k_accumulate<<<(PL.n_slots + 255) / 256, 256, 0, L.stream>>>(PL, L.rad.as<float4>(), d_accum, L.qcount.as<uint32_t>(), bounces,
+                                                                            c->counters.as<unsigned long long>());
                 if (finish && P.band && sb + P.s_count >= s1) {
                     // the slice's pixels are final: resolve its rows and start their copy to the caller's buffer while
                     // the other slices still render (rows of tile rows PL.rank, PL.rank + sub_world, ...)
@@ -691,9 +761,10 @@ int render_accum(crt_ctx* c, const crt_camera* cam, int nx, int ny, int s0, int 
                     }
                     finish->done = true;
                 }
-                CRT_CUDA(cudaMemcpyAsync(L.h_counts, L.qcount.p, sizeof(uint32_t) * n_levels, cudaMemcpyDeviceToHost, L.stream));
+                if (c->timing) CRT_CUDA(cudaMemcpyAsync(L.h_counts, L.qcount.p, sizeof(uint32_t) * n_levels, cudaMemcpyDeviceToHost, L.stream));
             }
-            // the queue counts size the statistics and the lanes' buffers are reused by the next sample batch
+            if (!c->timing) continue;
+            // CRT_OPT_TIMING: per-launch durations of this batch (the roofline's denominator)
             float batch_ms = 0.f;
             for (int l = 0; l < n_lanes; l++) {
                 crt_lane& L = c->lane[l];
@@ -709,22 +780,21 @@ int render_accum(crt_ctx* c, const crt_camera* cam, int nx, int ny, int s0, int 
                     if (verbose) fprintf(stderr, "[crt] lane %d bounce %d: %u rays, trace %.3f ms\n", l, b, L.h_counts[b], tms);
                 }
                 if (verbose) fprintf(stderr, "[crt] lane %d: bounces %.3f ms\n", l, bms);
-                total_paths += L.h_counts[0];
-                for (int b = 0; b < bounces; b++) total_rays += L.h_counts[b];
             }
             bounce_ms += batch_ms;
         }
+        // the other lanes' work joins the context's stream: whatever the caller queues there next (a reduce, a
+        // resolve, a copy) is ordered behind the whole frame
+        for (int l = 1; l < n_lanes; l++) {
+            CRT_CUDA(cudaEventRecord(c->lane[l].ev_join, c->lane[l].stream));
+            CRT_CUDA(cudaStreamWaitEvent(st, c->lane[l].ev_join, 0));
+        }
     }
-    CRT_CUDA(cudaEventRecord(c->ev1, st));
-    CRT_CUDA(cudaEventSynchronize(c->ev1));
+    CRT_CUDA(cudaEventRecord(c->ev_r1, st));
     CRT_CUDA(cudaGetLastError());
-    float ms = 0.f;
-    CRT_CUDA(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
-    c->host_counters.render_ms = ms;
+    c->render_ms_pending = true;
     c->host_counters.bounce_ms += bounce_ms;
     c->host_counters.trace_queue_ms += trace_q_ms;
-    c->host_counters.rays += total_rays;
-    c->host_counters.paths += total_paths;
     return CRT_OK;
 }
 

@@ -195,6 +195,8 @@ int launch_trace(crt_ctx* c, const crt_ray* d_rays, size_t n, float t_min, float
         uint32_t* wc = c->work_ctr.as<uint32_t>();
         const uint32_t un = (uint32_t)n;
         if (accel == CRT_ACCEL_LBVH_PACKET) {
+            // the packet's farthest closest hit is reduced over the raw bits of positive distances
+            if (t_min < 0.0f) { set_error("crt_trace: CRT_ACCEL_LBVH_PACKET needs t_min >= 0"); return CRT_ERR_INVALID; }
             int bpp = 1;
             cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bpp, k_trace_lbvh_packet<false, false>, TP_BLOCK, 0);
             const size_t capp = (size_t)c->sm_count * (bpp < 1 ? 1 : bpp);

@@ -156,4 +156,43 @@ inline void build_mesh(World& w, const SceneOptions& o)
     w.lookfrom = vec3(0, 60, 320); w.lookat = vec3(0, 0, 0);
 }
 
+// C4: grid x grid instances of a ~100,000-triangle displaced sphere (pitch 250) over a ground quad, flattened: every
+// instance's translation is added to its vertices (one fp32 addition each, as scenes.c4_instanced does), so the
+// triangles carry identity Transforms and take the plain path of the traversal. The reference's own instancing
+// device - one HitableList per instance under a translated Transform (hitable_list.h:11) - works too (scene.h turns
+// it into a chain of frames) and gives the reference's local-frame hit points instead.
+inline void build_instanced(World& w, const SceneOptions& o, int grid = 10, float pitch = 250.f)
+{
+    const int n_theta = o.n_theta == 1000 ? 500 : o.n_theta, n_phi = o.n_theta == 1000 ? 101 : o.n_phi;
+    std::vector<float> v;
+    std::vector<int> bands;
+    mesh_vertices(n_theta, n_phi, 0.0, v, &bands);
+    Material* even = new Lambertian(new ConstantTexture(vec3(0.7, 0.3, 0.2)));
+    Material* odd = new Metal(vec3(0.8, 0.8, 0.8), 0.1f);
+    Material* ground = new Lambertian(new ConstantTexture(vec3(0.5, 0.5, 0.5)));
+    std::vector<vec3> normals(bands.size());
+    for (size_t t = 0; t < bands.size(); t++) {
+        const vec3 p0(v[9 * t], v[9 * t + 1], v[9 * t + 2]), p1(v[9 * t + 3], v[9 * t + 4], v[9 * t + 5]), p2(v[9 * t + 6], v[9 * t + 7], v[9 * t + 8]);
+        vec3 n = -unit_vector(cross(p1 - p0, p2 - p0));
+        if (!(n[0] == n[0]) || !(n[1] == n[1]) || !(n[2] == n[2])) n = vec3(0, 1, 0);
+        normals[t] = n;
+    }
+    const float off0 = (float)(-(grid - 1) * (double)pitch / 2.0);
+    for (int a = 0; a < grid; a++)
+        for (int b = 0; b < grid; b++) {
+            const vec3 shift((float)(off0 + a * (double)pitch), 0.f, (float)(off0 + b * (double)pitch));
+            for (size_t t = 0; t < bands.size(); t++) {
+                vec3 p[3];
+                for (int k = 0; k < 3; k++) p[k] = vec3(v[9 * t + 3 * k], v[9 * t + 3 * k + 1], v[9 * t + 3 * k + 2]) + shift;
+                w.list.append(new Triangle(p, normals[t], (bands[t] & 1) ? odd : even, false, new Transform(), false));
+            }
+        }
+    const float h = 20000.f, y = -110.f;
+    vec3 q[4] = {vec3(-h, y, -h), vec3(h, y, -h), vec3(h, y, h), vec3(-h, y, h)};
+    vec3 t0[3] = {q[0], q[1], q[2]}, t1[3] = {q[0], q[2], q[3]};
+    w.list.append(new Triangle(t0, vec3(0, -1, 0), ground, false, new Transform(), false));
+    w.list.append(new Triangle(t1, vec3(0, -1, 0), ground, false, new Transform(), false));
+    w.lookfrom = vec3(0, 900, 2600); w.lookat = vec3(0, 0, 0);
+}
+
 }  // namespace crt_host

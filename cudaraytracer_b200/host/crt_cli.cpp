@@ -5,6 +5,7 @@
 //   crt_cli --scene bunny --obj objects/small_bunny.obj --out out/picture_
 //   crt_cli --scene spheres --nx 1200 --ny 800 --spp 64 --mode path
 //   crt_cli --scene mesh --frames 4 --animate --csv output.csv
+//   crt_cli --scene instanced --gpus 8 --nx 3840 --ny 2160 --spp 64 --mode path      (one host thread per GPU)
 //
 // Per frame it does what renderBVHAnimation does (core/render.h:191-237):
 // update the vertices, refit the BVH, render, copy back, write
@@ -19,6 +20,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "builtin_scenes.h"
@@ -32,7 +34,7 @@ namespace {
 struct Options {
     std::string scene = "bunny", out = "picture_", csv, mode = "lambert";
     crt_host::SceneOptions sc;
-    int nx = 1024, ny = 512, spp = 4, depth = 8, frames = 1, device = 0;
+    int nx = 1024, ny = 512, spp = 4, depth = 8, frames = 1, device = 0, gpus = 1;
     bool animate = false, quiet = false, overlap = false;
     std::string pose = "vertices";   // --pose vertices|points|bones: the form the per-frame geometry update takes
 };
@@ -66,6 +68,7 @@ Options parse(int argc, char** argv)
         else if (a == "--depth") o.depth = std::atoi(val());
         else if (a == "--frames") o.frames = std::atoi(val());
         else if (a == "--device") o.device = std::atoi(val());
+        else if (a == "--gpus") o.gpus = std::atoi(val());
         else if (a == "--segments") { o.sc.n_theta = std::atoi(val()); o.sc.n_phi = o.sc.n_theta / 2; }
         else if (a == "--seed") o.sc.seed = std::strtoull(val(), nullptr, 10);
         else if (a == "--animate") o.animate = true;
@@ -76,12 +79,79 @@ Options parse(int argc, char** argv)
             std::printf("usage: crt_cli [--scene bunny|spheres|mesh] [--obj FILE] [--camera framed|reference] [--nx N --ny N]\n"
                         "               [--spp N] [--depth N] [--mode path|lambert|normal] [--seed S] [--frames N]\n"
                         "               [--animate [--overlap] [--pose vertices|points|bones]]\n"
-                        "               [--segments N] [--out PREFIX] [--csv FILE] [--device D] [--quiet]\n");
+                        "               [--segments N] [--out PREFIX] [--csv FILE] [--device D] [--gpus N] [--quiet]\n");
             std::exit(0);
         } else die("unknown flag " + a);
     }
-    if (o.nx <= 0 || o.ny <= 0 || o.spp <= 0 || o.frames <= 0) die("nx, ny, spp and frames must be positive");
+    if (o.nx <= 0 || o.ny <= 0 || o.spp <= 0 || o.frames <= 0 || o.gpus <= 0) die("nx, ny, spp, frames and gpus must be positive");
     return o;
+}
+
+void build_world(crt_host::World& w, const Options& o)
+{
+    if (o.scene == "bunny") crt_host::build_bunny(w, o.sc);
+    else if (o.scene == "spheres") crt_host::build_spheres(w, o.sc);
+    else if (o.scene == "mesh") crt_host::build_mesh(w, o.sc);
+    else if (o.scene == "instanced") crt_host::build_instanced(w, o.sc);
+    else die("unknown --scene " + o.scene);
+}
+
+// --gpus N: one host thread per GPU (devices device .. device + N - 1), each with its own context; thread 0 plays
+// main(): it builds the scene, the others receive it over NVLink (crt_scene_broadcast), every GPU builds the same
+// LBVH and renders the tiles it owns of each frame, and the partial framebuffers are summed onto GPU 0
+// (crt_render_dist), which writes the PNG. With --animate every thread computes the frame's pose itself.
+int run_multi(const Options& o, int mode)
+{
+    const int world = o.gpus;
+    unsigned char id[CRT_COMM_ID_BYTES];
+    crt_host::check(crt_comm_unique_id(id), "crt_comm_unique_id");
+    std::vector<std::string> errors((size_t)world);
+    std::vector<crt_host::FrameTiming> rows;
+    auto rank_main = [&](int rank) {
+        try {
+            crt_host::Renderer r(o.device + rank);
+            crt_host::World w;
+            build_world(w, o);                                        // the camera literals; only rank 0 uploads the geometry
+            if (rank == 0) r.set_world(w.list);
+            r.comm_init(id, rank, world);
+            r.scene_broadcast(0);
+            double t0 = now_s();
+            r.create_BVHfromList();
+            const double build_s = now_s() - t0;
+            Camera cam(w.lookfrom, w.lookat, vec3(0, 1, 0), w.vfov, float(o.nx) / float(o.ny), w.aperture, w.focus);
+            std::vector<vec3> colorBuffer(rank == 0 ? (size_t)o.nx * o.ny : 0);
+            std::vector<float> verts;
+            const bool moving = o.animate && o.scene == "mesh";
+            for (int frame = 0; frame < o.frames; frame++) {
+                double update_s = 0.0;
+                if (moving) {
+                    t0 = now_s();
+                    crt_host::mesh_vertices(o.sc.n_theta, o.sc.n_phi, 0.3 * frame, verts, nullptr);
+                    r.update_vertices(verts.data(), 0, verts.size() / 9);
+                    r.Update_BVH();
+                    update_s = now_s() - t0;
+                }
+                t0 = now_s();
+                r.render_dist(rank == 0 ? colorBuffer.data() : nullptr, cam, o.nx, o.ny, o.spp, o.depth, mode, o.sc.seed + (uint64_t)frame);
+                const double render_s = now_s() - t0;
+                if (rank == 0) {
+                    if (!WritePng(o.nx, o.ny, frame, colorBuffer.data(), o.out.c_str())) throw std::runtime_error("cannot write " + o.out + std::to_string(frame) + ".png");
+                    rows.push_back({frame, render_s, update_s, frame == 0 ? build_s : 0.0});
+                    if (!o.quiet) std::printf("frame %d on %d GPUs: rendering %g s, update %g s\n", frame, world, render_s, update_s);
+                }
+            }
+        } catch (const std::exception& e) {
+            errors[(size_t)rank] = e.what();
+        }
+    };
+    std::vector<std::thread> threads;
+    for (int rank = 1; rank < world; rank++) threads.emplace_back(rank_main, rank);
+    rank_main(0);
+    for (auto& t : threads) t.join();
+    for (int rank = 0; rank < world; rank++)
+        if (!errors[(size_t)rank].empty()) die("GPU " + std::to_string(o.device + rank) + ": " + errors[(size_t)rank]);
+    if (!o.csv.empty() && !crt_host::write_csv(o.csv, rows)) die("cannot write " + o.csv);
+    return 0;
 }
 
 }  // namespace
@@ -93,12 +163,12 @@ int main(int argc, char** argv)
     if (o.mode == "path") mode = CRT_SHADE_PATH;
     else if (o.mode == "normal") mode = CRT_SHADE_NORMAL;
     else if (o.mode != "lambert") die("unknown --mode " + o.mode);
+    if (o.gpus > 1) {
+        try { return run_multi(o, mode); } catch (const std::exception& e) { die(e.what()); }
+    }
     try {
         crt_host::World w;
-        if (o.scene == "bunny") crt_host::build_bunny(w, o.sc);
-        else if (o.scene == "spheres") crt_host::build_spheres(w, o.sc);
-        else if (o.scene == "mesh") crt_host::build_mesh(w, o.sc);
-        else die("unknown --scene " + o.scene);
+        build_world(w, o);
 
         crt_host::Renderer r(o.device);
         r.set_world(w.list);

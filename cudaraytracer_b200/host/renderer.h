@@ -15,6 +15,8 @@
 //   render<<<>>> + D2H copy     render.h:105,222-226   render(colorBuffer, ...)    crt_render
 //   the loop body as a whole    render.h:206-233       render_frame(...)           crt_render_frame (steps overlapped)
 //   WritePng                    render.h:135           WritePng (png_out.h)        -
+//   (one GPU only in the reference)                    comm_init / scene_broadcast crt_comm_init / crt_scene_broadcast
+//                                                      render_dist(colorBuffer...) crt_render_dist (tiles per GPU + ncclReduce)
 //   StopWatch + writeCSV        swatch.h, CSVWriter.h  counters(), write_csv()     crt_get_counters
 //
 // Errors: the reference prints and exits (core/deviceManage.h:3-17). The C ABI
@@ -125,6 +127,21 @@ public:
     void pose_async(int pose_kind, const float* pose, size_t first, size_t n)
     {
         check(crt_scene_pose_async(ctx_, pose_kind, pose, first, n), "crt_scene_pose_async");
+    }
+
+    // Several GPUs, one Renderer (context) per GPU, each driven by its own host thread or process: rank 0 draws the
+    // id (crt_comm_unique_id) and hands it to the others; comm_init is collective. scene_broadcast ships rank 0's
+    // uploaded scene to the other GPUs over NVLink; every rank then calls create_BVHfromList. render_dist renders
+    // this rank's tiles of the frame, sums the partial framebuffers onto rank 0 (ncclReduce) and, there, resolves and
+    // copies the image into colorBuffer (ignored, may be null, on the other ranks).
+    void comm_init(const void* id, int rank, int world) { check(crt_comm_init(ctx_, id, rank, world), "crt_comm_init"); }
+    void scene_broadcast(int root = 0) { check(crt_scene_broadcast(ctx_, root), "crt_scene_broadcast"); }
+    void render_dist(vec3* colorBuffer, const Camera& camera, int nx, int ny, int samples, int max_depth,
+                     int shade_mode = CRT_SHADE_LAMBERT, uint64_t seed = 0)
+    {
+        const crt_camera cam = camera.to_crt();
+        check(crt_render_dist(ctx_, &cam, nx, ny, samples, max_depth, shade_mode, seed, colorBuffer ? &colorBuffer[0].e[0] : nullptr),
+              "crt_render_dist");
     }
 
     // (*world)->hit for a batch of rays (render.h:53).

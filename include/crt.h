@@ -112,10 +112,15 @@ typedef enum {
     CRT_OPT_LANES = 7,      /* render: at most 1..4 slices of the frame in flight on their own streams (default 4; a slice is
                              * never smaller than 2 M camera samples), so one slice's
                              * latency-bound last bounces overlap the other's wide launches; images do not depend on it */
-    CRT_OPT_WIDE_BELOW = 9, /* render: a bounce with fewer rays than this (default 32768) is traced one WARP per ray, the lanes
-                             * working through the ray's stack 32 entries abreast, because so small a launch is bound by
-                             * its longest ray; 0: always one ray per lane. Hits and images do not depend on it */
+    CRT_OPT_WIDE_BELOW = 9, /* render: once a bounce's queue holds fewer paths than this (default 32768) one launch carries them all to
+                             * termination, one WARP per path (closest hits with the lanes working through the ray's stack 32 entries
+                             * abreast, then the material, then the next ray), because launches that small are bound by their longest
+                             * ray and by launch latency; 0: every bounce is a wavefront launch. Images do not depend on it */
     CRT_OPT_BUILDER = 8,    /* tree topology of crt_accel_build: CRT_BUILDER_LBVH (default) or CRT_BUILDER_PLOC; hits and images do not depend on it */
+    CRT_OPT_TIMING = 10,    /* 1: crt_render* records an event pair around every closest-hit launch and waits for the device, so that
+                             * crt_counters.trace_queue_ms / bounce_ms are maintained (the roofline's denominator); 0 (default): render
+                             * calls only queue work */
+    CRT_OPT_SLICE_MIN = 11, /* tuning: fewest camera samples a slice of a frame may hold (default 2,000,000; see CRT_OPT_LANES) */
     CRT_OPT_REFILL = 4      /* tuning: idle lanes per warp that trigger a refill from the ray queue, 1..32 (default 12) */
 } crt_option;
 
@@ -140,8 +145,8 @@ typedef struct {
     float    refit_ms;        /* last crt_accel_refit */
     float    render_ms;       /* last crt_render* call, device time */
     float    trace_ms;        /* last crt_trace (host-buffer form), device time of the kernel */
-    float    bounce_ms;       /* device time of all trace+shade launches since crt_reset_counters */
-    float    trace_queue_ms;  /* of which the closest-hit kernels (k_trace_packet, k_trace_queue) alone */
+    float    bounce_ms;       /* CRT_OPT_TIMING only: device time of all trace+shade launches since crt_reset_counters */
+    float    trace_queue_ms;  /* CRT_OPT_TIMING only: of which the closest-hit kernels (k_trace_packet, k_trace_queue) alone */
     /* records fetched, the memory side of the roofline: equal to the tests above where
      * every ray walks its own stack; in the packet kernel (camera rays) one fetch serves
      * the <= 32 rays of a packet, while each ray still executes the test */
@@ -273,7 +278,8 @@ int crt_render_frame_pose(crt_ctx* ctx, int pose_kind, const float* pose, size_t
  * asynchronous). Needs a built acceleration structure. */
 int crt_scene_pose_async(crt_ctx* ctx, int pose_kind, const float* pose, size_t first, size_t n);
 
-/* Multi-GPU building blocks (device pointers, asynchronous on crt_stream()).
+/* Multi-GPU building blocks (device pointers, asynchronous on crt_stream(): the calls return once their launches
+ * are queued, and d_accum / d_rgb are valid in stream order there).
  * crt_render_accum_device adds nothing to d_accum: it overwrites it with, per
  * pixel this part owns, the sum over samples [sample_begin, sample_end) in
  * sample order, and 0 elsewhere. crt_resolve_device applies
@@ -285,6 +291,32 @@ int crt_resolve_device(crt_ctx* ctx, const float* d_accum, size_t n_pixels, int 
 /* WritePng's conversion (core/render.h:137-146) on the GPU: vertical flip,
  * char(255.99*c), alpha 255. d_rgba8: nx*ny*4 bytes, row 0 at the top. */
 int crt_pack_rgba8_device(crt_ctx* ctx, const float* d_rgb, int nx, int ny, uint8_t* d_rgba8);
+
+/* ---- several GPUs: one context per GPU, one communicator across them ----
+ * The reference drives a single GPU (kernel.cu:41-111); this is the exchange step of the sharded path. Ranks may be
+ * threads of one process (crt_cli --gpus N) or one process per GPU (torchrun). NCCL is loaded at run time
+ * (libnccl.so.2); without it these calls fail with CRT_ERR_STATE and nothing else changes. All collectives are
+ * issued on crt_stream() and every rank of the communicator must make the same call.
+ *   crt_comm_unique_id   rank 0 creates the 128-byte id and hands it to every rank (any transport)
+ *   crt_comm_init        collective; gives the context its rank
+ *   crt_scene_broadcast  the scene uploaded on `root` travels to all ranks over NVLink (ncclBroadcast per SoA
+ *                        buffer); each rank then calls crt_accel_build - the build is deterministic, so all trees agree
+ *   crt_reduce_accum_device  sum of the ranks' accumulators onto `root`, in place there. With the tile partition
+ *                        (crt_render_accum_device(rank, world)) each pixel is non-zero on one rank: the sum is exact
+ *   crt_gather_device    rank r's `bytes` land at d_recv + r * bytes on `root` (hit records of a crt_trace batch
+ *                        split across ranks)
+ *   crt_render_dist      one frame: every rank renders its tiles, reduce, rank 0 resolves and copies the image to
+ *                        rgb_out (may be NULL elsewhere); bit-identical to crt_render on one GPU */
+#define CRT_COMM_ID_BYTES 128
+int crt_comm_unique_id(void* id_out);
+int crt_comm_init(crt_ctx* ctx, const void* id, int rank, int world);
+int crt_comm_destroy(crt_ctx* ctx);
+int crt_comm_info(crt_ctx* ctx, int* rank, int* world, int* nccl_version);
+int crt_scene_broadcast(crt_ctx* ctx, int root);
+int crt_reduce_accum_device(crt_ctx* ctx, float* d_accum, size_t n_floats, int root);
+int crt_gather_device(crt_ctx* ctx, const void* d_send, size_t bytes, void* d_recv, int root);
+int crt_render_dist(crt_ctx* ctx, const crt_camera* cam, int nx, int ny, int spp, int max_depth, int shade_mode,
+                    uint64_t seed, float* rgb_out);
 
 /* ---- timing and work counters: replaces StopWatch + CSV
  *      (swatch.h:4-18, Loader/CSVWriter.h:8-32) ---- */

@@ -104,6 +104,19 @@ class Scene:
         """Reference BVHNode build (ref only). Returns seconds."""
         return self.lib._fn("bvh_build")(self.h, int(seed))
 
+    def use_bvh(self, flag=True):
+        """ref only: ref_render goes through the reference's BVHNode (after bvh_build) instead of the list scan."""
+        return bool(self.lib._fn("scene_use_bvh")(self.h, 1 if flag else 0))
+
+    def bvh_stats(self, rays, t_min=0.001, t_max=3.4028234663852886e38):
+        """ref only: (box tests per ray, primitives handed to leaf scans per ray) of the reference's BVHNode walk."""
+        rays = np.ascontiguousarray(rays, dtype=np.float32).reshape(-1, 6)
+        a, b = C.c_uint64(0), C.c_uint64(0)
+        r = self.lib._fn("bvh_stats")(self.h, rays, rays.shape[0], float(t_min), float(t_max), C.byref(a), C.byref(b))
+        assert r == 0, "bvh_stats needs bvh_build first"
+        n = max(1, rays.shape[0])
+        return a.value / n, b.value / n
+
     def trace(self, rays, t_min=0.001, t_max=3.4028234663852886e38, use_bvh=False, want_pn=False):
         rays = np.ascontiguousarray(rays, dtype=np.float32).reshape(-1, 6)
         n = rays.shape[0]
@@ -190,6 +203,10 @@ class OracleLib:
             f("bvh_build").argtypes = [vp, C.c_uint64]
             f("bvh_refit").restype = C.c_double
             f("bvh_refit").argtypes = [vp]
+            f("scene_use_bvh").restype = C.c_int
+            f("scene_use_bvh").argtypes = [vp, C.c_int]
+            f("bvh_stats").restype = C.c_int
+            f("bvh_stats").argtypes = [vp, _f32p, C.c_size_t, C.c_float, C.c_float, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
 
     # ---- functions ----
     def num_threads(self):

@@ -104,6 +104,7 @@ struct RefScene {
     BVHNode* bvh = nullptr;
     Hitable** bvh_storage = nullptr;
     int d1 = 1;
+    int use_bvh = 0;   // ref_render goes through the reference's BVHNode instead of the list scan
 };
 
 Transform* identity_transform() { return new Transform(vec3(0), vec3(0), vec3(1)); }
@@ -318,6 +319,45 @@ double ref_bvh_refit(void* h)
     return std::chrono::duration<double>(t1 - t0).count();
 }
 
+// Which accelerator ref_render uses: 0 = HitableList scan (the parity oracle), 1 = the reference's shipping BVHNode
+// (kernel.cu:24-39 renders through it; needs ref_bvh_build first). Returns the setting in force.
+int ref_scene_use_bvh(void* h, int flag)
+{
+    RefScene* s = (RefScene*)h;
+    s->use_bvh = (flag && s->bvh) ? 1 : 0;
+    return s->use_bvh;
+}
+
+// Statistics of the reference's BVHNode traversal (hitable/bvh.h:160-190 with Hitable::hit, hitable/hitable.h:29-38)
+// for n rays: nodes whose box was tested and primitives handed to a leaf's list scan. The walk below restates the
+// control flow only to COUNT; it calls the reference's own Transform::TransformRay and AABB::hit, and like the
+// reference it descends into both children and never shrinks t_max.
+static void bvh_count(BVHNode* node, const Ray& r, float t_min, float t_max, uint64_t& nodes, uint64_t& prims)
+{
+    Ray tr = node->transform->TransformRay(r);
+    nodes++;
+    if (!node->box.hit(tr, t_min, t_max)) return;
+    if (node->isLeaf) { prims += (uint64_t)node->childList->list_size; return; }
+    bvh_count(node->left, tr, t_min, t_max, nodes, prims);
+    bvh_count(node->right, tr, t_min, t_max, nodes, prims);
+}
+
+int ref_bvh_stats(void* h, const float* rays, size_t n, float t_min, float t_max, uint64_t* nodes_out, uint64_t* prims_out)
+{
+    RefScene* s = (RefScene*)h;
+    if (!s->bvh) return -1;
+    uint64_t nodes = 0, prims = 0;
+#pragma omp parallel for schedule(dynamic, 64) reduction(+ : nodes, prims)
+    for (long long i = 0; i < (long long)n; i++) {
+        const float* q = rays + 6 * i;
+        Ray r(vec3(q[0], q[1], q[2]), vec3(q[3], q[4], q[5]), 0.f);
+        bvh_count(s->bvh, r, t_min, t_max, nodes, prims);
+    }
+    if (nodes_out) *nodes_out = nodes;
+    if (prims_out) *prims_out = prims;
+    return 0;
+}
+
 // Closest hit for n rays through (*world)->hit (core/render.h:53). rays: n x 6
 // floats (origin, direction). use_bvh selects the reference BVHNode instead of
 // the list scan. Outputs may be NULL. Returns seconds spent.
@@ -413,7 +453,7 @@ double ref_render(void* h, const float* cam22, int nx, int ny, int ns, int max_d
 {
     RefScene* s = (RefScene*)h;
     if (!s->world) return -1;
-    Hitable* world_ptr = s->world;
+    Hitable* world_ptr = (s->use_bvh && s->bvh) ? (Hitable*)s->bvh : (Hitable*)s->world;
     Hitable** world = &world_ptr;
     Camera cam = camera_from(cam22);
     if (y_step < 1) y_step = 1;

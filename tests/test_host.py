@@ -228,13 +228,16 @@ def test_bench_reference_arm_contract(tmp_path):
     """`bench.py --impl reference` prints one JSON line with the agreed keys
     (run here on a tiny budget by monkey-patching nothing: just 1 step)."""
     import json
-    env = dict(os.environ, CRT_BENCH_REF_BUDGET="2")
+    env = dict(os.environ, CRT_BENCH_REF_BUDGET="2", CRT_BENCH_C3_SEGMENTS="300")   # 89 k triangles: the BVHNode build takes 1 s, not 25
     out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0"],
                          capture_output=True, text=True, env=env, timeout=600)
     assert out.returncode == 0, out.stderr[-2000:]
     line = json.loads(out.stdout.strip().splitlines()[-1])
     assert line["impl"] == "reference" and line["metric"] == "Mrays/s" and line["value"] > 0
     assert line["cpu_baseline"]["kind"] in ("reference", "port") and line["cpu_baseline"]["cores"] >= 1
+    if line["cpu_baseline"]["kind"] == "reference":      # the reference's shipping accelerator, build time reported beside it
+        assert "BVHNode" in line["cpu_baseline"]["accel"] and line["cpu_baseline"]["bvh_build_s"] > 0
+        assert line["cpu_baseline"]["box_tests_per_camera_ray"] > 1
     assert line["e2e"]["h2d_bytes_per_step"] == 0
 
 
