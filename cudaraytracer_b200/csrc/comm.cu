@@ -172,7 +172,8 @@ int crt_scene_broadcast(crt_ctx* c, int root)
     if (r != CRT_OK) return r;
     if (root < 0 || root >= c->comm_world) { set_error("crt_scene_broadcast: bad root %d", root); return CRT_ERR_INVALID; }
     if (c->pose_pending) { set_error("crt_scene_broadcast: a pose is still queued (crt_sync first)"); return CRT_ERR_STATE; }
-    unsigned long long head[8] = {c->n_tri, c->n_sph, c->n_mats, c->idx_first, c->n_idx_tri, c->n_points, c->n_frames, 0ull};
+    unsigned long long head[10] = {c->n_tri, c->n_sph, c->n_mats, c->idx_first, c->n_idx_tri, c->n_points, c->n_frames, c->n_rect,
+                                   c->tri_has_chain ? 1ull : 0ull, c->sph_has_chain ? 1ull : 0ull};
     DevBuf hb;
     CRT_CUDA(hb.reserve(sizeof head));
     if (c->comm_rank == root) CRT_CUDA(cudaMemcpyAsync(hb.p, head, sizeof head, cudaMemcpyHostToDevice, c->stream));
@@ -184,7 +185,7 @@ int crt_scene_broadcast(crt_ctx* c, int root)
     }
     hb.release();
     if (r != CRT_OK) return r;
-    const size_t n_tri = head[0], n_sph = head[1], n_mats = head[2], n_idx = head[4], n_frames = head[6];
+    const size_t n_tri = head[0], n_sph = head[1], n_mats = head[2], n_idx = head[4], n_frames = head[6], n_rect = head[7];
     if ((r = bcast(c, c->mats, n_mats * sizeof(DMat), root)) != CRT_OK) return r;
     if ((r = bcast(c, c->tri_in, n_tri * 48, root)) != CRT_OK) return r;
     if ((r = bcast(c, c->tri_mat, n_tri * 4, root)) != CRT_OK) return r;
@@ -194,13 +195,18 @@ int crt_scene_broadcast(crt_ctx* c, int root)
     if ((r = bcast(c, c->sph_id, n_sph * 4, root)) != CRT_OK) return r;
     if ((r = bcast(c, c->tri_idx, n_idx * 12, root)) != CRT_OK) return r;
     if ((r = bcast(c, c->frames, n_frames * sizeof(DFrame), root)) != CRT_OK) return r;
-    if ((r = bcast(c, c->tri_frame, n_frames ? n_tri * 4 : 0, root)) != CRT_OK) return r;
-    if ((r = bcast(c, c->sph_frame, n_frames ? n_sph * 4 : 0, root)) != CRT_OK) return r;
+    if ((r = bcast(c, c->tri_frame, head[8] ? n_tri * 4 : 0, root)) != CRT_OK) return r;
+    if ((r = bcast(c, c->sph_frame, head[9] ? n_sph * 4 : 0, root)) != CRT_OK) return r;
+    if ((r = bcast(c, c->rect_mat, n_rect * 4, root)) != CRT_OK) return r;
+    if ((r = bcast(c, c->rect_id, n_rect * 4, root)) != CRT_OK) return r;
+    if ((r = bcast(c, c->rect_frame, n_rect * 4, root)) != CRT_OK) return r;
     CRT_CUDA(cudaStreamSynchronize(c->stream));
     if (c->comm_rank != root) {
         c->n_tri = n_tri; c->n_sph = n_sph; c->n_mats = n_mats;
         c->idx_first = head[3]; c->n_idx_tri = n_idx; c->n_points = head[5];
         c->n_frames = n_frames;
+        c->n_rect = n_rect;
+        c->tri_has_chain = head[8] != 0; c->sph_has_chain = head[9] != 0;
         c->n_parts = 0;
         c->accel_valid = false;
     }

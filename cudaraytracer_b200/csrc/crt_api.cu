@@ -200,7 +200,7 @@ void crt_destroy(crt_ctx* c)
                       &c->keys[0], &c->keys[1], &c->vals[0], &c->vals[1], &c->hist, &c->nodes, &c->recs,
                       &c->child, &c->parent, &c->leaf_parent, &c->range, &c->node_box, &c->leaf_box, &c->flags,
                       &c->bounds, &c->depth_out, &c->ploc_box[0], &c->ploc_box[1], &c->ploc_nn, &c->ploc_tmp, &c->ploc_blk, &c->work_ctr, &c->accum, &c->rgb,
-                      &c->rays_tmp, &c->hits_tmp, &c->counters, &c->rest, &c->part_id, &c->part_T, &c->tri_idx, &c->node_cone, &c->frames, &c->tri_frame, &c->sph_frame};
+                      &c->rays_tmp, &c->hits_tmp, &c->counters, &c->rest, &c->part_id, &c->part_T, &c->tri_idx, &c->node_cone, &c->frames, &c->tri_frame, &c->sph_frame, &c->rect_mat, &c->rect_id, &c->rect_frame};
     for (DevBuf* b : bufs) b->release();
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
@@ -335,6 +335,7 @@ int crt_scene_set_triangles(crt_ctx* c, const float* tri, const uint32_t* mat_id
     if ((r = upload_ids(c->tri_id, prim_id, n, 0u, c->stream)) != CRT_OK) return r;
     CRT_CUDA(cudaStreamSynchronize(c->stream));
     c->n_tri = n;
+    c->tri_has_chain = false;
     c->n_parts = 0;
     c->n_idx_tri = 0;
     c->n_points = 0;
@@ -361,8 +362,99 @@ int crt_scene_set_spheres(crt_ctx* c, const float* sph, const uint32_t* mat_id, 
     if ((r = upload_ids(c->sph_id, prim_id, n, (uint32_t)c->n_tri, c->stream)) != CRT_OK) return r;
     CRT_CUDA(cudaStreamSynchronize(c->stream));
     c->n_sph = n;
+    c->sph_has_chain = false;
     c->sph_id_default = prim_id == nullptr;
     c->sph_id_first = (uint32_t)c->n_tri;
+    c->accel_valid = false;
+    return CRT_OK;
+}
+
+// ---- chains of Transforms and rectangles ----
+static int check_chains(const crt_ctx* c, const uint32_t* chain, size_t n, bool need, const char* who)
+{
+    for (size_t i = 0; i < n; i++) {
+        const uint32_t first = chain[i] >> 8, count = chain[i] & 255u;
+        if (chain[i] == 0u && !need) continue;
+        if (count == 0u || (size_t)first + count > c->n_frames) {
+            set_error("%s: primitive %zu names frames [%u, %u) of %zu", who, i, first, first + count, c->n_frames);
+            return CRT_ERR_INVALID;
+        }
+    }
+    return CRT_OK;
+}
+
+int crt_scene_set_frames(crt_ctx* c, const crt_frame* frames, size_t n)
+{
+    CRT_CHECK_SETTLED(c);
+    if (n > 0 && !frames) { set_error("crt_scene_set_frames: null table"); return CRT_ERR_INVALID; }
+    if (n >= (1u << 24)) { set_error("crt_scene_set_frames: at most 2^24 frames"); return CRT_ERR_INVALID; }
+    std::vector<DFrame> d(n);
+    for (size_t i = 0; i < n; i++) {
+        memcpy(d[i].m, frames[i].rows, sizeof d[i].m);
+        d[i].px = frames[i].position[0]; d[i].py = frames[i].position[1]; d[i].pz = frames[i].position[2];
+        d[i].has_rot = frames[i].has_rotation ? 1u : 0u;
+        d[i].pad[0] = d[i].pad[1] = d[i].pad[2] = 0u;
+    }
+    int r = upload(c->frames, d.data(), n * sizeof(DFrame), c->stream);
+    if (r != CRT_OK) return r;
+    CRT_CUDA(cudaStreamSynchronize(c->stream));
+    c->n_frames = n;
+    // chains name frames by number: a new table invalidates them
+    c->tri_has_chain = c->sph_has_chain = false;
+    c->n_rect = 0;
+    c->accel_valid = false;
+    return CRT_OK;
+}
+
+int crt_scene_set_triangle_chains(crt_ctx* c, const uint32_t* chain, size_t n)
+{
+    CRT_CHECK_SETTLED(c);
+    if (!chain || n == 0) { c->tri_has_chain = false; c->accel_valid = false; return CRT_OK; }
+    if (n != c->n_tri) { set_error("crt_scene_set_triangle_chains: %zu chains for %zu triangles", n, c->n_tri); return CRT_ERR_INVALID; }
+    int r = check_chains(c, chain, n, false, "crt_scene_set_triangle_chains");
+    if (r != CRT_OK) return r;
+    if ((r = upload(c->tri_frame, chain, n * 4, c->stream)) != CRT_OK) return r;
+    CRT_CUDA(cudaStreamSynchronize(c->stream));
+    bool any = false;
+    for (size_t i = 0; i < n && !any; i++) any = chain[i] != 0u;
+    c->tri_has_chain = any;
+    c->accel_valid = false;
+    return CRT_OK;
+}
+
+int crt_scene_set_sphere_chains(crt_ctx* c, const uint32_t* chain, size_t n)
+{
+    CRT_CHECK_SETTLED(c);
+    if (!chain || n == 0) { c->sph_has_chain = false; c->accel_valid = false; return CRT_OK; }
+    if (n != c->n_sph) { set_error("crt_scene_set_sphere_chains: %zu chains for %zu spheres", n, c->n_sph); return CRT_ERR_INVALID; }
+    int r = check_chains(c, chain, n, false, "crt_scene_set_sphere_chains");
+    if (r != CRT_OK) return r;
+    if ((r = upload(c->sph_frame, chain, n * 4, c->stream)) != CRT_OK) return r;
+    CRT_CUDA(cudaStreamSynchronize(c->stream));
+    bool any = false;
+    for (size_t i = 0; i < n && !any; i++) any = chain[i] != 0u;
+    c->sph_has_chain = any;
+    c->accel_valid = false;
+    return CRT_OK;
+}
+
+int crt_scene_set_rectangles(crt_ctx* c, const uint32_t* chain, const uint8_t* flip_normal, const uint32_t* mat_id,
+                             const uint32_t* prim_id, size_t n)
+{
+    CRT_CHECK_SETTLED(c);
+    if (n == 0) { c->n_rect = 0; c->accel_valid = false; return CRT_OK; }
+    if (!chain || !prim_id) { set_error("crt_scene_set_rectangles: a rectangle needs its chain (it is the unit square of a frame) and its id"); return CRT_ERR_INVALID; }
+    if (n >= (1ull << 28)) { set_error("crt_scene_set_rectangles: too many rectangles"); return CRT_ERR_INVALID; }
+    int r = check_mat_ids(c, mat_id, n, "crt_scene_set_rectangles");
+    if (r != CRT_OK) return r;
+    if ((r = check_chains(c, chain, n, true, "crt_scene_set_rectangles")) != CRT_OK) return r;
+    std::vector<uint32_t> m(n);
+    for (size_t i = 0; i < n; i++) m[i] = (mat_id ? mat_id[i] : 0u) | ((flip_normal && flip_normal[i]) ? CRT_RECT_FLIP : 0u);
+    if ((r = upload(c->rect_mat, m.data(), n * 4, c->stream)) != CRT_OK) return r;
+    if ((r = upload(c->rect_id, prim_id, n * 4, c->stream)) != CRT_OK) return r;
+    if ((r = upload(c->rect_frame, chain, n * 4, c->stream)) != CRT_OK) return r;
+    CRT_CUDA(cudaStreamSynchronize(c->stream));
+    c->n_rect = n;
     c->accel_valid = false;
     return CRT_OK;
 }
@@ -448,7 +540,7 @@ int crt_scene_update_points(crt_ctx* c, const float* points, size_t n_points)
 int crt_scene_pose_async(crt_ctx* c, int pose_kind, const float* pose, size_t first, size_t n)
 {
     CRT_CHECK_SETTLED(c);
-    if (!c->accel_valid || c->n_prims != (uint32_t)(c->n_tri + c->n_sph)) {
+    if (!c->accel_valid || c->n_prims != (uint32_t)(c->n_tri + c->n_sph + c->n_rect)) {
         set_error("crt_scene_pose_async: call crt_accel_build first (a pose only refits)");
         return CRT_ERR_STATE;
     }
@@ -603,7 +695,7 @@ int crt_render_frame_pose(crt_ctx* c, int pose_kind, const float* pose, size_t f
     CRT_CHECK_SETTLED(c);
     if (!rgb_out) { set_error("crt_render_frame: rgb_out is null"); return CRT_ERR_INVALID; }
     if (nx <= 0 || ny <= 0 || spp < 1) { set_error("crt_render_frame: nx, ny and spp must be positive"); return CRT_ERR_INVALID; }
-    if (!c->accel_valid || c->n_prims != (uint32_t)(c->n_tri + c->n_sph)) {
+    if (!c->accel_valid || c->n_prims != (uint32_t)(c->n_tri + c->n_sph + c->n_rect)) {
         set_error("crt_render_frame: call crt_accel_build first (a frame only refits)");
         return CRT_ERR_STATE;
     }

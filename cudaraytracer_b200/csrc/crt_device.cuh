@@ -17,7 +17,9 @@ namespace crt {
 //             e1 = v1 - v0, e2 = v2 - v0 (the subtraction triangle.h:69-70
 //             performs per test, done once; same float result)
 //   sphere:   r0 = {centre.xyz, radius}, r1 = r2 = 0
-//   both:     r3 = {prim_id, mat_id | kind << 31, 0, 0} as uint bits
+//   rectangle (shapes/rectangle.h: the unit square of its frame's z = 0 plane): r0 = r1 = r2 = 0
+//   all:      r3 = {prim_id, mat_id (15 bits) | CRT_KIND_* flags, chain, 0} as uint bits; chain = (first << 8) | count
+//             names the primitive's run of DFrame records (0 = the plain case: no frame, see chain_ray)
 // 4-wide node: 96 B of payload at a 128 B stride (one cache line), read with three 256-bit loads:
 //   words 5k..5k+4 = child k: {lo.x, lo.y, lo.z, half2(ext.x, ext.y), half2(ext.z, A_k)}; A = (A_0, A_1, A_2) is the
 //        normal-cone vector of the NODE's own subtree (0 = none; lbvh.cu:cone_to_halves, crt_traverse.cuh:node_backfacing),
@@ -31,6 +33,9 @@ namespace crt {
 //   words 24..31  = padding
 #define CRT_SLOT_EMPTY ((int)0x80000000)
 #define CRT_KIND_SPHERE 0x80000000u
+#define CRT_KIND_RECT 0x40000000u
+#define CRT_RECT_FLIP 0x20000000u
+#define CRT_MAT_MASK 0x7FFFu
 
 // type: crt_material_type, or CRT_DMAT_CHECKER + it for a Lambertian / DiffuseLight whose texture is a
 // CheckerTexture(even = r g b, odd = r2 g2 b2)
@@ -44,6 +49,7 @@ struct DFrame { float m[9]; float px, py, pz; uint32_t has_rot; uint32_t pad[3];
 struct AccelView {
     const float4* nodes;
     const float4* recs;
+    const DFrame* frames;  // chains of enclosing Transforms (null when the scene has none)
     int root;            // child-style reference of the root
     uint32_t n_prims;
 };
@@ -106,6 +112,79 @@ CRT_HD bool sphere_test(v3 oc, v3 d, float radius, float t_min, float t_best, fl
         if (tmp <= t_best && tmp > t_min) { t_out = tmp; return true; }
     }
     return false;
+}
+
+// shapes/rectangle.h:21-44 in the rectangle's own frame: the unit square of the plane z = 0, answered only by rays
+// that travel AGAINST its normal (the opposite of Triangle's rule), bounds inclusive. The list keeps a hit only if
+// t < closest (hitable/hitable_list.h:84), hence t <= t_best here and the caller's tie rule; a NaN t (direction and
+// origin both in the plane) passes every reference comparison but not that last one.
+CRT_HD bool rect_test(v3 o, v3 d, bool flip, float t_min, float t_best, float& t_out, float& u_out, float& v_out)
+{
+    const v3 normal = V(0.0f, 0.0f, flip ? -1.0f : 1.0f);
+    if (vdot(d, normal) > 0.0f) return false;              // rectangle.h:24
+    const float t = x::div(-o.z, d.z);                     // rectangle.h:25
+    if (t < t_min || t > t_best) return false;             // rectangle.h:26
+    const float px = x::add(o.x, x::mul(t, d.x));          // rectangle.h:33-34
+    const float py = x::add(o.y, x::mul(t, d.y));
+    if (px < -0.5f || px > 0.5f || py < -0.5f || py > 0.5f) return false;
+    if (!(t == t)) return false;
+    t_out = t;
+    u_out = x::div(x::sub(px, -0.5f), x::sub(0.5f, -0.5f));   // rectangle.h:37-38
+    v_out = x::div(x::sub(py, -0.5f), x::sub(0.5f, -0.5f));
+    return true;
+}
+
+// ---- chains of enclosing Transforms ---------------------------------------------
+// rotate(v, rotation) (core/vec3.h:200-217) with the matrix rows precomputed on the host (they need libm's
+// sin/cos): component k = (v * row_k).sum() = v.x m[3k] + v.y m[3k+1] + v.z m[3k+2], summed left to right.
+CRT_HD v3 vrot(const float* m, v3 v)
+{
+    return V(x::add(x::add(x::mul(v.x, m[0]), x::mul(v.y, m[1])), x::mul(v.z, m[2])),
+             x::add(x::add(x::mul(v.x, m[3]), x::mul(v.y, m[4])), x::mul(v.z, m[5])),
+             x::add(x::add(x::mul(v.x, m[6]), x::mul(v.y, m[7])), x::mul(v.z, m[8])));
+}
+
+// The ray as a primitive's collision_detection receives it. Every Hitable on the way down - the world list, nested
+// lists, the primitive itself - maps the ray in its hit() by TransformRay = Translate(Rotate(Scale(r)))
+// (hitable/hitable.h:34, hitable/transform.h:11-14,38-54): direction re-normalised (scale is 1), origin and
+// direction rotated, position subtracted from the origin. A chain lists those levels outermost first. The plain
+// case (chain 0) is two levels without rotation: d = unit(unit(d)) = ray_dir_local, and the one translation a
+// sphere may carry is its centre.
+CRT_HD void chain_ray(const DFrame* __restrict__ frames, uint32_t chain, v3 o, v3 d_raw, v3& ol, v3& dl)
+{
+    const DFrame* f = frames + (chain >> 8);
+    const uint32_t n = chain & 255u;
+    for (uint32_t i = 0; i < n; i++) {
+        d_raw = vunit(d_raw);                                            // transform.h:50-54 (ScaleRay, scale 1)
+        if (f[i].has_rot) { o = vrot(f[i].m, o); d_raw = vrot(f[i].m, d_raw); }   // transform.h:43-48
+        o = vsub(o, V(f[i].px, f[i].py, f[i].pz));                       // transform.h:38-41
+    }
+    ol = o;
+    dl = d_raw;
+}
+
+// The normal on its way back up: every level's hit() rotates it by +rotation (hitable/hitable.h:36; not the inverse,
+// SURVEY 9 Q6), innermost first.
+CRT_HD v3 chain_normal(const DFrame* __restrict__ frames, uint32_t chain, v3 n)
+{
+    const DFrame* f = frames + (chain >> 8);
+    for (int i = (int)(chain & 255u) - 1; i >= 0; i--)
+        if (f[i].has_rot) n = vrot(f[i].m, n);
+    return n;
+}
+
+// A primitive under a chain against the world ray (o, d_raw = the direction as shade() holds it): the test runs in
+// the primitive's own frame, as the reference's does. info = record word r3.y.
+CRT_HD bool framed_test(const DFrame* __restrict__ frames, uint32_t chain, uint32_t info, float4 r0, float4 r1, float4 r2,
+                        v3 o, v3 d_raw, float t_min, float t_best, float& t, float& u, float& v)
+{
+    v3 ol, dl;
+    chain_ray(frames, chain, o, d_raw, ol, dl);
+    u = v = 0.0f;
+    if (info & CRT_KIND_SPHERE) return sphere_test(vsub(ol, V(r0.x, r0.y, r0.z)), dl, r0.w, t_min, t_best, t);
+    if (info & CRT_KIND_RECT) return rect_test(ol, dl, (info & CRT_RECT_FLIP) != 0u, t_min, t_best, t, u, v);
+    return triangle_test(ol, dl, V(r0.x, r0.y, r0.z), V(r1.x, r1.y, r1.z), V(r2.x, r2.y, r2.z), V(r0.w, r1.w, r2.w),
+                         t_min, t_best, t, u, v);
 }
 
 // ---- camera ----------------------------------------------------------------

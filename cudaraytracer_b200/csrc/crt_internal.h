@@ -87,6 +87,10 @@ struct crt_ctx {
     // chains of enclosing Transforms (rotation): the table and, per primitive, (first << 8) | count, 0 = none
     crt::DevBuf frames, tri_frame, sph_frame;
     size_t n_frames = 0;
+    bool tri_has_chain = false, sph_has_chain = false;   // tri_frame / sph_frame hold a chain word per primitive
+    // rectangles (shapes/rectangle.h): the unit square of a frame; material id | CRT_RECT_FLIP, primitive id, chain
+    crt::DevBuf rect_mat, rect_id, rect_frame;
+    size_t n_rect = 0;
     // multi-GPU (comm.cu): NCCL communicator of this context's rank
     void* comm = nullptr;
     int comm_rank = 0, comm_world = 1;
@@ -139,6 +143,8 @@ size_t radix_sort_hist_bytes();
 int lbvh_build(crt_ctx* c, bool refit_only, cudaStream_t async = nullptr);
 
 // trace.cu
+// anything but plain triangles (spheres, rectangles, chains of Transforms) takes the kernels' general instantiation
+inline bool scene_is_general(const crt_ctx* c) { return c->n_sph > 0 || c->n_rect > 0 || c->tri_has_chain; }
 int launch_trace(crt_ctx* c, const crt_ray* d_rays, size_t n, float t_min, float t_max, int accel, crt_hit* d_hits);
 AccelView accel_view(const crt_ctx* c);
 

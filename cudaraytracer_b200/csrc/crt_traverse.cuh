@@ -199,6 +199,17 @@ __device__ __forceinline__ bool node_backfacing(const float (&w)[24], const v3& 
 #endif
 }
 
+// A primitive under a chain of Transforms (rotated / nested Hitables, rectangles): the rare path, kept out of line so
+// that the plain triangle and sphere tests keep their registers. tuv: t, u, v out.
+static __device__ __noinline__ bool framed_test_dev(const DFrame* __restrict__ frames, uint32_t chain, uint32_t info, float4 r0, float4 r1,
+                                             float4 r2, v3 o, v3 d_raw, float t_min, float t_best, float* tuv)
+{
+    float t = 0.f, u = 0.f, v = 0.f;
+    const bool ok = framed_test(frames, chain, info, r0, r1, r2, o, d_raw, t_min, t_best, t, u, v);
+    tuv[0] = t; tuv[1] = u; tuv[2] = v;
+    return ok;
+}
+
 // order-preserving float <-> uint32 (for REDUX min/max over a warp)
 __device__ __forceinline__ uint32_t f2sortable(float f)
 {
@@ -383,7 +394,14 @@ __device__ __forceinline__ void traverse_persistent(const AccelView& A, const ui
                 const uint32_t pid = __float_as_uint(r3.x);
                 float t, u = 0.0f, v = 0.0f;
                 bool ok;
-                if (HAS_SPH && (__float_as_uint(r3.y) & CRT_KIND_SPHERE)) {
+                if (HAS_SPH && __float_as_uint(r3.z) != 0u) {
+                    if (COUNT) cnt.spheres++;
+                    v3 oo, dr;
+                    src.load(ray_i, oo, dr);            // the direction as the caller gave it: the chain normalises per level
+                    float tuv[3];
+                    ok = framed_test_dev(A.frames, __float_as_uint(r3.z), __float_as_uint(r3.y), r0, r1, r2, o, dr, t_min, best.t, tuv);
+                    t = tuv[0]; u = tuv[1]; v = tuv[2];
+                } else if (HAS_SPH && (__float_as_uint(r3.y) & CRT_KIND_SPHERE)) {
                     if (COUNT) cnt.spheres++;
                     ok = sphere_test(vsub(o, V(r0.x, r0.y, r0.z)), d, r0.w, t_min, best.t, t);
                 } else {
@@ -592,7 +610,15 @@ __device__ __forceinline__ void traverse_packets(const AccelView& A, const uint3
                             const uint32_t pid = __float_as_uint(r3.x);
                             float t, u = 0.0f, v = 0.0f;
                             bool ok;
-                            if (HAS_SPH && (__float_as_uint(r3.y) & CRT_KIND_SPHERE)) {
+                            if (HAS_SPH && __float_as_uint(r3.z) != 0u) {
+                                if (COUNT && live) cnt.spheres++;
+                                if (COUNT && lane == 0) cnt.sph_f++;
+                                v3 oo, dr;
+                                src.load(live ? ray_i : first, oo, dr);
+                                float tuv[3];
+                                ok = framed_test_dev(A.frames, __float_as_uint(r3.z), __float_as_uint(r3.y), r0, r1, r2, o, dr, t_min, best.t, tuv);
+                                t = tuv[0]; u = tuv[1]; v = tuv[2];
+                            } else if (HAS_SPH && (__float_as_uint(r3.y) & CRT_KIND_SPHERE)) {
                                 if (COUNT && live) cnt.spheres++;
                                 if (COUNT && lane == 0) cnt.sph_f++;
                                 ok = sphere_test(vsub(o, V(r0.x, r0.y, r0.z)), d, r0.w, t_min, best.t, t);
@@ -648,7 +674,7 @@ __device__ __forceinline__ void traverse_packets(const AccelView& A, const uint3
 
 // One ray, the whole warp: o and d (= ray_dir_local of the raw direction) are warp-uniform, and so is the result.
 template <bool COUNT, bool HAS_SPH>
-__device__ __forceinline__ Hit trace_wide_one(const AccelView& A, const v3 o, const v3 d, const float t_min, const float t_max,
+__device__ __forceinline__ Hit trace_wide_one(const AccelView& A, const v3 o, const v3 d_raw, const float t_min, const float t_max,
                                               uint2* s_stack, TraceCounters& cnt)
 {
     constexpr uint32_t FULL = 0xffffffffu;
@@ -656,6 +682,7 @@ __device__ __forceinline__ Hit trace_wide_one(const AccelView& A, const v3 o, co
     const uint32_t lt_mask = (1u << lane) - 1u;
     constexpr uint32_t WIDE_LIMIT = CRT_WIDE_STACK - CRT_STACK_ENTRIES;
     {
+        const v3 d = ray_dir_local(d_raw);
         const RaySlabs S = make_slabs(o, d);
         Hit best;                                    // warp-uniform
         best.t = t_max; best.k = 0xFFFFFFFFu; best.id = CRT_MISS_ID; best.u = best.v = 0.f;
@@ -730,7 +757,12 @@ __device__ __forceinline__ Hit trace_wide_one(const AccelView& A, const v3 o, co
                     const uint32_t pid = __float_as_uint(r3.x);
                     float t, u = 0.0f, v = 0.0f;
                     bool ok;
-                    if (HAS_SPH && (__float_as_uint(r3.y) & CRT_KIND_SPHERE)) {
+                    if (HAS_SPH && __float_as_uint(r3.z) != 0u) {
+                        if (COUNT) { cnt.spheres++; cnt.sph_f++; }
+                        float tuv[3];
+                        ok = framed_test_dev(A.frames, __float_as_uint(r3.z), __float_as_uint(r3.y), r0, r1, r2, o, d_raw, t_min, bound, tuv);
+                        t = tuv[0]; u = tuv[1]; v = tuv[2];
+                    } else if (HAS_SPH && (__float_as_uint(r3.y) & CRT_KIND_SPHERE)) {
                         if (COUNT) { cnt.spheres++; cnt.sph_f++; }
                         ok = sphere_test(vsub(o, V(r0.x, r0.y, r0.z)), d, r0.w, t_min, bound, t);
                     } else {
@@ -787,7 +819,7 @@ __device__ __forceinline__ void traverse_wide(const AccelView& A, const uint32_t
         if (ray_i >= n) break;
         v3 o, dr;
         src.load(ray_i, o, dr);                     // the same address in every lane: one broadcast load
-        const Hit best = trace_wide_one<COUNT, HAS_SPH>(A, o, ray_dir_local(dr), t_min, t_max, s_stack, cnt);
+        const Hit best = trace_wide_one<COUNT, HAS_SPH>(A, o, dr, t_min, t_max, s_stack, cnt);
         if (lane == 0) sink.store(ray_i, best);
     }
 }

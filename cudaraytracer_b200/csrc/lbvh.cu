@@ -34,25 +34,94 @@ __device__ __forceinline__ Box box_union(const Box& a, const Box& b)
     return r;
 }
 
-// Box of input primitive p (triangles first, then spheres): the reference's
-// Triangle::bounding_box / Sphere::bounding_box + TransformAABB for a pure
-// translation (shapes/triangle.h:102-115, shapes/sphere.h:58-62,
-// hitable/transform.h:22-31), widened by a relative 2^-21 so that ulp-level
-// differences between the box test and the exact primitive test cannot cull a hit.
-__device__ __forceinline__ Box prim_box(const float* __restrict__ tri_in, const float* __restrict__ sph_in,
-                                        uint32_t n_tri, uint32_t p)
+// The primitives as uploaded: triangles first, then spheres, then rectangles; a primitive may sit under a chain of
+// Transforms (crt_device.cuh:chain_ray), rectangles always do.
+struct PrimSrc {
+    const float* tri_in;
+    const float* sph_in;
+    const uint32_t *tri_mat, *tri_id, *sph_mat, *sph_id, *rect_mat, *rect_id;
+    const uint32_t *tri_chain, *sph_chain, *rect_chain;   // null: no chains of that kind
+    const DFrame* frames;
+    const float* pad_bounds;                               // scene box that scales the padding of chained boxes, or null
+    uint32_t n_tri, n_sph, n_rect;
+};
+
+__device__ __forceinline__ uint32_t prim_chain(const PrimSrc& S, uint32_t p)
+{
+    if (p < S.n_tri) return S.tri_chain ? S.tri_chain[p] : 0u;
+    if (p < S.n_tri + S.n_sph) return S.sph_chain ? S.sph_chain[p - S.n_tri] : 0u;
+    return S.rect_chain[p - S.n_tri - S.n_sph];
+}
+
+// A point of a chained primitive's own frame in world space: the inverse of chain_ray's map, innermost level first.
+// The rotation matrices are orthonormal up to rounding, so the transpose inverts them to a few 1e-7.
+__device__ __forceinline__ void chain_point_to_world(const DFrame* __restrict__ frames, uint32_t chain, float& x, float& y, float& z)
+{
+    const DFrame* f = frames + (chain >> 8);
+    for (int i = (int)(chain & 255u) - 1; i >= 0; i--) {
+        x += f[i].px; y += f[i].py; z += f[i].pz;
+        if (f[i].has_rot) {
+            const float* m = f[i].m;
+            const float wx = m[0] * x + m[3] * y + m[6] * z, wy = m[1] * x + m[4] * y + m[7] * z, wz = m[2] * x + m[5] * y + m[8] * z;
+            x = wx; y = wy; z = wz;
+        }
+    }
+}
+
+// Box of input primitive p: the reference's Triangle::bounding_box / Sphere::bounding_box / Rectangle::bounding_box
+// (shapes/triangle.h:102-115, shapes/sphere.h:58-62, shapes/rectangle.h:11-14) in WORLD space, widened by a relative
+// 2^-21 so that ulp-level differences between the box test and the exact primitive test cannot cull a hit.
+// A primitive under a chain is tested in its own frame (crt_device.cuh:framed_test) on a ray that was rotated and
+// translated in fp32, so where its world-space image lies is only known up to the rounding of that map, which grows
+// with the distance of the ray origin: its box is padded by 2^-16 of the scene's largest coordinate per level
+// (rays that start within 16 scene sizes are covered). The reference's own TransformAABB rotates only two corners
+// (hitable/transform.h:22-31, marked "wrong?" by its author) and is not followed: the list scan, which is the
+// behaviour reproduced, uses no boxes.
+__device__ __forceinline__ Box prim_box(const PrimSrc& S, uint32_t p)
 {
     Box b;
-    if (p < n_tri) {
-        const float* t = tri_in + 12 * (size_t)p;
-        const float x0 = t[0], y0 = t[1], z0 = t[2], x1 = t[3], y1 = t[4], z1 = t[5], x2 = t[6], y2 = t[7], z2 = t[8];
-        b.lx = fminf(x0, fminf(x1, x2)); b.ly = fminf(y0, fminf(y1, y2)); b.lz = fminf(z0, fminf(z1, z2));
-        b.hx = fmaxf(x0, fmaxf(x1, x2)); b.hy = fmaxf(y0, fmaxf(y1, y2)); b.hz = fmaxf(z0, fmaxf(z1, z2));
+    const uint32_t chain = prim_chain(S, p);
+    if (chain == 0u) {
+        if (p < S.n_tri) {
+            const float* t = S.tri_in + 12 * (size_t)p;
+            const float x0 = t[0], y0 = t[1], z0 = t[2], x1 = t[3], y1 = t[4], z1 = t[5], x2 = t[6], y2 = t[7], z2 = t[8];
+            b.lx = fminf(x0, fminf(x1, x2)); b.ly = fminf(y0, fminf(y1, y2)); b.lz = fminf(z0, fminf(z1, z2));
+            b.hx = fmaxf(x0, fmaxf(x1, x2)); b.hy = fmaxf(y0, fmaxf(y1, y2)); b.hz = fmaxf(z0, fmaxf(z1, z2));
+        } else {
+            const float* s = S.sph_in + 4 * (size_t)(p - S.n_tri);
+            const float r = fabsf(s[3]);
+            b.lx = s[0] - r; b.ly = s[1] - r; b.lz = s[2] - r;
+            b.hx = s[0] + r; b.hy = s[1] + r; b.hz = s[2] + r;
+        }
     } else {
-        const float* s = sph_in + 4 * (size_t)(p - n_tri);
-        const float r = fabsf(s[3]);
-        b.lx = s[0] - r; b.ly = s[1] - r; b.lz = s[2] - r;
-        b.hx = s[0] + r; b.hy = s[1] + r; b.hz = s[2] + r;
+        float c[4][3];
+        int nc;
+        float r = 0.0f;
+        if (p < S.n_tri) {
+            const float* t = S.tri_in + 12 * (size_t)p;
+            for (int k = 0; k < 3; k++) { c[k][0] = t[3 * k]; c[k][1] = t[3 * k + 1]; c[k][2] = t[3 * k + 2]; }
+            nc = 3;
+        } else if (p < S.n_tri + S.n_sph) {
+            const float* s = S.sph_in + 4 * (size_t)(p - S.n_tri);
+            c[0][0] = s[0]; c[0][1] = s[1]; c[0][2] = s[2];
+            r = fabsf(s[3]);
+            nc = 1;
+        } else {
+            for (int k = 0; k < 4; k++) { c[k][0] = (k & 1) ? 0.5f : -0.5f; c[k][1] = (k & 2) ? 0.5f : -0.5f; c[k][2] = 0.0f; }
+            nc = 4;
+        }
+        b = Box{INFINITY, INFINITY, INFINITY, -INFINITY, -INFINITY, -INFINITY};
+        for (int k = 0; k < nc; k++) {
+            chain_point_to_world(S.frames, chain, c[k][0], c[k][1], c[k][2]);
+            b.lx = fminf(b.lx, c[k][0]); b.ly = fminf(b.ly, c[k][1]); b.lz = fminf(b.lz, c[k][2]);
+            b.hx = fmaxf(b.hx, c[k][0]); b.hy = fmaxf(b.hy, c[k][1]); b.hz = fmaxf(b.hz, c[k][2]);
+        }
+        float scale = fmaxf(fmaxf(fabsf(b.lx), fabsf(b.hx)), fmaxf(fmaxf(fabsf(b.ly), fabsf(b.hy)), fmaxf(fabsf(b.lz), fabsf(b.hz)))) + r;
+        if (S.pad_bounds)
+            for (int k = 0; k < 6; k++) scale = fmaxf(scale, fabsf(S.pad_bounds[k]));
+        const float pad = r + scale * 1.52587890625e-5f * (float)(chain & 255u) + 1e-30f;   // 2^-16 per level
+        if (!(scale < INFINITY)) b = Box{-INFINITY, -INFINITY, -INFINITY, INFINITY, INFINITY, INFINITY};   // NaN / inf geometry: never culled
+        b.lx -= pad; b.ly -= pad; b.lz -= pad; b.hx += pad; b.hy += pad; b.hz += pad;
     }
     const float k = 4.76837158e-7f;   // 2^-21
     const float tiny = 1e-30f;
@@ -94,13 +163,12 @@ __device__ __forceinline__ bool is_oversize(const Box& b, const float* __restric
 }
 
 __global__ void __launch_bounds__(256)
-k_scene_bounds(const float* __restrict__ tri_in, const float* __restrict__ sph_in, uint32_t n_tri, uint32_t n,
-               const float* __restrict__ all_bounds, float* __restrict__ bounds)
+k_scene_bounds(PrimSrc S, uint32_t n, const float* __restrict__ all_bounds, float* __restrict__ bounds)
 {
     // all_bounds == nullptr: pass 1, every primitive; otherwise pass 2, only those that are not oversize
     Box b = {INFINITY, INFINITY, INFINITY, -INFINITY, -INFINITY, -INFINITY};
     for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x) {
-        const Box pb = prim_box(tri_in, sph_in, n_tri, p);
+        const Box pb = prim_box(S, p);
         if (all_bounds == nullptr || !is_oversize(pb, all_bounds)) b = box_union(b, pb);
     }
     for (int o = 16; o > 0; o >>= 1) {
@@ -129,12 +197,11 @@ __device__ __forceinline__ uint64_t expand21(uint64_t v)
 }
 
 __global__ void __launch_bounds__(256)
-k_morton(const float* __restrict__ tri_in, const float* __restrict__ sph_in, uint32_t n_tri, uint32_t n,
-         const float* __restrict__ bounds, uint64_t* __restrict__ keys, uint32_t* __restrict__ vals)
+k_morton(PrimSrc S, uint32_t n, const float* __restrict__ bounds, uint64_t* __restrict__ keys, uint32_t* __restrict__ vals)
 {
     const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n) return;
-    const Box b = prim_box(tri_in, sph_in, n_tri, p);
+    const Box b = prim_box(S, p);
     const bool oversize = is_oversize(b, bounds);
     // grid over the regular primitives; if every primitive is oversize, over all of them
     const float* gb = bounds[6] <= bounds[9] ? bounds + 6 : bounds;
@@ -258,7 +325,8 @@ __device__ __forceinline__ Cone cone_merge(const Cone& a, const Cone& b)
 __device__ __forceinline__ Cone leaf_cone(const float4* __restrict__ recs, size_t k)
 {
     const float4 r0 = __ldcg(recs + 4 * k), r1 = __ldcg(recs + 4 * k + 1), r2 = __ldcg(recs + 4 * k + 2), r3 = __ldcg(recs + 4 * k + 3);
-    if (__float_as_uint(r3.y) & CRT_KIND_SPHERE) return cone_none();
+    // spheres and rectangles have no stored normal to cull by; a chained triangle's normal test runs in its own frame
+    if ((__float_as_uint(r3.y) & (CRT_KIND_SPHERE | CRT_KIND_RECT)) || __float_as_uint(r3.z) != 0u) return cone_none();
     return cone_of_normal(r0.w, r1.w, r2.w);
 }
 
@@ -287,9 +355,7 @@ __device__ __forceinline__ void cone_to_halves(const Cone& c, uint32_t& hx, uint
 // CONES: also merge the normal cones (a build; a refit leaves them alone: no pose update changes a stored normal)
 template <bool CONES>
 __global__ void __launch_bounds__(256)
-k_fit(const float* __restrict__ tri_in, const uint32_t* __restrict__ tri_mat, const uint32_t* __restrict__ tri_id,
-      const float* __restrict__ sph_in, const uint32_t* __restrict__ sph_mat, const uint32_t* __restrict__ sph_id,
-      uint32_t n_tri, uint32_t n, const uint32_t* __restrict__ perm, const int2* __restrict__ child,
+k_fit(PrimSrc S, uint32_t n, const uint32_t* __restrict__ perm, const int2* __restrict__ child,
       const int* __restrict__ parent, const int* __restrict__ leaf_parent, int* __restrict__ flags,
       float4* __restrict__ recs, float4* __restrict__ leaf_box, float4* __restrict__ node_box,
       float4* __restrict__ node_cone)
@@ -297,24 +363,32 @@ k_fit(const float* __restrict__ tri_in, const uint32_t* __restrict__ tri_mat, co
     const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= n) return;
     const uint32_t p = perm[k];
+    const uint32_t n_tri = S.n_tri;
+    const float chain_bits = __uint_as_float(prim_chain(S, p));
     if (p < n_tri) {
-        const float* t = tri_in + 12 * (size_t)p;
+        const float* t = S.tri_in + 12 * (size_t)p;
         const v3 v0 = V(t[0], t[1], t[2]);
         const v3 e1 = vsub(V(t[3], t[4], t[5]), v0);       // triangle.h:69
         const v3 e2 = vsub(V(t[6], t[7], t[8]), v0);       // triangle.h:70
         recs[4 * (size_t)k] = make_float4(v0.x, v0.y, v0.z, t[9]);
         recs[4 * (size_t)k + 1] = make_float4(e1.x, e1.y, e1.z, t[10]);
         recs[4 * (size_t)k + 2] = make_float4(e2.x, e2.y, e2.z, t[11]);
-        recs[4 * (size_t)k + 3] = make_float4(__uint_as_float(tri_id[p]), __uint_as_float(tri_mat[p]), 0.f, 0.f);
-    } else {
+        recs[4 * (size_t)k + 3] = make_float4(__uint_as_float(S.tri_id[p]), __uint_as_float(S.tri_mat[p]), chain_bits, 0.f);
+    } else if (p < n_tri + S.n_sph) {
         const uint32_t q = p - n_tri;
-        const float* s = sph_in + 4 * (size_t)q;
+        const float* s = S.sph_in + 4 * (size_t)q;
         recs[4 * (size_t)k] = make_float4(s[0], s[1], s[2], s[3]);
         recs[4 * (size_t)k + 1] = make_float4(0.f, 0.f, 0.f, 0.f);
         recs[4 * (size_t)k + 2] = make_float4(0.f, 0.f, 0.f, 0.f);
-        recs[4 * (size_t)k + 3] = make_float4(__uint_as_float(sph_id[q]), __uint_as_float(sph_mat[q] | CRT_KIND_SPHERE), 0.f, 0.f);
+        recs[4 * (size_t)k + 3] = make_float4(__uint_as_float(S.sph_id[q]), __uint_as_float(S.sph_mat[q] | CRT_KIND_SPHERE), chain_bits, 0.f);
+    } else {
+        const uint32_t q = p - n_tri - S.n_sph;                  // rect_mat carries CRT_RECT_FLIP
+        recs[4 * (size_t)k] = make_float4(0.f, 0.f, 0.f, 0.f);
+        recs[4 * (size_t)k + 1] = make_float4(0.f, 0.f, 0.f, 0.f);
+        recs[4 * (size_t)k + 2] = make_float4(0.f, 0.f, 0.f, 0.f);
+        recs[4 * (size_t)k + 3] = make_float4(__uint_as_float(S.rect_id[q]), __uint_as_float(S.rect_mat[q] | CRT_KIND_RECT), chain_bits, 0.f);
     }
-    store_box(leaf_box, k, prim_box(tri_in, sph_in, n_tri, p));
+    store_box(leaf_box, k, prim_box(S, p));
     if (n < 2) return;
     __threadfence();
     int node = leaf_parent[k];
@@ -465,12 +539,11 @@ constexpr int PLOC_R = 32;   // largest search radius (shared-memory halo)
 constexpr int PLOC_B = 256;
 
 __global__ void __launch_bounds__(256)
-k_ploc_init(const float* __restrict__ tri_in, const float* __restrict__ sph_in, uint32_t n_tri, uint32_t n,
-            const uint32_t* __restrict__ perm, float4* __restrict__ lo, float4* __restrict__ hi)
+k_ploc_init(PrimSrc S, uint32_t n, const uint32_t* __restrict__ perm, float4* __restrict__ lo, float4* __restrict__ hi)
 {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    const Box b = prim_box(tri_in, sph_in, n_tri, perm[i]);
+    const Box b = prim_box(S, perm[i]);
     lo[i] = make_float4(b.lx, b.ly, b.lz, __int_as_float(~(int)i));   // .w: reference of the cluster's subtree
     hi[i] = make_float4(b.hx, b.hy, b.hz, __int_as_float(1));         // .w: primitives below it
 }
@@ -683,7 +756,7 @@ static inline unsigned int grid_for(size_t n, int block) { return (unsigned int)
 // PLOC rounds on the Morton-sorted primitives, then the depth-first renumbering.
 // Leaves child / parent / leaf_parent / range and the permutation in the state
 // k_hierarchy leaves them in (root = node 0, leaf references = record positions).
-static int ploc_topology(crt_ctx* c, const float* tri_in, const float* sph_in, uint32_t n_tri, uint32_t n)
+static int ploc_topology(crt_ctx* c, const PrimSrc& S, uint32_t n)
 {
     cudaStream_t st = c->stream;
     CRT_CUDA(c->ploc_box[0].reserve((size_t)n * 32));
@@ -697,7 +770,7 @@ static int ploc_topology(crt_ctx* c, const float* tri_in, const float* sph_in, u
     float4* lo[2] = {c->ploc_box[0].as<float4>(), c->ploc_box[1].as<float4>()};
     float4* hi[2] = {lo[0] + n, lo[1] + n};
     int* size = c->flags.as<int>();                         // free until k_fit: primitives below each inner node
-    k_ploc_init<<<grid_for(n, 256), 256, 0, st>>>(tri_in, sph_in, n_tri, n, c->vals[c->perm_buf].as<uint32_t>(), lo[0], hi[0]);
+    k_ploc_init<<<grid_for(n, 256), 256, 0, st>>>(S, n, c->vals[c->perm_buf].as<uint32_t>(), lo[0], hi[0]);
     int nc = (int)n, created = 0, cur = 0;
     while (nc > 1) {
         const unsigned int nb = grid_for((size_t)nc, PLOC_B);
@@ -733,7 +806,7 @@ static int ploc_topology(crt_ctx* c, const float* tri_in, const float* sph_in, u
 // c->ev_up1 and reads the duration from (ev_up0, ev_up1) once it has synchronised (crt_render_frame).
 int lbvh_build(crt_ctx* c, bool refit_only, cudaStream_t async)
 {
-    const size_t n = c->n_tri + c->n_sph;
+    const size_t n = c->n_tri + c->n_sph + c->n_rect;
     if (n >= (1ull << 28)) { set_error("too many primitives (%zu), limit is 2^28", n); return CRT_ERR_INVALID; }
     if (async && !refit_only) { set_error("lbvh_build: only a refit can be queued without waiting"); return CRT_ERR_INVALID; }
     cudaStream_t st = async ? async : c->stream;
@@ -752,9 +825,17 @@ int lbvh_build(crt_ctx* c, bool refit_only, cudaStream_t async)
         if (!async) CRT_CUDA(cudaEventSynchronize(ev_end));
         return CRT_OK;
     }
-    const float* tri_in = c->tri_in.as<float>();
-    const float* sph_in = c->sph_in.as<float>();
-    const uint32_t n_tri = (uint32_t)c->n_tri;
+    PrimSrc S;
+    S.tri_in = c->tri_in.as<float>(); S.sph_in = c->sph_in.as<float>();
+    S.tri_mat = c->tri_mat.as<uint32_t>(); S.tri_id = c->tri_id.as<uint32_t>();
+    S.sph_mat = c->sph_mat.as<uint32_t>(); S.sph_id = c->sph_id.as<uint32_t>();
+    S.rect_mat = c->rect_mat.as<uint32_t>(); S.rect_id = c->rect_id.as<uint32_t>();
+    S.tri_chain = c->tri_has_chain ? c->tri_frame.as<uint32_t>() : nullptr;
+    S.sph_chain = c->sph_has_chain ? c->sph_frame.as<uint32_t>() : nullptr;
+    S.rect_chain = c->rect_frame.as<uint32_t>();
+    S.frames = c->frames.as<DFrame>();
+    S.pad_bounds = nullptr;
+    S.n_tri = (uint32_t)c->n_tri; S.n_sph = (uint32_t)c->n_sph; S.n_rect = (uint32_t)c->n_rect;
     const uint32_t un = (uint32_t)n;
 
     if (!refit_only) {
@@ -777,10 +858,9 @@ int lbvh_build(crt_ctx* c, bool refit_only, cudaStream_t async)
 
         k_init_bounds<<<1, 32, 0, st>>>(c->bounds.as<float>());
         const unsigned int gb = min(grid_for(n, 256), (unsigned int)(c->sm_count * 8));
-        k_scene_bounds<<<gb, 256, 0, st>>>(tri_in, sph_in, n_tri, un, nullptr, c->bounds.as<float>());
-        k_scene_bounds<<<gb, 256, 0, st>>>(tri_in, sph_in, n_tri, un, c->bounds.as<float>(), c->bounds.as<float>() + 6);
-        k_morton<<<grid_for(n, 256), 256, 0, st>>>(tri_in, sph_in, n_tri, un, c->bounds.as<float>(),
-                                                    c->keys[0].as<uint64_t>(), c->vals[0].as<uint32_t>());
+        k_scene_bounds<<<gb, 256, 0, st>>>(S, un, nullptr, c->bounds.as<float>());
+        k_scene_bounds<<<gb, 256, 0, st>>>(S, un, c->bounds.as<float>(), c->bounds.as<float>() + 6);
+        k_morton<<<grid_for(n, 256), 256, 0, st>>>(S, un, c->bounds.as<float>(), c->keys[0].as<uint64_t>(), c->vals[0].as<uint32_t>());
         uint64_t* keys[2] = {c->keys[0].as<uint64_t>(), c->keys[1].as<uint64_t>()};
         uint32_t* vals[2] = {c->vals[0].as<uint32_t>(), c->vals[1].as<uint32_t>()};
         c->perm_buf = radix_sort_pairs(st, keys, vals, un, 0, 64, c->hist.as<uint32_t>());
@@ -789,22 +869,19 @@ int lbvh_build(crt_ctx* c, bool refit_only, cudaStream_t async)
                                                               c->range.as<int2>(), c->parent.as<int>(),
                                                               c->leaf_parent.as<int>());
         if (n > 1 && c->builder == CRT_BUILDER_PLOC) {
-            const int r = ploc_topology(c, tri_in, sph_in, n_tri, un);
+            const int r = ploc_topology(c, S, un);
             if (r != CRT_OK) return r;
         }
     }
     if (n > 1) CRT_CUDA(cudaMemsetAsync(c->flags.p, 0, (n - 1) * 4, st));
+    S.pad_bounds = c->bounds.as<float>();       // the final boxes of chained primitives are padded by the scene's scale
     if (refit_only)
-        k_fit<false><<<grid_for(n, 256), 256, 0, st>>>(tri_in, c->tri_mat.as<uint32_t>(), c->tri_id.as<uint32_t>(), sph_in,
-                                            c->sph_mat.as<uint32_t>(), c->sph_id.as<uint32_t>(), n_tri, un,
-                                            c->vals[c->perm_buf].as<uint32_t>(), c->child.as<int2>(),
+        k_fit<false><<<grid_for(n, 256), 256, 0, st>>>(S, un, c->vals[c->perm_buf].as<uint32_t>(), c->child.as<int2>(),
                                             c->parent.as<int>(), c->leaf_parent.as<int>(), c->flags.as<int>(),
                                             c->recs.as<float4>(), c->leaf_box.as<float4>(),
                                             c->node_box.as<float4>(), c->node_cone.as<float4>());
     else
-        k_fit<true><<<grid_for(n, 256), 256, 0, st>>>(tri_in, c->tri_mat.as<uint32_t>(), c->tri_id.as<uint32_t>(), sph_in,
-                                            c->sph_mat.as<uint32_t>(), c->sph_id.as<uint32_t>(), n_tri, un,
-                                            c->vals[c->perm_buf].as<uint32_t>(), c->child.as<int2>(),
+        k_fit<true><<<grid_for(n, 256), 256, 0, st>>>(S, un, c->vals[c->perm_buf].as<uint32_t>(), c->child.as<int2>(),
                                             c->parent.as<int>(), c->leaf_parent.as<int>(), c->flags.as<int>(),
                                             c->recs.as<float4>(), c->leaf_box.as<float4>(),
                                             c->node_box.as<float4>(), c->node_cone.as<float4>());

@@ -306,20 +306,27 @@ __device__ __forceinline__ bool shade_step(const RenderParams& P, const AccelVie
             rng.key = crt_rng_key_from(P.seed_key, (uint32_t)py * (uint32_t)P.nx + (uint32_t)px, (uint32_t)(P.s_begin + (int)s_local));
             rng.ctr = S.pack & 0xFFFFFFu;
         }
-        const v3 dl = ray_dir_local(d);
         float4 r0, r1, r2, r3;
         ldg256(A.recs + 4 * (size_t)hk, r0, r1);
         ldg256(A.recs + 4 * (size_t)hk + 2, r2, r3);
-        const uint32_t inf_y = __float_as_uint(r3.y);
+        const uint32_t inf_y = __float_as_uint(r3.y), chain = __float_as_uint(r3.z);
+        // the ray in the hit primitive's own frame: hit point and normal are reported there
+        v3 ol = o, dl;
+        if (HAS_SPH && chain != 0u) chain_ray(A.frames, chain, o, d, ol, dl);
+        else dl = ray_dir_local(d);
         v3 p, n;
         if (HAS_SPH && (inf_y & CRT_KIND_SPHERE)) {
-            p = vadd(vsub(o, V(r0.x, r0.y, r0.z)), vscale(ht, dl));        // sphere.h:40 (local frame)
+            p = vadd(vsub(ol, V(r0.x, r0.y, r0.z)), vscale(ht, dl));       // sphere.h:40 (local frame)
             n = vdivf(p, r0.w);                                            // sphere.h:41
+        } else if (HAS_SPH && (inf_y & CRT_KIND_RECT)) {
+            p = vadd(ol, vscale(ht, dl));                                  // rectangle.h:41
+            n = V(0.0f, 0.0f, (inf_y & CRT_RECT_FLIP) ? -1.0f : 1.0f);     // rectangle.h:23,42
         } else {
-            p = vadd(o, vscale(ht, dl));                                   // triangle.h:95
+            p = vadd(ol, vscale(ht, dl));                                  // triangle.h:95
             n = V(r0.w, r1.w, r2.w);                                       // triangle.h:96
         }
-        const uint32_t mat_id = inf_y & 0x7FFFFFFFu;
+        if (HAS_SPH && chain != 0u) n = chain_normal(A.frames, chain, n);  // hitable.h:36, every level on the way up
+        const uint32_t mat_id = inf_y & CRT_MAT_MASK;
         const DMat m = load_mat(mats, mat_id);
         const bool odd = checker_odd(m, p);                                // texture.h:31
         const v3 e = emitted(m, odd);                                      // render.h:56
@@ -458,7 +465,7 @@ k_tail(RenderParams P, AccelView A, const DMat* __restrict__ mats, const float4*
         PathState S;
         load_path(P, q_in, i, S);                   // one address for the warp: broadcast loads
         for (;;) {
-            const Hit h = trace_wide_one<COUNT, HAS_SPH>(A, S.o, ray_dir_local(S.d), 0.001f, FLT_MAX, stack, cnt);   // render.h:53
+            const Hit h = trace_wide_one<COUNT, HAS_SPH>(A, S.o, S.d, 0.001f, FLT_MAX, stack, cnt);   // render.h:53
             v3 L;
             if (!shade_step<COUNT, HAS_SPH>(P, A, mats, S, h.t, h.k, L, n_scatter)) {
                 if (lane == 0) __stcs(rad + S.path_id, make_float4(L.x, L.y, L.z, 0.0f));
@@ -692,7 +699,7 @@ int render_accum(crt_ctx* c, const crt_camera* cam, int nx, int ny, int s0, int 
         }
         size_grids(c);
         const AccelView A = accel_view(c);
-        const bool sph = c->n_sph > 0;
+        const bool sph = scene_is_general(c);
         const int bounces = mode == CRT_SHADE_PATH ? max_depth + 1 : 1;
         static const bool verbose = getenv("CRT_TRACE_TIMING") != nullptr;   // development aid
 

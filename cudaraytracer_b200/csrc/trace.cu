@@ -18,6 +18,7 @@ AccelView accel_view(const crt_ctx* c)
     AccelView a;
     a.nodes = c->nodes.as<float4>();
     a.recs = c->recs.as<float4>();
+    a.frames = c->frames.as<DFrame>();
     a.root = c->root;
     a.n_prims = c->n_prims;
     return a;
@@ -103,19 +104,28 @@ k_trace_lbvh_packet(AccelView A, const crt_ray* __restrict__ rays, uint32_t n, u
 
 constexpr int BRUTE_TILE = 64;
 
+// chains / rectangles (BruteExtra): per-primitive chain words in input order (null = none of that kind) and the
+// rectangles' material word (CRT_RECT_FLIP), id and chain
+struct BruteExtra {
+    const DFrame* frames;
+    const uint32_t *tri_chain, *sph_chain, *rect_chain, *rect_mat, *rect_id;
+    uint32_t n_rect;
+};
+
 template <bool COUNT>
 __global__ void __launch_bounds__(TRACE_BLOCK)
 k_trace_brute(const float* __restrict__ tri_in, const uint32_t* __restrict__ tri_id, uint32_t n_tri,
-              const float* __restrict__ sph_in, const uint32_t* __restrict__ sph_id, uint32_t n_sph,
+              const float* __restrict__ sph_in, const uint32_t* __restrict__ sph_id, uint32_t n_sph, BruteExtra X,
               const crt_ray* __restrict__ rays, size_t n, float t_min, float t_max, crt_hit* __restrict__ hits,
               unsigned long long* __restrict__ counters)
 {
     __shared__ float s_prim[BRUTE_TILE * 12];
     __shared__ uint32_t s_id[BRUTE_TILE];
+    __shared__ uint32_t s_chain[BRUTE_TILE];
     const size_t i = (size_t)blockIdx.x * TRACE_BLOCK + threadIdx.x;
     const bool live = i < n;
-    v3 o = V(0.f, 0.f, 0.f), d = V(0.f, 0.f, 1.f);
-    if (live) { load_ray(rays, i, o, d); d = ray_dir_local(d); }
+    v3 o = V(0.f, 0.f, 0.f), d = V(0.f, 0.f, 1.f), d_raw = d;
+    if (live) { load_ray(rays, i, o, d_raw); d = ray_dir_local(d_raw); }
     float best_t = t_max, best_u = 0.f, best_v = 0.f;
     uint32_t best_id = CRT_MISS_ID;
     TraceCounters cnt = {0u, 0u, 0u, 0u, 0u, 0u, 0u};
@@ -124,7 +134,7 @@ k_trace_brute(const float* __restrict__ tri_in, const uint32_t* __restrict__ tri
         const uint32_t m = min((uint32_t)BRUTE_TILE, n_tri - base);
         __syncthreads();
         for (uint32_t j = threadIdx.x; j < m * 12; j += TRACE_BLOCK) s_prim[j] = tri_in[(size_t)base * 12 + j];
-        for (uint32_t j = threadIdx.x; j < m; j += TRACE_BLOCK) s_id[j] = tri_id[base + j];
+        for (uint32_t j = threadIdx.x; j < m; j += TRACE_BLOCK) { s_id[j] = tri_id[base + j]; s_chain[j] = X.tri_chain ? X.tri_chain[base + j] : 0u; }
         __syncthreads();
         if (!live) continue;
         for (uint32_t j = 0; j < m; j++) {
@@ -134,7 +144,9 @@ k_trace_brute(const float* __restrict__ tri_in, const uint32_t* __restrict__ tri
             const v3 e2 = vsub(V(t[6], t[7], t[8]), v0);
             float tt, u, v;
             if (COUNT) cnt.tris++;
-            if (!triangle_test(o, d, v0, e1, e2, V(t[9], t[10], t[11]), t_min, best_t, tt, u, v)) continue;
+            v3 ol = o, dl = d;
+            if (s_chain[j]) chain_ray(X.frames, s_chain[j], o, d_raw, ol, dl);
+            if (!triangle_test(ol, dl, v0, e1, e2, V(t[9], t[10], t[11]), t_min, best_t, tt, u, v)) continue;
             if (tt == best_t && (best_id == CRT_MISS_ID || s_id[j] >= best_id)) continue;
             best_t = tt; best_u = u; best_v = v; best_id = s_id[j];
         }
@@ -143,19 +155,30 @@ k_trace_brute(const float* __restrict__ tri_in, const uint32_t* __restrict__ tri
         const uint32_t m = min((uint32_t)BRUTE_TILE, n_sph - base);
         __syncthreads();
         for (uint32_t j = threadIdx.x; j < m * 4; j += TRACE_BLOCK) s_prim[j] = sph_in[(size_t)base * 4 + j];
-        for (uint32_t j = threadIdx.x; j < m; j += TRACE_BLOCK) s_id[j] = sph_id[base + j];
+        for (uint32_t j = threadIdx.x; j < m; j += TRACE_BLOCK) { s_id[j] = sph_id[base + j]; s_chain[j] = X.sph_chain ? X.sph_chain[base + j] : 0u; }
         __syncthreads();
         if (!live) continue;
         for (uint32_t j = 0; j < m; j++) {
             const float* s = s_prim + 4 * j;
             float tt;
             if (COUNT) cnt.spheres++;
-            if (!sphere_test(vsub(o, V(s[0], s[1], s[2])), d, s[3], t_min, best_t, tt)) continue;
+            v3 ol = o, dl = d;
+            if (s_chain[j]) chain_ray(X.frames, s_chain[j], o, d_raw, ol, dl);
+            if (!sphere_test(vsub(ol, V(s[0], s[1], s[2])), dl, s[3], t_min, best_t, tt)) continue;
             if (tt == best_t && (best_id == CRT_MISS_ID || s_id[j] >= best_id)) continue;
             best_t = tt; best_u = 0.f; best_v = 0.f; best_id = s_id[j];
         }
     }
     if (live) {
+        for (uint32_t j = 0; j < X.n_rect; j++) {             // shapes/rectangle.h: few, read straight from global memory
+            float tt, u, v;
+            if (COUNT) cnt.spheres++;
+            v3 ol, dl;
+            chain_ray(X.frames, X.rect_chain[j], o, d_raw, ol, dl);
+            if (!rect_test(ol, dl, (X.rect_mat[j] & CRT_RECT_FLIP) != 0u, t_min, best_t, tt, u, v)) continue;
+            if (tt == best_t && (best_id == CRT_MISS_ID || X.rect_id[j] >= best_id)) continue;
+            best_t = tt; best_u = u; best_v = v; best_id = X.rect_id[j];
+        }
         const bool hit = best_id != CRT_MISS_ID;
         reinterpret_cast<float4*>(hits)[i] =
             make_float4(hit ? best_t : 0.0f, __uint_as_float(best_id), hit ? best_u : 0.0f, hit ? best_v : 0.0f);
@@ -170,13 +193,19 @@ int launch_trace(crt_ctx* c, const crt_ray* d_rays, size_t n, float t_min, float
     cudaStream_t st = c->stream;
     if (accel == CRT_ACCEL_BRUTE) {
         const unsigned int grid = (unsigned int)((n + TRACE_BLOCK - 1) / TRACE_BLOCK);
+        BruteExtra X;
+        X.frames = c->frames.as<DFrame>();
+        X.tri_chain = c->tri_has_chain ? c->tri_frame.as<uint32_t>() : nullptr;
+        X.sph_chain = c->sph_has_chain ? c->sph_frame.as<uint32_t>() : nullptr;
+        X.rect_chain = c->rect_frame.as<uint32_t>(); X.rect_mat = c->rect_mat.as<uint32_t>(); X.rect_id = c->rect_id.as<uint32_t>();
+        X.n_rect = (uint32_t)c->n_rect;
         if (c->count_work)
             k_trace_brute<true><<<grid, TRACE_BLOCK, 0, st>>>(c->tri_in.as<float>(), c->tri_id.as<uint32_t>(), (uint32_t)c->n_tri,
-                                                              c->sph_in.as<float>(), c->sph_id.as<uint32_t>(), (uint32_t)c->n_sph,
+                                                              c->sph_in.as<float>(), c->sph_id.as<uint32_t>(), (uint32_t)c->n_sph, X,
                                                               d_rays, n, t_min, t_max, d_hits, counters);
         else
             k_trace_brute<false><<<grid, TRACE_BLOCK, 0, st>>>(c->tri_in.as<float>(), c->tri_id.as<uint32_t>(), (uint32_t)c->n_tri,
-                                                               c->sph_in.as<float>(), c->sph_id.as<uint32_t>(), (uint32_t)c->n_sph,
+                                                               c->sph_in.as<float>(), c->sph_id.as<uint32_t>(), (uint32_t)c->n_sph, X,
                                                                d_rays, n, t_min, t_max, d_hits, counters);
     } else if (accel == CRT_ACCEL_LBVH || accel == CRT_ACCEL_LBVH_PACKET) {
         if (!c->accel_valid) { set_error("crt_trace: call crt_accel_build first"); return CRT_ERR_STATE; }
@@ -191,7 +220,7 @@ int launch_trace(crt_ctx* c, const crt_ray* d_rays, size_t n, float t_min, float
         size_t blocks = (want + (TP_BLOCK / 32) - 1) / (TP_BLOCK / 32);
         const size_t cap = (size_t)c->sm_count * bps;
         const unsigned int grid = (unsigned int)(blocks < cap ? blocks : cap);
-        const bool sph = c->n_sph > 0;
+        const bool sph = scene_is_general(c);
         uint32_t* wc = c->work_ctr.as<uint32_t>();
         const uint32_t un = (uint32_t)n;
         if (accel == CRT_ACCEL_LBVH_PACKET) {

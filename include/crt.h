@@ -189,6 +189,29 @@ int crt_scene_set_triangles(crt_ctx* ctx, const float* tri, const uint32_t* mat_
                             const uint32_t* prim_id, size_t n);
 int crt_scene_set_spheres(crt_ctx* ctx, const float* sph, const uint32_t* mat_id,
                           const uint32_t* prim_id, size_t n);
+/* ---- rotated and nested Hitables, rectangles: the reference's Transform (hitable/transform.h:7-55) ----
+ * Every Hitable::hit maps the ray into the object's own frame before the test and rotates the normal on the way
+ * back (hitable/hitable.h:29-38): direction re-normalised, origin and direction rotated by the Euler angles
+ * (core/vec3.h:200-217), position subtracted. The test then runs IN that frame and reports the hit point there
+ * (SURVEY 9 Q6). To reproduce that bit for bit a primitive may carry a CHAIN: the run of frames - one per Hitable
+ * from the world list down to the primitive itself, outermost first - its ray passes through. A chain word is
+ * (first << 8) | count into the table of crt_scene_set_frames; 0 is the plain case (a primitive directly in the world
+ * list under the identity, or a sphere whose only transform is its own translation, given as its centre): vertices
+ * and centres are then world-space values and no frame is read. With a chain the triangle vertices, the sphere
+ * centre (normally 0) and the rectangle live in the innermost frame. rows: the three rows of the matrix rotate()
+ * builds, computed by the caller (they need libm's sinf/cosf; host/scene.h:rotation_rows); has_rotation = 0 skips
+ * the multiplication (rotate() by zero angles is the identity). Scale other than 1 is not expressible (the
+ * reference's ScaleRay divides only the direction).
+ * crt_scene_set_frames drops every chain and rectangle set before it; set it first. */
+typedef struct { float rows[9]; float position[3]; uint32_t has_rotation; } crt_frame;
+int crt_scene_set_frames(crt_ctx* ctx, const crt_frame* frames, size_t n);
+int crt_scene_set_triangle_chains(crt_ctx* ctx, const uint32_t* chain, size_t n_tri);   /* after crt_scene_set_triangles */
+int crt_scene_set_sphere_chains(crt_ctx* ctx, const uint32_t* chain, size_t n_sph);     /* after crt_scene_set_spheres */
+/* shapes/rectangle.h:4-44: the unit square [-0.5, 0.5]^2 of its frame's z = 0 plane, normal +z (flip_normal: -z),
+ * answered only by rays that travel against the normal. chain and prim_id are required. */
+int crt_scene_set_rectangles(crt_ctx* ctx, const uint32_t* chain, const uint8_t* flip_normal, const uint32_t* mat_id,
+                             const uint32_t* prim_id, size_t n);
+
 /* Replaces updateFBXObj / update_pose (createScene.h:99-140): overwrite the
  * vertices of triangles [first, first+n) with n x 9 floats. Like
  * Triangle::SetVertices (shapes/triangle.h:40-45) the stored normals stay. */
