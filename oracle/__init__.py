@@ -95,6 +95,23 @@ class Scene:
             None if ids is None else ids.ctypes.data_as(C.c_void_p), n)
         self.n_prims += n
 
+    def add_chained(self, kind, data, mat, ids, levels, flip=None):
+        """n primitives under the chain of Transforms `levels` = [(position, rotation_degrees), ...], outermost first,
+        the last being the primitives' own (ref_scene_add_chained). kind 0: data (n, 12) triangles in their own
+        frame; 1: data (n,) radii; 2: rectangles (shapes/rectangle.h), flip (n,) = flipNormal."""
+        ids = np.ascontiguousarray(ids, np.uint32)
+        n = len(ids)
+        mat = np.ascontiguousarray(mat, np.uint32)
+        lv = np.ascontiguousarray(np.asarray([list(p) + list(r) for p, r in levels], np.float32).reshape(-1, 6))
+        d = np.zeros(1, np.float32) if data is None else np.ascontiguousarray(data, np.float32).reshape(-1)
+        fl = np.zeros(n, np.uint8) if flip is None else np.ascontiguousarray(flip, np.uint8)
+        fn = self.lib._fn("scene_add_chained")
+        fn.restype = C.c_int
+        fn.argtypes = [C.c_void_p, C.c_int, _f32p, _u32p, _u32p, _u8p, C.c_size_t, _f32p, C.c_int]
+        r = fn(self.h, int(kind), d, mat, ids, fl, n, lv, len(lv))
+        assert r == 0
+        self.n_prims += n
+
     def finalize(self):
         r = self.lib._fn("scene_finalize")(self.h)
         assert r == 0, "scene_finalize failed (bad material index?)"
@@ -224,6 +241,15 @@ class OracleLib:
         fn.argtypes = [_f32p, C.c_size_t, np.ctypeslib.ndpointer(np.uint8, flags="C_CONTIGUOUS")]
         fn(pts, len(pts), out)
         return out.astype(bool)
+
+    def rotation_rows(self, rot):
+        """The three rows of the matrix rotate() builds for Euler angles `rot` in degrees (core/vec3.h:200-214)."""
+        out = np.zeros(9, np.float32)
+        fn = self._fn("rotation_rows")
+        fn.restype = None
+        fn.argtypes = [_f32p, _f32p]
+        fn(np.ascontiguousarray(rot, np.float32), out)
+        return out
 
     def scatter(self, mtype, albedo, param, ray, p, normal, randoms):
         """One Material::scatter call with an injected (0,1] sequence.

@@ -84,7 +84,10 @@ typedef struct { v3 position, rotation, scale; } xform_t; /* hitable/transform.h
 typedef struct { float t; v3 p, normal; uint32_t mat; uint32_t id; float u, v; } hitrec_t; /* hitable/hitable.h:11-18 */
 
 typedef struct {
-    int kind;          /* 0 triangle, 1 sphere */
+    int kind;          /* 0 triangle, 1 sphere, 2 rectangle (shapes/rectangle.h) */
+    int flip;          /* rectangle: flipNormal */
+    int n_outer;       /* enclosing HitableLists between the world list and this primitive */
+    xform_t* outer;    /* their Transforms, outermost first */
     v3 v0, v1, v2, n;  /* triangle: shapes/triangle.h:49-50 */
     float radius;      /* sphere: shapes/sphere.h:22 */
     xform_t xf;
@@ -177,12 +180,39 @@ static int sphere_test(const prim_t* p, ray_t r, float t_min, float t_max, hitre
     return 0;
 }
 
-/* hitable/hitable.h:29-38 for one primitive */
+/* shapes/rectangle.h:21-44 */
+static int rect_test(const prim_t* p, ray_t r, float t_min, float t_max, hitrec_t* rec)
+{
+    v3 normal = p->flip ? V(0, 0, -1) : V(0, 0, 1);
+    if (vdot(r.d, normal) > 0) return 0;
+    float t = -r.o.z / r.d.z;
+    if (t < t_min || t > t_max) return 0;
+    float x0 = -0.5f, x1 = 0.5f, y0 = -0.5f, y1 = 0.5f;
+    float x = r.o.x + t * r.d.x;
+    float y = r.o.y + t * r.d.y;
+    if (x < x0 || x > x1 || y < y0 || y > y1) return 0;
+    rec->u = (x - x0) / (x1 - x0);
+    rec->v = (y - y0) / (y1 - y0);
+    rec->t = t;
+    rec->mat = p->mat;
+    rec->id = p->id;
+    rec->p = vadd(r.o, vscale(t, r.d));
+    rec->normal = normal;
+    return 1;
+}
+
+/* hitable/hitable.h:29-38 for one primitive, below the HitableLists that enclose it (each of them a Hitable whose
+ * hit() transforms the ray on the way down and rotates the normal on the way up; a list of one entry returns its
+ * entry's hit when t < t_max, hitable_list.h:84) */
 static int prim_hit(const prim_t* p, ray_t r, float t_min, float t_max, int d1, hitrec_t* rec)
 {
+    for (int l = 0; l < p->n_outer; l++) r = transform_ray(&p->outer[l], r);
     ray_t lr = transform_ray(&p->xf, r);
-    int flag = p->kind == 0 ? triangle_test(p, lr, t_min, t_max, d1, rec) : sphere_test(p, lr, t_min, t_max, rec);
+    int flag = p->kind == 0 ? triangle_test(p, lr, t_min, t_max, d1, rec)
+             : p->kind == 1 ? sphere_test(p, lr, t_min, t_max, rec) : rect_test(p, lr, t_min, t_max, rec);
     if (flag) rec->normal = vrotate(rec->normal, p->xf.rotation);
+    if (flag && p->n_outer > 0 && !(rec->t < t_max)) flag = 0;
+    if (flag) for (int l = p->n_outer - 1; l >= 0; l--) rec->normal = vrotate(rec->normal, p->outer[l].rotation);
     return flag;
 }
 
@@ -492,6 +522,45 @@ void oracle_scene_add_spheres(void* h, const float* sph, const uint32_t* mat, co
         p[i].radius = sph[4 * i + 3];
         p[i].mat = mat ? mat[i] : 0;
         p[i].id = ids ? ids[i] : (uint32_t)(base + i);
+    }
+}
+
+/* same contract as ref_scene_add_chained (oracle/ref_harness.cpp) */
+int oracle_scene_add_chained(void* h, int kind, const float* data, const uint32_t* mat, const uint32_t* ids, const uint8_t* flip,
+                             size_t n, const float* levels, int n_levels)
+{
+    struct oracle_scene* s = (struct oracle_scene*)h;
+    if (kind < 0 || kind > 2 || n_levels < 1 || !levels || !ids) return -1;
+    prim_t* p = push_prims(s, n);
+    for (size_t i = 0; i < n; i++) {
+        memset(&p[i], 0, sizeof(prim_t));
+        p[i].kind = kind;
+        if (kind == 0) {
+            const float* t = data + 12 * i;
+            p[i].v0 = V(t[0], t[1], t[2]); p[i].v1 = V(t[3], t[4], t[5]); p[i].v2 = V(t[6], t[7], t[8]);
+            p[i].n = V(t[9], t[10], t[11]);
+        }
+        if (kind == 1) p[i].radius = data[i];
+        p[i].flip = flip ? flip[i] : 0;
+        p[i].n_outer = n_levels - 1;
+        p[i].outer = p[i].n_outer ? (xform_t*)malloc(sizeof(xform_t) * (size_t)p[i].n_outer) : NULL;
+        for (int l = 0; l < n_levels; l++) {
+            const float* q = levels + 6 * l;
+            xform_t x = {{q[0], q[1], q[2]}, {q[3], q[4], q[5]}, {1, 1, 1}};
+            if (l < n_levels - 1) p[i].outer[l] = x; else p[i].xf = x;
+        }
+        p[i].mat = mat ? mat[i] : 0;
+        p[i].id = ids[i];
+    }
+    return 0;
+}
+
+/* the rows rotate() builds (vec3.h:211-213), as ref_rotation_rows */
+void oracle_rotation_rows(const float* rot3, float* out9)
+{
+    for (int j = 0; j < 3; j++) {
+        v3 v = vrotate(V(j == 0 ? 1.f : 0.f, j == 1 ? 1.f : 0.f, j == 2 ? 1.f : 0.f), V(rot3[0], rot3[1], rot3[2]));
+        out9[j] = v.x; out9[3 + j] = v.y; out9[6 + j] = v.z;
     }
 }
 

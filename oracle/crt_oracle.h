@@ -17,6 +17,9 @@ void   oracle_checker_odd(const float* points, size_t n, uint8_t* out);
 int    oracle_scene_add_checker_material(void* scene, uint32_t type, const float* even, const float* odd);
 void   oracle_scene_add_triangles(void* scene, const float* tri, const uint32_t* mat, const uint32_t* ids, size_t n);
 void   oracle_scene_add_spheres(void* scene, const float* sph, const uint32_t* mat, const uint32_t* ids, size_t n);
+int    oracle_scene_add_chained(void* scene, int kind, const float* data, const uint32_t* mat, const uint32_t* ids,
+                                const uint8_t* flip, size_t n, const float* levels, int n_levels);
+void   oracle_rotation_rows(const float* rot3, float* out9);
 int    oracle_scene_finalize(void* scene);
 double oracle_trace(void* scene, const float* rays, size_t n, float t_min, float t_max, int use_bvh,
                     float* out_t, uint32_t* out_id, float* out_p, float* out_n);

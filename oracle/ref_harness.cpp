@@ -43,6 +43,7 @@
 #include "hitable/bvh.h"
 #include "shapes/sphere.h"
 #include "shapes/triangle.h"
+#include "shapes/rectangle.h"
 #include "material/material.h"
 #include "Loader/obj_loader.h"
 
@@ -89,11 +90,28 @@ public:
     uint32_t id;
 };
 
+class TaggedRectangle : public Rectangle {
+public:
+    TaggedRectangle(Material* m, bool flip, Transform* t, uint32_t id_) : Rectangle(m, flip, t), id(id_) {}
+    bool collision_detection(const Ray& r, float t_min, float t_max, HitRecord& rec,
+                             int frameIndex) const override
+    {
+        if (!Rectangle::collision_detection(r, t_min, t_max, rec, frameIndex)) return false;
+        tag(rec, id);                               // Rectangle writes rec.u / rec.v (rectangle.h:37-38); the id replaces them
+        return true;
+    }
+    uint32_t id;
+};
+
 struct PendingPrim {
-    int kind;  // 0 triangle, 1 sphere
+    int kind;  // 0 triangle, 1 sphere, 2 rectangle
     float data[12];
     uint32_t mat;
     uint32_t id;
+    int flip = 0;
+    // Transforms of the Hitables between the world list and this primitive, outermost first; the last one is the
+    // primitive's own. Empty: the plain case (identity for a triangle, position = centre for a sphere).
+    std::vector<float> levels;   // 6 floats each: position, rotation in degrees
 };
 
 struct RefScene {
@@ -266,6 +284,43 @@ void ref_scene_add_spheres(void* h, const float* sph, const uint32_t* mat, const
     }
 }
 
+// Primitives under a chain of Transforms: `levels` (n_levels x 6 floats: position, rotation in degrees) are the
+// Transforms of the Hitables between the world list and the primitive, outermost first, the last being the
+// primitive's own. kind 0: data = n x 12 floats (v0 v1 v2 normal in the primitive's frame); kind 1: data = n radii;
+// kind 2 (Rectangle, shapes/rectangle.h): no data, flip = flipNormal per rectangle. Every primitive gets its own
+// nest of single-entry HitableLists, which the list scan cannot tell from shared ones.
+int ref_scene_add_chained(void* h, int kind, const float* data, const uint32_t* mat, const uint32_t* ids, const uint8_t* flip,
+                          size_t n, const float* levels, int n_levels)
+{
+    RefScene* s = (RefScene*)h;
+    if (kind < 0 || kind > 2 || n_levels < 1 || !levels || !ids) return -1;
+    for (size_t i = 0; i < n; i++) {
+        PendingPrim p;
+        p.kind = kind;
+        memset(p.data, 0, sizeof p.data);
+        if (kind == 0) memcpy(p.data, data + 12 * i, 48);
+        if (kind == 1) p.data[3] = data[i];
+        p.mat = mat ? mat[i] : 0;
+        p.id = ids[i];
+        p.flip = flip ? flip[i] : 0;
+        p.levels.assign(levels, levels + 6 * (size_t)n_levels);
+        s->pending.push_back(p);
+    }
+    return 0;
+}
+
+// rotate(v, rotation) (core/vec3.h:200-217) applied to the three unit vectors: out9[3 k + j] = rotate(e_j)[k], i.e.
+// the rows rotate0..2 the function builds, as this host's libm evaluates them.
+void ref_rotation_rows(const float* rot3, float* out9)
+{
+    const vec3 r(rot3[0], rot3[1], rot3[2]);
+    for (int j = 0; j < 3; j++) {
+        vec3 e(j == 0 ? 1.f : 0.f, j == 1 ? 1.f : 0.f, j == 2 ? 1.f : 0.f);
+        vec3 v = rotate(e, r);
+        for (int k = 0; k < 3; k++) out9[3 * k + j] = v[k];
+    }
+}
+
 // Builds the reference objects. The world is a HitableList whose entry order
 // is ascending prim id, i.e. the caller's list order, with an explicit
 // identity Transform (the reference's default-constructed one is
@@ -278,6 +333,31 @@ int ref_scene_finalize(void* h)
     for (const PendingPrim& p : s->pending) {
         if (p.mat >= s->mats.size()) return -1;
         Material* m = s->mats[p.mat];
+        if (!p.levels.empty()) {
+            // one nested HitableList per enclosing level, then the primitive under its own Transform
+            const size_t nl = p.levels.size() / 6;
+            auto xf = [&](size_t l) {
+                const float* q = p.levels.data() + 6 * l;
+                return new Transform(vec3(q[0], q[1], q[2]), vec3(q[3], q[4], q[5]), vec3(1));
+            };
+            Hitable* leaf;
+            if (p.kind == 0) {
+                vec3 vs[3] = {vec3(p.data[0], p.data[1], p.data[2]), vec3(p.data[3], p.data[4], p.data[5]),
+                              vec3(p.data[6], p.data[7], p.data[8])};
+                leaf = new TaggedTriangle(vs, vec3(p.data[9], p.data[10], p.data[11]), m, xf(nl - 1), p.id, s->d1 != 0);
+            } else if (p.kind == 1) {
+                leaf = new TaggedSphere(xf(nl - 1), p.data[3], m, p.id);
+            } else {
+                leaf = new TaggedRectangle(m, p.flip != 0, xf(nl - 1), p.id);
+            }
+            for (size_t l = nl - 1; l-- > 0;) {
+                Hitable** one = (Hitable**)malloc(sizeof(Hitable*));
+                one[0] = leaf;
+                leaf = new HitableList(one, 1, xf(l));
+            }
+            s->prims.push_back(leaf);
+            continue;
+        }
         if (p.kind == 0) {
             vec3 vs[3] = {vec3(p.data[0], p.data[1], p.data[2]), vec3(p.data[3], p.data[4], p.data[5]),
                           vec3(p.data[6], p.data[7], p.data[8])};

@@ -26,6 +26,12 @@ def oracle_scene(lib, sc, d1=True):
         s.add_triangles(sc["tri"], sc["tri_mat"], np.arange(nt, dtype=np.uint32))
     if ns:
         s.add_spheres(sc["sph"], sc["sph_mat"], np.arange(nt, nt + ns, dtype=np.uint32))
+    next_id = nt + ns
+    for it in sc.get("chained", []):            # ids continue in list order, as scenes.flatten_chained numbers them
+        mat = np.asarray(it["mat"], np.uint32).reshape(-1)
+        ids = np.arange(next_id, next_id + len(mat), dtype=np.uint32)
+        next_id += len(mat)
+        s.add_chained(it["kind"], it.get("data"), mat, ids, it["levels"], it.get("flip"))
     return s.finalize()
 
 
