@@ -29,6 +29,7 @@ TILE = 32
 ABI_SYMBOLS = [
     "crt_abi_version", "crt_create", "crt_destroy", "crt_last_error", "crt_set_option", "crt_sync", "crt_stream",
     "crt_scene_set_materials", "crt_scene_set_triangles", "crt_scene_set_spheres", "crt_scene_update_vertices",
+    "crt_scene_set_frames", "crt_scene_set_triangle_chains", "crt_scene_set_sphere_chains", "crt_scene_set_rectangles",
     "crt_scene_set_indices", "crt_scene_update_points", "crt_scene_set_parts", "crt_scene_move_parts",
     "crt_render_frame_pose", "crt_scene_pose_async",
     "crt_accel_build", "crt_accel_refit", "crt_trace", "crt_trace_device", "crt_render", "crt_render_frame",
@@ -94,6 +95,10 @@ def load_library():
     lib.crt_scene_set_triangles.argtypes = [vp, vp, vp, vp, sz]
     lib.crt_scene_set_spheres.argtypes = [vp, vp, vp, vp, sz]
     lib.crt_scene_update_vertices.argtypes = [vp, vp, sz, sz]
+    lib.crt_scene_set_frames.argtypes = [vp, vp, sz]
+    lib.crt_scene_set_triangle_chains.argtypes = [vp, vp, sz]
+    lib.crt_scene_set_sphere_chains.argtypes = [vp, vp, sz]
+    lib.crt_scene_set_rectangles.argtypes = [vp, vp, vp, vp, vp, sz]
     lib.crt_scene_set_indices.argtypes = [vp, vp, sz, sz, sz]
     lib.crt_scene_update_points.argtypes = [vp, vp, sz]
     lib.crt_render_frame_pose.argtypes = [vp, C.c_int, vp, sz, sz, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint64, vp]
@@ -239,9 +244,42 @@ class Context:
         ids = None if ids is None else np.ascontiguousarray(ids, np.uint32)
         self._check(self.lib.crt_scene_set_spheres(self._h, _ptr(sph), _ptr(mat), _ptr(ids), sph.shape[0]))
 
+    def set_frames(self, frames):
+        """crt_scene_set_frames: (n, 13) float32 rows = 9 matrix entries, position, has_rotation."""
+        fr = np.ascontiguousarray(frames, np.float32).reshape(-1, 13)
+        raw = np.zeros((len(fr), 13), np.uint32)
+        raw[:, :12] = fr[:, :12].view(np.uint32)
+        raw[:, 12] = (fr[:, 12] != 0).astype(np.uint32)
+        self._check(self.lib.crt_scene_set_frames(self._h, _ptr(raw), raw.shape[0]))
+
+    def set_triangle_chains(self, chain):
+        chain = np.ascontiguousarray(chain, np.uint32)
+        self._check(self.lib.crt_scene_set_triangle_chains(self._h, _ptr(chain), chain.shape[0]))
+
+    def set_sphere_chains(self, chain):
+        chain = np.ascontiguousarray(chain, np.uint32)
+        self._check(self.lib.crt_scene_set_sphere_chains(self._h, _ptr(chain), chain.shape[0]))
+
+    def set_rectangles(self, chain, flip, mat, ids):
+        chain, mat, ids = (np.ascontiguousarray(a, np.uint32) for a in (chain, mat, ids))
+        flip = np.ascontiguousarray(flip, np.uint8)
+        self._check(self.lib.crt_scene_set_rectangles(self._h, _ptr(chain), _ptr(flip), _ptr(mat), _ptr(ids), chain.shape[0]))
+
     def set_scene(self, scene):
-        """Upload a scenes.py dict; triangles get ids 0..n_tri-1, spheres follow."""
+        """Upload a scenes.py dict; triangles get ids 0..n_tri-1, spheres follow, then the primitives of
+        scene["chained"] (rotated / nested Hitables and rectangles, scenes.flatten_chained) in list order."""
         self.set_materials(scene["mats"])
+        if scene.get("chained"):
+            from . import scenes as _scenes
+            f = _scenes.flatten_chained(scene)
+            self.set_frames(f["frames"])
+            self.set_triangles(f["tri"], f["tri_mat"], f["tri_id"])
+            self.set_triangle_chains(f["tri_chain"])
+            self.set_spheres(f["sph"], f["sph_mat"], f["sph_id"])
+            self.set_sphere_chains(f["sph_chain"])
+            self.set_rectangles(f["rect_chain"], f["rect_flip"], f["rect_mat"], f["rect_id"])
+            return
+        self.set_frames(np.zeros((0, 13), np.float32))
         self.set_triangles(scene["tri"], scene["tri_mat"])
         self.set_spheres(scene["sph"], scene["sph_mat"])
 

@@ -58,6 +58,88 @@ def rng_uniform(key, ctr):
     return ((bits >> np.uint32(8)) + np.uint32(1)).astype(np.float32) * np.float32(1.0 / 16777216.0)
 
 
+_libm = None
+
+
+def _sincosf(x):
+    """libm's sinf / cosf of a float32, as the host-compiled reference calls them (core/vec3.h:202-209)."""
+    global _libm
+    import ctypes as C
+    if _libm is None:
+        _libm = C.CDLL("libm.so.6")
+        for f in (_libm.sinf, _libm.cosf):
+            f.restype = C.c_float
+            f.argtypes = [C.c_float]
+    return np.float32(_libm.sinf(float(x))), np.float32(_libm.cosf(float(x)))
+
+
+def rotation_rows(rot):
+    """rotate()'s matrix (core/vec3.h:200-214) for Euler angles in degrees: rows rotate0, rotate1, rotate2 as nine
+    float32 values, every product and sum rounded to float32 in the reference's order (the Z angle is negated)."""
+    f = np.float32
+    rx = f(np.float64(np.pi / 180.0) * np.float64(f(rot[0])))
+    ry = f(np.float64(np.pi / 180.0) * np.float64(f(rot[1])))
+    rz = f(np.float64(-(np.pi / 180.0)) * np.float64(f(rot[2])))
+    (sx, cx), (sy, cy), (sz, cz) = _sincosf(rx), _sincosf(ry), _sincosf(rz)
+    r0 = [cy * cz, (-cy) * sz, sy]
+    r1 = [f(f(sx * sy) * cz) + f(cx * sz), f(f((-sx) * sy) * sz) + f(cx * cz), (-sx) * cy]
+    r2 = [f(f((-cx) * sy) * cz) + f(sx * sz), f(f(cx * sy) * sz) + f(sx * cz), cx * cy]
+    return np.asarray(r0 + r1 + r2, np.float32)
+
+
+IDENTITY_ROWS = np.asarray([1, 0, 0, 0, 1, 0, 0, 0, 1], np.float32)
+
+
+def flatten_chained(scene):
+    """The arrays crt_scene_set_frames / _triangle_chains / _sphere_chains / _rectangles take for scene["chained"]:
+    a list of items dict(kind, data, mat, levels[, flip]) - `levels` are the (position, rotation) pairs of the
+    Transforms between the world list and the item's primitives, outermost first, the last the primitives' own
+    (oracle.Scene.add_chained takes the same). On the device a chain also holds the world list's own identity
+    level, because every level re-normalises the direction (crt_device.cuh:chain_ray). Primitive ids: the plain
+    triangles, the plain spheres, then the items in list order (the order of the reference's world list).
+    Returns dict(frames (n, 13), tri, tri_mat, tri_id, tri_chain, sph, sph_mat, sph_id, sph_chain,
+    rect_chain, rect_flip, rect_mat, rect_id)."""
+    frames = []
+    n_t, n_s = len(scene["tri"]), len(scene["sph"])
+    tri, tri_mat, tri_chain = [scene["tri"]], [scene["tri_mat"]], [np.zeros(n_t, np.uint32)]
+    sph, sph_mat, sph_chain = [scene["sph"]], [scene["sph_mat"]], [np.zeros(n_s, np.uint32)]
+    next_id = n_t + n_s
+    tri_id = [np.arange(n_t, dtype=np.uint32)]
+    sph_id = [np.arange(n_t, next_id, dtype=np.uint32)]
+    rect = dict(chain=[], flip=[], mat=[], id=[])
+    for it in scene.get("chained", []):
+        first = len(frames)
+        frames.append(np.concatenate([IDENTITY_ROWS, np.zeros(3, np.float32), [0]]))
+        for pos, rot in it["levels"]:
+            has_rot = any(float(a) != 0.0 for a in rot)
+            rows = rotation_rows(rot) if has_rot else IDENTITY_ROWS
+            frames.append(np.concatenate([rows, np.asarray(pos, np.float32), [1 if has_rot else 0]]))
+        chain = np.uint32((first << 8) | (len(it["levels"]) + 1))
+        mat = np.asarray(it["mat"], np.uint32).reshape(-1)
+        n = len(mat)
+        ids = np.arange(next_id, next_id + n, dtype=np.uint32)
+        next_id += n
+        if it["kind"] == 0:
+            tri.append(np.asarray(it["data"], np.float32).reshape(-1, 12)); tri_mat.append(mat); tri_id.append(ids)
+            tri_chain.append(np.full(n, chain, np.uint32))
+        elif it["kind"] == 1:
+            r = np.asarray(it["data"], np.float32).reshape(-1, 1)
+            sph.append(np.concatenate([np.zeros((n, 3), np.float32), r], axis=1)); sph_mat.append(mat); sph_id.append(ids)
+            sph_chain.append(np.full(n, chain, np.uint32))
+        else:
+            rect["chain"].append(np.full(n, chain, np.uint32)); rect["mat"].append(mat); rect["id"].append(ids)
+            rect["flip"].append(np.asarray(it.get("flip", np.zeros(n)), np.uint8).reshape(-1))
+
+    def cat(parts, dt):
+        return np.ascontiguousarray(np.concatenate(parts).astype(dt)) if parts else np.zeros((0,), dt)
+
+    return dict(frames=np.ascontiguousarray(np.stack(frames).astype(np.float32)) if frames else np.zeros((0, 13), np.float32),
+                tri=cat(tri, np.float32).reshape(-1, 12), tri_mat=cat(tri_mat, np.uint32), tri_id=cat(tri_id, np.uint32),
+                tri_chain=cat(tri_chain, np.uint32), sph=cat(sph, np.float32).reshape(-1, 4), sph_mat=cat(sph_mat, np.uint32),
+                sph_id=cat(sph_id, np.uint32), sph_chain=cat(sph_chain, np.uint32), rect_chain=cat(rect["chain"], np.uint32),
+                rect_flip=cat(rect["flip"], np.uint8), rect_mat=cat(rect["mat"], np.uint32), rect_id=cat(rect["id"], np.uint32))
+
+
 class Stream:
     """Sequential (0, 1] draws of one stream, for host-side scene generation."""
 
