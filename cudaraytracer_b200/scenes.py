@@ -493,6 +493,110 @@ def light_panels(nx=160, ny=120, spp=8):
                 nx=nx, ny=ny, spp=spp, max_depth=8)
 
 
+def rotated_scene(seed=1, n_items=24, nx=160, ny=120, spp=4):
+    """Triangles, spheres and rectangles under the reference's Transform (hitable/transform.h): own rotations and
+    translations, identity levels, and up to three nested HitableLists, beside plain primitives - the cases of
+    VERDICT r1 row a8. Lengths ~1, spread over ~10 units around the origin."""
+    rng = np.random.default_rng(seed)
+    f = np.float32
+    mats = [(LAMBERTIAN, (0.7, 0.3, 0.2), 0.0), (METAL, (0.8, 0.8, 0.9), 0.1), (DIELECTRIC, (1, 1, 1), 1.5),
+            (DIFFUSE_LIGHT, (3.0, 2.5, 2.0), 0.0), (LAMBERTIAN, (0.2, 0.3, 0.1), 0.0, (0.9, 0.9, 0.9))]
+
+    def tris(n, scale=2.0):
+        v0 = rng.normal(size=(n, 3)) * 0.5
+        v1 = v0 + rng.normal(size=(n, 3)) * scale
+        v2 = v0 + rng.normal(size=(n, 3)) * scale
+        nrm = np.cross(v1 - v0, v2 - v0)
+        nrm /= np.linalg.norm(nrm, axis=1, keepdims=True)
+        nrm *= rng.choice([-1.0, 1.0], size=(n, 1))
+        return np.concatenate([v0, v1, v2, nrm], axis=1).astype(f)
+
+    def level(kind):
+        pos = (rng.normal(size=3) * 4.0).astype(f)
+        rot = (rng.normal(size=3) * [60.0, 120.0, 45.0]).astype(f)
+        if kind == "identity":
+            return (np.zeros(3, f), np.zeros(3, f))
+        if kind == "translate":
+            return (pos, np.zeros(3, f))
+        if kind == "rotate":
+            return (np.zeros(3, f), rot)
+        if kind == "axis":                       # multiples of 90 degrees: sin/cos land on (almost) 0 and 1
+            return (pos, (rng.integers(-2, 3, size=3) * 90).astype(f))
+        return (pos, rot)
+
+    kinds = ["full", "full", "rotate", "translate", "identity", "axis"]
+    chained = []
+    for i in range(n_items):
+        depth = 1 + (i % 3)
+        levels = [level(kinds[int(rng.integers(0, len(kinds)))]) for _ in range(depth)]
+        what = i % 4
+        n = int(rng.integers(1, 4))
+        mat = rng.integers(0, len(mats), size=n).astype(np.uint32)
+        if what in (0, 3):
+            chained.append(dict(kind=0, data=tris(n), mat=mat, levels=levels))
+        elif what == 1:
+            chained.append(dict(kind=1, data=(rng.uniform(0.5, 2.0, size=n) * rng.choice([1.0, 1.0, -1.0], size=n)).astype(f), mat=mat, levels=levels))
+        else:
+            chained.append(dict(kind=2, data=None, mat=mat, flip=rng.integers(0, 2, size=n).astype(np.uint8), levels=levels))
+    plain = tris(6)
+    plain[:, 0:9] += np.tile(rng.normal(size=(6, 3)) * 4.0, (1, 3)).astype(f)
+    sph = np.concatenate([rng.normal(size=(5, 3)) * 4.0, rng.uniform(0.5, 1.5, size=(5, 1))], axis=1).astype(f)
+    return dict(name="rotated_%d" % seed, tri=np.ascontiguousarray(plain), tri_mat=rng.integers(0, len(mats), size=6).astype(np.uint32),
+                sph=np.ascontiguousarray(sph), sph_mat=rng.integers(0, len(mats), size=5).astype(np.uint32), mats=mats, chained=chained,
+                camera=camera_dict((0, 3, 26), (0, 0, 0), 40, aperture=0.05, focus_dist=24.0), nx=nx, ny=ny, spp=spp, max_depth=8)
+
+
+def cornell_box(nx=200, ny=200, spp=8, obj_path=None):
+    """A Cornell box out of the reference's own parts (row f3 of SURVEY 8f): five walls and a ceiling light that are
+    Rectangles - the unit square of shapes/rectangle.h, turned and placed by Transform rotations (scale stays 1,
+    SURVEY 9 Q7, so the box is one unit wide) - the short block of objects/cbox_smallbox.obj (a//n faces, scaled by
+    1/555 into the unit box) as triangles under two nested lists, a glass sphere under a rotated Transform, a
+    checkered floor. A Rectangle answers rays that travel AGAINST its normal (rectangle.h:24), a Triangle rays that
+    travel ALONG its stored normal (triangle.h:61)."""
+    f = np.float32
+    mats = [(LAMBERTIAN, (0.73, 0.73, 0.73), 0.0), (LAMBERTIAN, (0.65, 0.05, 0.05), 0.0), (LAMBERTIAN, (0.12, 0.45, 0.15), 0.0),
+            (DIFFUSE_LIGHT, (1.2, 1.2, 1.1), 0.0), (LAMBERTIAN, (0.73, 0.73, 0.73), 0.0, (0.2, 0.2, 0.6)), (DIELECTRIC, (1, 1, 1), 1.5),
+            (METAL, (0.8, 0.85, 0.88), 0.0)]
+
+    def rect(pos, rot, mat, flip=0):
+        return dict(kind=2, data=None, mat=np.asarray([mat], np.uint32), flip=np.asarray([flip], np.uint8),
+                    levels=[(np.asarray(pos, f), np.asarray(rot, f))])
+
+    # The box spans [-0.5, 0.5]^3 and the camera looks down -z from z = 2.4. A frame maps WORLD to LOCAL: local =
+    # rotate(world) - position (transform.h:38-48). A wall whose inward normal is N sits at C = -0.5 N; its rotation
+    # must turn N into the rectangle's +z, and then position = rotate(C) = (0, 0, -0.5) for every wall.
+    wall = (0.0, 0.0, -0.5)
+    chained = [
+        rect(wall, (0, 0, 0), 0),                              # back wall, N = +z
+        rect(wall, (90, 0, 0), 4),                             # floor, N = +y, checkered
+        rect(wall, (-90, 0, 0), 0),                            # ceiling, N = -y
+        rect(wall, (0, -90, 0), 1),                            # wall at x = -0.5, N = +x, red
+        rect(wall, (0, 90, 0), 2),                             # wall at x = +0.5, N = -x, green
+        rect((0.0, 0.0, -0.49), (-90, 0, 0), 3),               # a luminous sheet just below the ceiling
+    ]
+    tri = np.zeros((0, 12), f)
+    if obj_path is None:
+        obj_path = os.path.join(_GOLDEN, "cbox_smallbox.npz")
+    if os.path.exists(obj_path):
+        g = np.load(obj_path)
+        pts = (g["points"].astype(f) / f(555.0)).astype(f)
+        idx = g["idx"].astype(np.int64) - 1
+        v0, v1, v2 = pts[idx[:, 2]], pts[idx[:, 1]], pts[idx[:, 0]]     # winding reversed as createScene.h:183
+        tri = pack_tris(v0, v1, v2)
+        tri[:, 9:12] = -tri_normals(v0, v1, v2)                           # stored normals point into the block (SURVEY 9 Q1)
+    if len(tri):
+        # the block sits under two nested lists: a shift to the floor, a turn about y, then its own offset
+        chained.append(dict(kind=0, data=tri, mat=np.full(len(tri), 6, np.uint32),
+                            levels=[(np.asarray((0.12, -0.5, -0.05), f), np.zeros(3, f)), (np.zeros(3, f), np.asarray((0, 20, 0), f)),
+                                    (np.asarray((-0.335, 0.0, -0.303), f), np.zeros(3, f))]))
+    chained.append(dict(kind=1, data=np.asarray([0.17], f), mat=np.asarray([5], np.uint32),
+                        levels=[(rotation_rows((0, 30, 0)).reshape(3, 3) @ np.asarray((-0.22, -0.33, 0.18), f), np.asarray((0, 30, 0), f))]))
+    e_tri, e_mat = _empty_tris()
+    e_sph, e_smat = _empty_sph()
+    return dict(name="cornell_unit", tri=e_tri, tri_mat=e_mat, sph=e_sph, sph_mat=e_smat, mats=mats, chained=chained,
+                camera=camera_dict((0, 0, 2.4), (0, 0, 0), 40), nx=nx, ny=ny, spp=spp, max_depth=8)
+
+
 def checker_scene(nx=160, ny=100, spp=4):
     """CheckerTexture (material/texture.h:25-42) under a Lambertian and under a DiffuseLight, on triangles and on
     spheres: a checkered ground sphere in the manner of the reference's random scene, a checkered wall of triangles

@@ -81,6 +81,67 @@ void emu_trace(const float* tri, const uint32_t* tri_id, uint32_t n_tri, const f
     }
 }
 
+// The same scan over primitives under chains of Transforms (crt_device.cuh:framed_test), the host twin of what the
+// traversal kernels run for them: frames = n x 13 floats (9 rows, position, has_rotation), kind / chain / ids per
+// primitive in id order, tri12 / sph4 indexed by `slot` (position in its kind's array). Also returns the hit point
+// and the normal as shade() would see them (local frame, normal rotated up the chain).
+void emu_trace_chained(const float* frames13, uint32_t n_frames, const uint32_t* kind, const uint32_t* chain, const uint32_t* slot,
+                       const uint32_t* ids, const uint8_t* flip, uint32_t n_prims, const float* tri12, const float* sph4,
+                       const float* rays, size_t n, float t_min, float t_max, float* out_t, uint32_t* out_id, float* out_p, float* out_n)
+{
+    DFrame* fr = new DFrame[n_frames ? n_frames : 1];
+    for (uint32_t i = 0; i < n_frames; i++) {
+        memcpy(fr[i].m, frames13 + 13 * i, 36);
+        fr[i].px = frames13[13 * i + 9]; fr[i].py = frames13[13 * i + 10]; fr[i].pz = frames13[13 * i + 11];
+        fr[i].has_rot = frames13[13 * i + 12] != 0.f;
+    }
+    for (size_t i = 0; i < n; i++) {
+        const float* q = rays + 6 * i;
+        const v3 o = V(q[0], q[1], q[2]), d_raw = V(q[3], q[4], q[5]);
+        const v3 d = ray_dir_local(d_raw);
+        float best = t_max;
+        uint32_t best_id = CRT_MISS_ID, best_j = 0;
+        for (uint32_t j = 0; j < n_prims; j++) {
+            float4 r0 = make_float4(0, 0, 0, 0), r1 = r0, r2 = r0;
+            uint32_t info = 0;
+            if (kind[j] == 0) {
+                const float* t = tri12 + 12 * (size_t)slot[j];
+                const v3 v0 = V(t[0], t[1], t[2]), e1 = vsub(V(t[3], t[4], t[5]), v0), e2 = vsub(V(t[6], t[7], t[8]), v0);
+                r0 = make_float4(v0.x, v0.y, v0.z, t[9]); r1 = make_float4(e1.x, e1.y, e1.z, t[10]); r2 = make_float4(e2.x, e2.y, e2.z, t[11]);
+            } else if (kind[j] == 1) {
+                const float* s = sph4 + 4 * (size_t)slot[j];
+                r0 = make_float4(s[0], s[1], s[2], s[3]);
+                info = CRT_KIND_SPHERE;
+            } else {
+                info = CRT_KIND_RECT | (flip[j] ? CRT_RECT_FLIP : 0u);
+            }
+            float tt, u, v;
+            bool ok;
+            if (chain[j]) ok = framed_test(fr, chain[j], info, r0, r1, r2, o, d_raw, t_min, best, tt, u, v);
+            else if (kind[j] == 1) ok = sphere_test(vsub(o, V(r0.x, r0.y, r0.z)), d, r0.w, t_min, best, tt);
+            else ok = triangle_test(o, d, V(r0.x, r0.y, r0.z), V(r1.x, r1.y, r1.z), V(r2.x, r2.y, r2.z), V(r0.w, r1.w, r2.w), t_min, best, tt, u, v);
+            if (!ok) continue;
+            if (tt == best && (best_id == CRT_MISS_ID || ids[j] >= best_id)) continue;
+            best = tt; best_id = ids[j]; best_j = j;
+        }
+        out_t[i] = best_id != CRT_MISS_ID ? best : 0.f;
+        out_id[i] = best_id;
+        if (best_id == CRT_MISS_ID) continue;
+        // hit point and normal as render.cu:shade_step derives them
+        const uint32_t j = best_j;
+        v3 ol = o, dl;
+        if (chain[j]) chain_ray(fr, chain[j], o, d_raw, ol, dl); else dl = d;
+        v3 p, nn;
+        if (kind[j] == 1) { const float* s = sph4 + 4 * (size_t)slot[j]; p = vadd(vsub(ol, V(s[0], s[1], s[2])), vscale(best, dl)); nn = vdivf(p, s[3]); }
+        else if (kind[j] == 2) { p = vadd(ol, vscale(best, dl)); nn = V(0.f, 0.f, flip[j] ? -1.f : 1.f); }
+        else { const float* t = tri12 + 12 * (size_t)slot[j]; p = vadd(ol, vscale(best, dl)); nn = V(t[9], t[10], t[11]); }
+        if (chain[j]) nn = chain_normal(fr, chain[j], nn);
+        out_p[3 * i] = p.x; out_p[3 * i + 1] = p.y; out_p[3 * i + 2] = p.z;
+        out_n[3 * i] = nn.x; out_n[3 * i + 1] = nn.y; out_n[3 * i + 2] = nn.z;
+    }
+    delete[] fr;
+}
+
 void emu_sky(const float* d, float* out)
 {
     v3 s = background_sky(V(d[0], d[1], d[2]));
