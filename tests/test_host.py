@@ -13,7 +13,7 @@ import pytest
 import oracle
 import cudaraytracer_b200 as crt
 from cudaraytracer_b200 import scenes, multi
-from util import best_oracle, oracle_scene, GOLDEN
+from util import best_oracle, oracle_kinds, oracle_scene, GOLDEN
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 EMU = os.path.join(ROOT, "tests", "emu", "libcrt_emu.so")
@@ -153,6 +153,82 @@ def test_device_functions_on_host_match_oracle():
         emu.emu_trace(sc["tri"], np.arange(nt, dtype=np.uint32), nt, sc["sph"], np.arange(nt, nt + ns, dtype=np.uint32), ns,
                       rays, len(rays), 0.001, 3.4028234663852886e38, t1, i1)
         assert np.array_equal(i0, i1) and np.array_equal(t0, t1)
+
+
+def _emu_chained(emu, sc, rays, t_min=0.001, t_max=3.4028234663852886e38):
+    """tests/emu emu_trace_chained over a scene with scene["chained"]: the device's framed tests, on the host."""
+    f = scenes.flatten_chained(sc)
+    nt, ns, nr = len(f["tri"]), len(f["sph"]), len(f["rect_id"])
+    kind = np.concatenate([np.zeros(nt), np.ones(ns), np.full(nr, 2)]).astype(np.uint32)
+    chain = np.concatenate([f["tri_chain"], f["sph_chain"], f["rect_chain"]]).astype(np.uint32)
+    slot = np.concatenate([np.arange(nt), np.arange(ns), np.arange(nr)]).astype(np.uint32)
+    ids = np.concatenate([f["tri_id"], f["sph_id"], f["rect_id"]]).astype(np.uint32)
+    flip = np.concatenate([np.zeros(nt + ns, np.uint8), f["rect_flip"]]).astype(np.uint8)
+    order = np.argsort(ids, kind="stable")
+    kind, chain, slot, ids, flip = (np.ascontiguousarray(a[order]) for a in (kind, chain, slot, ids, flip))
+    u8p = np.ctypeslib.ndpointer(np.uint8, flags="C_CONTIGUOUS")
+    emu.emu_trace_chained.restype = None
+    emu.emu_trace_chained.argtypes = [f32p, C.c_uint32, u32p, u32p, u32p, u32p, u8p, C.c_uint32, f32p, f32p, f32p, C.c_size_t,
+                                      C.c_float, C.c_float, f32p, u32p, f32p, f32p]
+    n = len(rays)
+    t, pid = np.zeros(n, np.float32), np.zeros(n, np.uint32)
+    p, nn = np.zeros((n, 3), np.float32), np.zeros((n, 3), np.float32)
+    tri = f["tri"] if nt else np.zeros((1, 12), np.float32)
+    sph = f["sph"] if ns else np.zeros((1, 4), np.float32)
+    emu.emu_trace_chained(f["frames"], len(f["frames"]), kind, chain, slot, ids, flip, len(ids), tri, sph,
+                          np.ascontiguousarray(rays, np.float32), n, t_min, t_max, t, pid, p, nn)
+    return t, pid, p, nn
+
+
+@pytest.mark.parametrize("seed", [1, 2, 3])
+def test_transform_chains_device_code_on_host_matches_oracles(seed):
+    """Row a8 (hitable/hitable.h:29-38, hitable/transform.h:11-54, core/vec3.h:200-217) and Rectangle
+    (shapes/rectangle.h): the device's chain_ray / framed_test / chain_normal, compiled for the host, against the
+    unmodified reference classes (nested HitableLists under rotated Transforms) and against the C restatement:
+    primitive ids, t, the local-frame hit point and the normal rotated up the chain, bit for bit."""
+    emu = C.CDLL(EMU)
+    sc = scenes.rotated_scene(seed=seed, n_items=30)
+    rng = np.random.default_rng(seed)
+    cam = crt.camera_for(sc, 96, 72)
+    rays = np.concatenate([scenes.primary_rays(cam, 96, 72),
+                           np.concatenate([rng.normal(size=(6000, 3)) * 6, rng.normal(size=(6000, 3))], axis=1).astype(np.float32)])
+    t1, i1, p1, n1 = _emu_chained(emu, sc, rays)
+    assert (i1 != crt.MISS).sum() > 1000
+    for k in oracle_kinds():
+        t0, i0, p0, n0 = oracle_scene(oracle.load(k), sc).trace(rays, want_pn=True)
+        hit = i0 != crt.MISS
+        assert np.array_equal(i0, i1), "%s: %d ids differ" % (k, (i0 != i1).sum())
+        assert np.array_equal(t0, t1)
+        assert np.array_equal(p0[hit], p1[hit]) and np.array_equal(n0[hit], n1[hit])
+    # every kind of primitive was hit through a chain, and plain ones too
+    kinds_hit = set()
+    f = scenes.flatten_chained(sc)
+    for name, ids, ch in (("tri", f["tri_id"], f["tri_chain"]), ("sph", f["sph_id"], f["sph_chain"]), ("rect", f["rect_id"], f["rect_chain"])):
+        for chained in (False, True):
+            sel = ids[(ch != 0) == chained]
+            if np.isin(i1, sel).any():
+                kinds_hit.add((name, chained))
+    assert {("tri", True), ("sph", True), ("rect", True), ("tri", False), ("sph", False)} <= kinds_hit
+
+
+def test_cornell_box_oracles_agree():
+    """The Cornell box of row f3 (Rectangles + cbox_smallbox.obj + DiffuseLight + CheckerTexture): oracle/_ref and the C
+    restatement render the same image, and the device code on the host finds the same hits."""
+    emu = C.CDLL(EMU)
+    sc = scenes.cornell_box()
+    assert sum(len(np.atleast_1d(it["mat"])) for it in sc["chained"] if it["kind"] == 0) == 12      # the block's 12 triangles
+    cam = crt.camera_for(sc, 64, 64)
+    rays = scenes.primary_rays(cam, 64, 64)
+    t1, i1, _, _ = _emu_chained(emu, sc, rays)
+    imgs = []
+    for k in oracle_kinds():
+        o = oracle_scene(oracle.load(k), sc)
+        t0, i0 = o.trace(rays)
+        assert np.array_equal(i0, i1) and np.array_equal(t0, t1)
+        imgs.append(o.render(cam, 64, 64, 2, 8, 0, 5))
+    assert len(set(i1.tolist())) >= 8
+    if len(imgs) == 2:
+        assert np.array_equal(imgs[0], imgs[1])
 
 
 def test_scene_generators():
