@@ -195,4 +195,54 @@ inline void build_instanced(World& w, const SceneOptions& o, int grid = 10, floa
     w.lookfrom = vec3(0, 900, 2600); w.lookat = vec3(0, 0, 0);
 }
 
+// A Cornell box out of the reference's own parts, the same scene as scenes.cornell_box: five walls
+// and a luminous sheet that are Rectangles - the unit square of shapes/rectangle.h turned and placed by Transform
+// rotations (scale stays 1, SURVEY 9 Q7, so the box is one unit wide) - the block of objects/cbox_smallbox.obj
+// ("f a//n" faces; scaled by 1/555) as Triangles inside two nested HitableLists, a glass sphere under a rotated
+// Transform, a CheckerTexture floor. A frame maps world to local: local = rotate(world) - position
+// (hitable/transform.h:38-48); a wall with inward normal N needs the rotation that turns N into +z, and its
+// position is then (0, 0, -0.5).
+inline void build_cornell(World& w, const SceneOptions& o)
+{
+    Material* white = new Lambertian(new ConstantTexture(vec3(0.73f, 0.73f, 0.73f)));
+    Material* red = new Lambertian(new ConstantTexture(vec3(0.65f, 0.05f, 0.05f)));
+    Material* green = new Lambertian(new ConstantTexture(vec3(0.12f, 0.45f, 0.15f)));
+    Material* light = new DiffuseLight(new ConstantTexture(vec3(1.2f, 1.2f, 1.1f)));
+    Material* floor_m = new Lambertian(new CheckerTexture(new ConstantTexture(vec3(0.73f, 0.73f, 0.73f)), new ConstantTexture(vec3(0.2f, 0.2f, 0.6f))));
+    Material* glass = new Dielectric(1.5f);
+    Material* metal = new Metal(vec3(0.8f, 0.85f, 0.88f), 0.0f);
+    auto wall = [&](float z, vec3 rot, Material* m) {
+        w.list.append(new Rectangle(m, false, new Transform(vec3(0.f, 0.f, z), rot, vec3(1.f))));
+    };
+    wall(-0.5f, vec3(0.f, 0.f, 0.f), white);            // back wall, N = +z
+    wall(-0.5f, vec3(90.f, 0.f, 0.f), floor_m);         // floor, N = +y
+    wall(-0.5f, vec3(-90.f, 0.f, 0.f), white);          // ceiling, N = -y
+    wall(-0.5f, vec3(0.f, -90.f, 0.f), red);            // wall at x = -0.5
+    wall(-0.5f, vec3(0.f, 90.f, 0.f), green);           // wall at x = +0.5
+    wall(-0.49f, vec3(-90.f, 0.f, 0.f), light);         // a luminous sheet just below the ceiling
+    const std::string obj = o.obj == "objects/small_bunny.obj" ? std::string("objects/cbox_smallbox.obj") : o.obj;
+    if (!loadObj(obj, w.obj)) throw std::runtime_error("can't open the file " + obj);
+    HitableList* turned = new HitableList(0);
+    turned->transform = new Transform(vec3(0.f), vec3(0.f, 20.f, 0.f), vec3(1.f));
+    for (int i = 0; i < w.obj.mesh.nTriangles; i++) {
+        const vec3 idx = w.obj.mesh.idxVertex[i];
+        const int k[3] = {int(idx[2]) - 1, int(idx[1]) - 1, int(idx[0]) - 1};      // 1-based, winding reversed (createScene.h:183)
+        vec3 p[3];
+        for (int j = 0; j < 3; j++) {
+            if (k[j] < 0 || k[j] >= w.obj.mesh.nPoints) throw std::out_of_range("build_cornell: face index out of range");
+            const vec3 q = w.obj.mesh.points[k[j]];
+            p[j] = vec3(q[0] / 555.f, q[1] / 555.f, q[2] / 555.f);
+        }
+        const vec3 n = -unit_vector(cross(p[1] - p[0], p[2] - p[0]));           // stored normals point into the block
+        Triangle* t = new Triangle(p, n, metal, false, new Transform(vec3(0.02f, 0.f, -0.03f), vec3(0.f), vec3(1.f)), false);
+        turned->append(t);
+        w.triangles.push_back(t);
+    }
+    Hitable* inner[1] = {turned};
+    w.list.append(new HitableList(inner, 1, new Transform(vec3(0.17f, -0.351f, 0.1f), vec3(0.f), vec3(1.f))));
+    const vec3 rot(0.f, 30.f, 0.f);
+    w.list.append(new Sphere(new Transform(rotate(vec3(-0.22f, -0.33f, 0.18f), rot), rot, vec3(1.f)), 0.17f, glass));
+    w.lookfrom = vec3(0.f, 0.f, 2.4f); w.lookat = vec3(0.f, 0.f, 0.f);
+}
+
 }  // namespace crt_host

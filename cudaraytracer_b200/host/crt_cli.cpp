@@ -76,7 +76,7 @@ Options parse(int argc, char** argv)
         else if (a == "--pose") o.pose = val();
         else if (a == "--quiet") o.quiet = true;
         else if (a == "--help" || a == "-h") {
-            std::printf("usage: crt_cli [--scene bunny|spheres|mesh] [--obj FILE] [--camera framed|reference] [--nx N --ny N]\n"
+            std::printf("usage: crt_cli [--scene bunny|spheres|mesh|instanced|cornell] [--obj FILE] [--camera framed|reference] [--nx N --ny N]\n"
                         "               [--spp N] [--depth N] [--mode path|lambert|normal] [--seed S] [--frames N]\n"
                         "               [--animate [--overlap] [--pose vertices|points|bones]]\n"
                         "               [--segments N] [--out PREFIX] [--csv FILE] [--device D] [--gpus N] [--quiet]\n");
@@ -93,6 +93,7 @@ void build_world(crt_host::World& w, const Options& o)
     else if (o.scene == "spheres") crt_host::build_spheres(w, o.sc);
     else if (o.scene == "mesh") crt_host::build_mesh(w, o.sc);
     else if (o.scene == "instanced") crt_host::build_instanced(w, o.sc);
+    else if (o.scene == "cornell") crt_host::build_cornell(w, o.sc);
     else die("unknown --scene " + o.scene);
 }
 

@@ -6,6 +6,7 @@
 //
 //   reference (file:line)                              here                        C ABI
 //   create_FBXMesh / init_List  createScene.h:167,192  set_world(list)             crt_scene_set_*
+//   Transform rotations, Rectangle hitable/transform.h  set_world (chains of frames)  crt_scene_set_frames / _chains / _rectangles
 //   create_BVHfromList          createScene.h:212      create_BVHfromList()        crt_accel_build
 //   updateFBXObj                createScene.h:125      update_vertices(...)        crt_scene_update_vertices
 //   update_pose(newPos, idx)    createScene.h:99,125   set_indices / update_points crt_scene_set_indices / _update_points
@@ -166,10 +167,17 @@ private:
     void upload()
     {
         check(crt_scene_set_materials(ctx_, flat_.mats.data(), flat_.mats.size()), "crt_scene_set_materials");
+        check(crt_scene_set_frames(ctx_, flat_.frames.data(), flat_.frames.size()), "crt_scene_set_frames");   // drops old chains
         check(crt_scene_set_triangles(ctx_, flat_.tri.data(), flat_.tri_mat.data(), flat_.tri_id.data(), flat_.n_triangles()),
               "crt_scene_set_triangles");
         check(crt_scene_set_spheres(ctx_, flat_.sph.data(), flat_.sph_mat.data(), flat_.sph_id.data(), flat_.n_spheres()),
               "crt_scene_set_spheres");
+        if (flat_.has_chains()) {
+            check(crt_scene_set_triangle_chains(ctx_, flat_.tri_chain.data(), flat_.n_triangles()), "crt_scene_set_triangle_chains");
+            check(crt_scene_set_sphere_chains(ctx_, flat_.sph_chain.data(), flat_.n_spheres()), "crt_scene_set_sphere_chains");
+        }
+        check(crt_scene_set_rectangles(ctx_, flat_.rect_chain.data(), flat_.rect_flip.data(), flat_.rect_mat.data(), flat_.rect_id.data(),
+                                       flat_.n_rectangles()), "crt_scene_set_rectangles");
     }
     crt_ctx* ctx_ = nullptr;
     FlatScene flat_;

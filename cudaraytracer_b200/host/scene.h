@@ -17,6 +17,7 @@
 //   HitableList                         hitable/hitable_list.h:6-74   HitableList
 //   Sphere                              shapes/sphere.h:6-24          Sphere
 //   Triangle                            shapes/triangle.h:5-54        Triangle
+//   Rectangle                           shapes/rectangle.h:4-44       Rectangle
 //   Texture / ConstantTexture           material/texture.h:6-22       same
 //   Material / Lambertian / Metal /     material/material.h:42-161    same (describe() instead of scatter())
 //   Dielectric / DiffuseLight
@@ -56,10 +57,11 @@ public:
     Transform() : position(vec3(0.f)), rotation(vec3(0.f)), scale(vec3(1.f)) {}
     Transform(vec3 p, vec3 r, vec3 s) : position(p), rotation(r), scale(s) {}
     void ResetTransform() { position = vec3(0.f); rotation = vec3(0.f); scale = vec3(1.f); }
-    bool is_pure_translation() const
-    {
-        return rotation[0] == 0.f && rotation[1] == 0.f && rotation[2] == 0.f && scale[0] == 1.f && scale[1] == 1.f && scale[2] == 1.f;
-    }
+    bool has_rotation() const { return rotation[0] != 0.f || rotation[1] != 0.f || rotation[2] != 0.f; }
+    bool has_position() const { return position[0] != 0.f || position[1] != 0.f || position[2] != 0.f; }
+    bool unit_scale() const { return scale[0] == 1.f && scale[1] == 1.f && scale[2] == 1.f; }
+    bool is_pure_translation() const { return !has_rotation() && unit_scale(); }
+    bool is_identity() const { return is_pure_translation() && !has_position(); }
     vec3 position, rotation, scale;
 };
 
@@ -171,17 +173,54 @@ public:
 // positions in a depth-first walk of the list, i.e. the order in which the
 // reference's HitableList scan would visit them (first wins ties,
 // hitable/hitable_list.h:84).
+//
+// Transforms. Every Hitable::hit maps the ray into the object's frame (hitable/hitable.h:29-38,
+// hitable/transform.h:11-14): direction re-normalised, origin and direction rotated, position subtracted - once per
+// Hitable on the way from the world list down to the primitive - and reports hit point and normal in the innermost
+// frame. A primitive is PLAIN when that walk is the world list under the identity and then the
+// primitive itself without rotation (a triangle also without position; a sphere's position is its centre): the
+// arrays then hold world-space values and the kernels take their fast path. Anything else - a rotation, a
+// translated triangle, a list inside a list - keeps the reference's arithmetic through a CHAIN: the primitive's run
+// of crt_frame records, outermost first (crt_scene_set_frames; include/crt.h), with its vertices left in its own
+// frame. Chains of primitives that sit in the same nest of lists share the frames of the enclosing levels.
 struct FlatScene {
     std::vector<float> tri;          // 12 floats per triangle: v0, v1, v2, stored normal
-    std::vector<uint32_t> tri_mat, tri_id;
+    std::vector<uint32_t> tri_mat, tri_id, tri_chain;
     std::vector<float> sph;          // 4 floats per sphere: centre, radius
-    std::vector<uint32_t> sph_mat, sph_id;
+    std::vector<uint32_t> sph_mat, sph_id, sph_chain;
+    std::vector<uint32_t> rect_chain, rect_mat, rect_id;   // shapes/rectangle.h: the unit square of a frame
+    std::vector<uint8_t> rect_flip;
+    std::vector<crt_frame> frames;
     std::vector<crt_material> mats;
     std::map<const Material*, uint32_t> mat_index;
     uint32_t next_id = 0;
 
     size_t n_triangles() const { return tri_mat.size(); }
     size_t n_spheres() const { return sph_mat.size(); }
+    size_t n_rectangles() const { return rect_mat.size(); }
+    bool has_chains() const { return !frames.empty(); }
+
+    // The chain word of a primitive whose ray passes the Transforms `levels` (world list first, its own last):
+    // (first << 8) | count. Each primitive gets its own run of frames (a run must be contiguous).
+    uint32_t add_chain(const std::vector<const Transform*>& levels)
+    {
+        if (levels.size() > 255) throw std::invalid_argument("flatten: more than 255 nested Hitables");
+        const uint32_t first = (uint32_t)frames.size();
+        for (const Transform* t : levels) {
+            crt_frame f;
+            const bool rot = t->has_rotation();
+            // the rows rotate() builds (core/vec3.h:211-213): rotate(e_j)[k] is entry j of row k
+            const vec3 c0 = rot ? rotate(vec3(1.f, 0.f, 0.f), t->rotation) : vec3(1.f, 0.f, 0.f);
+            const vec3 c1 = rot ? rotate(vec3(0.f, 1.f, 0.f), t->rotation) : vec3(0.f, 1.f, 0.f);
+            const vec3 c2 = rot ? rotate(vec3(0.f, 0.f, 1.f), t->rotation) : vec3(0.f, 0.f, 1.f);
+            for (int k = 0; k < 3; k++) { f.rows[3 * k] = c0[k]; f.rows[3 * k + 1] = c1[k]; f.rows[3 * k + 2] = c2[k]; }
+            f.position[0] = t->position[0]; f.position[1] = t->position[1]; f.position[2] = t->position[2];
+            f.has_rotation = rot ? 1u : 0u;
+            frames.push_back(f);
+        }
+        if (first + levels.size() >= (1u << 24)) throw std::invalid_argument("flatten: more than 2^24 frames");
+        return (first << 8) | (uint32_t)levels.size();
+    }
 
     uint32_t material(const Material* m)
     {
@@ -202,24 +241,26 @@ public:
     Hitable() { transform = new Transform(); }                       // hitable.h:27 allocates too
     virtual ~Hitable() {}
 
-    // Replaces hit()/collision_detection(): append this object's primitives to
-    // `out` as seen from a parent frame translated by `parent_offset`.
-    // Hitable::hit maps the ray by TransformRay = Translate(Rotate(Scale(r)))
-    // (hitable/transform.h:11-14); for rotation 0 and scale 1 that is
-    // origin - position, so nested frames add their positions.
-    virtual void flatten(FlatScene& out, const vec3& parent_offset) const = 0;
+    // Replaces hit()/collision_detection(): append this object's primitives to `out`. `above` holds the Transforms of
+    // the Hitables the ray passed on its way here, the world list's first.
+    virtual void flatten(FlatScene& out, std::vector<const Transform*>& above) const = 0;
 
     Transform* transform;
 
 protected:
-    vec3 frame_offset(const vec3& parent_offset, const char* who) const
+    const Transform* own_transform(const char* who) const
     {
         if (!transform) throw std::invalid_argument(std::string(who) + ": null Transform");
-        if (!transform->is_pure_translation())
-            throw std::invalid_argument(std::string(who) + ": only rotation 0 / scale 1 transforms are supported; the reference's "
-                                        "ScaleRay does not scale the origin and its normal rotation is not the inverse "
-                                        "(hitable/transform.h:50-54, hitable/hitable.h:36; SURVEY 9 Q6/Q7)");
-        return parent_offset + transform->position;
+        if (!transform->unit_scale())
+            throw std::invalid_argument(std::string(who) + ": scale must be 1; the reference's ScaleRay divides only the direction "
+                                        "and does not scale the origin (hitable/transform.h:50-54; SURVEY 9 Q7)");
+        return transform;
+    }
+    // plain = the world list under the identity, then this primitive without rotation (and, for a triangle, without
+    // position): nothing but the sphere's centre is needed to reproduce the reference's arithmetic
+    static bool is_plain(const std::vector<const Transform*>& above, const Transform* own, bool allow_position)
+    {
+        return above.size() == 1 && above[0]->is_identity() && !own->has_rotation() && (allow_position || !own->has_position());
     }
 };
 
@@ -250,13 +291,14 @@ public:
     }
     void freeMemory() { std::free(list); list = nullptr; list_size = 0; cap_ = 0; }
 
-    void flatten(FlatScene& out, const vec3& parent_offset) const override
+    void flatten(FlatScene& out, std::vector<const Transform*>& above) const override
     {
-        const vec3 off = frame_offset(parent_offset, "HitableList");
+        above.push_back(own_transform("HitableList"));
         for (int i = 0; i < list_size; i++) {
             if (!list[i]) throw std::invalid_argument("HitableList: null entry");
-            list[i]->flatten(out, off);
+            list[i]->flatten(out, above);
         }
+        above.pop_back();
     }
 
     Hitable** list;
@@ -277,13 +319,20 @@ class Sphere : public Hitable {                                      // shapes/s
 public:
     Sphere(Transform* t) : Hitable(t), radius(0.f), material(nullptr) {}
     Sphere(Transform* t, float r, Material* mat) : Hitable(t), radius(r), material(mat) {}
-    void flatten(FlatScene& out, const vec3& parent_offset) const override
+    void flatten(FlatScene& out, std::vector<const Transform*>& above) const override
     {
-        // The sphere sits at its frame's origin (sphere.h:31); the hit point and
-        // normal stay in that frame, which the GPU kernel
-        // reproduces from centre = accumulated position.
-        const vec3 c = frame_offset(parent_offset, "Sphere");
-        out.sph.insert(out.sph.end(), {c[0], c[1], c[2], radius});
+        // The sphere sits at its frame's origin (sphere.h:31); the hit point and normal stay in that frame
+        // (SURVEY 9 Q6). Plain: the kernel reproduces that from centre = the sphere's own position.
+        const Transform* own = own_transform("Sphere");
+        if (is_plain(above, own, true)) {
+            out.sph.insert(out.sph.end(), {own->position[0], own->position[1], own->position[2], radius});
+            out.sph_chain.push_back(0u);
+        } else {
+            above.push_back(own);
+            out.sph.insert(out.sph.end(), {0.f, 0.f, 0.f, radius});
+            out.sph_chain.push_back(out.add_chain(above));
+            above.pop_back();
+        }
         out.sph_mat.push_back(out.material(material));
         out.sph_id.push_back(out.next_id++);
     }
@@ -307,20 +356,22 @@ public:
     }
     void SetVertices(vec3 vs[3]) { for (int i = 0; i < 3; i++) vertices[i] = vs[i]; }   // triangle.h:40-45 (normal stays)
 
-    void flatten(FlatScene& out, const vec3& parent_offset) const override
+    void flatten(FlatScene& out, std::vector<const Transform*>& above) const override
     {
         if (backCulling) throw std::invalid_argument("Triangle: backCulling is never set by live reference code and is not supported");
-        // A translated frame is baked into the vertices. For a non-zero offset the
-        // reference would report the hit point in the LOCAL frame;
-        // baking reports it in world space (deviation D2). Mesh
-        // triangles use identity transforms (createScene.h:184), where both agree.
-        const vec3 off = frame_offset(parent_offset, "Triangle");
-        const bool zero = off[0] == 0.f && off[1] == 0.f && off[2] == 0.f;
-        for (int i = 0; i < 3; i++) {
-            const vec3 v = zero ? vertices[i] : vertices[i] + off;
-            out.tri.insert(out.tri.end(), {v[0], v[1], v[2]});
-        }
+        // Mesh triangles carry identity transforms (createScene.h:184): plain. A triangle that is translated, rotated
+        // or nested keeps its vertices in its own frame and gets a chain, so that hit point and normal come out in
+        // that frame as the reference reports them.
+        const Transform* own = own_transform("Triangle");
+        for (int i = 0; i < 3; i++) out.tri.insert(out.tri.end(), {vertices[i][0], vertices[i][1], vertices[i][2]});
         out.tri.insert(out.tri.end(), {normal[0], normal[1], normal[2]});
+        if (is_plain(above, own, false)) {
+            out.tri_chain.push_back(0u);
+        } else {
+            above.push_back(own);
+            out.tri_chain.push_back(out.add_chain(above));
+            above.pop_back();
+        }
         out.tri_mat.push_back(out.material(material));
         out.tri_id.push_back(out.next_id++);
     }
@@ -333,10 +384,31 @@ public:
     Material* material;
 };
 
+class Rectangle : public Hitable {                                   // shapes/rectangle.h:4-19
+public:
+    Rectangle() : mat_ptr(nullptr), flipNormal(false) {}
+    Rectangle(Material* mat, bool flip) : mat_ptr(mat), flipNormal(flip) {}
+    Rectangle(Material* mat, bool flip, Transform* t) : Hitable(t), mat_ptr(mat), flipNormal(flip) {}
+    void flatten(FlatScene& out, std::vector<const Transform*>& above) const override
+    {
+        // the unit square of its frame's z = 0 plane (rectangle.h:28-31): it only becomes a wall through its
+        // Transform, so it always has a chain
+        above.push_back(own_transform("Rectangle"));
+        out.rect_chain.push_back(out.add_chain(above));
+        above.pop_back();
+        out.rect_flip.push_back(flipNormal ? 1 : 0);
+        out.rect_mat.push_back(out.material(mat_ptr));
+        out.rect_id.push_back(out.next_id++);
+    }
+    Material* mat_ptr;
+    bool flipNormal;
+};
+
 inline FlatScene flatten_scene(const Hitable& world)
 {
     FlatScene f;
-    world.flatten(f, vec3(0.f));
+    std::vector<const Transform*> above;
+    world.flatten(f, above);
     return f;
 }
 

@@ -90,6 +90,14 @@ def rotation_rows(rot):
 IDENTITY_ROWS = np.asarray([1, 0, 0, 0, 1, 0, 0, 0, 1], np.float32)
 
 
+def rotate_point(v, rot):
+    """rotate(v, rot) of core/vec3.h:200-217 in float32: component k = (v * row_k).sum(), summed left to right."""
+    f = np.float32
+    m = rotation_rows(rot)
+    v = np.asarray(v, f)
+    return np.asarray([f(f(f(v[0] * m[3 * k]) + f(v[1] * m[3 * k + 1])) + f(v[2] * m[3 * k + 2])) for k in range(3)], f)
+
+
 def flatten_chained(scene):
     """The arrays crt_scene_set_frames / _triangle_chains / _sphere_chains / _rectangles take for scene["chained"]:
     a list of items dict(kind, data, mat, levels[, flip]) - `levels` are the (position, rotation) pairs of the
@@ -585,12 +593,13 @@ def cornell_box(nx=200, ny=200, spp=8, obj_path=None):
         tri = pack_tris(v0, v1, v2)
         tri[:, 9:12] = -tri_normals(v0, v1, v2)                           # stored normals point into the block
     if len(tri):
-        # the block sits under two nested lists: a shift to the floor, a turn about y, then its own offset
+        # the block (centred on its own origin by the loader) sits under two nested lists - a shift onto the floor, a
+        # turn about y - and every triangle carries the same small offset of its own
         chained.append(dict(kind=0, data=tri, mat=np.full(len(tri), 6, np.uint32),
-                            levels=[(np.asarray((0.12, -0.5, -0.05), f), np.zeros(3, f)), (np.zeros(3, f), np.asarray((0, 20, 0), f)),
-                                    (np.asarray((-0.335, 0.0, -0.303), f), np.zeros(3, f))]))
+                            levels=[(np.asarray((0.17, -0.351, 0.1), f), np.zeros(3, f)), (np.zeros(3, f), np.asarray((0, 20, 0), f)),
+                                    (np.asarray((0.02, 0.0, -0.03), f), np.zeros(3, f))]))
     chained.append(dict(kind=1, data=np.asarray([0.17], f), mat=np.asarray([5], np.uint32),
-                        levels=[(rotation_rows((0, 30, 0)).reshape(3, 3) @ np.asarray((-0.22, -0.33, 0.18), f), np.asarray((0, 30, 0), f))]))
+                        levels=[(rotate_point((-0.22, -0.33, 0.18), (0, 30, 0)), np.asarray((0, 30, 0), f))]))
     e_tri, e_mat = _empty_tris()
     e_sph, e_smat = _empty_sph()
     return dict(name="cornell_unit", tri=e_tri, tri_mat=e_mat, sph=e_sph, sph_mat=e_smat, mats=mats, chained=chained,

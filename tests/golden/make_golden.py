@@ -63,15 +63,15 @@ def main():
     pts, idx = ref.parse_obj("/root/reference/CudaTest/objects/small_bunny.obj")
     np.savez_compressed(os.path.join(HERE, "small_bunny_parsed.npz"), points=pts, idx=idx)
 
-    # objects/cbox_smallbox.obj has "f a//n" faces, which the reference's parseObjByName does not read (its
-    # parseFaceIndex, obj_loader.h:113-118, is unused): parsed here field by field; the host loader must agree
-    cp, cf = [], []
+    # objects/cbox_smallbox.obj has "f a//n" faces, which the reference's parseObjByName mangles (it reads each face
+    # token with operator>> as a float; its parseFaceIndex, obj_loader.h:113-118, is unused): the points - centred by
+    # the reference's own computeMean / centering - come from the reference, the faces are read here field by field
+    cpts, _ = ref.parse_obj("/root/reference/CudaTest/objects/cbox_smallbox.obj")
+    cf = []
     for line in open("/root/reference/CudaTest/objects/cbox_smallbox.obj"):
-        if line.startswith("v "):
-            cp.append([float(x) for x in line.split()[1:4]])
-        elif line.startswith("f "):
+        if line.startswith("f "):
             cf.append([float(t.split("/")[0]) for t in line.split()[1:4]])
-    np.savez_compressed(os.path.join(HERE, "cbox_smallbox.npz"), points=np.asarray(cp, np.float32), idx=np.asarray(cf, np.float32))
+    np.savez_compressed(os.path.join(HERE, "cbox_smallbox.npz"), points=cpts, idx=np.asarray(cf, np.float32))
 
     sc = scenes.c1_bunny()
     s = oracle_scene(ref, sc)

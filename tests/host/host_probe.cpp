@@ -6,7 +6,7 @@
 //   host_probe obj    <file.obj> <out.bin>
 //   host_probe png    <w> <h> <comp> <in.raw> <out.png>
 //   host_probe writepng <nx> <ny> <in_rgb_f32.raw> <prefix>
-//   host_probe reject <rotation|scale|texture|nomat>
+//   host_probe reject <scale|texture|nomat>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -36,7 +36,7 @@ static void dump_flat(const FlatScene& s, const char* path)
 {
     FILE* f = std::fopen(path, "wb");
     if (!f) { std::perror(path); std::exit(2); }
-    const uint64_t hdr[3] = {s.n_triangles(), s.n_spheres(), s.mats.size()};
+    const uint64_t hdr[5] = {s.n_triangles(), s.n_spheres(), s.mats.size(), s.n_rectangles(), s.frames.size()};
     put(f, hdr, sizeof hdr);
     put(f, s.tri.data(), s.tri.size() * 4);
     put(f, s.tri_mat.data(), s.tri_mat.size() * 4);
@@ -45,6 +45,13 @@ static void dump_flat(const FlatScene& s, const char* path)
     put(f, s.sph_mat.data(), s.sph_mat.size() * 4);
     put(f, s.sph_id.data(), s.sph_id.size() * 4);
     put(f, s.mats.data(), s.mats.size() * sizeof(crt_material));
+    put(f, s.tri_chain.data(), s.tri_chain.size() * 4);
+    put(f, s.sph_chain.data(), s.sph_chain.size() * 4);
+    put(f, s.rect_chain.data(), s.rect_chain.size() * 4);
+    put(f, s.rect_mat.data(), s.rect_mat.size() * 4);
+    put(f, s.rect_id.data(), s.rect_id.size() * 4);
+    put(f, s.rect_flip.data(), s.rect_flip.size());
+    put(f, s.frames.data(), s.frames.size() * sizeof(crt_frame));
     std::fclose(f);
 }
 
@@ -62,6 +69,7 @@ int main(int argc, char** argv)
             if (which == "bunny") crt_host::build_bunny(w, o);
             else if (which == "spheres") crt_host::build_spheres(w, o);
             else if (which == "mesh") crt_host::build_mesh(w, o);
+            else if (which == "cornell") crt_host::build_cornell(w, o);
             else if (which == "nested") {
                 // a list inside a translated list (hitable_list.h:11): offsets add up
                 Material* m = new Metal(vec3(0.8f, 0.6f, 0.2f), 3.0f);          // fuzz clamps to 1
@@ -142,8 +150,7 @@ int main(int argc, char** argv)
             const std::string what = argv[2];
             HitableList l;
             Material* m = new Lambertian(new ConstantTexture(vec3(0.5f)));
-            if (what == "rotation") l.append(new Sphere(new Transform(vec3(0.f), vec3(0, 30, 0), vec3(1.f)), 1.f, m));
-            else if (what == "scale") l.append(new Sphere(new Transform(vec3(0.f), vec3(0.f), vec3(2.f)), 1.f, m));
+            if (what == "scale") l.append(new Sphere(new Transform(vec3(0.f), vec3(0.f), vec3(2.f)), 1.f, m));
             else if (what == "nomat") l.append(new Sphere(new Transform(), 1.f, nullptr));
             else if (what == "texture") {
                 struct Odd : Texture { vec3 value(float, float, const vec3& p) const override { return p; } };
