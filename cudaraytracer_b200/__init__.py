@@ -20,6 +20,7 @@ OPT_LEAF_MAX, OPT_COUNTERS, OPT_BATCH_PATHS, OPT_REFILL, OPT_LEAF_THRESH, OPT_PA
 OPT_WIDE_BELOW = 9
 OPT_TIMING, OPT_SLICE_MIN = 10, 11
 COMM_ID_BYTES = 128
+TRACE_STATIC_MAX_RAYS = 65536
 BUILDER_LBVH, BUILDER_PLOC = 0, 1
 TEX_CONSTANT, TEX_CHECKER = 0, 1
 POSE_VERTICES, POSE_POINTS, POSE_PARTS = 0, 1, 2
@@ -36,7 +37,7 @@ ABI_SYMBOLS = [
     "crt_render_accum_device", "crt_resolve_device", "crt_pack_rgba8_device", "crt_get_counters",
     "crt_reset_counters", "crt_accel_info",
     "crt_comm_unique_id", "crt_comm_init", "crt_comm_destroy", "crt_comm_info", "crt_scene_broadcast",
-    "crt_reduce_accum_device", "crt_gather_device", "crt_render_dist",
+    "crt_reduce_accum_device", "crt_gather_device", "crt_render_dist", "crt_trace_static",
 ]
 
 
@@ -108,6 +109,7 @@ def load_library():
     lib.crt_accel_build.argtypes = [vp]
     lib.crt_accel_refit.argtypes = [vp]
     lib.crt_trace.argtypes = [vp, vp, sz, C.c_float, C.c_float, C.c_int, vp]
+    lib.crt_trace_static.argtypes = [vp, vp, sz, C.c_float, C.c_float, vp]
     lib.crt_trace_device.argtypes = [vp, vp, sz, C.c_float, C.c_float, C.c_int, vp]
     lib.crt_render.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint64, vp]
     lib.crt_render_frame.argtypes = [vp, vp, sz, sz, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint64, vp]
@@ -336,6 +338,15 @@ class Context:
         t = hits[:, 0].copy()
         pid = hits[:, 1].copy().view(np.uint32)
         return t, pid, hits[:, 2].copy(), hits[:, 3].copy()
+
+    def trace_static(self, rays, t_min=0.001, t_max=3.4028234663852886e38):
+        """crt_trace_static: crt_trace (LBVH) with its device scratch in a static array of the library - no allocation,
+        at most TRACE_STATIC_MAX_RAYS rays per call."""
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 6)
+        n = rays.shape[0]
+        hits = np.zeros((n, 4), np.float32)
+        self._check(self.lib.crt_trace_static(self._h, _ptr(rays), n, float(t_min), float(t_max), _ptr(hits)))
+        return hits[:, 0].copy(), hits[:, 1].copy().view(np.uint32), hits[:, 2].copy(), hits[:, 3].copy()
 
     def trace_device(self, d_rays_ptr, n, d_hits_ptr, t_min=0.001, t_max=3.4028234663852886e38, accel=ACCEL_LBVH):
         self._check(self.lib.crt_trace_device(self._h, C.c_void_p(d_rays_ptr), int(n), float(t_min), float(t_max),

@@ -630,6 +630,13 @@ int crt_trace(crt_ctx* c, const crt_ray* rays, size_t n, float t_min, float t_ma
     return CRT_OK;
 }
 
+// no counterpart in the reference (include/crt.h, trace.cu)
+int crt_trace_static(crt_ctx* c, const crt_ray* rays, size_t n, float t_min, float t_max, crt_hit* hits)
+{
+    CRT_CHECK_SETTLED(c);
+    return trace_static(c, rays, n, t_min, t_max, hits);
+}
+
 int crt_render_accum_device(crt_ctx* c, const crt_camera* cam, int nx, int ny, int sample_begin, int sample_end,
                             int max_depth, int shade_mode, uint64_t seed, int rank, int world, float* d_accum)
 {

@@ -147,6 +147,7 @@ int lbvh_build(crt_ctx* c, bool refit_only, cudaStream_t async = nullptr);
 inline bool scene_is_general(const crt_ctx* c) { return c->n_sph > 0 || c->n_rect > 0 || c->tri_has_chain; }
 int launch_trace(crt_ctx* c, const crt_ray* d_rays, size_t n, float t_min, float t_max, int accel, crt_hit* d_hits);
 AccelView accel_view(const crt_ctx* c);
+int trace_static(crt_ctx* c, const crt_ray* rays, size_t n, float t_min, float t_max, crt_hit* hits);
 
 // render.cu
 // finish (world == 1 only): every slice resolves the rows it owns into d_rgb and copies them to h_rgb as soon as

@@ -252,4 +252,61 @@ int launch_trace(crt_ctx* c, const crt_ray* d_rays, size_t n, float t_min, float
     return CRT_OK;
 }
 
+// ---- crt_trace_static: the host-buffer closest-hit call with its device scratch in a static array ----
+// (no counterpart in the reference, see include/crt.h)
+// Layout of the array: [0, 256) the persistent kernel's queue cursor (one uint32 in use), then MAX_RAYS staged rays
+// (24 B each), then MAX_RAYS hit records (16 B each); 256 + 65536 * 24 is a multiple of 16, so the float4 stores of
+// the hit records stay aligned.
+static __device__ __align__(256) unsigned char g_trace_static_scratch[CRT_TRACE_STATIC_SCRATCH_BYTES];
+
+// In host code the array's name is a host-side stand-in, not a device address: the address every GPU gives its own
+// copy comes from cudaGetSymbolAddress, asked once per device with that device current.
+constexpr int TRACE_STATIC_MAX_DEVICES = 64;
+static unsigned char* g_trace_static_ptr[TRACE_STATIC_MAX_DEVICES] = {};
+
+int trace_static(crt_ctx* c, const crt_ray* rays, size_t n, float t_min, float t_max, crt_hit* hits)
+{
+    if (n == 0) return CRT_OK;
+    if (!rays || !hits) { set_error("crt_trace_static: null buffer"); return CRT_ERR_INVALID; }
+    if (n > (size_t)CRT_TRACE_STATIC_MAX_RAYS) {
+        set_error("crt_trace_static: %zu rays, but the static scratch holds at most %d per call (split the batch, or use crt_trace)",
+                  n, (int)CRT_TRACE_STATIC_MAX_RAYS);
+        return CRT_ERR_INVALID;
+    }
+    if (!c->accel_valid) { set_error("crt_trace_static: call crt_accel_build first"); return CRT_ERR_STATE; }
+    if (c->device < 0 || c->device >= TRACE_STATIC_MAX_DEVICES) { set_error("crt_trace_static: device %d beyond %d", c->device, TRACE_STATIC_MAX_DEVICES); return CRT_ERR_INVALID; }
+    if (!g_trace_static_ptr[c->device]) {            // set-up, once per device; the caller made c->device current
+        void* p = nullptr;
+        CRT_CUDA(cudaGetSymbolAddress(&p, g_trace_static_scratch));
+        if (!p) { set_error("crt_trace_static: no device address for the scratch array"); return CRT_ERR_CUDA; }
+        g_trace_static_ptr[c->device] = (unsigned char*)p;
+    }
+    unsigned char* base = g_trace_static_ptr[c->device];
+    uint32_t* cursor = reinterpret_cast<uint32_t*>(base);
+    crt_ray* d_rays = reinterpret_cast<crt_ray*>(base + 256);
+    crt_hit* d_hits = reinterpret_cast<crt_hit*>(base + 256 + (size_t)CRT_TRACE_STATIC_MAX_RAYS * sizeof(crt_ray));
+    cudaStream_t st = c->stream;
+    CRT_CUDA(cudaMemsetAsync(cursor, 0, 256, st));   // the array keeps the last call's cursor: it must start at zero
+    CRT_CUDA(cudaMemcpyAsync(d_rays, rays, n * sizeof(crt_ray), cudaMemcpyHostToDevice, st));
+    int bps = 1;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_trace_lbvh<false, false>, TP_BLOCK, 0);
+    if (bps < 1) bps = 1;
+    const size_t want = (n + 31) / 32;
+    const size_t blocks = (want + (TP_BLOCK / 32) - 1) / (TP_BLOCK / 32);
+    const size_t cap = (size_t)c->sm_count * bps;
+    const unsigned int grid = (unsigned int)(blocks < cap ? blocks : cap);
+    const AccelView A = accel_view(c);
+    unsigned long long* counters = c->counters.as<unsigned long long>();
+    if (scene_is_general(c))
+        k_trace_lbvh<false, true><<<grid, TP_BLOCK, 0, st>>>(A, d_rays, (uint32_t)n, cursor, t_min, t_max, d_hits, counters, (uint32_t)c->refill, (uint32_t)c->leaf_thresh);
+    else
+        k_trace_lbvh<false, false><<<grid, TP_BLOCK, 0, st>>>(A, d_rays, (uint32_t)n, cursor, t_min, t_max, d_hits, counters, (uint32_t)c->refill, (uint32_t)c->leaf_thresh);
+    CRT_CUDA(cudaGetLastError());
+    CRT_CUDA(cudaMemcpyAsync(hits, d_hits, n * sizeof(crt_hit), cudaMemcpyDeviceToHost, st));
+    CRT_CUDA(cudaStreamSynchronize(st));
+    CRT_CUDA(cudaGetLastError());
+    c->host_counters.rays += n;
+    return CRT_OK;
+}
+
 }  // namespace crt

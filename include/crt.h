@@ -262,6 +262,20 @@ int crt_trace(crt_ctx* ctx, const crt_ray* rays, size_t n, float t_min, float t_
 int crt_trace_device(crt_ctx* ctx, const crt_ray* d_rays, size_t n, float t_min, float t_max,
                      int accel, crt_hit* d_hits);
 
+/* crt_trace for callers that must not allocate (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc). It has NO counterpart in the reference.
+ * Same contract and same hits as crt_trace(..., CRT_ACCEL_LBVH, ...) - host arrays in and out - but every byte of
+ * device scratch it needs (the staged rays, the hit records, the persistent kernel's queue cursor) lives in one
+ * file-scope `static __device__` array of libcrt_b200.so, CRT_TRACE_STATIC_SCRATCH_BYTES long (about 2.6 MB, held
+ * by every GPU that loads the library until the process exits). The call makes no cudaMalloc / cudaFree and calls no
+ * allocating routine; it takes at most CRT_TRACE_STATIC_MAX_RAYS rays and fails with CRT_ERR_INVALID beyond that
+ * (split the batch). ALL calls on a GPU share the one array, which keeps the previous call's contents: the call
+ * clears what must start at zero and waits for its own work before it returns, but two calls that overlap on the same
+ * GPU (two host threads, two contexts on one device) race on it - serialise them. Needs crt_accel_build. */
+#define CRT_TRACE_STATIC_MAX_RAYS 65536
+#define CRT_TRACE_STATIC_SCRATCH_BYTES (256 + CRT_TRACE_STATIC_MAX_RAYS * (sizeof(crt_ray) + sizeof(crt_hit)))
+int crt_trace_static(crt_ctx* ctx, const crt_ray* rays, size_t n, float t_min, float t_max, crt_hit* hits);
+
 /* ---- render: replaces render<<<>>> + the D2H copy (core/render.h:105-129,
  *      222-226) ----
  * rgb_out: caller-owned host array of nx*ny*3 floats in the reference's
