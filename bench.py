@@ -406,7 +406,11 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    def step(seed):
+    gather = (not weak) and args.combine == "gather"
+
+    def step(seed, marks=None):
+        if marks is not None:
+            marks[0].record(ext)
         if weak:
             # every rank renders the named frame's full work: its own range of 16 samples of every pixel
             ctx.render_accum_device(cam, nx, ny, spp * rank, spp * (rank + 1), depth, crt.SHADE_PATH, seed, 0, 1,
@@ -414,8 +418,16 @@ def run_ours(args):
         else:
             # the frame is fixed; ranks split its 32x32 tiles (bit-identical to the 1-GPU image)
             ctx.render_accum_device(cam, nx, ny, 0, spp, depth, crt.SHADE_PATH, seed, rank, world, accum.data_ptr())
+        if marks is not None:
+            marks[1].record(ext)
         if world > 1:
-            ctx.reduce_accum_device(accum.data_ptr(), nx * ny * 3, 0)
+            if gather:
+                # every pixel was rendered by one rank: its tiles go straight to rank 0 (1/N of the frame per rank)
+                ctx.gather_tiles_device(accum.data_ptr(), nx, ny, 0)
+            else:
+                ctx.reduce_accum_device(accum.data_ptr(), nx * ny * 3, 0)
+        if marks is not None:
+            marks[2].record(ext)
         if rank == 0:
             ctx.resolve_device(accum.data_ptr(), nx * ny, spp * world if weak else spp, rgb.data_ptr())
 
@@ -503,6 +515,20 @@ def run_ours(args):
         rays, paths, bounce_ms = float(c["rays"]), float(c["paths"]), alone_ms
     value = rays / (ms * 1e-3) / 1e6
 
+    # ---- N > 1: where a step's time goes on every rank (one extra frame with events around its parts) ----
+    per_rank = None
+    if world > 1:
+        marks = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+        barrier()
+        step(60, marks)
+        ctx.sync()
+        mine = torch.tensor([marks[0].elapsed_time(marks[1]), marks[1].elapsed_time(marks[2])], dtype=torch.float64, device=dev)
+        allr = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(allr, mine)
+        per_rank = {"render_ms": [round(float(t[0]), 3) for t in allr],
+                    "exchange_ms": [round(float(t[1]), 3) for t in allr],
+                    "note": "one frame after a barrier; exchange_ms includes waiting for the slowest rank's render"}
+
     # ---- N > 1: is the combined frame the right image? ----
     parity_n = None
     if world > 1:
@@ -572,7 +598,10 @@ def run_ours(args):
                        "lanes": lanes, "parallelism": ("single" if world == 1 else
                                        "samples%d: every rank renders 16 spp of every pixel (sample range [16r, 16r+16)), %d spp in the combined frame" % (world, spp * world)
                                        if weak else "tiles%d: the fixed %d-spp frame, 32x32 tiles, tile index mod N" % (world, spp)),
-                       "combine": ("crt_reduce_accum_device: ncclReduce(sum) of the %.1f MB accumulators onto rank 0, issued by libcrt_b200.so on its own communicator" % (nx * ny * 12 / 1e6)) if world > 1 else "none",
+                       "combine": "none" if world == 1 else
+                                  ("crt_gather_tiles_device: every rank sends the tiles it rendered (%.1f MB, 1/N of the frame) to rank 0 with ncclSend/ncclRecv, issued by libcrt_b200.so on its own communicator" % (nx * ny * 12 / 1e6 / world)) if gather else
+                                  ("crt_reduce_accum_device: ncclReduce(sum) of the %.1f MB accumulators onto rank 0, issued by libcrt_b200.so on its own communicator" % (nx * ny * 12 / 1e6)),
+                       "per_rank": per_rank,
                        "l2": "per-step working set (queues %.1f GB + LBVH %.2f GB) exceeds the 126 MB L2; no explicit flush" % (
                            min(nx * ny * spp, 1 << 25) * 128 / 1e9, info["bytes"] / 1e9),
                        "rays_per_path": rays / max(1.0, paths)},
@@ -586,7 +615,7 @@ def run_ours(args):
                              if world == 1 and args.e2e_api == "frame" else
                              "crt_scene_update_vertices + crt_accel_refit + crt_render per frame, host buffers, wall clock"
                              if world == 1 else
-                             "per rank: %s, render of the rank's share, crt_reduce_accum_device; rank 0: resolve + read-back to a pinned host buffer; wall clock, max over ranks" % (
+                             "per rank: %s, render of the rank's share, tile gather (or reduce); rank 0: resolve + read-back to a pinned host buffer; wall clock, max over ranks" % (
                                  "crt_scene_update_vertices + crt_accel_refit" if args.e2e_api == "calls" else
                                  "crt_scene_pose_async(%s) (upload + refit beside ray generation)" % ("points" if args.e2e_api == "points" else "vertices")))},
             "gpu_launches": launches,
@@ -676,6 +705,8 @@ def main():
     ap.add_argument("--workload", default="c3", choices=["c3", "c4"],
                     help="c3 (default): the configuration the metric is quoted on; c4: the 10 M-triangle instanced scene at "
                          "4K x 64 spp (BASELINE.json configs[3], tile partition + NCCL reduce under torchrun)")
+    ap.add_argument("--combine", default="gather", choices=["gather", "reduce"],
+                    help="N > 1, tile partition: gather = each rank's tiles to rank 0 (default); reduce = ncclReduce of the full frames")
     ap.add_argument("--scaling", default=None, choices=["weak", "strong"],
                     help="N > 1: strong (default) = the configured 16-spp frame split by tiles; weak = every rank renders the "
                          "full 16-spp frame's work on its own sample range")

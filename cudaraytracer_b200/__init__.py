@@ -20,6 +20,7 @@ OPT_LEAF_MAX, OPT_COUNTERS, OPT_BATCH_PATHS, OPT_REFILL, OPT_LEAF_THRESH, OPT_PA
 OPT_WIDE_BELOW = 9
 OPT_TIMING, OPT_SLICE_MIN = 10, 11
 COMM_ID_BYTES = 128
+DBG_NODES, DBG_RECS, DBG_KEYS, DBG_PERM, DBG_CHILD, DBG_RANGE, DBG_LEAF_BOX, DBG_NODE_BOX = range(8)
 TRACE_STATIC_MAX_RAYS = 65536
 BUILDER_LBVH, BUILDER_PLOC = 0, 1
 TEX_CONSTANT, TEX_CHECKER = 0, 1
@@ -37,7 +38,8 @@ ABI_SYMBOLS = [
     "crt_render_accum_device", "crt_resolve_device", "crt_pack_rgba8_device", "crt_get_counters",
     "crt_reset_counters", "crt_accel_info",
     "crt_comm_unique_id", "crt_comm_init", "crt_comm_destroy", "crt_comm_info", "crt_scene_broadcast",
-    "crt_reduce_accum_device", "crt_gather_device", "crt_render_dist", "crt_trace_static",
+    "crt_reduce_accum_device", "crt_gather_tiles_device", "crt_gather_device", "crt_render_dist", "crt_trace_static",
+    "crt_debug_sort_pairs", "crt_debug_read",
 ]
 
 
@@ -127,6 +129,9 @@ def load_library():
     lib.crt_comm_info.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]
     lib.crt_scene_broadcast.argtypes = [vp, C.c_int]
     lib.crt_reduce_accum_device.argtypes = [vp, vp, sz, C.c_int]
+    lib.crt_debug_sort_pairs.argtypes = [vp, vp, vp, sz, C.c_int, C.c_int]
+    lib.crt_debug_read.argtypes = [vp, C.c_int, vp, sz, C.POINTER(C.c_int)]
+    lib.crt_gather_tiles_device.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int]
     lib.crt_gather_device.argtypes = [vp, vp, sz, vp, C.c_int]
     lib.crt_render_dist.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint64, vp]
     for name in ABI_SYMBOLS:
@@ -418,6 +423,9 @@ class Context:
     def reduce_accum_device(self, d_accum_ptr, n_floats, root=0):
         self._check(self.lib.crt_reduce_accum_device(self._h, C.c_void_p(d_accum_ptr), int(n_floats), int(root)))
 
+    def gather_tiles_device(self, d_accum_ptr, nx, ny, root=0):
+        self._check(self.lib.crt_gather_tiles_device(self._h, C.c_void_p(d_accum_ptr), int(nx), int(ny), int(root)))
+
     def gather_device(self, d_send_ptr, nbytes, d_recv_ptr, root=0):
         self._check(self.lib.crt_gather_device(self._h, C.c_void_p(d_send_ptr), int(nbytes),
                                                C.c_void_p(d_recv_ptr) if d_recv_ptr else None, int(root)))
@@ -432,6 +440,17 @@ class Context:
         self._check(self.lib.crt_render_dist(self._h, _ptr(cam), nx, ny, spp, max_depth, int(mode), int(seed),
                                              _ptr(rgb) if rank == 0 else None))
         return rgb if rank == 0 else None
+
+    # ---- test hooks ----
+    def debug_sort_pairs(self, d_keys_ptr, d_vals_ptr, n, begin_bit=0, end_bit=64):
+        self._check(self.lib.crt_debug_sort_pairs(self._h, C.c_void_p(d_keys_ptr), C.c_void_p(d_vals_ptr), int(n), begin_bit, end_bit))
+
+    def debug_read(self, which, dtype, count):
+        """(array, root): `count` items of `dtype` from the internal buffer `which` (DBG_*)."""
+        out = np.zeros(count, dtype)
+        root = C.c_int(0)
+        self._check(self.lib.crt_debug_read(self._h, int(which), _ptr(out), out.nbytes, C.byref(root)))
+        return out, root.value
 
     def sync(self):
         self._check(self.lib.crt_sync(self._h))

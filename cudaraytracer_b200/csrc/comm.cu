@@ -99,6 +99,26 @@ int bcast(crt_ctx* c, DevBuf& buf, size_t bytes, int root)
     return CRT_OK;
 }
 
+// The tiles rank `part` of `world` owns (tile index % world == part), as a compact array [local tile][32 x 32][3]:
+// PACK copies them out of the full frame, UNPACK copies them back in. Pixels beyond the image edge are skipped.
+template <bool PACK>
+__global__ void __launch_bounds__(256)
+k_tiles(float* __restrict__ frame, float* __restrict__ compact, int nx, int ny, int tiles_x, int part, int world, int n_local)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;          // one thread per pixel of a local tile
+    const size_t lt = i >> 10;
+    if (lt >= (size_t)n_local) return;
+    const uint32_t s = (uint32_t)(i & 1023u);
+    const size_t t = lt * (size_t)world + (size_t)part;
+    const int ty = (int)(t / (size_t)tiles_x), tx = (int)(t - (size_t)ty * tiles_x);
+    const int x = tx * CRT_TILE + (int)(s & 31u), y = ty * CRT_TILE + (int)(s >> 5);
+    if (x >= nx || y >= ny) return;
+    float* f = frame + 3 * ((size_t)y * nx + x);
+    float* q = compact + 3 * i;
+    if (PACK) { q[0] = f[0]; q[1] = f[1]; q[2] = f[2]; }
+    else { f[0] = q[0]; f[1] = q[1]; f[2] = q[2]; }
+}
+
 }  // namespace
 
 }  // namespace crt
@@ -225,6 +245,59 @@ int crt_reduce_accum_device(crt_ctx* c, float* d_accum, size_t n_floats, int roo
     return CRT_OK;
 }
 
+// The tile partition's own exchange: every pixel of the frame is rendered by exactly one rank, so instead of summing
+// N full frames (crt_reduce_accum_device: 24.9 MB through every link for the C3 frame) each rank packs the tiles it
+// owns (1/N of the frame) and sends them straight to `root`, which copies them into its frame: 1/N of the bytes per
+// link, all ranks into the root at once through the switch, and a copy instead of an addition, so the combined frame
+// is the single-GPU frame bit for bit by construction. d_accum: the nx x ny x 3 frame crt_render_accum_device(rank,
+// world) wrote on this rank; complete on `root` afterwards.
+int crt_gather_tiles_device(crt_ctx* c, float* d_accum, int nx, int ny, int root)
+{
+    int r = need_comm(c, "crt_gather_tiles_device");
+    if (r != CRT_OK) return r;
+    const int world = c->comm_world, rank = c->comm_rank;
+    if (!d_accum || nx <= 0 || ny <= 0 || root < 0 || root >= world) { set_error("crt_gather_tiles_device: bad arguments"); return CRT_ERR_INVALID; }
+    if (world == 1) return CRT_OK;
+    const int tiles_x = (nx + CRT_TILE - 1) / CRT_TILE, tiles_y = (ny + CRT_TILE - 1) / CRT_TILE;
+    const long long tiles = (long long)tiles_x * tiles_y;
+    auto n_local = [&](int p) { return tiles > p ? (tiles - p + world - 1) / world : 0ll; };
+    const size_t tile_floats = (size_t)CRT_TILE * CRT_TILE * 3;
+    ncclComm_t comm = (ncclComm_t)c->comm;
+    cudaStream_t st = c->stream;
+    if (rank != root) {
+        const long long nl = n_local(rank);
+        if (nl == 0) return CRT_OK;
+        CRT_CUDA(c->tile_stage.reserve((size_t)nl * tile_floats * 4));
+        k_tiles<true><<<(unsigned int)((nl * 1024 + 255) / 256), 256, 0, st>>>(d_accum, c->tile_stage.as<float>(), nx, ny, tiles_x, rank, world, (int)nl);
+        CRT_CUDA(cudaGetLastError());
+        CRT_NCCL(g_nccl.Send(c->tile_stage.p, (size_t)nl * tile_floats, ncclFloat32, root, comm, st));
+        return CRT_OK;
+    }
+    size_t total = 0;
+    for (int p = 0; p < world; p++) if (p != root) total += (size_t)n_local(p) * tile_floats;
+    CRT_CUDA(c->tile_stage.reserve(total * 4));
+    CRT_NCCL(g_nccl.GroupStart());
+    ncclResult_t res = ncclSuccess;
+    size_t off = 0;
+    for (int p = 0; p < world && res == ncclSuccess; p++) {
+        if (p == root || n_local(p) == 0) continue;
+        res = g_nccl.Recv(c->tile_stage.as<float>() + off, (size_t)n_local(p) * tile_floats, ncclFloat32, p, comm, st);
+        off += (size_t)n_local(p) * tile_floats;
+    }
+    ncclResult_t end = g_nccl.GroupEnd();
+    if (res != ncclSuccess) return nccl_fail(res, "ncclRecv");
+    if (end != ncclSuccess) return nccl_fail(end, "ncclGroupEnd");
+    off = 0;
+    for (int p = 0; p < world; p++) {
+        if (p == root || n_local(p) == 0) continue;
+        const long long nl = n_local(p);
+        k_tiles<false><<<(unsigned int)((nl * 1024 + 255) / 256), 256, 0, st>>>(d_accum, c->tile_stage.as<float>() + off, nx, ny, tiles_x, p, world, (int)nl);
+        off += (size_t)nl * tile_floats;
+    }
+    CRT_CUDA(cudaGetLastError());
+    return CRT_OK;
+}
+
 // Rank r's `bytes` at d_send arrive at d_recv + r * bytes on `root` (d_recv is only read there).
 int crt_gather_device(crt_ctx* c, const void* d_send, size_t bytes, void* d_recv, int root)
 {
@@ -252,7 +325,7 @@ int crt_gather_device(crt_ctx* c, const void* d_send, size_t bytes, void* d_recv
 }
 
 // One frame across the communicator's GPUs (collective): every rank renders the tiles it owns of the SAME frame
-// (bit-identical to the one-GPU image), the accumulators are summed onto rank 0, which resolves and copies the image
+// (bit-identical to the one-GPU image), the tiles travel to rank 0 (crt_gather_tiles_device), which resolves and copies the image
 // to rgb_out (ignored on the other ranks, may be NULL there). Returns when the frame is in rgb_out (rank 0) or when
 // this rank's share is queued (others).
 int crt_render_dist(crt_ctx* c, const crt_camera* cam, int nx, int ny, int spp, int max_depth, int shade_mode,
@@ -265,7 +338,7 @@ int crt_render_dist(crt_ctx* c, const crt_camera* cam, int nx, int ny, int spp, 
     const size_t npix = (size_t)nx * ny;
     CRT_CUDA(c->accum.reserve(npix * 12));
     if ((r = crt_render_accum_device(c, cam, nx, ny, 0, spp, max_depth, shade_mode, seed, c->comm_rank, c->comm_world, c->accum.as<float>())) != CRT_OK) return r;
-    if ((r = crt_reduce_accum_device(c, c->accum.as<float>(), npix * 3, 0)) != CRT_OK) return r;
+    if ((r = crt_gather_tiles_device(c, c->accum.as<float>(), nx, ny, 0)) != CRT_OK) return r;
     if (c->comm_rank == 0) {
         CRT_CUDA(c->rgb.reserve(npix * 12));
         if ((r = launch_resolve(c, c->accum.as<float>(), npix, spp, c->rgb.as<float>())) != CRT_OK) return r;

@@ -200,7 +200,7 @@ void crt_destroy(crt_ctx* c)
                       &c->keys[0], &c->keys[1], &c->vals[0], &c->vals[1], &c->hist, &c->nodes, &c->recs,
                       &c->child, &c->parent, &c->leaf_parent, &c->range, &c->node_box, &c->leaf_box, &c->flags,
                       &c->bounds, &c->depth_out, &c->ploc_box[0], &c->ploc_box[1], &c->ploc_nn, &c->ploc_tmp, &c->ploc_blk, &c->work_ctr, &c->accum, &c->rgb,
-                      &c->rays_tmp, &c->hits_tmp, &c->counters, &c->rest, &c->part_id, &c->part_T, &c->tri_idx, &c->node_cone, &c->frames, &c->tri_frame, &c->sph_frame, &c->rect_mat, &c->rect_id, &c->rect_frame};
+                      &c->rays_tmp, &c->hits_tmp, &c->counters, &c->rest, &c->part_id, &c->part_T, &c->tri_idx, &c->node_cone, &c->frames, &c->tri_frame, &c->sph_frame, &c->rect_mat, &c->rect_id, &c->rect_frame, &c->tile_stage};
     for (DevBuf* b : bufs) b->release();
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
@@ -764,6 +764,59 @@ int crt_reset_counters(crt_ctx* c)
     c->host_counters = crt_counters{};
     c->host_counters.build_ms = b;
     c->host_counters.refit_ms = r;
+    return CRT_OK;
+}
+
+int crt_debug_sort_pairs(crt_ctx* c, uint64_t* d_keys, uint32_t* d_vals, size_t n, int begin_bit, int end_bit)
+{
+    CRT_CHECK_SETTLED(c);
+    if (n == 0) return CRT_OK;
+    if (!d_keys || !d_vals || n >= (1ull << 32) || begin_bit < 0 || end_bit > 64 || begin_bit >= end_bit || (begin_bit & 7) || (end_bit & 7)) {
+        set_error("crt_debug_sort_pairs: bad arguments");
+        return CRT_ERR_INVALID;
+    }
+    DevBuf k2, v2, hist;
+    CRT_CUDA(k2.reserve(n * 8));
+    CRT_CUDA(v2.reserve(n * 4));
+    CRT_CUDA(hist.reserve(radix_sort_hist_bytes()));
+    uint64_t* keys[2] = {d_keys, k2.as<uint64_t>()};
+    uint32_t* vals[2] = {d_vals, v2.as<uint32_t>()};
+    const int where = radix_sort_pairs(c->stream, keys, vals, (uint32_t)n, begin_bit, end_bit, hist.as<uint32_t>());
+    if (where != 0) {
+        cudaMemcpyAsync(d_keys, k2.p, n * 8, cudaMemcpyDeviceToDevice, c->stream);
+        cudaMemcpyAsync(d_vals, v2.p, n * 4, cudaMemcpyDeviceToDevice, c->stream);
+    }
+    cudaError_t e = cudaStreamSynchronize(c->stream);
+    if (e == cudaSuccess) e = cudaGetLastError();
+    k2.release(); v2.release(); hist.release();
+    if (e != cudaSuccess) return cuda_fail(e, "crt_debug_sort_pairs", __FILE__, __LINE__);
+    return CRT_OK;
+}
+
+int crt_debug_read(crt_ctx* c, int which, void* host_out, size_t bytes, int* root_out)
+{
+    CRT_CHECK_SETTLED(c);
+    if (!c->accel_valid) { set_error("crt_debug_read: no acceleration structure"); return CRT_ERR_STATE; }
+    if (root_out) *root_out = c->root;
+    if (bytes == 0) return CRT_OK;
+    if (!host_out) { set_error("crt_debug_read: null buffer"); return CRT_ERR_INVALID; }
+    const size_t n = c->n_prims, ni = n > 1 ? n - 1 : 0;
+    const DevBuf* b = nullptr;
+    size_t have = 0;
+    switch (which) {
+    case CRT_DBG_NODES: b = &c->nodes; have = ni * 128; break;
+    case CRT_DBG_RECS: b = &c->recs; have = n * 64; break;
+    case CRT_DBG_KEYS: b = &c->keys[c->builder == CRT_BUILDER_PLOC ? 0 : c->perm_buf]; have = n * 8; break;
+    case CRT_DBG_PERM: b = &c->vals[c->perm_buf]; have = n * 4; break;
+    case CRT_DBG_CHILD: b = &c->child; have = ni * 8; break;
+    case CRT_DBG_RANGE: b = &c->range; have = ni * 8; break;
+    case CRT_DBG_LEAF_BOX: b = &c->leaf_box; have = n * 32; break;
+    case CRT_DBG_NODE_BOX: b = &c->node_box; have = ni * 32; break;
+    default: set_error("crt_debug_read: unknown buffer %d", which); return CRT_ERR_INVALID;
+    }
+    if (bytes > have || bytes > b->cap) { set_error("crt_debug_read: %zu bytes asked, the buffer holds %zu", bytes, have); return CRT_ERR_INVALID; }
+    CRT_CUDA(cudaMemcpyAsync(host_out, b->p, bytes, cudaMemcpyDeviceToHost, c->stream));
+    CRT_CUDA(cudaStreamSynchronize(c->stream));
     return CRT_OK;
 }
 

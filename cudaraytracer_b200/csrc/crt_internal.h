@@ -93,6 +93,7 @@ struct crt_ctx {
     size_t n_rect = 0;
     // multi-GPU (comm.cu): NCCL communicator of this context's rank
     void* comm = nullptr;
+    crt::DevBuf tile_stage;                // crt_gather_tiles_device: packed tiles (own on a sender, everybody else's on the root)
     int comm_rank = 0, comm_world = 1;
     // rigid parts (bones): rest-pose vertices (n_tri x 9 floats), part of each triangle, the current translations
     crt::DevBuf rest, part_id, part_T;

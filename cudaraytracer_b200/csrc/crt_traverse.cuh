@@ -63,6 +63,18 @@ namespace crt {
 #define CRT_STACK_ENTRIES (CRT_STACK_SMEM + CRT_STACK_LOCAL)
 #define CRT_NODE_DONE ((int)0x80000000)
 
+// Slack of every "is this box entered before the closest hit so far" comparison, relative to the distance: 2^-17.
+// The box distances are accurate to a few 2^-24, but the distance a PRIMITIVE test reports is not: the reference's
+// Moeller-Trumbore arithmetic (shapes/triangle.h:69-92) loses k 2^-24 t / cos(incidence) to cancellation in
+// s = o - v0 and the two cross products, so a triangle hit at a grazing angle can report a t that lies outside its
+// own box's interval by more than the 2^-21 the boxes are widened by. Which hit wins must not depend on the order
+// in which a traversal meets two such near-ties (the list scan meets them all), so a subtree is only skipped when
+// its entry distance exceeds the closest hit by this margin. Measured at C4's size (camera 2,700 units from the
+// scene, 5.3e8 camera rays): with 2^-21 the packet and the per-ray traversal disagreed on 14 pixels of the frame
+// (profiles/r02_e_c4_invariance.txt); the margin costs < 0.1 % more node visits.
+#define CRT_T_SLACK 7.62939453125e-6f           // 2^-17
+#define CRT_T_SLACK1 1.00000762939453125f       // 1 + 2^-17
+
 constexpr int TP_BLOCK = 128;    // threads per block of every traversal kernel
 #ifndef CRT_TRACE_MIN_BLOCKS
 #define CRT_TRACE_MIN_BLOCKS 8   // resident blocks per SM the register allocation must allow
@@ -279,7 +291,7 @@ __device__ __forceinline__ void traverse_persistent(const AccelView& A, const ui
             if (sp < CRT_STACK_SMEM) { node = lds32(stack_base + sp * LEVEL); tn = __int_as_float(lds32(tstack_base + sp * LEVEL)); }
             else { node = lstack[sp - CRT_STACK_SMEM]; tn = lstack_t[sp - CRT_STACK_SMEM]; }
             // still entered before the current closest hit? (the slack of the test that pushed it)
-            if (tn <= best.t * 1.0000005f) break;
+            if (tn <= best.t * CRT_T_SLACK1) break;
         }
     };
 #else
@@ -357,7 +369,7 @@ __device__ __forceinline__ void traverse_persistent(const AccelView& A, const ui
                     const float az = fmaf(f[5 * k + 2], S.iz, S.cz_lo), bz = fmaf(hz, S.iz, S.cz_hi);
                     const float tn = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), t_min));
                     const float tf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), best.t));
-                    const bool h = tn <= tf * 1.0000005f && ref[k] != CRT_SLOT_EMPTY;
+                    const bool h = tn <= tf * CRT_T_SLACK1 && ref[k] != CRT_SLOT_EMPTY;
                     key[k] = h ? tn : INFINITY;
                     n_hit += h ? 1 : 0;
                 }
@@ -522,8 +534,8 @@ __device__ __forceinline__ void traverse_packets(const AccelView& A, const uint3
                             const float ny = fminf(fminf(y00, y01), fminf(y10, y11)), fy = fmaxf(fmaxf(y00, y01), fmaxf(y10, y11));
                             const float nz = fminf(fminf(z00, z01), fminf(z10, z11)), fz = fmaxf(fmaxf(z00, z01), fmaxf(z10, z11));
                             float tn = fmaxf(fmaxf(nx, ny), nz), tf = fminf(fminf(fx, fy), fz);
-                            tn = fmaf(-fabsf(tn), 4.76837158203125e-7f, tn);       // 2^-21 towards "enters earlier"
-                            tf = fmaf(fabsf(tf), 4.76837158203125e-7f, tf);        // and "leaves later"
+                            tn = fmaf(-fabsf(tn), CRT_T_SLACK, tn);                // towards "enters earlier"
+                            tf = fmaf(fabsf(tf), CRT_T_SLACK, tf);                 // and "leaves later"
                             tn = fmaxf(tn, t_min);
                             tf = fminf(tf, t_far);
                             // two-level select on the bits of kid (a chain of ?: compiles to divergent branches)
@@ -570,7 +582,7 @@ __device__ __forceinline__ void traverse_packets(const AccelView& A, const uint3
                                 const float az = fmaf(f[5 * k + 2], S.iz, S.cz_lo), bz = fmaf(hz, S.iz, S.cz_hi);
                                 const float tn = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), t_min));
                                 const float tf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), best.t));
-                                const bool h = live && tn <= tf * 1.0000005f;
+                                const bool h = live && tn <= tf * CRT_T_SLACK1;
                                 const uint32_t m = ref[k] != CRT_SLOT_EMPTY ? __ballot_sync(FULL, h) : 0u;   // ref is uniform
                                 // entry distance of the first lane that enters the child; uniform
                                 key[k] = m ? __shfl_sync(FULL, tn, __ffs(m) - 1) : INFINITY;
@@ -702,7 +714,7 @@ __device__ __forceinline__ Hit trace_wide_one(const AccelView& A, const v3 o, co
             sp -= p;
             const int ref = (int)e.x;
             // still entered before the current closest hit? (same slack as the test that pushed it)
-            const bool alive = have && __uint_as_float(e.y) <= best.t * 1.0000005f;
+            const bool alive = have && __uint_as_float(e.y) <= best.t * CRT_T_SLACK1;
 
             // ---- inner node: the four children against the ray ----
             float key[4] = {INFINITY, INFINITY, INFINITY, INFINITY};
@@ -724,7 +736,7 @@ __device__ __forceinline__ Hit trace_wide_one(const AccelView& A, const v3 o, co
                     const float az = fmaf(f[5 * k + 2], S.iz, S.cz_lo), bz = fmaf(hz, S.iz, S.cz_hi);
                     const float tn = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), t_min));
                     const float tf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), best.t));
-                    const bool h = tn <= tf * 1.0000005f && cref[k] != CRT_SLOT_EMPTY;
+                    const bool h = tn <= tf * CRT_T_SLACK1 && cref[k] != CRT_SLOT_EMPTY;
                     key[k] = h ? tn : INFINITY;
                     n_hit += h ? 1 : 0;
                 }

@@ -340,9 +340,12 @@ int crt_pack_rgba8_device(crt_ctx* ctx, const float* d_rgb, int nx, int ny, uint
  *                        buffer); each rank then calls crt_accel_build - the build is deterministic, so all trees agree
  *   crt_reduce_accum_device  sum of the ranks' accumulators onto `root`, in place there. With the tile partition
  *                        (crt_render_accum_device(rank, world)) each pixel is non-zero on one rank: the sum is exact
+ *   crt_gather_tiles_device  the tile partition's own exchange: each rank sends only the tiles it rendered (1/N of the
+ *                        frame) to `root`, which copies them into its d_accum - the frame there is then the single-GPU
+ *                        frame bit for bit; what crt_render_dist uses
  *   crt_gather_device    rank r's `bytes` land at d_recv + r * bytes on `root` (hit records of a crt_trace batch
  *                        split across ranks)
- *   crt_render_dist      one frame: every rank renders its tiles, reduce, rank 0 resolves and copies the image to
+ *   crt_render_dist      one frame: every rank renders its tiles, tile gather, rank 0 resolves and copies the image to
  *                        rgb_out (may be NULL elsewhere); bit-identical to crt_render on one GPU */
 #define CRT_COMM_ID_BYTES 128
 int crt_comm_unique_id(void* id_out);
@@ -351,6 +354,7 @@ int crt_comm_destroy(crt_ctx* ctx);
 int crt_comm_info(crt_ctx* ctx, int* rank, int* world, int* nccl_version);
 int crt_scene_broadcast(crt_ctx* ctx, int root);
 int crt_reduce_accum_device(crt_ctx* ctx, float* d_accum, size_t n_floats, int root);
+int crt_gather_tiles_device(crt_ctx* ctx, float* d_accum, int nx, int ny, int root);
 int crt_gather_device(crt_ctx* ctx, const void* d_send, size_t bytes, void* d_recv, int root);
 int crt_render_dist(crt_ctx* ctx, const crt_camera* cam, int nx, int ny, int spp, int max_depth, int shade_mode,
                     uint64_t seed, float* rgb_out);
@@ -359,6 +363,21 @@ int crt_render_dist(crt_ctx* ctx, const crt_camera* cam, int nx, int ny, int spp
  *      (swatch.h:4-18, Loader/CSVWriter.h:8-32) ---- */
 int crt_get_counters(crt_ctx* ctx, crt_counters* out);
 int crt_reset_counters(crt_ctx* ctx);
+
+/* ---- test hooks: the builder's stages on their own (no counterpart in the reference, whose builder is one recursive
+ *      function, hitable/bvh.h:76-125) ----
+ * crt_debug_sort_pairs: the hand-written LSD radix sort of the LBVH build on caller-owned DEVICE arrays: n (64-bit
+ *      key, 32-bit value) pairs, stably sorted by key bits [begin_bit, end_bit) (multiples of 8), result back in
+ *      d_keys / d_vals; synchronous.
+ * crt_debug_read: copies an internal device buffer of the last crt_accel_build to host memory: CRT_DBG_NODES (one
+ *      128-byte 4-wide node per binary node, layout in csrc/crt_device.cuh), CRT_DBG_RECS (64 bytes per sorted
+ *      primitive), CRT_DBG_KEYS (sorted 64-bit Morton keys), CRT_DBG_PERM (sorted position -> input index),
+ *      CRT_DBG_CHILD / CRT_DBG_RANGE (int2 per binary node: children, covered range), CRT_DBG_LEAF_BOX /
+ *      CRT_DBG_NODE_BOX (two float4 per entry). `bytes` must not exceed the buffer; *root_out gets the root reference. */
+typedef enum { CRT_DBG_NODES = 0, CRT_DBG_RECS = 1, CRT_DBG_KEYS = 2, CRT_DBG_PERM = 3, CRT_DBG_CHILD = 4, CRT_DBG_RANGE = 5,
+               CRT_DBG_LEAF_BOX = 6, CRT_DBG_NODE_BOX = 7 } crt_debug_buffer;
+int crt_debug_sort_pairs(crt_ctx* ctx, uint64_t* d_keys, uint32_t* d_vals, size_t n, int begin_bit, int end_bit);
+int crt_debug_read(crt_ctx* ctx, int which, void* host_out, size_t bytes, int* root_out);
 
 /* Sizes of the acceleration structure, for reports. */
 int crt_accel_info(crt_ctx* ctx, uint64_t* n_prims, uint64_t* n_nodes, uint64_t* bytes, int* max_depth);

@@ -1,0 +1,54 @@
+"""One rank's share of the C3 (or C4) frame on ONE GPU: renders tiles rank, rank + world, ... of the frame K times and
+prints the device time per frame. Development aid for the strong-scaling work (what a rank of an N-GPU run executes,
+without the reduce); run it under `ncu --metrics gpu__time_duration.sum` for the per-kernel list.
+  python scripts/frame_part.py [--world 8] [--rank 0] [--lanes 4] [--slice-min N] [--steps 10] [--workload c3|c4] [--timing]"""
+import argparse
+import sys
+
+import torch
+
+sys.path.insert(0, ".")
+import cudaraytracer_b200 as crt
+from cudaraytracer_b200 import scenes
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--world", type=int, default=8)
+ap.add_argument("--rank", type=int, default=0)
+ap.add_argument("--lanes", type=int, default=4)
+ap.add_argument("--slice-min", type=int, default=0)
+ap.add_argument("--steps", type=int, default=10)
+ap.add_argument("--wide-below", type=int, default=-1)
+ap.add_argument("--workload", default="c3")
+ap.add_argument("--timing", action="store_true", help="CRT_OPT_TIMING: per-bounce lines on stderr (needs CRT_TRACE_TIMING=1 in the environment)")
+a = ap.parse_args()
+sc = scenes.c4_instanced() if a.workload == "c4" else scenes.c3_mesh()
+nx, ny, spp, depth = sc["nx"], sc["ny"], sc["spp"], sc["max_depth"]
+cam = crt.camera_for(sc)
+ctx = crt.Context(0)
+ctx.set_option(crt.OPT_LANES, a.lanes)
+if a.slice_min:
+    ctx.set_option(crt.OPT_SLICE_MIN, a.slice_min)
+if a.wide_below >= 0:
+    ctx.set_option(crt.OPT_WIDE_BELOW, a.wide_below)
+ctx.set_scene(sc)
+ctx.build()
+dev = torch.device("cuda", 0)
+accum = torch.zeros(ny, nx, 3, dtype=torch.float32, device=dev)
+ext = torch.cuda.ExternalStream(ctx.stream(), device=dev)
+if a.timing:
+    ctx.set_option(crt.OPT_TIMING, 1)
+for i in range(3):
+    ctx.render_accum_device(cam, nx, ny, 0, spp, depth, crt.SHADE_PATH, 1 + i, a.rank, a.world, accum.data_ptr())
+ctx.sync()
+ctx.reset_counters()
+e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+e0.record(ext)
+for i in range(a.steps):
+    ctx.render_accum_device(cam, nx, ny, 0, spp, depth, crt.SHADE_PATH, 100 + i, a.rank, a.world, accum.data_ptr())
+e1.record(ext)
+ctx.sync()
+c = ctx.counters()
+print("world %d rank %d lanes %d(%d in use) slice_min %d: %.3f ms/frame, %.0f Mrays/s, %d launches/frame" % (
+    a.world, a.rank, a.lanes, c["lanes"], a.slice_min, e0.elapsed_time(e1) / a.steps, c["rays"] / e0.elapsed_time(e1) / 1e3, c["launches"] // a.steps), flush=True)
+del accum, e0, e1, ext
+ctx.close()
