@@ -71,8 +71,32 @@ struct Hit {
 // (hitable/hitable.h:34, hitable/transform.h:50-54).
 CRT_HD v3 ray_dir_local(v3 d) { return vunit(vunit(d)); }
 
+// Deviation D3: one axis of "where is the ray inside the triangle's bounding box". The box is that of v0, v0 + e1,
+// v0 + e2, its planes moved out by 2^-16 of its largest coordinate; the plane distances are (plane - o) * (1 / d)
+// in plain rounded float operations, so that every kernel, the host emulation and both oracles evaluate the same bits.
+CRT_HD void d3_axis(float o, float d, float a, float e1, float e2, float& t_near, float& t_far)
+{
+    const float b = x::add(a, e1), c = x::add(a, e2);
+    float lo = fminf(a, fminf(b, c)), hi = fmaxf(a, fmaxf(b, c));
+    // planes moved out by 2^-16 of the box's largest coordinate: half of what the tree's boxes are widened by
+    // (lbvh.cu:prim_box), so a ray that passes here also passes every box test on the way down
+    const float pad = x::add(x::mul(fmaxf(fabsf(lo), fabsf(hi)), 1.52587890625e-5f), 1e-30f);
+    lo = x::sub(lo, pad);
+    hi = x::add(hi, pad);
+    const float inv = fabsf(d) > 1e-18f ? x::div(1.0f, d) : copysignf(1e18f, d);
+    const float t0 = x::mul(x::sub(lo, o), inv), t1 = x::mul(x::sub(hi, o), inv);
+    t_near = fmaxf(t_near, fminf(t0, t1));
+    t_far = fminf(t_far, fmaxf(t0, t1));
+}
+#define CRT_D3_EPS 3.0517578125e-5f   // 2^-15
+
 // shapes/triangle.h:57-100 plus deviation D1 (accept only t_min < t < t_max;
-// SURVEY §9 Q2). v0/e1/e2/n as stored in the record. A candidate with t equal
+// SURVEY §9 Q2) and deviation D3: the hit distance must lie where the ray is inside the triangle's own bounding box
+// (within 2^-15 relative). The reference's Moeller-Trumbore arithmetic loses all accuracy on sliver triangles and
+// then reports "hits" tens of units away from the triangle (measured on C4's pole slivers, profiles/r02_g_c4_walk.txt):
+// the list scan takes them, any bounding-volume hierarchy - the reference's own BVHNode included, whose leaves test
+// their box first (hitable/bvh.h:165) - cannot reach them, and which of two traversals stumbles on one would decide
+// the pixel. D3 makes the answer a function of the ray and the triangle alone. v0/e1/e2/n as stored in the record. A candidate with t equal
 // to the current best is still returned (t <= t_best); the caller breaks the
 // tie by primitive id.
 CRT_HD bool triangle_test(v3 o, v3 d, v3 v0, v3 e1, v3 e2, v3 n, float t_min, float t_best,
@@ -92,6 +116,11 @@ CRT_HD bool triangle_test(v3 o, v3 d, v3 v0, v3 e1, v3 e2, v3 n, float t_min, fl
     if (v < 0.0f || x::add(u, v) > 1.0f) return false;     // triangle.h:89
     float t = x::mul(f, vdot(e2, q));                      // triangle.h:92
     if (!(t > t_min && t <= t_best)) return false;         // D1
+    float t_near = -INFINITY, t_far = INFINITY;            // D3
+    d3_axis(o.x, d.x, v0.x, e1.x, e2.x, t_near, t_far);
+    d3_axis(o.y, d.y, v0.y, e1.y, e2.y, t_near, t_far);
+    d3_axis(o.z, d.z, v0.z, e1.z, e2.z, t_near, t_far);
+    if (!(t >= x::sub(t_near, x::mul(fabsf(t_near), CRT_D3_EPS)) && t <= x::add(t_far, x::mul(fabsf(t_far), CRT_D3_EPS)))) return false;
     t_out = t; u_out = u; v_out = v;
     return true;
 }

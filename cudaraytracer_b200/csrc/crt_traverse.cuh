@@ -63,17 +63,20 @@ namespace crt {
 #define CRT_STACK_ENTRIES (CRT_STACK_SMEM + CRT_STACK_LOCAL)
 #define CRT_NODE_DONE ((int)0x80000000)
 
-// Slack of every "is this box entered before the closest hit so far" comparison, relative to the distance: 2^-17.
+// Slack of every "is this box entered before the closest hit so far" comparison, relative to the distance: 2^-14,
+// twice the tolerance of deviation D3 (crt_device.cuh:triangle_test), so that a triangle hit D3 accepts (its distance
+// lies within 2^-15 of its own box's interval, and every ancestor's box contains that box) is never in a subtree the
+// traversal skipped unless a strictly closer hit exists.
 // The box distances are accurate to a few 2^-24, but the distance a PRIMITIVE test reports is not: the reference's
 // Moeller-Trumbore arithmetic (shapes/triangle.h:69-92) loses k 2^-24 t / cos(incidence) to cancellation in
 // s = o - v0 and the two cross products, so a triangle hit at a grazing angle can report a t that lies outside its
 // own box's interval by more than the 2^-21 the boxes are widened by. Which hit wins must not depend on the order
 // in which a traversal meets two such near-ties (the list scan meets them all), so a subtree is only skipped when
 // its entry distance exceeds the closest hit by this margin. Measured at C4's size (camera 2,700 units from the
-// scene, 5.3e8 camera rays): with 2^-21 the packet and the per-ray traversal disagreed on 14 pixels of the frame
-// (profiles/r02_e_c4_invariance.txt); the margin costs < 0.1 % more node visits.
-#define CRT_T_SLACK 7.62939453125e-6f           // 2^-17
-#define CRT_T_SLACK1 1.00000762939453125f       // 1 + 2^-17
+// scene, 5.3e8 camera rays): with 2^-21 and without D3 the packet and the per-ray traversal disagreed on 14 pixels
+// of the frame (profiles/r02_e_c4_invariance.txt).
+#define CRT_T_SLACK 6.103515625e-5f             // 2^-14
+#define CRT_T_SLACK1 1.00006103515625f          // 1 + 2^-14
 
 constexpr int TP_BLOCK = 128;    // threads per block of every traversal kernel
 #ifndef CRT_TRACE_MIN_BLOCKS

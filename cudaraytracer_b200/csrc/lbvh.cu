@@ -69,8 +69,8 @@ __device__ __forceinline__ void chain_point_to_world(const DFrame* __restrict__ 
 }
 
 // Box of input primitive p: the reference's Triangle::bounding_box / Sphere::bounding_box / Rectangle::bounding_box
-// (shapes/triangle.h:102-115, shapes/sphere.h:58-62, shapes/rectangle.h:11-14) in WORLD space, widened by a relative
-// 2^-21 so that ulp-level differences between the box test and the exact primitive test cannot cull a hit.
+// (shapes/triangle.h:102-115, shapes/sphere.h:58-62, shapes/rectangle.h:11-14) in WORLD space, widened per axis by
+// 2^-15 of its largest coordinate (see the end of this function).
 // A primitive under a chain is tested in its own frame (crt_device.cuh:framed_test) on a ray that was rotated and
 // translated in fp32, so where its world-space image lies is only known up to the rounding of that map, which grows
 // with the distance of the ray origin: its box is padded by 2^-16 of the scene's largest coordinate per level
@@ -111,22 +111,29 @@ __device__ __forceinline__ Box prim_box(const PrimSrc& S, uint32_t p)
             nc = 4;
         }
         b = Box{INFINITY, INFINITY, INFINITY, -INFINITY, -INFINITY, -INFINITY};
+        float local_max = 0.0f;                     // D3 pads the triangle's box in its OWN frame, by its coordinates there
+        for (int k = 0; k < nc; k++) local_max = fmaxf(local_max, fmaxf(fabsf(c[k][0]), fmaxf(fabsf(c[k][1]), fabsf(c[k][2]))));
         for (int k = 0; k < nc; k++) {
             chain_point_to_world(S.frames, chain, c[k][0], c[k][1], c[k][2]);
             b.lx = fminf(b.lx, c[k][0]); b.ly = fminf(b.ly, c[k][1]); b.lz = fminf(b.lz, c[k][2]);
             b.hx = fmaxf(b.hx, c[k][0]); b.hy = fmaxf(b.hy, c[k][1]); b.hz = fmaxf(b.hz, c[k][2]);
         }
         float scale = fmaxf(fmaxf(fabsf(b.lx), fabsf(b.hx)), fmaxf(fmaxf(fabsf(b.ly), fabsf(b.hy)), fmaxf(fabsf(b.lz), fabsf(b.hz)))) + r;
+        scale = fmaxf(scale, local_max);
         if (S.pad_bounds)
             for (int k = 0; k < 6; k++) scale = fmaxf(scale, fabsf(S.pad_bounds[k]));
         const float pad = r + scale * 1.52587890625e-5f * (float)(chain & 255u) + 1e-30f;   // 2^-16 per level
         if (!(scale < INFINITY)) b = Box{-INFINITY, -INFINITY, -INFINITY, INFINITY, INFINITY, INFINITY};   // NaN / inf geometry: never culled
         b.lx -= pad; b.ly -= pad; b.lz -= pad; b.hx += pad; b.hy += pad; b.hz += pad;
     }
-    const float k = 4.76837158e-7f;   // 2^-21
-    const float tiny = 1e-30f;
-    b.lx -= fabsf(b.lx) * k + tiny; b.ly -= fabsf(b.ly) * k + tiny; b.lz -= fabsf(b.lz) * k + tiny;
-    b.hx += fabsf(b.hx) * k + tiny; b.hy += fabsf(b.hy) * k + tiny; b.hz += fabsf(b.hz) * k + tiny;
+    // every axis widened by 2^-15 of its largest coordinate: twice what deviation D3 (crt_device.cuh:triangle_test)
+    // pads the triangle's own box by, so that a hit D3 accepts is always inside every box on the way down
+    const float k = 3.0517578125e-5f;   // 2^-15
+    const float tiny = 1e-29f;
+    const float mx = fmaxf(fabsf(b.lx), fabsf(b.hx)) * k + tiny, my = fmaxf(fabsf(b.ly), fabsf(b.hy)) * k + tiny,
+                mz = fmaxf(fabsf(b.lz), fabsf(b.hz)) * k + tiny;
+    b.lx -= mx; b.ly -= my; b.lz -= mz;
+    b.hx += mx; b.hy += my; b.hz += mz;
     return b;
 }
 

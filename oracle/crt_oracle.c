@@ -125,6 +125,21 @@ static ray_t transform_ray(const xform_t* xf, ray_t r)
     return r;
 }
 
+/* Deviation D3 (see cudaraytracer_b200/csrc/crt_device.cuh:triangle_test): one axis of the interval in which the ray
+ * is inside the box of v0, v0 + e1, v0 + e2; plain rounded float operations in this order. */
+static void d3_axis(float o, float d, float a, float e1, float e2, float* t_near, float* t_far)
+{
+    float b = a + e1, c = a + e2;
+    float lo = fminf(a, fminf(b, c)), hi = fmaxf(a, fmaxf(b, c));
+    float pad = fmaxf(fabsf(lo), fabsf(hi)) * 1.52587890625e-5f + 1e-30f;   /* 2^-16 of the largest coordinate */
+    lo = lo - pad;
+    hi = hi + pad;
+    float inv = fabsf(d) > 1e-18f ? 1.0f / d : copysignf(1e18f, d);
+    float t0 = (lo - o) * inv, t1 = (hi - o) * inv;
+    *t_near = fmaxf(*t_near, fminf(t0, t1));
+    *t_far = fminf(*t_far, fmaxf(t0, t1));
+}
+
 /* shapes/triangle.h:57-100 */
 static int triangle_test(const prim_t* p, ray_t r, float t_min, float t_max, int d1, hitrec_t* rec)
 {
@@ -144,6 +159,17 @@ static int triangle_test(const prim_t* p, ray_t r, float t_min, float t_max, int
     if (v < 0.0 || u + v > 1.0) return 0;
     float t = f * vdot(e2, q);
     if (d1 && !(t > t_min && t < t_max)) return 0;   /* deviation D1 */
+    if (d1) {                                         /* deviation D3, applied together with D1 */
+        const float E = 3.0517578125e-5f;             /* 2^-15 */
+        float t_near = -INFINITY, t_far = INFINITY, m;
+        d3_axis(r.o.x, r.d.x, p->v0.x, e1.x, e2.x, &t_near, &t_far);
+        d3_axis(r.o.y, r.d.y, p->v0.y, e1.y, e2.y, &t_near, &t_far);
+        d3_axis(r.o.z, r.d.z, p->v0.z, e1.z, e2.z, &t_near, &t_far);
+        m = fabsf(t_near) * E;
+        if (!(t >= t_near - m)) return 0;
+        m = fabsf(t_far) * E;
+        if (!(t <= t_far + m)) return 0;
+    }
     rec->t = t;
     rec->p = vadd(r.o, vscale(t, r.d));       /* ray.h:18 */
     rec->normal = p->n;

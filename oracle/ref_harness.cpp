@@ -61,6 +61,21 @@ inline uint32_t untag(const HitRecord& rec)
     return uint32_t(rec.u) | (uint32_t(rec.v) << 16);
 }
 
+// Deviation D3 (cudaraytracer_b200/csrc/crt_device.cuh:triangle_test): one axis of the interval in which the ray is
+// inside the box of v0, v0 + e1, v0 + e2, in plain rounded float operations in this order.
+inline void d3_axis(float o, float d, float a, float e1, float e2, float& t_near, float& t_far)
+{
+    float b = a + e1, c = a + e2;
+    float lo = fminf(a, fminf(b, c)), hi = fmaxf(a, fmaxf(b, c));
+    float pad = fmaxf(fabsf(lo), fabsf(hi)) * 1.52587890625e-5f + 1e-30f;   /* 2^-16 of the largest coordinate */
+    lo = lo - pad;
+    hi = hi + pad;
+    float inv = fabsf(d) > 1e-18f ? 1.0f / d : copysignf(1e18f, d);
+    float t0 = (lo - o) * inv, t1 = (hi - o) * inv;
+    t_near = fmaxf(t_near, fminf(t0, t1));
+    t_far = fminf(t_far, fmaxf(t0, t1));
+}
+
 class TaggedTriangle : public Triangle {
 public:
     TaggedTriangle(vec3 vs[3], vec3 n, Material* m, Transform* t, uint32_t id_, bool d1_)
@@ -70,6 +85,17 @@ public:
     {
         if (!Triangle::collision_detection(r, t_min, t_max, rec, frameIndex)) return false;
         if (d1 && !(rec.t > t_min && rec.t < t_max)) return false;
+        if (d1) {                                   // deviation D3, applied together with D1
+            const vec3 e1 = vertices[1] - vertices[0], e2 = vertices[2] - vertices[0];
+            const vec3 o = r.origin(), d = r.direction();
+            float t_near = -INFINITY, t_far = INFINITY;
+            for (int k = 0; k < 3; k++) d3_axis(o[k], d[k], vertices[0][k], e1[k], e2[k], t_near, t_far);
+            const float E = 3.0517578125e-5f;        // 2^-15
+            float m = fabsf(t_near) * E;
+            if (!(rec.t >= t_near - m)) return false;
+            m = fabsf(t_far) * E;
+            if (!(rec.t <= t_far + m)) return false;
+        }
         tag(rec, id);
         return true;
     }
