@@ -71,16 +71,26 @@ struct Hit {
 // (hitable/hitable.h:34, hitable/transform.h:50-54).
 CRT_HD v3 ray_dir_local(v3 d) { return vunit(vunit(d)); }
 
-// Deviation D3: one axis of "where is the ray inside the triangle's bounding box". The box is that of v0, v0 + e1,
-// v0 + e2, its planes moved out by 2^-16 of its largest coordinate; the plane distances are (plane - o) * (1 / d)
-// in plain rounded float operations, so that every kernel, the host emulation and both oracles evaluate the same bits.
+// Deviation D3: a triangle hit counts only if its distance t lies where the ray is inside the triangle's own bounding
+// box - the box of v0, v0 + e1, v0 + e2 with its planes moved out by 2^-16 of its largest coordinate - within 2^-15
+// relative. The reference's Moeller-Trumbore arithmetic loses all accuracy on sliver triangles and then reports, with
+// u and v in range, a t that is tens of units off (measured on C4's pole slivers, profiles/r02_g_c4_walk.txt): the
+// list scan takes such hits, any bounding-volume hierarchy - the reference's own BVHNode included, whose leaves test
+// their box first (hitable/bvh.h:165) - cannot reach them, and which of two traversals stumbles on one would decide
+// the pixel. With D3 the answer is a function of the ray and the triangle alone, and an accepted hit lies inside the
+// triangle's padded box, hence inside every box above it (lbvh.cu:prim_box widens by twice as much, and the
+// traversals skip a box only beyond 2^-14 of the closest hit, crt_traverse.cuh:CRT_T_SLACK).
+//
+// d3_interval is the definition, in plain rounded float operations that every side (kernels, host emulation, both
+// oracles) evaluates bit for bit. d3_agrees is a shortcut only this header takes: when the point along the ray,
+// o + t d, agrees with the point the barycentrics give, v0 + u e1 + v e2 (which lies in the box by construction), to
+// within HALF of D3's tolerances, d3_interval is certain to accept, and its three divisions are skipped. Almost every
+// real hit takes the shortcut; grazing hits, whose u and v are themselves inaccurate, fall through to the definition.
 CRT_HD void d3_axis(float o, float d, float a, float e1, float e2, float& t_near, float& t_far)
 {
     const float b = x::add(a, e1), c = x::add(a, e2);
     float lo = fminf(a, fminf(b, c)), hi = fmaxf(a, fmaxf(b, c));
-    // planes moved out by 2^-16 of the box's largest coordinate: half of what the tree's boxes are widened by
-    // (lbvh.cu:prim_box), so a ray that passes here also passes every box test on the way down
-    const float pad = x::add(x::mul(fmaxf(fabsf(lo), fabsf(hi)), 1.52587890625e-5f), 1e-30f);
+    const float pad = x::add(x::mul(fmaxf(fabsf(lo), fabsf(hi)), 1.52587890625e-5f), 1e-30f);   // 2^-16
     lo = x::sub(lo, pad);
     hi = x::add(hi, pad);
     const float inv = fabsf(d) > 1e-18f ? x::div(1.0f, d) : copysignf(1e18f, d);
@@ -90,17 +100,33 @@ CRT_HD void d3_axis(float o, float d, float a, float e1, float e2, float& t_near
 }
 #define CRT_D3_EPS 3.0517578125e-5f   // 2^-15
 
-// shapes/triangle.h:57-100 plus deviation D1 (accept only t_min < t < t_max;
-// SURVEY §9 Q2) and deviation D3: the hit distance must lie where the ray is inside the triangle's own bounding box
-// (within 2^-15 relative). The reference's Moeller-Trumbore arithmetic loses all accuracy on sliver triangles and
-// then reports "hits" tens of units away from the triangle (measured on C4's pole slivers, profiles/r02_g_c4_walk.txt):
-// the list scan takes them, any bounding-volume hierarchy - the reference's own BVHNode included, whose leaves test
-// their box first (hitable/bvh.h:165) - cannot reach them, and which of two traversals stumbles on one would decide
-// the pixel. D3 makes the answer a function of the ray and the triangle alone. v0/e1/e2/n as stored in the record. A candidate with t equal
-// to the current best is still returned (t <= t_best); the caller breaks the
-// tie by primitive id.
-CRT_HD bool triangle_test(v3 o, v3 d, v3 v0, v3 e1, v3 e2, v3 n, float t_min, float t_best,
-                          float& t_out, float& u_out, float& v_out)
+CRT_HD bool d3_interval(v3 o, v3 d, v3 v0, v3 e1, v3 e2, float t)
+{
+    float t_near = -INFINITY, t_far = INFINITY;
+    d3_axis(o.x, d.x, v0.x, e1.x, e2.x, t_near, t_far);
+    d3_axis(o.y, d.y, v0.y, e1.y, e2.y, t_near, t_far);
+    d3_axis(o.z, d.z, v0.z, e1.z, e2.z, t_near, t_far);
+    return t >= x::sub(t_near, x::mul(fabsf(t_near), CRT_D3_EPS)) && t <= x::add(t_far, x::mul(fabsf(t_far), CRT_D3_EPS));
+}
+
+CRT_HD bool d3_agrees_axis(float o, float d, float a, float e1, float e2, float t, float t_eps, float u, float v)
+{
+    const float pp = fmaf(v, e2, fmaf(u, e1, a));
+    const float p = fmaf(t, d, o);
+    return fabsf(p - pp) <= fmaf(fabsf(pp), 7.62939453125e-6f, t_eps * fabsf(d));   // 2^-17 of the coordinate + 2^-16 of t |d|
+}
+CRT_HD bool d3_agrees(v3 o, v3 d, v3 v0, v3 e1, v3 e2, float t, float u, float v)
+{
+    const float t_eps = t * 1.52587890625e-5f;
+    return d3_agrees_axis(o.x, d.x, v0.x, e1.x, e2.x, t, t_eps, u, v) && d3_agrees_axis(o.y, d.y, v0.y, e1.y, e2.y, t, t_eps, u, v) &&
+           d3_agrees_axis(o.z, d.z, v0.z, e1.z, e2.z, t, t_eps, u, v);
+}
+
+// shapes/triangle.h:57-100 plus deviation D1 (accept only t_min < t < t_max) and deviation D3 (above).
+// v0/e1/e2/n as stored in the record. A candidate with t equal to the current best is still returned (t <= t_best);
+// the caller breaks the tie by primitive id.
+CRT_HD bool triangle_candidate(v3 o, v3 d, v3 v0, v3 e1, v3 e2, v3 n, float t_min, float t_best,
+                               float& t_out, float& u_out, float& v_out)
 {
     const float EPSILON = 0.000001f;                       // triangle.h:9,22
     if (vdot(d, n) < 0.0f) return false;                   // triangle.h:61
@@ -116,13 +142,15 @@ CRT_HD bool triangle_test(v3 o, v3 d, v3 v0, v3 e1, v3 e2, v3 n, float t_min, fl
     if (v < 0.0f || x::add(u, v) > 1.0f) return false;     // triangle.h:89
     float t = x::mul(f, vdot(e2, q));                      // triangle.h:92
     if (!(t > t_min && t <= t_best)) return false;         // D1
-    float t_near = -INFINITY, t_far = INFINITY;            // D3
-    d3_axis(o.x, d.x, v0.x, e1.x, e2.x, t_near, t_far);
-    d3_axis(o.y, d.y, v0.y, e1.y, e2.y, t_near, t_far);
-    d3_axis(o.z, d.z, v0.z, e1.z, e2.z, t_near, t_far);
-    if (!(t >= x::sub(t_near, x::mul(fabsf(t_near), CRT_D3_EPS)) && t <= x::add(t_far, x::mul(fabsf(t_far), CRT_D3_EPS)))) return false;
     t_out = t; u_out = u; v_out = v;
     return true;
+}
+
+CRT_HD bool triangle_test(v3 o, v3 d, v3 v0, v3 e1, v3 e2, v3 n, float t_min, float t_best,
+                          float& t_out, float& u_out, float& v_out)
+{
+    if (!triangle_candidate(o, d, v0, e1, e2, n, t_min, t_best, t_out, u_out, v_out)) return false;
+    return d3_agrees(o, d, v0, e1, e2, t_out, u_out, v_out) || d3_interval(o, d, v0, e1, e2, t_out);   // D3
 }
 
 // shapes/sphere.h:27-55; oc = origin in the sphere's frame (origin - centre,

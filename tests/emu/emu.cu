@@ -142,6 +142,23 @@ void emu_trace_chained(const float* frames13, uint32_t n_frames, const uint32_t*
     delete[] fr;
 }
 
+// Deviation D3's two forms on n (ray, triangle) pairs: rays n x 6 (origin, unit direction), tris n x 12. out[i]: bit 0
+// = the triangle test up to D1 gives a candidate, bit 1 = the shortcut d3_agrees accepts it, bit 2 = the definition
+// d3_interval accepts it. The shortcut must imply the definition.
+void emu_d3(const float* rays, const float* tris, size_t n, uint8_t* out)
+{
+    for (size_t i = 0; i < n; i++) {
+        const float* q = rays + 6 * i;
+        const float* t = tris + 12 * i;
+        const v3 o = V(q[0], q[1], q[2]), d = V(q[3], q[4], q[5]);
+        const v3 v0 = V(t[0], t[1], t[2]), e1 = vsub(V(t[3], t[4], t[5]), v0), e2 = vsub(V(t[6], t[7], t[8]), v0);
+        float tt, u, v;
+        out[i] = 0;
+        if (!triangle_candidate(o, d, v0, e1, e2, V(t[9], t[10], t[11]), 0.001f, 3.4e38f, tt, u, v)) continue;
+        out[i] = 1 | (d3_agrees(o, d, v0, e1, e2, tt, u, v) ? 2 : 0) | (d3_interval(o, d, v0, e1, e2, tt) ? 4 : 0);
+    }
+}
+
 void emu_sky(const float* d, float* out)
 {
     v3 s = background_sky(V(d[0], d[1], d[2]));

@@ -231,6 +231,49 @@ def test_cornell_box_oracles_agree():
         assert np.array_equal(imgs[0], imgs[1])
 
 
+def test_d3_shortcut_implies_the_definition():
+    """crt_device.cuh: d3_agrees (the kernels' shortcut: ray point vs barycentric point, half tolerances) must never
+    accept what d3_interval (deviation D3's definition, the one the oracles evaluate) rejects. Millions of ray /
+    triangle pairs: well-shaped triangles, slivers, far origins, grazing incidence, large and tiny coordinates."""
+    emu = C.CDLL(EMU)
+    u8p = np.ctypeslib.ndpointer(np.uint8, flags="C_CONTIGUOUS")
+    emu.emu_d3.restype = None
+    emu.emu_d3.argtypes = [f32p, f32p, C.c_size_t, u8p]
+    rng = np.random.default_rng(7)
+    total = np.zeros(8, np.int64)
+    for scale, aspect, dist, graze in ((1, 1, 30, 0), (100, 1, 3000, 0), (1, 1e-3, 30, 0), (100, 1e-4, 2600, 0), (1000, 1, 5, 0),
+                                       (1e-3, 1, 1, 0), (1, 1, 30, 1), (100, 1e-2, 2600, 1), (1, 1e-5, 300, 1)):
+        n = 400000
+        c = rng.normal(size=(n, 3)) * scale * 3
+        a = rng.normal(size=(n, 3)) * scale
+        b = rng.normal(size=(n, 3)) * scale
+        b = a * (1 - aspect) + b * aspect if aspect < 1 else b           # slivers: the second edge nearly along the first
+        v0, v1, v2 = c, c + a, c + b
+        nrm = np.cross(a, b)
+        nrm /= np.maximum(np.linalg.norm(nrm, axis=1, keepdims=True), 1e-300)
+        w = rng.random((n, 2))
+        w = np.where(w.sum(1, keepdims=True) > 1, 1 - w, w)
+        target = v0 + a * w[:, :1] + b * w[:, 1:]
+        d = rng.normal(size=(n, 3))
+        if graze:                                                        # directions almost in the triangle's plane
+            d -= nrm * (d * nrm).sum(1, keepdims=True) * (1 - 10.0 ** rng.uniform(-5, -1, size=(n, 1)))
+        d /= np.linalg.norm(d, axis=1, keepdims=True)
+        sign = np.where((d * nrm).sum(1, keepdims=True) >= 0, 1.0, -1.0)   # stored normal along the ray (SURVEY 9 Q1)
+        o = target - d * dist * rng.uniform(0.2, 1.0, size=(n, 1))
+        d32 = d.astype(np.float32)
+        d32 /= np.linalg.norm(d32, axis=1, keepdims=True)
+        rays = np.ascontiguousarray(np.concatenate([o, d32], axis=1), np.float32)
+        tris = np.ascontiguousarray(np.concatenate([v0, v1, v2, nrm * sign], axis=1), np.float32)
+        out = np.zeros(n, np.uint8)
+        emu.emu_d3(rays, tris, n, out)
+        total += np.bincount(out, minlength=8)
+    cand = total[1] + total[3] + total[5] + total[7]
+    assert cand > 1_000_000
+    assert total[3] == 0, "%d candidates pass the shortcut but fail the definition" % total[3]
+    assert total[7] > 0.5 * cand                                          # the shortcut is the common case
+    assert total[1] > 0                                                   # and the definition does reject something here
+
+
 def test_scene_generators():
     c3 = scenes.c3_mesh(n_theta=100, n_phi=50)
     assert len(c3["tri"]) == 2 * 100 * 49 + 2 and np.isfinite(c3["tri"]).all()
