@@ -11,7 +11,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libcrt_b200.so")
+LIB_PATH = os.environ.get("CRT_LIB") or os.path.join(_HERE, "libcrt_b200.so")   # CRT_LIB: development aid (A/B builds)
 
 MISS = 0xFFFFFFFF
 SHADE_PATH, SHADE_LAMBERT, SHADE_NORMAL = 0, 1, 2

@@ -72,7 +72,7 @@ struct Hit {
 CRT_HD v3 ray_dir_local(v3 d) { return vunit(vunit(d)); }
 
 // Deviation D3: a triangle hit counts only if its distance t lies where the ray is inside the triangle's own bounding
-// box - the box of v0, v0 + e1, v0 + e2 with its planes moved out by 2^-16 of its largest coordinate - within 2^-15
+// box - the box of v0, v0 + e1, v0 + e2 with its planes moved out by 2^-22 of its largest coordinate - within 2^-15
 // relative. The reference's Moeller-Trumbore arithmetic loses all accuracy on sliver triangles and then reports, with
 // u and v in range, a t that is tens of units off (measured on C4's pole slivers, profiles/r02_g_c4_walk.txt): the
 // list scan takes such hits, any bounding-volume hierarchy - the reference's own BVHNode included, whose leaves test
@@ -90,7 +90,7 @@ CRT_HD void d3_axis(float o, float d, float a, float e1, float e2, float& t_near
 {
     const float b = x::add(a, e1), c = x::add(a, e2);
     float lo = fminf(a, fminf(b, c)), hi = fmaxf(a, fmaxf(b, c));
-    const float pad = x::add(x::mul(fmaxf(fabsf(lo), fabsf(hi)), 1.52587890625e-5f), 1e-30f);   // 2^-16
+    const float pad = x::add(x::mul(fmaxf(fabsf(lo), fabsf(hi)), 2.384185791015625e-7f), 1e-30f);   // 2^-22
     lo = x::sub(lo, pad);
     hi = x::add(hi, pad);
     const float inv = fabsf(d) > 1e-18f ? x::div(1.0f, d) : copysignf(1e18f, d);
@@ -99,6 +99,9 @@ CRT_HD void d3_axis(float o, float d, float a, float e1, float e2, float& t_near
     t_far = fminf(t_far, fmaxf(t0, t1));
 }
 #define CRT_D3_EPS 3.0517578125e-5f   // 2^-15
+#ifndef CRT_D3
+#define CRT_D3 1                      // 0: development switch for A/B timing only (parity with the oracles is lost)
+#endif
 
 CRT_HD bool d3_interval(v3 o, v3 d, v3 v0, v3 e1, v3 e2, float t)
 {
@@ -113,7 +116,7 @@ CRT_HD bool d3_agrees_axis(float o, float d, float a, float e1, float e2, float 
 {
     const float pp = fmaf(v, e2, fmaf(u, e1, a));
     const float p = fmaf(t, d, o);
-    return fabsf(p - pp) <= fmaf(fabsf(pp), 7.62939453125e-6f, t_eps * fabsf(d));   // 2^-17 of the coordinate + 2^-16 of t |d|
+    return fabsf(p - pp) <= fmaf(fabsf(pp), 1.1920928955078125e-7f, t_eps * fabsf(d));   // 2^-23 of the coordinate + 2^-16 of t |d|
 }
 CRT_HD bool d3_agrees(v3 o, v3 d, v3 v0, v3 e1, v3 e2, float t, float u, float v)
 {
@@ -150,7 +153,11 @@ CRT_HD bool triangle_test(v3 o, v3 d, v3 v0, v3 e1, v3 e2, v3 n, float t_min, fl
                           float& t_out, float& u_out, float& v_out)
 {
     if (!triangle_candidate(o, d, v0, e1, e2, n, t_min, t_best, t_out, u_out, v_out)) return false;
+#if CRT_D3
     return d3_agrees(o, d, v0, e1, e2, t_out, u_out, v_out) || d3_interval(o, d, v0, e1, e2, t_out);   // D3
+#else
+    return true;
+#endif
 }
 
 // shapes/sphere.h:27-55; oc = origin in the sphere's frame (origin - centre,

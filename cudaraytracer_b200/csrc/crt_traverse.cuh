@@ -75,8 +75,10 @@ namespace crt {
 // its entry distance exceeds the closest hit by this margin. Measured at C4's size (camera 2,700 units from the
 // scene, 5.3e8 camera rays): with 2^-21 and without D3 the packet and the per-ray traversal disagreed on 14 pixels
 // of the frame (profiles/r02_e_c4_invariance.txt).
+#ifndef CRT_T_SLACK
 #define CRT_T_SLACK 6.103515625e-5f             // 2^-14
 #define CRT_T_SLACK1 1.00006103515625f          // 1 + 2^-14
+#endif
 
 constexpr int TP_BLOCK = 128;    // threads per block of every traversal kernel
 #ifndef CRT_TRACE_MIN_BLOCKS

@@ -70,7 +70,7 @@ __device__ __forceinline__ void chain_point_to_world(const DFrame* __restrict__ 
 
 // Box of input primitive p: the reference's Triangle::bounding_box / Sphere::bounding_box / Rectangle::bounding_box
 // (shapes/triangle.h:102-115, shapes/sphere.h:58-62, shapes/rectangle.h:11-14) in WORLD space, widened per axis by
-// 2^-15 of its largest coordinate (see the end of this function).
+// 2^-21 of its largest coordinate (see the end of this function).
 // A primitive under a chain is tested in its own frame (crt_device.cuh:framed_test) on a ray that was rotated and
 // translated in fp32, so where its world-space image lies is only known up to the rounding of that map, which grows
 // with the distance of the ray origin: its box is padded by 2^-16 of the scene's largest coordinate per level
@@ -126,9 +126,14 @@ __device__ __forceinline__ Box prim_box(const PrimSrc& S, uint32_t p)
         if (!(scale < INFINITY)) b = Box{-INFINITY, -INFINITY, -INFINITY, INFINITY, INFINITY, INFINITY};   // NaN / inf geometry: never culled
         b.lx -= pad; b.ly -= pad; b.lz -= pad; b.hx += pad; b.hy += pad; b.hz += pad;
     }
-    // every axis widened by 2^-15 of its largest coordinate: twice what deviation D3 (crt_device.cuh:triangle_test)
+    // every axis widened by 2^-21 of its largest coordinate (a few ulps: enough for the roundings between a hit point
+    // and the planes, little enough that the boxes of a bounce ray's neighbouring triangles stay clear of its origin -
+    // 2^-15 cost 25 % more triangle tests per ray on C3, profiles/r02_ab_d3.txt): twice what deviation D3 (crt_device.cuh:triangle_test)
     // pads the triangle's own box by, so that a hit D3 accepts is always inside every box on the way down
-    const float k = 3.0517578125e-5f;   // 2^-15
+#ifndef CRT_BOX_PAD
+#define CRT_BOX_PAD 4.76837158203125e-7f   // 2^-21
+#endif
+    const float k = CRT_BOX_PAD;
     const float tiny = 1e-29f;
     const float mx = fmaxf(fabsf(b.lx), fabsf(b.hx)) * k + tiny, my = fmaxf(fabsf(b.ly), fabsf(b.hy)) * k + tiny,
                 mz = fmaxf(fabsf(b.lz), fabsf(b.hz)) * k + tiny;

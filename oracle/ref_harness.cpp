@@ -67,7 +67,7 @@ inline void d3_axis(float o, float d, float a, float e1, float e2, float& t_near
 {
     float b = a + e1, c = a + e2;
     float lo = fminf(a, fminf(b, c)), hi = fmaxf(a, fmaxf(b, c));
-    float pad = fmaxf(fabsf(lo), fabsf(hi)) * 1.52587890625e-5f + 1e-30f;   /* 2^-16 of the largest coordinate */
+    float pad = fmaxf(fabsf(lo), fabsf(hi)) * 2.384185791015625e-7f + 1e-30f;   /* 2^-22 of the largest coordinate */
     lo = lo - pad;
     hi = hi + pad;
     float inv = fabsf(d) > 1e-18f ? 1.0f / d : copysignf(1e18f, d);

@@ -32,6 +32,16 @@ if a.wide_below >= 0:
     ctx.set_option(crt.OPT_WIDE_BELOW, a.wide_below)
 ctx.set_scene(sc)
 ctx.build()
+ctx.set_option(crt.OPT_COUNTERS, 1)
+ctx.reset_counters()
+_acc = torch.zeros(ny, nx, 3, dtype=torch.float32, device="cuda:0")
+ctx.render_accum_device(cam, nx, ny, 0, spp, depth, crt.SHADE_PATH, 1, a.rank, a.world, _acc.data_ptr())
+ctx.sync()
+w = ctx.counters()
+ctx.set_option(crt.OPT_COUNTERS, 0)
+print("   nodes/ray %.4f tris/ray %.4f node fetches/ray %.4f tri fetches/ray %.4f" % (w["nodes_visited"] / w["rays"], w["tris_tested"] / w["rays"],
+      w["node_fetches"] / w["rays"], w["tri_fetches"] / w["rays"]), flush=True)
+del _acc
 dev = torch.device("cuda", 0)
 accum = torch.zeros(ny, nx, 3, dtype=torch.float32, device=dev)
 ext = torch.cuda.ExternalStream(ctx.stream(), device=dev)
