@@ -182,6 +182,9 @@ int crt_create(int device, crt_ctx** out)
         CRT_CUDA(cudaEventCreateWithFlags(&L.ev_join, cudaEventDisableTiming));
         for (auto& e : L.ev_trace) CRT_CUDA(cudaEventCreate(&e));
         CRT_CUDA(cudaMallocHost((void**)&L.h_counts, sizeof(uint32_t) * (CRT_MAX_DEPTH + 3)));
+        CRT_CUDA(cudaHostAlloc((void**)&L.tail_hint, sizeof(uint32_t), cudaHostAllocMapped));
+        *L.tail_hint = 0u;
+        CRT_CUDA(cudaHostGetDevicePointer((void**)&L.tail_hint_dev, L.tail_hint, 0));
     }
     CRT_CUDA(c->counters.reserve(sizeof(unsigned long long) * CNT_COUNT));
     CRT_CUDA(cudaMemsetAsync(c->counters.p, 0, sizeof(unsigned long long) * CNT_COUNT, c->stream));
@@ -221,6 +224,7 @@ void crt_destroy(crt_ctx* c)
         if (L.ev_join) cudaEventDestroy(L.ev_join);
         for (auto& e : L.ev_trace) if (e) cudaEventDestroy(e);
         if (L.h_counts) cudaFreeHost(L.h_counts);
+        if (L.tail_hint) cudaFreeHost(L.tail_hint);
         if (l > 0 && L.stream) cudaStreamDestroy(L.stream);
     }
     if (c->stream) cudaStreamDestroy(c->stream);
@@ -263,6 +267,9 @@ int crt_set_option(crt_ctx* c, int option, int64_t value)
         return CRT_OK;
     case CRT_OPT_TIMING:
         c->timing = value != 0;
+        return CRT_OK;
+    case CRT_OPT_TAIL_HINT:
+        c->tail_hint = value != 0;
         return CRT_OK;
     case CRT_OPT_SLICE_MIN:
         if (value < 1) { set_error("CRT_OPT_SLICE_MIN must be >= 1"); return CRT_ERR_INVALID; }

@@ -63,6 +63,11 @@ struct crt_lane {
     cudaEvent_t ev_join = nullptr;         // end of the lane's share of a render call, joined into the context's stream
     cudaEvent_t ev_trace[2 * (crt::CRT_MAX_DEPTH + 1)] = {};
     uint32_t* h_counts = nullptr;          // pinned copy of qcount
+    // CRT_OPT_TAIL_HINT: a mapped pinned word the slice's k_accumulate writes, (key << 8) | bounce: the first bounce of
+    // the last frame with this key whose queue was short enough for k_tail (0: none). Read by the host, unsynchronised:
+    // any value it can hold gives the same image
+    uint32_t* tail_hint = nullptr;
+    uint32_t* tail_hint_dev = nullptr;     // the same word as the device addresses it
 };
 
 struct crt_ctx {
@@ -123,6 +128,7 @@ struct crt_ctx {
     int leaf_thresh = 8;                   // parked lanes that trigger the primitive-test phase
     int refill = 12;                       // idle lanes that trigger a refill in the persistent traversal
     int packet_primary = 1;                // camera rays through the packet kernel
+    bool tail_hint = true;                 // CRT_OPT_TAIL_HINT
     int64_t wide_below = 32768;            // CRT_OPT_WIDE_BELOW: bounces with fewer rays run one warp per ray
     int64_t batch_paths = 1ll << 25;
     int64_t slice_min_samples = 2000000;   // CRT_OPT_SLICE_MIN: a slice (lane) of a frame holds at least this many camera samples

@@ -495,12 +495,24 @@ k_tail(RenderParams P, AccelView A, const DMat* __restrict__ mats, const float4*
 // never reads the queue lengths, so a render call does not have to wait for its launches).
 __global__ void __launch_bounds__(256)
 k_accumulate(RenderParams P, const float4* __restrict__ rad, float* __restrict__ accum, const uint32_t* __restrict__ qcount,
-             int bounces, unsigned long long* __restrict__ counters)
+             int bounces, unsigned long long* __restrict__ counters, uint32_t wide_below, int forced_at, uint32_t hint_key,
+             uint32_t* __restrict__ hint)
 {
     if (blockIdx.x == 0 && (int)threadIdx.x < bounces) {
         const uint32_t q = qcount[threadIdx.x];
         if (q) atomicAdd(counters + CNT_RENDER_RAYS, (unsigned long long)q);
         if (threadIdx.x == 0 && q) atomicAdd(counters + CNT_RENDER_PATHS, (unsigned long long)q);
+    }
+    if (hint && blockIdx.x == 0 && threadIdx.x == 0) {
+        // CRT_OPT_TAIL_HINT, for the next frame of this shape: the first bounce whose queue k_tail takes. This frame's
+        // queue lengths are known up to the bounce where its own k_tail took over (forced_at, when the host guessed it)
+        const int last = forced_at ? forced_at : bounces - 1;
+        uint32_t h = 0u;
+        for (int b = 1; b <= last && !h; b++)
+            if (qcount[b] < wide_below) h = (uint32_t)b;
+        // guessed too early: up to twice the threshold the guess stands, beyond that the next frame queues every bounce
+        if (!h && forced_at && qcount[forced_at] < 2u * wide_below) h = (uint32_t)forced_at;
+        *reinterpret_cast<volatile uint32_t*>(hint) = (hint_key << 8) | h;
     }
     const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
     if (slot >= P.n_slots) return;
@@ -586,13 +598,20 @@ static void size_grids(crt_ctx* c)
 
 template <bool COUNT, bool HAS_SPH>
 static void launch_bounce(crt_ctx* c, crt_lane& L, int b, const RenderParams& P, const AccelView& A,
-                          const float4* q_in, const uint32_t* n_in, uint32_t* work_ctr, float4* q_out, uint32_t* n_out)
+                          const float4* q_in, const uint32_t* n_in, uint32_t* work_ctr, float4* q_out, uint32_t* n_out, int tail_at)
 {
     unsigned long long* counters = c->counters.as<unsigned long long>();
     const bool packet = b == 0 && c->packet_primary;
+    if (tail_at && b == tail_at) {   // CRT_OPT_TAIL_HINT: this queue goes to k_tail whatever its length
+        k_tail<COUNT, HAS_SPH><<<c->grid_tail, TP_BLOCK, 0, L.stream>>>(P, A, c->mats.as<DMat>(), q_in, n_in, work_ctr + 32,
+                                                                        L.rad.as<float4>(), counters, 0xffffffffu);
+        c->host_counters.launches++;
+        return;
+    }
     // the queue length is only known on the device: from the second bounce on, a queue of fewer than tail_below
-    // paths is left alone by the wavefront kernels (they return at once) and finished by k_tail
-    const uint32_t tail_below = b == 0 ? 0u : (uint32_t)c->wide_below;
+    // paths is left alone by the wavefront kernels (they return at once) and finished by k_tail. With a guess of the
+    // bounce where that happens (tail_at) the bounces before it are plain wavefront launches
+    const uint32_t tail_below = (b == 0 || tail_at) ? 0u : (uint32_t)c->wide_below;
     if (c->timing) cudaEventRecord(L.ev_trace[2 * b], L.stream);
     if (packet)   // camera rays: a warp holds the samples of one or two pixels
         k_trace_packet<COUNT, HAS_SPH><<<c->grid_packet, TP_BLOCK, 0, L.stream>>>(A, q_in, P.cap, n_in, work_ctr, L.hitbuf.as<float4>(),
@@ -723,28 +742,40 @@ int render_accum(crt_ctx* c, const crt_camera* cam, int nx, int ny, int s0, int 
                 const uint32_t total = PL.n_slots * (uint32_t)PL.s_count;
                 const unsigned int rg = (unsigned int)min((size_t)(total + RB - 1) / RB, (size_t)c->sm_count * 32);
                 k_raygen<<<rg, RB, 0, L.stream>>>(PL, L.queue[0].as<float4>(), L.qcount.as<uint32_t>());
-                c->host_counters.launches += 2 + 2 * (uint64_t)bounces;   // raygen, (trace, shade) per bounce, accumulate
+                // CRT_OPT_TAIL_HINT: where the last frame of this shape handed over to k_tail (crt_lane::tail_hint)
+                const uint32_t hint_key = ((uint32_t)nx * 0x9e3779b1u ^ (uint32_t)ny * 0x85ebca6bu ^ (uint32_t)PL.s_count * 0xc2b2ae35u ^
+                                           (uint32_t)max_depth * 0x27d4eb2fu ^ (uint32_t)PL.world * 0x165667b1u ^ (uint32_t)PL.rank * 0xd3a2646cu ^
+                                           (uint32_t)c->n_prims * 0xfd7046c5u ^ (uint32_t)c->wide_below * 0xb55a4f09u) & 0xffffffu;
+                int tail_at = 0;
+                const bool hinting = c->tail_hint && !c->timing && c->wide_below > 0 && bounces > 2;
+                if (hinting) {
+                    const uint32_t hv = *reinterpret_cast<volatile uint32_t*>(L.tail_hint);
+                    if ((hv >> 8) == hint_key && (int)(hv & 0xffu) < bounces) tail_at = (int)(hv & 0xffu);
+                }
+                const int n_bounces = tail_at ? tail_at + 1 : bounces;
+                c->host_counters.launches += 2 + 2 * (uint64_t)(tail_at ? tail_at : bounces);   // raygen, (trace, shade) per bounce, accumulate
                 if (c->timing) CRT_CUDA(cudaEventRecord(L.ev_begin, L.stream));
                 // ray generation does not read the scene: only the closest-hit launches wait for an upload and refit
                 // queued on another stream (crt_render_frame)
                 if (scene_ready && sb == s0) CRT_CUDA(cudaStreamWaitEvent(L.stream, scene_ready, 0));
-                for (int b = 0; b < bounces; b++) {
+                for (int b = 0; b < n_bounces; b++) {
                     const float4* qi = L.queue[b & 1].as<float4>();
                     float4* qo = L.queue[(b + 1) & 1].as<float4>();
                     const uint32_t* ni = L.qcount.as<uint32_t>() + b;
                     uint32_t* no = L.qcount.as<uint32_t>() + b + 1;
                     uint32_t* wc = L.work_ctr.as<uint32_t>() + b;
                     if (c->count_work) {
-                        if (sph) launch_bounce<true, true>(c, L, b, PL, A, qi, ni, wc, qo, no);
-                        else launch_bounce<true, false>(c, L, b, PL, A, qi, ni, wc, qo, no);
+                        if (sph) launch_bounce<true, true>(c, L, b, PL, A, qi, ni, wc, qo, no, tail_at);
+                        else launch_bounce<true, false>(c, L, b, PL, A, qi, ni, wc, qo, no, tail_at);
                     } else {
-                        if (sph) launch_bounce<false, true>(c, L, b, PL, A, qi, ni, wc, qo, no);
-                        else launch_bounce<false, false>(c, L, b, PL, A, qi, ni, wc, qo, no);
+                        if (sph) launch_bounce<false, true>(c, L, b, PL, A, qi, ni, wc, qo, no, tail_at);
+                        else launch_bounce<false, false>(c, L, b, PL, A, qi, ni, wc, qo, no, tail_at);
                     }
                 }
                 if (c->timing) CRT_CUDA(cudaEventRecord(L.ev_end, L.stream));
                 k_accumulate<<<(PL.n_slots + 255) / 256, 256, 0, L.stream>>>(PL, L.rad.as<float4>(), d_accum, L.qcount.as<uint32_t>(), bounces,
-                                                                            c->counters.as<unsigned long long>());
+                                                                            c->counters.as<unsigned long long>(), (uint32_t)c->wide_below, tail_at,
+                                                                            hint_key, hinting ? L.tail_hint_dev : nullptr);
                 if (finish && P.band && sb + P.s_count >= s1) {
                     // the slice's pixels are final: resolve its rows and start their copy to the caller's buffer while
                     // the other slices still render (rows of tile rows PL.rank, PL.rank + sub_world, ...)

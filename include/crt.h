@@ -121,6 +121,10 @@ typedef enum {
                              * crt_counters.trace_queue_ms / bounce_ms are maintained (the roofline's denominator); 0 (default): render
                              * calls only queue work */
     CRT_OPT_SLICE_MIN = 11, /* tuning: fewest camera samples a slice of a frame may hold (default 2,000,000; see CRT_OPT_LANES) */
+    CRT_OPT_TAIL_HINT = 12, /* 1 (default): a render call remembers, per slice, the bounce at which the previous frame of the same
+                             * shape handed its queue to the one-warp-per-path launch (CRT_OPT_WIDE_BELOW) and queues no launch
+                             * beyond it (a frame of depth 8 otherwise queues ~17 launches per slice that find an empty queue);
+                             * a wrong guess costs time, never a different image; 0: always queue every bounce */
     CRT_OPT_REFILL = 4      /* tuning: idle lanes per warp that trigger a refill from the ray queue, 1..32 (default 12) */
 } crt_option;
 
