@@ -1,6 +1,20 @@
 #!/bin/bash
-# why is one rank of 8 ~25 % slower with the same ray count? ranks 5 (slow) and 1 (fast), one slice: longest packet / ray per bounce
+# fewer resident warps for the camera-ray launch: every warp (and the longest packet) gets a larger share of its scheduler
 mkdir -p gpurun_out
-for r in 5 1; do
-  CRT_TRACE_TIMING=1 timeout 120 python scripts/frame_part.py --world 8 --rank $r --lanes 1 --steps 1 --timing 2>&1 | grep "nodes/ray\|bounce [012]" | head -8
-done
+for bps in 8 6 4 3; do
+  export CRT_PACKET_BPS=$bps
+  for cfg in "8 2" "8 6" "1 0"; do
+    set -- $cfg
+    echo -n "packet blocks/SM $bps: "
+    timeout 120 python scripts/frame_part.py --world $1 --rank $2 --steps 20 --lanes 2 | tail -1
+  done
+done 2>&1 | tee gpurun_out/m_ab_packet_bps.txt
+unset CRT_PACKET_BPS
+for bps in 6 4; do
+  export CRT_TRACE_BPS=$bps
+  for cfg in "8 2" "8 6" "1 0"; do
+    set -- $cfg
+    echo -n "queue-kernel blocks/SM $bps: "
+    timeout 120 python scripts/frame_part.py --world $1 --rank $2 --steps 20 --lanes 2 | tail -1
+  done
+done 2>&1 | tee -a gpurun_out/m_ab_packet_bps.txt
