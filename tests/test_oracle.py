@@ -218,3 +218,32 @@ def test_reference_bvh_agrees_with_its_list_scan():
     assert same.mean() > 0.995
     hit = same & (i0 != crt.MISS)
     assert np.allclose(t0[hit], t1[hit], rtol=1e-5)
+
+
+@pytest.mark.skipif(not oracle.available("ref"), reason="oracle/_ref not built")
+def test_reference_bvh_misses_flat_boxes():
+    """Why the parity oracle is the reference's LIST SCAN and not its BVHNode: AABB::hit (core/aabb.h) rejects a box
+    whose slab interval is empty, and an axis-aligned quad has a box of zero thickness - rays that the list scan
+    reports on C3's ground quad are reported as misses by the reference's own BVH (bench.py's cpu_baseline therefore
+    times the BVH but compares images against the list scan)."""
+    ref = oracle.load("ref")
+    g0, g1, g2, gn = scenes.ground_quad(-1.0, 50.0)
+    tilted = np.asarray([[-1, 0, -1, 1, 0.5, -1, 0, 0.2, 1]], np.float32)       # a triangle with a box of real thickness
+    tn = ref.triangle_normal(tilted[0])
+    quad = np.concatenate([g0, g1, g2, gn], axis=1).astype(np.float32)
+    tri = np.concatenate([quad, np.concatenate([tilted, tn[None, :]], axis=1)]).astype(np.float32)
+    sc = dict(tri=tri, tri_mat=np.zeros(len(tri), np.uint32), sph=np.zeros((0, 4), np.float32), sph_mat=np.zeros(0, np.uint32),
+              mats=[(scenes.LAMBERTIAN, (0.5, 0.5, 0.5), 0.0)])
+    s = oracle_scene(ref, sc)
+    s.bvh_build(seed=1)
+    rng = np.random.default_rng(4)
+    o = np.concatenate([rng.uniform(-20, 20, (400, 1)), np.full((400, 1), 5.0), rng.uniform(-20, 20, (400, 1))], axis=1)
+    d = np.concatenate([rng.uniform(-0.3, 0.3, (400, 1)), np.full((400, 1), -1.0), rng.uniform(-0.3, 0.3, (400, 1))], axis=1)
+    rays = np.concatenate([o, d], axis=1).astype(np.float32)
+    t0, i0 = s.trace(rays)
+    t1, i1 = s.trace(rays, use_bvh=True)
+    on_quad = (i0 == 0) | (i0 == 1)
+    assert on_quad.sum() > 300, "the list scan finds the ground"
+    assert (i1[on_quad] == crt.MISS).all(), "the reference's BVH never reports a primitive whose box is flat"
+    on_tilted = i0 == 2
+    assert on_tilted.any() and np.array_equal(i1[on_tilted], i0[on_tilted])
