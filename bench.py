@@ -696,7 +696,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-configs", action="store_true", help="skip the C1 / C2 / C5 sub-records of the N = 1 line")
-    ap.add_argument("--lanes", type=int, default=4, help="CRT_OPT_LANES of the timed region (1 for profiling: one slice, launches in bounce order)")
+    ap.add_argument("--lanes", type=int, default=3, help="CRT_OPT_LANES of the timed region (1 for profiling: one slice, launches in bounce order)")
     ap.add_argument("--slice-min", type=int, default=0, help="CRT_OPT_SLICE_MIN (tuning)")
     ap.add_argument("--e2e-api", default="points", choices=["points", "frame", "calls"],
                     help="end-to-end loop: points = the pose as the mesh's point array (crt_render_frame_pose, one overlapped "

@@ -80,7 +80,7 @@ struct crt_ctx {
     cudaEvent_t ev_up0 = nullptr, ev_up1 = nullptr, ev_frame = nullptr;
     bool pose_pending = false;             // crt_scene_pose_async: upload + refit in flight on up_stream, ev_frame marks their end
     crt_lane lane[CRT_MAX_LANES];
-    int n_lanes = 4;                       // CRT_OPT_LANES: most slices of a frame in flight
+    int n_lanes = 3;                       // CRT_OPT_LANES: most slices of a frame in flight (3: profiles/r02_o_ab_registers_lanes.txt)
 
     // scene as uploaded (caller's order)
     crt::DevBuf tri_in, tri_mat, tri_id;   // n_tri x 12 floats, u32, u32

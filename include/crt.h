@@ -109,7 +109,7 @@ typedef enum {
     CRT_OPT_LEAF_THRESH = 5,/* tuning: lanes parked on a leaf that trigger the primitive-test phase, 1..32 (default 8) */
     CRT_OPT_PACKET_PRIMARY = 6, /* 1 (default): camera rays are traced as one packet per warp; 0: like every other bounce;
                              * 2: packets without the shared interval box test (development aid) */
-    CRT_OPT_LANES = 7,      /* render: at most 1..4 slices of the frame in flight on their own streams (default 4; a slice is
+    CRT_OPT_LANES = 7,      /* render: at most 1..4 slices of the frame in flight on their own streams (default 3; a slice is
                              * never smaller than 2 M camera samples), so one slice's
                              * latency-bound last bounces overlap the other's wide launches; images do not depend on it */
     CRT_OPT_WIDE_BELOW = 9, /* render: once a bounce's queue holds fewer paths than this (default 32768) one launch carries them all to

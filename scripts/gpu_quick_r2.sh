@@ -1,20 +1,19 @@
 #!/bin/bash
-# fewer resident warps for the camera-ray launch: every warp (and the longest packet) gets a larger share of its scheduler
+# register budgets: queue kernel at 72 registers (min blocks 5), packet kernel at 72 (min blocks 6), against the default (64 / 62)
 mkdir -p gpurun_out
-for bps in 8 6 4 3; do
-  export CRT_PACKET_BPS=$bps
-  for cfg in "8 2" "8 6" "1 0"; do
-    set -- $cfg
-    echo -n "packet blocks/SM $bps: "
-    timeout 120 python scripts/frame_part.py --world $1 --rank $2 --steps 20 --lanes 2 | tail -1
+for lib in default t5 p6; do
+  if [ $lib = default ]; then unset CRT_LIB; else export CRT_LIB=$PWD/cudaraytracer_b200/libcrt_$lib.so; fi
+  for lanes in 2 4; do
+    echo -n "lib $lib: "
+    timeout 120 python scripts/frame_part.py --world 1 --steps 30 --lanes $lanes | tail -1
   done
-done 2>&1 | tee gpurun_out/m_ab_packet_bps.txt
-unset CRT_PACKET_BPS
-for bps in 6 4; do
-  export CRT_TRACE_BPS=$bps
-  for cfg in "8 2" "8 6" "1 0"; do
-    set -- $cfg
-    echo -n "queue-kernel blocks/SM $bps: "
-    timeout 120 python scripts/frame_part.py --world $1 --rank $2 --steps 20 --lanes 2 | tail -1
-  done
-done 2>&1 | tee -a gpurun_out/m_ab_packet_bps.txt
+done 2>&1 | tee gpurun_out/o_ab_registers.txt
+unset CRT_LIB
+for lanes in 2 3 4; do
+  timeout 300 python bench.py --no-cpu-baseline --no-configs --lanes $lanes > gpurun_out/o_bench_lanes$lanes.json 2>/dev/null
+  python - <<PY
+import json
+d = json.load(open("gpurun_out/o_bench_lanes$lanes.json"))
+print("bench lanes $lanes: value ms", round(d["ms_per_step"], 3), "e2e ms", round(d["e2e"]["ms_per_step"], 3), "frac", round(d["roofline"]["frac"], 3), "traffic", d["roofline"]["traffic"])
+PY
+done 2>&1 | tee -a gpurun_out/o_ab_registers.txt
