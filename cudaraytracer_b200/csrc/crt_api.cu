@@ -217,7 +217,7 @@ void crt_destroy(crt_ctx* c)
     for (int l = 0; l < CRT_MAX_LANES; l++) {
         crt_lane& L = c->lane[l];
         if (L.stream) cudaStreamSynchronize(L.stream);
-        DevBuf* lb[] = {&L.queue[0], &L.queue[1], &L.qcount, &L.work_ctr, &L.hitbuf, &L.rad};
+        DevBuf* lb[] = {&L.queue[0], &L.queue[1], &L.qcount, &L.work_ctr, &L.hitbuf, &L.rad, &L.deferred};
         for (DevBuf* b : lb) b->release();
         if (L.ev_begin) cudaEventDestroy(L.ev_begin);
         if (L.ev_end) cudaEventDestroy(L.ev_end);
@@ -270,6 +270,14 @@ int crt_set_option(crt_ctx* c, int option, int64_t value)
         return CRT_OK;
     case CRT_OPT_TAIL_HINT:
         c->tail_hint = value != 0;
+        return CRT_OK;
+    case CRT_OPT_PACKET_DEFER_BELOW:
+        if (value < 0) { set_error("CRT_OPT_PACKET_DEFER_BELOW must be >= 0"); return CRT_ERR_INVALID; }
+        c->packet_defer_below = value;
+        return CRT_OK;
+    case CRT_OPT_PACKET_DEFER:
+        if (value < 0 || value > (1 << 30)) { set_error("CRT_OPT_PACKET_DEFER must be in [0, 2^30]"); return CRT_ERR_INVALID; }
+        c->packet_defer = (int)value;
         return CRT_OK;
     case CRT_OPT_SLICE_MIN:
         if (value < 1) { set_error("CRT_OPT_SLICE_MIN must be >= 1"); return CRT_ERR_INVALID; }

@@ -58,7 +58,7 @@ constexpr int CRT_MAX_DEPTH = 16;
 constexpr int CRT_MAX_LANES = 4;
 struct crt_lane {
     cudaStream_t stream = nullptr;         // lane 0 uses the context's stream
-    crt::DevBuf queue[2], qcount, work_ctr, hitbuf, rad;
+    crt::DevBuf queue[2], qcount, work_ctr, hitbuf, rad, deferred;
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr;   // bounces of the current job (CRT_OPT_TIMING)
     cudaEvent_t ev_join = nullptr;         // end of the lane's share of a render call, joined into the context's stream
     cudaEvent_t ev_trace[2 * (crt::CRT_MAX_DEPTH + 1)] = {};
@@ -129,6 +129,8 @@ struct crt_ctx {
     int refill = 12;                       // idle lanes that trigger a refill in the persistent traversal
     int packet_primary = 1;                // camera rays through the packet kernel
     bool tail_hint = true;                 // CRT_OPT_TAIL_HINT
+    int packet_defer = 192;                // CRT_OPT_PACKET_DEFER: visits after which a camera-ray packet is handed on; 0 = never
+    int64_t packet_defer_below = 4000000;  // CRT_OPT_PACKET_DEFER_BELOW: only in slices of at most this many camera samples
     int64_t wide_below = 32768;            // CRT_OPT_WIDE_BELOW: bounces with fewer rays run one warp per ray
     int64_t batch_paths = 1ll << 25;
     int64_t slice_min_samples = 2000000;   // CRT_OPT_SLICE_MIN: a slice (lane) of a frame holds at least this many camera samples

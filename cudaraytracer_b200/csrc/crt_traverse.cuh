@@ -461,10 +461,26 @@ __device__ __forceinline__ void traverse_persistent(const AccelView& A, const ui
 //     lane's ray enters it, children are ordered by the first entering lane.
 #define CRT_PACKET_STACK CRT_STACK_ENTRIES   // same bound as the per-ray stack
 
-template <bool COUNT, bool HAS_SPH, class Src, class Sink>
+// Long packets are handed on. A camera-ray launch ends with its longest packet: two pixels on the limb of the mesh
+// walk ~500 dependent nodes and leaves where the average packet walks ~35, at ~1.3 us per visit while eight warps
+// share a scheduler - 0.5 ms on its own, more than the rest of a rank's share of a frame split over 8 GPUs takes, and
+// neither starting it first nor prefetching for it helps (profiles/r02_l_ab_packet_sched.txt). A packet that has made
+// `after` visits therefore stops: its rays' queue indices go on a list and a launch queued right behind (render.cu
+// k_trace_deferred) traces each listed ray with a whole WARP (trace_wide_one: the stack 32 entries abreast, ~15 rounds
+// instead of hundreds of steps), all listed rays at once. Nothing of the abandoned walk is kept, so the hit is the
+// closest hit of the ray as any other kernel finds it.
+struct PacketDefer {
+    uint32_t* list;      // queue indices of the rays handed on
+    uint32_t* n;         // entries reserved (may run past cap: then the packet walks on instead)
+    uint32_t cap;
+    uint32_t after;      // 0: never
+};
+
+template <bool COUNT, bool HAS_SPH, bool DEFER = false, class Src, class Sink>
 __device__ __forceinline__ void traverse_packets(const AccelView& A, const uint32_t n, uint32_t* work_ctr,
                                                  const float t_min, const float t_max, const Src& src,
-                                                 const Sink& sink, TraceCounters& cnt, const bool interval = true)
+                                                 const Sink& sink, TraceCounters& cnt, const bool interval = true,
+                                                 const PacketDefer defer = PacketDefer{nullptr, nullptr, 0u, 0u})
 {
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t kid = lane & 3u;
@@ -512,10 +528,23 @@ __device__ __forceinline__ void traverse_packets(const AccelView& A, const uint3
             float t_far = t_max;                 // warp-uniform: the largest closest-hit distance of the packet
             Hit best;
             best.t = t_max; best.k = 0xFFFFFFFFu; best.id = CRT_MISS_ID; best.u = best.v = 0.f;
+            bool handed_on = false;              // warp-uniform
             if (A.n_prims != 0u) {
                 int node = A.root;               // warp-uniform
                 uint32_t sp = 0;                 // warp-uniform
+                uint32_t visits = 0;             // warp-uniform
                 for (;;) {
+                    if (DEFER && ++visits > defer.after) {
+                        uint32_t base = 0;
+                        if (lane == 0) base = atomicAdd(defer.n, 32u);
+                        base = __shfl_sync(FULL, base, 0);
+                        if (base + 32u <= defer.cap) {
+                            defer.list[base + lane] = live ? ray_i : 0xFFFFFFFFu;
+                            handed_on = true;
+                            break;
+                        }
+                        visits = 0;              // the list is full: walk on (and ask again after another `after` visits)
+                    }
                     if (node >= 0) {
                         const float4* np = A.nodes + 8 * (size_t)(uint32_t)node;
                         const int4 refs = __ldg(reinterpret_cast<const int4*>(np + 5));
@@ -663,7 +692,7 @@ __device__ __forceinline__ void traverse_packets(const AccelView& A, const uint3
                     if (!got) break;
                 }
             }
-            if (live) sink.store(ray_i, best);
+            if (live && !handed_on) sink.store(ray_i, best);
             __syncwarp();
         }
     }

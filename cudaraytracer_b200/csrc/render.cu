@@ -250,15 +250,16 @@ k_trace_queue(AccelView A, const float4* __restrict__ q, uint32_t cap, const uin
 }
 
 // ---- closest hit for camera rays: one packet per warp (crt_traverse.cuh traverse_packets) ----
-template <bool COUNT, bool HAS_SPH>
+template <bool COUNT, bool HAS_SPH, bool DEFER>
 __global__ void __launch_bounds__(TP_BLOCK, CRT_PACKET_MIN_BLOCKS)
 k_trace_packet(AccelView A, const float4* __restrict__ q, uint32_t cap, const uint32_t* __restrict__ n_ptr,
-               uint32_t* __restrict__ work_ctr, float4* __restrict__ hits, unsigned long long* __restrict__ counters, int interval)
+               uint32_t* __restrict__ work_ctr, float4* __restrict__ hits, unsigned long long* __restrict__ counters, int interval,
+               PacketDefer defer)
 {
     TraceCounters cnt = {0u, 0u, 0u, 0u, 0u, 0u, 0u};
     QueueSrc src = {q, cap};
     QueueSink sink = {hits};
-    traverse_packets<COUNT, HAS_SPH>(A, *n_ptr, work_ctr, 0.001f, FLT_MAX, src, sink, cnt, interval != 0);   // render.h:53
+    traverse_packets<COUNT, HAS_SPH, DEFER>(A, *n_ptr, work_ctr, 0.001f, FLT_MAX, src, sink, cnt, interval != 0, defer);   // render.h:53
     if (COUNT) {
         const uint32_t nodes = __reduce_add_sync(0xffffffffu, cnt.nodes);
         const uint32_t tris = __reduce_add_sync(0xffffffffu, cnt.tris);
@@ -270,6 +271,48 @@ k_trace_packet(AccelView A, const float4* __restrict__ q, uint32_t cap, const ui
             atomicAdd(counters + CNT_NODE_F, (unsigned long long)cnt.node_f);
             atomicAdd(counters + CNT_TRI_F, (unsigned long long)cnt.tri_f);
             atomicAdd(counters + CNT_SPH_F, (unsigned long long)cnt.sph_f);
+        }
+    }
+}
+
+// ---- the rays of the packets that were handed on (crt_traverse.cuh PacketDefer): one warp per ray ----
+template <bool COUNT, bool HAS_SPH>
+__global__ void __launch_bounds__(TP_BLOCK)
+k_trace_deferred(AccelView A, const float4* __restrict__ q, uint32_t cap, const uint32_t* __restrict__ list,
+                 const uint32_t* __restrict__ n_ptr, uint32_t list_cap, uint32_t* __restrict__ cursor, float4* __restrict__ hits,
+                 unsigned long long* __restrict__ counters)
+{
+    __shared__ uint2 s_stack[(TP_BLOCK / 32) * CRT_WIDE_STACK];
+    const uint32_t n = min(*n_ptr, list_cap);
+    if (n == 0u) return;
+    const uint32_t lane = threadIdx.x & 31u;
+    uint2* stack = s_stack + (threadIdx.x >> 5) * CRT_WIDE_STACK;
+    TraceCounters cnt = {0u, 0u, 0u, 0u, 0u, 0u, 0u};
+    QueueSrc src = {q, cap};
+    QueueSink sink = {hits};
+    for (;;) {
+        uint32_t i = 0;
+        if (lane == 0) i = atomicAdd(cursor, 1u);
+        i = __shfl_sync(0xffffffffu, i, 0);
+        if (i >= n) break;
+        const uint32_t ray_i = list[i];
+        if (ray_i == 0xFFFFFFFFu) continue;             // a lane of the packet past the end of the queue
+        v3 o, dr;
+        src.load(ray_i, o, dr);
+        const Hit h = trace_wide_one<COUNT, HAS_SPH>(A, o, dr, 0.001f, FLT_MAX, stack, cnt);   // render.h:53
+        if (lane == 0) sink.store(ray_i, h);
+    }
+    if (COUNT) {
+        const uint32_t nodes = __reduce_add_sync(0xffffffffu, cnt.nodes);
+        const uint32_t tris = __reduce_add_sync(0xffffffffu, cnt.tris);
+        const uint32_t sph = __reduce_add_sync(0xffffffffu, cnt.spheres);
+        if (lane == 0) {
+            atomicAdd(counters + CNT_NODES, (unsigned long long)nodes);
+            atomicAdd(counters + CNT_TRIS, (unsigned long long)tris);
+            atomicAdd(counters + CNT_SPHERES, (unsigned long long)sph);
+            atomicAdd(counters + CNT_NODE_F, (unsigned long long)nodes);
+            atomicAdd(counters + CNT_TRI_F, (unsigned long long)tris);
+            atomicAdd(counters + CNT_SPH_F, (unsigned long long)sph);
         }
     }
 }
@@ -588,7 +631,7 @@ static void size_grids(crt_ctx* c)
     int bps = 1, bps_shade = 1, bps_packet = 1, bps_tail = 1;
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_trace_queue<false, false>, TP_BLOCK, 0);
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps_shade, k_shade<false, false>, RB, 0);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps_packet, k_trace_packet<false, false>, TP_BLOCK, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps_packet, k_trace_packet<false, false, false>, TP_BLOCK, 0);
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps_tail, k_tail<false, false>, TP_BLOCK, 0);
     c->grid_trace = c->sm_count * std::max(1, bps);
     c->grid_shade = c->sm_count * std::max(1, bps_shade);
@@ -613,10 +656,25 @@ static void launch_bounce(crt_ctx* c, crt_lane& L, int b, const RenderParams& P,
     // bounce where that happens (tail_at) the bounces before it are plain wavefront launches
     const uint32_t tail_below = (b == 0 || tail_at) ? 0u : (uint32_t)c->wide_below;
     if (c->timing) cudaEventRecord(L.ev_trace[2 * b], L.stream);
-    if (packet)   // camera rays: a warp holds the samples of one or two pixels
-        k_trace_packet<COUNT, HAS_SPH><<<c->grid_packet, TP_BLOCK, 0, L.stream>>>(A, q_in, P.cap, n_in, work_ctr, L.hitbuf.as<float4>(),
-                                                                                 counters, c->packet_primary == 1 ? 1 : 0);
-    else
+    if (packet) { // camera rays: a warp holds the samples of one or two pixels
+        // CRT_OPT_PACKET_DEFER: a packet stops after that many visits and its rays are traced one warp per ray by the
+        // launch behind it. Only for slices of at most CRT_OPT_PACKET_DEFER_BELOW camera samples: there the launch is
+        // as short as its longest packet; in a large slice the counting and the second launch cost more than they save
+        PacketDefer defer = {nullptr, nullptr, 0u, 0u};
+        const uint32_t list_cap = 1u << 18;
+        if (c->packet_defer > 0 && (long long)P.n_slots * P.s_count <= c->packet_defer_below && L.deferred.reserve((size_t)list_cap * 4) == cudaSuccess)
+            defer = PacketDefer{L.deferred.as<uint32_t>(), work_ctr + 64, list_cap, (uint32_t)c->packet_defer};
+        if (defer.after) {
+            k_trace_packet<COUNT, HAS_SPH, true><<<c->grid_packet, TP_BLOCK, 0, L.stream>>>(A, q_in, P.cap, n_in, work_ctr, L.hitbuf.as<float4>(),
+                                                                                           counters, c->packet_primary == 1 ? 1 : 0, defer);
+            k_trace_deferred<COUNT, HAS_SPH><<<c->grid_tail, TP_BLOCK, 0, L.stream>>>(A, q_in, P.cap, defer.list, defer.n, list_cap, work_ctr + 96,
+                                                                                     L.hitbuf.as<float4>(), counters);
+            c->host_counters.launches++;
+        } else {
+            k_trace_packet<COUNT, HAS_SPH, false><<<c->grid_packet, TP_BLOCK, 0, L.stream>>>(A, q_in, P.cap, n_in, work_ctr, L.hitbuf.as<float4>(),
+                                                                                            counters, c->packet_primary == 1 ? 1 : 0, defer);
+        }
+    } else
         k_trace_queue<COUNT, HAS_SPH><<<c->grid_trace, TP_BLOCK, 0, L.stream>>>(A, q_in, P.cap, n_in, work_ctr, L.hitbuf.as<float4>(),
                                                                                 counters, (uint32_t)c->refill, (uint32_t)c->leaf_thresh, tail_below);
     if (c->timing) cudaEventRecord(L.ev_trace[2 * b + 1], L.stream);
@@ -713,7 +771,7 @@ int render_accum(crt_ctx* c, const crt_camera* cam, int nx, int ny, int s0, int 
             CRT_CUDA(L.queue[1].reserve(cap * 64));
             CRT_CUDA(L.rad.reserve(cap * 16));
             CRT_CUDA(L.qcount.reserve(sizeof(uint32_t) * n_levels));
-            CRT_CUDA(L.work_ctr.reserve(sizeof(uint32_t) * 64));
+            CRT_CUDA(L.work_ctr.reserve(sizeof(uint32_t) * 128));
             CRT_CUDA(L.hitbuf.reserve(cap * 16));
         }
         size_grids(c);
@@ -738,7 +796,7 @@ int render_accum(crt_ctx* c, const crt_camera* cam, int nx, int ny, int s0, int 
                 PL.rank = l * world + rank;
                 PL.n_slots = (uint32_t)(sub_tiles(l) * CRT_TILE * CRT_TILE);
                 CRT_CUDA(cudaMemsetAsync(L.qcount.p, 0, sizeof(uint32_t) * n_levels, L.stream));
-                CRT_CUDA(cudaMemsetAsync(L.work_ctr.p, 0, sizeof(uint32_t) * 64, L.stream));
+                CRT_CUDA(cudaMemsetAsync(L.work_ctr.p, 0, sizeof(uint32_t) * 128, L.stream));   // [b] queue cursors, [32 + b] tail, [64 + b] / [96 + b] deferred rays: count, cursor
                 const uint32_t total = PL.n_slots * (uint32_t)PL.s_count;
                 const unsigned int rg = (unsigned int)min((size_t)(total + RB - 1) / RB, (size_t)c->sm_count * 32);
                 k_raygen<<<rg, RB, 0, L.stream>>>(PL, L.queue[0].as<float4>(), L.qcount.as<uint32_t>());

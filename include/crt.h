@@ -125,6 +125,12 @@ typedef enum {
                              * shape handed its queue to the one-warp-per-path launch (CRT_OPT_WIDE_BELOW) and queues no launch
                              * beyond it (a frame of depth 8 otherwise queues ~17 launches per slice that find an empty queue);
                              * a wrong guess costs time, never a different image; 0: always queue every bounce */
+    CRT_OPT_PACKET_DEFER = 13, /* render: a camera-ray packet that has visited this many nodes + leaves (default 192; the average
+                             * packet of C3 visits ~35, the longest ~500) stops, and its rays are traced one WARP per ray by a launch
+                             * queued right behind: a launch ends with its longest packet, and ~500 dependent visits take longer
+                             * than the rest of a rank's share of a frame split over 8 GPUs. 0: never. Images do not depend on it */
+    CRT_OPT_PACKET_DEFER_BELOW = 14, /* ... in slices of at most this many camera samples only (default 4,000,000): in a larger slice
+                             * the longest packet hides behind the others and the bookkeeping costs 1-2 % */
     CRT_OPT_REFILL = 4      /* tuning: idle lanes per warp that trigger a refill from the ray queue, 1..32 (default 12) */
 } crt_option;
 

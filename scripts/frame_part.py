@@ -21,6 +21,8 @@ ap.add_argument("--wide-below", type=int, default=-1)
 ap.add_argument("--workload", default="c3")
 ap.add_argument("--segments", type=int, default=0, help="c3 only: tessellation (default 1000 -> 998,002 triangles)")
 ap.add_argument("--tail-hint", type=int, default=1)
+ap.add_argument("--packet-defer", type=int, default=-1)
+ap.add_argument("--packet-defer-below", type=int, default=-1)
 ap.add_argument("--timing", action="store_true", help="CRT_OPT_TIMING: per-bounce lines on stderr (needs CRT_TRACE_TIMING=1 in the environment)")
 a = ap.parse_args()
 sc = scenes.c4_instanced() if a.workload == "c4" else (scenes.c3_mesh(n_theta=a.segments, n_phi=a.segments // 2) if a.segments else scenes.c3_mesh())
@@ -29,6 +31,10 @@ cam = crt.camera_for(sc)
 ctx = crt.Context(0)
 ctx.set_option(crt.OPT_LANES, a.lanes)
 ctx.set_option(crt.OPT_TAIL_HINT, a.tail_hint)
+if a.packet_defer >= 0:
+    ctx.set_option(crt.OPT_PACKET_DEFER, a.packet_defer)
+if a.packet_defer_below >= 0:
+    ctx.set_option(crt.OPT_PACKET_DEFER_BELOW, a.packet_defer_below)
 if a.slice_min:
     ctx.set_option(crt.OPT_SLICE_MIN, a.slice_min)
 if a.wide_below >= 0:
