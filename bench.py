@@ -379,6 +379,8 @@ def run_ours(args):
     cam = crt.camera_for(sc)
     ctx = crt.Context(local)
     ctx.set_option(crt.OPT_LANES, args.lanes)
+    if args.packet_defer >= 0:
+        ctx.set_option(crt.OPT_PACKET_DEFER, args.packet_defer)
     if args.slice_min:
         ctx.set_option(crt.OPT_SLICE_MIN, args.slice_min)
     ctx.set_scene(sc)
@@ -698,6 +700,7 @@ def main():
     ap.add_argument("--no-configs", action="store_true", help="skip the C1 / C2 / C5 sub-records of the N = 1 line")
     ap.add_argument("--lanes", type=int, default=3, help="CRT_OPT_LANES of the timed region (1 for profiling: one slice, launches in bounce order)")
     ap.add_argument("--slice-min", type=int, default=0, help="CRT_OPT_SLICE_MIN (tuning)")
+    ap.add_argument("--packet-defer", type=int, default=-1, help="CRT_OPT_PACKET_DEFER (A/B runs; default: the library's)")
     ap.add_argument("--e2e-api", default="points", choices=["points", "frame", "calls"],
                     help="end-to-end loop: points = the pose as the mesh's point array (crt_render_frame_pose, one overlapped "
                          "call per frame at N = 1); frame = all triangle vertices (crt_render_frame); calls = vertices through "
