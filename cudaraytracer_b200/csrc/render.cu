@@ -9,9 +9,13 @@
 //   per bounce:
 //   k_trace_packet (camera rays) / k_trace_queue (every other bounce): LBVH
 //                 closest hit for every queue entry (crt_traverse.cuh) -> hit buffer
+//                 k_trace_deferred (small slices): the rays of camera packets that stopped
+//                 after CRT_OPT_PACKET_DEFER visits, one warp per ray
 //   k_shade       material scatter (material.h:57-143): either a new ray into
 //                 the next queue (ballot compaction, one atomic per block) or
 //                 the path's radiance
+//   k_tail        once a bounce's queue is shorter than CRT_OPT_WIDE_BELOW: one warp per
+//                 path, closest hit + scatter until the path ends, in one launch
 //   k_accumulate  per pixel, adds the batch's samples IN SAMPLE ORDER, as the
 //                 reference's "col += shade(...)" loop does (render.h:115-122)
 //   k_resolve     col /= ns; sqrt; clip (render.h:123-128)
@@ -228,7 +232,7 @@ k_trace_queue(AccelView A, const float4* __restrict__ q, uint32_t cap, const uin
 {
     __shared__ int s_stack[CRT_STACK_WORDS * CRT_STACK_SMEM * TP_BLOCK];
     const uint32_t n = *n_ptr;
-    if (n < wide_below) return;                     // a launch this small belongs to k_trace_wide (queued right behind)
+    if (n < wide_below) return;                     // a queue this small belongs to k_tail (queued right behind)
     TraceCounters cnt = {0u, 0u, 0u, 0u, 0u, 0u, 0u};
     QueueSrc src = {q, cap};
     QueueSink sink = {hits};
