@@ -371,7 +371,7 @@ def run_ours(args):
         sc = scenes.c4_instanced()
         args.no_cpu_baseline = True      # the reference's single-thread BVH build over 10 M triangles takes minutes
         args.no_configs = True
-        args.e2e_api = "frame" if args.e2e_api == "points" else args.e2e_api
+        args.e2e_api = "parts" if args.e2e_api == "points" else args.e2e_api   # C4's pose: one translation per instance
     else:
         sc = scenes.c3_mesh()
     workload = WORKLOAD_C4 if args.workload == "c4" else WORKLOAD
@@ -383,6 +383,8 @@ def run_ours(args):
         ctx.set_option(crt.OPT_PACKET_DEFER, args.packet_defer)
     if args.slice_min:
         ctx.set_option(crt.OPT_SLICE_MIN, args.slice_min)
+    if args.batch_samples >= 0:
+        ctx.set_option(crt.OPT_BATCH_SAMPLES, args.batch_samples)
     ctx.set_scene(sc)
     ctx.build()
     build_cold_ms = ctx.counters()["build_ms"]      # first build: includes every allocation
@@ -402,6 +404,15 @@ def run_ours(args):
     if "points" in sc:
         host_points = torch.from_numpy(sc["points"]).pin_memory()
         ctx.set_indices(sc["tri_idx"], len(sc["points"]))
+    host_parts = None
+    if args.e2e_api == "parts":
+        # the instanced scene's pose form: every instance (and the ground) moves as one part, a frame uploads one
+        # translation per part (the reference's nowTransform, createScene.h:221-307) instead of 360 MB of vertices.
+        # The translations are zero, so the e2e loop renders the frame the device-resident loop renders
+        if "part_of_tri" not in sc:
+            raise SystemExit("--e2e-api parts needs a scene with a part per triangle (--workload c4)")
+        ctx.set_parts(sc["part_of_tri"], int(sc["n_parts"]))
+        host_parts = torch.zeros(int(sc["n_parts"]), 3, dtype=torch.float32).pin_memory()
 
     def barrier():
         if world > 1:
@@ -434,7 +445,10 @@ def run_ours(args):
             ctx.resolve_device(accum.data_ptr(), nx * ny, spp * world if weak else spp, rgb.data_ptr())
 
     def e2e_step(seed):
-        if world == 1 and args.e2e_api == "points":
+        if world == 1 and args.e2e_api == "parts":
+            ctx.render_frame_pose(crt.POSE_PARTS, host_parts.numpy(), cam, nx, ny, spp, depth, crt.SHADE_PATH, seed,
+                                  out=host_rgb.numpy())
+        elif world == 1 and args.e2e_api == "points":
             # the reference's loop body (render.h:206-233) as one call, the pose in the form updateFBXObj uploads it:
             # the point array (createScene.h:125-132); the face indices were set once
             ctx.render_frame_pose(crt.POSE_POINTS, host_points.numpy(), cam, nx, ny, spp, depth, crt.SHADE_PATH, seed,
@@ -450,7 +464,9 @@ def run_ours(args):
         else:
             # one process per GPU: every rank queues its pose upload + refit (crt_scene_pose_async) and renders its
             # share; the camera rays are generated while the pose lands
-            if args.e2e_api == "points":
+            if args.e2e_api == "parts":
+                ctx.pose_async(crt.POSE_PARTS, host_parts.numpy())
+            elif args.e2e_api == "points":
                 ctx.pose_async(crt.POSE_POINTS, host_points.numpy())
             elif args.e2e_api == "frame":
                 ctx.pose_async(crt.POSE_VERTICES, host_verts.numpy())
@@ -609,9 +625,11 @@ def run_ours(args):
                        "rays_per_path": rays / max(1.0, paths)},
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "Mrays/s", "ms_per_step": 1e3 * e2e_s / args.steps,
-                    "h2d_bytes_per_step": int((host_points.numel() if args.e2e_api == "points" else host_verts.numel()) * 4 + 88),
+                    "h2d_bytes_per_step": int((host_parts.numel() if args.e2e_api == "parts" else host_points.numel() if args.e2e_api == "points" else host_verts.numel()) * 4 + 88),
                     "d2h_bytes_per_step": int(nx * ny * 12),
-                    "what": (("crt_render_frame_pose(CRT_POSE_POINTS): upload of the %d mesh points (the form the reference's updateFBXObj uploads, createScene.h:125-132) + gather into the triangles + refit + render + read-back, overlapped, per frame, pinned host buffers, wall clock" % (host_points.numel() // 3))
+                    "what": (("crt_render_frame_pose(CRT_POSE_PARTS): upload of one translation per part (%d instances + the ground; the reference's nowTransform, createScene.h:221-307) + move of every triangle with its part + refit + render + read-back, overlapped, per frame, pinned host buffers, wall clock" % (host_parts.shape[0] - 1))
+                             if world == 1 and args.e2e_api == "parts" else
+                             ("crt_render_frame_pose(CRT_POSE_POINTS): upload of the %d mesh points (the form the reference's updateFBXObj uploads, createScene.h:125-132) + gather into the triangles + refit + render + read-back, overlapped, per frame, pinned host buffers, wall clock" % (host_points.numel() // 3))
                              if world == 1 and args.e2e_api == "points" else
                              "crt_render_frame (upload of all triangle vertices + refit + render + read-back, overlapped) per frame, pinned host buffers, wall clock"
                              if world == 1 and args.e2e_api == "frame" else
@@ -619,7 +637,8 @@ def run_ours(args):
                              if world == 1 else
                              "per rank: %s, render of the rank's share, tile gather (or reduce); rank 0: resolve + read-back to a pinned host buffer; wall clock, max over ranks" % (
                                  "crt_scene_update_vertices + crt_accel_refit" if args.e2e_api == "calls" else
-                                 "crt_scene_pose_async(%s) (upload + refit beside ray generation)" % ("points" if args.e2e_api == "points" else "vertices")))},
+                                 "crt_scene_pose_async(%s) (upload + refit beside ray generation)" % (
+                                     "one translation per part" if args.e2e_api == "parts" else "points" if args.e2e_api == "points" else "vertices")))},
             "gpu_launches": launches,
             "roofline": {"kernel": "closest hit over the 4-wide LBVH: k_trace_packet (camera rays) + k_trace_queue (bounces), %d launches/step" % bounce_launches,
                          "bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
@@ -700,10 +719,11 @@ def main():
     ap.add_argument("--no-configs", action="store_true", help="skip the C1 / C2 / C5 sub-records of the N = 1 line")
     ap.add_argument("--lanes", type=int, default=3, help="CRT_OPT_LANES of the timed region (1 for profiling: one slice, launches in bounce order)")
     ap.add_argument("--slice-min", type=int, default=0, help="CRT_OPT_SLICE_MIN (tuning)")
+    ap.add_argument("--batch-samples", type=int, default=-1, help="CRT_OPT_BATCH_SAMPLES (A/B runs; default: the library's)")
     ap.add_argument("--packet-defer", type=int, default=-1, help="CRT_OPT_PACKET_DEFER (A/B runs; default: the library's)")
-    ap.add_argument("--e2e-api", default="points", choices=["points", "frame", "calls"],
+    ap.add_argument("--e2e-api", default="points", choices=["points", "frame", "calls", "parts"],
                     help="end-to-end loop: points = the pose as the mesh's point array (crt_render_frame_pose, one overlapped "
-                         "call per frame at N = 1); frame = all triangle vertices (crt_render_frame); calls = vertices through "
+                         "call per frame at N = 1); parts = one translation per instance (--workload c4's default); frame = all triangle vertices (crt_render_frame); calls = vertices through "
                          "the three separate calls")
     ap.add_argument("--workload", default="c3", choices=["c3", "c4"],
                     help="c3 (default): the configuration the metric is quoted on; c4: the 10 M-triangle instanced scene at "

@@ -18,7 +18,7 @@ SHADE_PATH, SHADE_LAMBERT, SHADE_NORMAL = 0, 1, 2
 ACCEL_LBVH, ACCEL_BRUTE, ACCEL_LBVH_PACKET = 0, 1, 2
 OPT_LEAF_MAX, OPT_COUNTERS, OPT_BATCH_PATHS, OPT_REFILL, OPT_LEAF_THRESH, OPT_PACKET_PRIMARY, OPT_LANES, OPT_BUILDER = 1, 2, 3, 4, 5, 6, 7, 8
 OPT_WIDE_BELOW = 9
-OPT_TIMING, OPT_SLICE_MIN, OPT_TAIL_HINT, OPT_PACKET_DEFER, OPT_PACKET_DEFER_BELOW = 10, 11, 12, 13, 14
+OPT_TIMING, OPT_SLICE_MIN, OPT_TAIL_HINT, OPT_PACKET_DEFER, OPT_PACKET_DEFER_BELOW, OPT_BATCH_SAMPLES = 10, 11, 12, 13, 14, 15
 COMM_ID_BYTES = 128
 DBG_NODES, DBG_RECS, DBG_KEYS, DBG_PERM, DBG_CHILD, DBG_RANGE, DBG_LEAF_BOX, DBG_NODE_BOX = range(8)
 TRACE_STATIC_MAX_RAYS = 65536

@@ -287,6 +287,10 @@ int crt_set_option(crt_ctx* c, int option, int64_t value)
         if (value < 1) { set_error("CRT_OPT_BATCH_PATHS must be >= 1"); return CRT_ERR_INVALID; }
         c->batch_paths = value;
         return CRT_OK;
+    case CRT_OPT_BATCH_SAMPLES:
+        if (value < 0 || value > (1 << 20)) { set_error("CRT_OPT_BATCH_SAMPLES must be in [0, 2^20]"); return CRT_ERR_INVALID; }
+        c->batch_samples = (int)value;
+        return CRT_OK;
     }
     set_error("crt_set_option: unknown option %d", option);
     return CRT_ERR_INVALID;

@@ -133,6 +133,7 @@ struct crt_ctx {
     int64_t packet_defer_below = 4000000;  // CRT_OPT_PACKET_DEFER_BELOW: only in slices of at most this many camera samples
     int64_t wide_below = 32768;            // CRT_OPT_WIDE_BELOW: bounces with fewer rays run one warp per ray
     int64_t batch_paths = 1ll << 25;
+    int batch_samples = 64;                // CRT_OPT_BATCH_SAMPLES: a frame beyond batch_paths is cut into tile groups of up to this many samples per pixel; 0: into sample batches of all tiles
     int64_t slice_min_samples = 2000000;   // CRT_OPT_SLICE_MIN: a slice (lane) of a frame holds at least this many camera samples
     int timing = 0;                        // CRT_OPT_TIMING: per-launch events, render calls wait for the device
     int grid_trace = 0, grid_shade = 0, grid_packet = 0, grid_tail = 0;   // persistent grids (render.cu:size_grids)

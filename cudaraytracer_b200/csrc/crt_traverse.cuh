@@ -460,6 +460,9 @@ __device__ __forceinline__ void traverse_persistent(const AccelView& A, const ui
 //     tests the four boxes against its own ray, a child is entered when any
 //     lane's ray enters it, children are ordered by the first entering lane.
 #define CRT_PACKET_STACK CRT_STACK_ENTRIES   // same bound as the per-ray stack
+#ifndef CRT_PACKET_STACK_SMEM
+#define CRT_PACKET_STACK_SMEM 0              // entries of a warp's packet stack in shared memory (see traverse_packets)
+#endif
 
 // Long packets are handed on. A camera-ray launch ends with its longest packet: two pixels on the limb of the mesh
 // walk ~500 dependent nodes and leaves where the average packet walks ~35, at ~1.3 us per visit while eight warps
@@ -487,11 +490,23 @@ __device__ __forceinline__ void traverse_packets(const AccelView& A, const uint3
 #ifndef CRT_PACKET_STACK_T
 #define CRT_PACKET_STACK_T 1
 #endif
-#if CRT_PACKET_STACK_T
-    float wstack_t[CRT_PACKET_STACK];   // entry distance of each stacked child (interval test only): an entry beyond the
-                                        // packet's farthest closest hit is dropped when popped, without fetching its node
+    // The packet's stack is warp-uniform: one sequence of {child reference, entry distance} for the 32 lanes.
+    // CRT_PACKET_STACK_SMEM > 0: its first that-many entries live in shared memory, one copy per WARP (8 bytes an entry);
+    // every lane stores the same value to the same address and later reads what it stored itself, so no lane depends
+    // on another lane's store, and every push follows a __ballot_sync / __shfl_sync of the same node step, which all
+    // lanes reach only after their pops of the step before (no lane can overwrite an entry another still has to pop).
+    // Deeper entries, and with CRT_PACKET_STACK_SMEM == 0 all of them, are per-lane local arrays in which every lane
+    // keeps the same values (slot X of 32 lanes is one 128-byte line: a warp with 20 entries holds 5 KB of L1).
+    // The entry distance (interval test only): an entry beyond the packet's farthest closest hit is dropped when
+    // popped, without fetching its node.
+#if CRT_PACKET_STACK_SMEM
+    __shared__ int2 s_pstack[(TP_BLOCK / 32) * CRT_PACKET_STACK_SMEM];
+    int2* const pstack = s_pstack + (threadIdx.x >> 5) * CRT_PACKET_STACK_SMEM;
 #endif
-    int wstack[CRT_PACKET_STACK];   // every lane keeps the same (warp-uniform) stack; slot X of 32 lanes is one 128-byte line of local memory
+#if CRT_PACKET_STACK_T
+    float wstack_t[CRT_PACKET_STACK - CRT_PACKET_STACK_SMEM];
+#endif
+    int wstack[CRT_PACKET_STACK - CRT_PACKET_STACK_SMEM];
     constexpr uint32_t FULL = 0xffffffffu;
     // packets per grab
     uint32_t chunk = (n / (gridDim.x * (TP_BLOCK / 32u) * 8u)) & ~31u;
@@ -533,6 +548,42 @@ __device__ __forceinline__ void traverse_packets(const AccelView& A, const uint3
                 int node = A.root;               // warp-uniform
                 uint32_t sp = 0;                 // warp-uniform
                 uint32_t visits = 0;             // warp-uniform
+                auto push = [&](int r, float tn) {
+#if CRT_PACKET_STACK_SMEM
+                    if (sp < (uint32_t)CRT_PACKET_STACK_SMEM) { pstack[sp++] = make_int2(r, __float_as_int(tn)); return; }
+#endif
+#if CRT_PACKET_STACK_T
+                    wstack_t[sp - CRT_PACKET_STACK_SMEM] = tn;
+#endif
+                    wstack[sp - CRT_PACKET_STACK_SMEM] = r;
+                    sp++;
+                };
+                // the nearest stacked child that is still entered before the packet's farthest closest hit -> node
+                auto pop_next = [&]() -> bool {
+                    while (sp > 0u) {
+                        --sp;
+                        float tn = 0.0f;
+#if CRT_PACKET_STACK_SMEM
+                        if (sp < (uint32_t)CRT_PACKET_STACK_SMEM) {
+                            const int2 e = pstack[sp];
+                            node = e.x;
+                            tn = __int_as_float(e.y);
+                        } else
+#endif
+                        {
+                            node = wstack[sp - CRT_PACKET_STACK_SMEM];
+#if CRT_PACKET_STACK_T
+                            tn = wstack_t[sp - CRT_PACKET_STACK_SMEM];
+#endif
+                        }
+#if CRT_PACKET_STACK_T
+                        if (tn > t_far) continue;
+#endif
+                        (void)tn;
+                        return true;
+                    }
+                    return false;
+                };
                 for (;;) {
                     if (DEFER && ++visits > defer.after) {
                         uint32_t base = 0;
@@ -580,16 +631,7 @@ __device__ __forceinline__ void traverse_packets(const AccelView& A, const uint3
                             if ((m4 & (m4 - 1u)) == 0u) {
                                 // none or one child entered (the common case): no ordering needed
                                 if (m4 == 0u) {
-                                    bool got = false;
-                                    while (sp > 0u) {
-                                        node = wstack[--sp];
-#if CRT_PACKET_STACK_T
-                                        if (wstack_t[sp] > t_far) continue;
-#endif
-                                        got = true;
-                                        break;
-                                    }
-                                    if (!got) break;
+                                    if (!pop_next()) break;
                                 } else {
                                     const int e_lo = (m4 & 1u) ? refs.x : refs.y, e_hi = (m4 & 4u) ? refs.z : refs.w;
                                     node = (m4 & 3u) ? e_lo : e_hi;
@@ -633,16 +675,10 @@ __device__ __forceinline__ void traverse_packets(const AccelView& A, const uint3
                         }
                         CRT_CSWAP(0, 1) CRT_CSWAP(2, 3) CRT_CSWAP(0, 2) CRT_CSWAP(1, 3) CRT_CSWAP(1, 2)
 #undef CRT_CSWAP
-#if CRT_PACKET_STACK_T
                         // the per-lane test orders children by the first entering lane: not a bound for the packet
-                        if (n_hit > 3) { wstack_t[sp] = uni ? key[3] : 0.0f; wstack[sp++] = ref[3]; }
-                        if (n_hit > 2) { wstack_t[sp] = uni ? key[2] : 0.0f; wstack[sp++] = ref[2]; }
-                        if (n_hit > 1) { wstack_t[sp] = uni ? key[1] : 0.0f; wstack[sp++] = ref[1]; }
-#else
-                        if (n_hit > 3) wstack[sp++] = ref[3];
-                        if (n_hit > 2) wstack[sp++] = ref[2];
-                        if (n_hit > 1) wstack[sp++] = ref[1];
-#endif
+                        if (n_hit > 3) push(ref[3], uni ? key[3] : 0.0f);
+                        if (n_hit > 2) push(ref[2], uni ? key[2] : 0.0f);
+                        if (n_hit > 1) push(ref[1], uni ? key[1] : 0.0f);
                         if (n_hit > 0) { node = ref[0]; continue; }
                     } else {
                         const uint32_t ref = ~(uint32_t)node;
@@ -680,16 +716,7 @@ __device__ __forceinline__ void traverse_packets(const AccelView& A, const uint3
                         // distances are positive, so their bit patterns order like the values
                         if (uni) t_far = __uint_as_float(__reduce_max_sync(FULL, live ? __float_as_uint(best.t) : 0u));
                     }
-                    bool got = false;
-                    while (sp > 0u) {
-                        node = wstack[--sp];
-#if CRT_PACKET_STACK_T
-                        if (wstack_t[sp] > t_far) continue;
-#endif
-                        got = true;
-                        break;
-                    }
-                    if (!got) break;
+                    if (!pop_next()) break;
                 }
             }
             if (live && !handed_on) sink.store(ray_i, best);

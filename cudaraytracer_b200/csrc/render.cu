@@ -49,6 +49,7 @@ struct RenderParams {
     int band;             // 1: the unit dealt out is a whole tile ROW (rows rank, rank + world, ...), so a job's pixels
                           // are bands of full image rows that can be read back with one strided copy
     uint32_t n_slots;     // slots of this job: its tiles * CRT_TILE^2
+    uint32_t tile_base;   // the job's first tile, counted in the (sub-)rank's own tiles (a frame beyond the batch size is cut into tile groups)
     int s_begin;          // first sample index of this batch
     int s_count;          // samples in this batch
     int max_depth;
@@ -62,7 +63,7 @@ struct RenderParams {
 // consecutive slots (one warp) cover an 8x4 block.
 __device__ __forceinline__ bool slot_to_pixel(const RenderParams& P, uint32_t slot, int& x, int& y)
 {
-    const uint32_t lt = slot >> 10, s = slot & 1023u;
+    const uint32_t lt = (slot >> 10) + P.tile_base, s = slot & 1023u;
     uint32_t tx, ty;
     if (P.band) {
         const uint32_t r = lt / (uint32_t)P.tiles_x;
@@ -442,8 +443,11 @@ __device__ __forceinline__ void load_path(const RenderParams& P, const float4* _
 }
 
 // one thread per queue entry, fully converged. A queue of fewer than `tail_below` entries belongs to k_tail.
+#ifndef CRT_SHADE_MIN_BLOCKS
+#define CRT_SHADE_MIN_BLOCKS 1   // development switch (A/B of the register budget; profiles/r02_s_ab.txt)
+#endif
 template <bool COUNT, bool HAS_SPH>
-__global__ void __launch_bounds__(RB)
+__global__ void __launch_bounds__(RB, CRT_SHADE_MIN_BLOCKS)
 k_shade(RenderParams P, AccelView A, const DMat* __restrict__ mats, const float4* __restrict__ q_in,
         const float4* __restrict__ hits, const uint32_t* __restrict__ n_in_ptr, float4* __restrict__ q_out,
         uint32_t* __restrict__ n_out_ptr, float4* __restrict__ rad, unsigned long long* __restrict__ counters,
@@ -739,7 +743,7 @@ int render_accum(crt_ctx* c, const crt_camera* cam, int nx, int ny, int s0, int 
     const long long units = P.band ? tiles_y : tiles;              // what is dealt out to ranks and slices
     const long long unit_tiles = P.band ? P.tiles_x : 1;
     const long long local_tiles = units > rank ? (units - rank + world - 1) / world * unit_tiles : 0;
-    P.rank = rank; P.world = world;
+    P.rank = rank; P.world = world; P.tile_base = 0u;
     if (local_tiles * CRT_TILE * CRT_TILE >= (1ll << 31)) { set_error("crt_render: image too large"); return CRT_ERR_INVALID; }
     P.max_depth = max_depth; P.mode = mode; P.seed = seed; P.seed_key = crt_rng_seed_key(seed);
 
@@ -761,12 +765,29 @@ int render_accum(crt_ctx* c, const crt_camera* cam, int nx, int ny, int s0, int 
             return units > sr ? (units - sr + sub_world - 1) / sub_world : 0ll;
         };
         auto sub_tiles = [&](int l) { return sub_units(l) * unit_tiles; };
-        const long long lane_slots = sub_tiles(0) * CRT_TILE * CRT_TILE;               // lane 0 has the most tiles
-        long long per_batch = c->batch_paths / (local_tiles * CRT_TILE * CRT_TILE);      // samples of all slices together
-        if (per_batch < 1) per_batch = 1;
-        if (per_batch > n_samples) per_batch = n_samples;
-        while (lane_slots * per_batch >= (1ll << 31) && per_batch > 1) per_batch--;
-        const size_t cap = (size_t)lane_slots * (size_t)per_batch;
+        // A frame with more camera samples than batch_paths runs as several jobs per slice. CRT_OPT_BATCH_SAMPLES > 0:
+        // the slice's tiles are cut into groups, and a group is rendered with up to that many samples per pixel at once,
+        // so a warp of camera rays still holds the samples of one or two pixels and walks the tree as one packet (a 4K x
+        // 64 spp frame on one GPU used to run as 16 batches of FOUR samples over every tile: eight pixels per warp).
+        // 0: sample batches over all of the slice's tiles. Either way a pixel's jobs follow each other in sample order on
+        // one stream, so d_accum is summed in the same order and the image does not depend on the cut.
+        const long long lane_tiles0 = sub_tiles(0);                                      // lane 0 has the most tiles
+        const long long slot_sz = (long long)CRT_TILE * CRT_TILE;
+        const long long lane_paths = std::max(1ll, (long long)(c->batch_paths / n_lanes));
+        long long per_batch, tiles_job;                                                  // samples per job, tiles per job and slice
+        if (c->batch_samples > 0 && lane_tiles0 * slot_sz * n_samples > lane_paths) {
+            per_batch = std::min((long long)n_samples, (long long)c->batch_samples);
+            per_batch = std::max(1ll, std::min(per_batch, lane_paths / slot_sz));
+            tiles_job = std::max(1ll, std::min(lane_tiles0, lane_paths / (slot_sz * per_batch)));
+        } else {
+            per_batch = c->batch_paths / (local_tiles * slot_sz);                        // samples of all slices together
+            if (per_batch < 1) per_batch = 1;
+            if (per_batch > n_samples) per_batch = n_samples;
+            tiles_job = lane_tiles0;
+        }
+        while (tiles_job * slot_sz * per_batch >= (1ll << 31) && per_batch > 1) per_batch--;
+        while (tiles_job * slot_sz * per_batch >= (1ll << 31) && tiles_job > 1) tiles_job--;
+        const size_t cap = (size_t)(tiles_job * slot_sz) * (size_t)per_batch;
         P.cap = (uint32_t)cap;
         const int n_levels = CRT_MAX_DEPTH + 3;
         for (int l = 0; l < n_lanes; l++) {
@@ -789,16 +810,20 @@ int render_accum(crt_ctx* c, const crt_camera* cam, int nx, int ny, int s0, int 
         for (int l = 1; l < n_lanes; l++) CRT_CUDA(cudaStreamWaitEvent(c->lane[l].stream, c->ev_fork, 0));
 
         for (int sb = s0; sb < s1; sb += (int)per_batch) {
-            P.s_begin = sb;
-            P.s_count = (s1 - sb) < per_batch ? (s1 - sb) : (int)per_batch;
+          P.s_begin = sb;
+          P.s_count = (s1 - sb) < per_batch ? (s1 - sb) : (int)per_batch;
+          for (long long g0 = 0; g0 < lane_tiles0; g0 += tiles_job) {
             for (int l = 0; l < n_lanes; l++) {
                 crt_lane& L = c->lane[l];
                 L.h_counts[0] = 0;
-                if (sub_tiles(l) == 0) continue;
+                if (sub_tiles(l) <= g0) continue;
+                const bool first_job = sb == s0 && g0 == 0;
+                const bool last_job = sb + P.s_count >= s1 && g0 + tiles_job >= sub_tiles(l);   // of this slice
                 RenderParams PL = P;
                 PL.world = sub_world;
                 PL.rank = l * world + rank;
-                PL.n_slots = (uint32_t)(sub_tiles(l) * CRT_TILE * CRT_TILE);
+                PL.tile_base = (uint32_t)g0;
+                PL.n_slots = (uint32_t)(std::min(tiles_job, sub_tiles(l) - g0) * slot_sz);
                 CRT_CUDA(cudaMemsetAsync(L.qcount.p, 0, sizeof(uint32_t) * n_levels, L.stream));
                 CRT_CUDA(cudaMemsetAsync(L.work_ctr.p, 0, sizeof(uint32_t) * 128, L.stream));   // [b] queue cursors, [32 + b] tail, [64 + b] / [96 + b] deferred rays: count, cursor
                 const uint32_t total = PL.n_slots * (uint32_t)PL.s_count;
@@ -819,7 +844,7 @@ int render_accum(crt_ctx* c, const crt_camera* cam, int nx, int ny, int s0, int 
                 if (c->timing) CRT_CUDA(cudaEventRecord(L.ev_begin, L.stream));
                 // ray generation does not read the scene: only the closest-hit launches wait for an upload and refit
                 // queued on another stream (crt_render_frame)
-                if (scene_ready && sb == s0) CRT_CUDA(cudaStreamWaitEvent(L.stream, scene_ready, 0));
+                if (scene_ready && first_job) CRT_CUDA(cudaStreamWaitEvent(L.stream, scene_ready, 0));
                 for (int b = 0; b < n_bounces; b++) {
                     const float4* qi = L.queue[b & 1].as<float4>();
                     float4* qo = L.queue[(b + 1) & 1].as<float4>();
@@ -838,7 +863,7 @@ int render_accum(crt_ctx* c, const crt_camera* cam, int nx, int ny, int s0, int 
                 k_accumulate<<<(PL.n_slots + 255) / 256, 256, 0, L.stream>>>(PL, L.rad.as<float4>(), d_accum, L.qcount.as<uint32_t>(), bounces,
                                                                             c->counters.as<unsigned long long>(), (uint32_t)c->wide_below, tail_at,
                                                                             hint_key, hinting ? L.tail_hint_dev : nullptr);
-                if (finish && P.band && sb + P.s_count >= s1) {
+                if (finish && P.band && last_job) {
                     // the slice's pixels are final: resolve its rows and start their copy to the caller's buffer while
                     // the other slices still render (rows of tile rows PL.rank, PL.rank + sub_world, ...)
                     const int n_bands = (int)sub_units(l);
@@ -882,6 +907,7 @@ int render_accum(crt_ctx* c, const crt_camera* cam, int nx, int ny, int s0, int 
                 if (verbose) fprintf(stderr, "[crt] lane %d: bounces %.3f ms\n", l, bms);
             }
             bounce_ms += batch_ms;
+          }
         }
         // the other lanes' work joins the context's stream: whatever the caller queues there next (a reduce, a
         // resolve, a copy) is ordered behind the whole frame

@@ -369,10 +369,11 @@ def c4_instanced(grid=10, pitch=250.0, n_theta=500, n_phi=101, nx=3840, ny=2160,
     base = c3_mesh(n_theta, n_phi)
     tri0 = base["tri"][:-2]
     mat0 = base["tri_mat"][:-2]
-    tris, mats_idx = [], []
+    tris, mats_idx, parts = [], [], []
     off0 = -(grid - 1) * pitch / 2.0
     for a in range(grid):
         for b in range(grid):
+            parts.append(np.full(len(tri0), a * grid + b, np.uint32))
             t = tri0.copy()
             shift = np.asarray([off0 + a * pitch, 0.0, off0 + b * pitch], np.float32)
             for k in range(3):
@@ -382,8 +383,12 @@ def c4_instanced(grid=10, pitch=250.0, n_theta=500, n_phi=101, nx=3840, ny=2160,
     g0, g1, g2, gn = ground_quad(-110.0, 20000.0)
     tris.append(np.concatenate([g0, g1, g2, gn], axis=1))
     mats_idx.append(np.asarray([2, 2], np.uint32))
+    parts.append(np.full(2, grid * grid, np.uint32))                    # the ground is a part of its own
     out = dict(base)
+    for k in ("points", "tri_idx"):                                     # the base mesh's point form does not describe this scene
+        out.pop(k, None)
     out.update(name="C4_instanced_%dM" % round(sum(len(t) for t in tris) / 1e6), tri=np.ascontiguousarray(np.concatenate(tris)),
+               part_of_tri=np.concatenate(parts), n_parts=grid * grid + 1,
                tri_mat=np.concatenate(mats_idx).astype(np.uint32),
                camera=camera_dict((0, 900, 2600), (0, 0, 0), 40), nx=nx, ny=ny, spp=spp)
     return out

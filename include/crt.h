@@ -131,6 +131,11 @@ typedef enum {
                              * than the rest of a rank's share of a frame split over 8 GPUs. 0: never. Images do not depend on it */
     CRT_OPT_PACKET_DEFER_BELOW = 14, /* ... in slices of at most this many camera samples only (default 4,000,000): in a larger slice
                              * the longest packet hides behind the others and the bookkeeping costs 1-2 % */
+    CRT_OPT_BATCH_SAMPLES = 15, /* render: how a frame with more camera samples than CRT_OPT_BATCH_PATHS is cut into jobs. n > 0 (default 64):
+                             * into GROUPS OF TILES, each rendered with up to n samples per pixel at once, so that a warp of camera
+                             * rays still holds the samples of one or two pixels (a 4K x 64 spp frame on one GPU: 16 tile groups x 64
+                             * samples instead of 16 batches of 4 samples over every tile); 0: into sample batches over all of the
+                             * rank's tiles. A pixel's samples are accumulated in sample order either way: images do not depend on it */
     CRT_OPT_REFILL = 4      /* tuning: idle lanes per warp that trigger a refill from the ray queue, 1..32 (default 12) */
 } crt_option;
 
