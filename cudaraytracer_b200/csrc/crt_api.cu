@@ -182,8 +182,8 @@ int crt_create(int device, crt_ctx** out)
         CRT_CUDA(cudaEventCreateWithFlags(&L.ev_join, cudaEventDisableTiming));
         for (auto& e : L.ev_trace) CRT_CUDA(cudaEventCreate(&e));
         CRT_CUDA(cudaMallocHost((void**)&L.h_counts, sizeof(uint32_t) * (CRT_MAX_DEPTH + 3)));
-        CRT_CUDA(cudaHostAlloc((void**)&L.tail_hint, sizeof(uint32_t), cudaHostAllocMapped));
-        *L.tail_hint = 0u;
+        CRT_CUDA(cudaHostAlloc((void**)&L.tail_hint, sizeof(uint32_t) * CRT_TAIL_HINTS, cudaHostAllocMapped));
+        for (int i = 0; i < CRT_TAIL_HINTS; i++) L.tail_hint[i] = 0u;
         CRT_CUDA(cudaHostGetDevicePointer((void**)&L.tail_hint_dev, L.tail_hint, 0));
     }
     CRT_CUDA(c->counters.reserve(sizeof(unsigned long long) * CNT_COUNT));

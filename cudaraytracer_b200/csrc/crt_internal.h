@@ -56,6 +56,7 @@ constexpr int CRT_MAX_DEPTH = 16;
 // One slice of a frame in flight (render.cu): its own stream, wavefront
 // queues, hit and radiance buffers, queue counters and timing events.
 constexpr int CRT_MAX_LANES = 4;
+#define CRT_TAIL_HINTS 64
 struct crt_lane {
     cudaStream_t stream = nullptr;         // lane 0 uses the context's stream
     crt::DevBuf queue[2], qcount, work_ctr, hitbuf, rad, deferred;
@@ -66,8 +67,8 @@ struct crt_lane {
     // CRT_OPT_TAIL_HINT: a mapped pinned word the slice's k_accumulate writes, (key << 8) | bounce: the first bounce of
     // the last frame with this key whose queue was short enough for k_tail (0: none). Read by the host, unsynchronised:
     // any value it can hold gives the same image
-    uint32_t* tail_hint = nullptr;
-    uint32_t* tail_hint_dev = nullptr;     // the same word as the device addresses it
+    uint32_t* tail_hint = nullptr;         // CRT_TAIL_HINTS words: one per tile group of a frame cut into several (render.cu)
+    uint32_t* tail_hint_dev = nullptr;     // the same words as the device addresses them
 };
 
 struct crt_ctx {

@@ -54,7 +54,9 @@ namespace crt {
 #define CRT_STACK_SMEM 16     // levels kept in shared memory (reference + entry distance each)
 #define CRT_STACK_WORDS 2
 #else
-#define CRT_STACK_SMEM 32     // levels kept in shared memory
+#ifndef CRT_STACK_SMEM
+#define CRT_STACK_SMEM 32     // levels kept in shared memory (16 KB a block: half of an SM's 256 KB at 8 blocks, the other half is L1)
+#endif
 #define CRT_STACK_WORDS 1
 #endif
 #define CRT_STACK_LOCAL (288 - CRT_STACK_SMEM)   // spill levels. A descent pushes <= 3 references per inner node, so a tree of depth D needs

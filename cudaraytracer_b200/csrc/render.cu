@@ -444,7 +444,8 @@ __device__ __forceinline__ void load_path(const RenderParams& P, const float4* _
 
 // one thread per queue entry, fully converged. A queue of fewer than `tail_below` entries belongs to k_tail.
 #ifndef CRT_SHADE_MIN_BLOCKS
-#define CRT_SHADE_MIN_BLOCKS 1   // development switch (A/B of the register budget; profiles/r02_s_ab.txt)
+#define CRT_SHADE_MIN_BLOCKS 10  // 48 registers instead of 56, no spills: 10 resident blocks instead of 9 hide more of the record and
+                                 // queue latency (C3 frame 6.95 -> 6.76 ms, profiles/r02_s_ab.txt)
 #endif
 template <bool COUNT, bool HAS_SPH>
 __global__ void __launch_bounds__(RB, CRT_SHADE_MIN_BLOCKS)
@@ -832,11 +833,15 @@ int render_accum(crt_ctx* c, const crt_camera* cam, int nx, int ny, int s0, int 
                 // CRT_OPT_TAIL_HINT: where the last frame of this shape handed over to k_tail (crt_lane::tail_hint)
                 const uint32_t hint_key = ((uint32_t)nx * 0x9e3779b1u ^ (uint32_t)ny * 0x85ebca6bu ^ (uint32_t)PL.s_count * 0xc2b2ae35u ^
                                            (uint32_t)max_depth * 0x27d4eb2fu ^ (uint32_t)PL.world * 0x165667b1u ^ (uint32_t)PL.rank * 0xd3a2646cu ^
-                                           (uint32_t)c->n_prims * 0xfd7046c5u ^ (uint32_t)c->wide_below * 0xb55a4f09u) & 0xffffffu;
+                                           (uint32_t)c->n_prims * 0xfd7046c5u ^ (uint32_t)c->wide_below * 0xb55a4f09u ^ PL.tile_base * 0x2545f491u ^
+                                           PL.n_slots * 0x9fb21c65u) & 0xffffffu;
+                // a frame cut into tile groups: the groups show different parts of the scene, so each keeps its own hint
+                // (one group's sky would send the next group's million bounce rays to the one-warp-per-path launch)
+                const uint32_t hint_slot = (uint32_t)((g0 / tiles_job) % CRT_TAIL_HINTS);
                 int tail_at = 0;
                 const bool hinting = c->tail_hint && !c->timing && c->wide_below > 0 && bounces > 2;
                 if (hinting) {
-                    const uint32_t hv = *reinterpret_cast<volatile uint32_t*>(L.tail_hint);
+                    const uint32_t hv = *reinterpret_cast<volatile uint32_t*>(L.tail_hint + hint_slot);
                     if ((hv >> 8) == hint_key && (int)(hv & 0xffu) < bounces) tail_at = (int)(hv & 0xffu);
                 }
                 const int n_bounces = tail_at ? tail_at + 1 : bounces;
@@ -862,7 +867,7 @@ int render_accum(crt_ctx* c, const crt_camera* cam, int nx, int ny, int s0, int 
                 if (c->timing) CRT_CUDA(cudaEventRecord(L.ev_end, L.stream));
                 k_accumulate<<<(PL.n_slots + 255) / 256, 256, 0, L.stream>>>(PL, L.rad.as<float4>(), d_accum, L.qcount.as<uint32_t>(), bounces,
                                                                             c->counters.as<unsigned long long>(), (uint32_t)c->wide_below, tail_at,
-                                                                            hint_key, hinting ? L.tail_hint_dev : nullptr);
+                                                                            hint_key, hinting ? L.tail_hint_dev + hint_slot : nullptr);
                 if (finish && P.band && last_job) {
                     // the slice's pixels are final: resolve its rows and start their copy to the caller's buffer while
                     // the other slices still render (rows of tile rows PL.rank, PL.rank + sub_world, ...)
