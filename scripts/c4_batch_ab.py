@@ -16,14 +16,17 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--steps", type=int, default=3)
 ap.add_argument("--settings", default="0,64,32,16")
 ap.add_argument("--lanes", default="3")
+ap.add_argument("--builder", type=int, default=0, help="CRT_OPT_BUILDER: 0 LBVH (default), 1 PLOC")
 a = ap.parse_args()
 t0 = time.time()
 sc = scenes.c4_instanced()
 nx, ny, spp, depth = sc["nx"], sc["ny"], sc["spp"], sc["max_depth"]
 cam = crt.camera_for(sc)
 ctx = crt.Context(0)
+ctx.set_option(crt.OPT_BUILDER, a.builder)
 ctx.set_scene(sc)
 ctx.build()
+print("builder %d" % a.builder)
 print("scene + build: %.1f s, %d triangles" % (time.time() - t0, len(sc["tri"])), flush=True)
 dev = torch.device("cuda", 0)
 accum = torch.zeros(ny, nx, 3, dtype=torch.float32, device=dev)
