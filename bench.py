@@ -385,6 +385,8 @@ def run_ours(args):
         ctx.set_option(crt.OPT_SLICE_MIN, args.slice_min)
     if args.batch_samples >= 0:
         ctx.set_option(crt.OPT_BATCH_SAMPLES, args.batch_samples)
+    if args.builder == "ploc":
+        ctx.set_option(crt.OPT_BUILDER, crt.BUILDER_PLOC)
     ctx.set_scene(sc)
     ctx.build()
     build_cold_ms = ctx.counters()["build_ms"]      # first build: includes every allocation
@@ -610,7 +612,7 @@ def run_ours(args):
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": scaling,
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "paths_per_s": paths / (ms * 1e-3),
-            "config": {"workload": workload, "triangles": int(info["n_prims"]), "lbvh_depth": info["max_depth"],
+            "config": {"workload": workload, "triangles": int(info["n_prims"]), "builder": args.builder, "lbvh_depth": info["max_depth"],
                        "lbvh_build_ms": build_ms, "lbvh_build_cold_ms": build_cold_ms, "lbvh_refit_ms": refit_ms,
                        "reference_csv_columns": "rendering = ms_per_step, update = lbvh_refit_ms (+ the pose upload, inside e2e), build = lbvh_build_ms (kernel.cu:61, core/render.h:212-230)",
                        "lanes": lanes, "parallelism": ("single" if world == 1 else
@@ -719,6 +721,7 @@ def main():
     ap.add_argument("--no-configs", action="store_true", help="skip the C1 / C2 / C5 sub-records of the N = 1 line")
     ap.add_argument("--lanes", type=int, default=3, help="CRT_OPT_LANES of the timed region (1 for profiling: one slice, launches in bounce order)")
     ap.add_argument("--slice-min", type=int, default=0, help="CRT_OPT_SLICE_MIN (tuning)")
+    ap.add_argument("--builder", default="lbvh", choices=["lbvh", "ploc"], help="CRT_OPT_BUILDER (tree topology; images do not depend on it)")
     ap.add_argument("--batch-samples", type=int, default=-1, help="CRT_OPT_BATCH_SAMPLES (A/B runs; default: the library's)")
     ap.add_argument("--packet-defer", type=int, default=-1, help="CRT_OPT_PACKET_DEFER (A/B runs; default: the library's)")
     ap.add_argument("--e2e-api", default="points", choices=["points", "frame", "calls", "parts"],

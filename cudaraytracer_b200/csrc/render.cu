@@ -39,7 +39,10 @@
 
 namespace crt {
 
-constexpr int RB = 128;   // threads per block of the wavefront kernels
+#ifndef CRT_RB
+#define CRT_RB 128
+#endif
+constexpr int RB = CRT_RB;   // threads per block of the wavefront kernels
 
 struct RenderParams {
     DCamera cam;
@@ -443,12 +446,15 @@ __device__ __forceinline__ void load_path(const RenderParams& P, const float4* _
 }
 
 // one thread per queue entry, fully converged. A queue of fewer than `tail_below` entries belongs to k_tail.
+#ifndef CRT_SHADE_PREFETCH
+#define CRT_SHADE_PREFETCH 0
+#endif
 #ifndef CRT_SHADE_MIN_BLOCKS
 #define CRT_SHADE_MIN_BLOCKS 10  // 48 registers instead of 56, no spills: 10 resident blocks instead of 9 hide more of the record and
                                  // queue latency (C3 frame 6.95 -> 6.76 ms, profiles/r02_s_ab.txt)
 #endif
 template <bool COUNT, bool HAS_SPH>
-__global__ void __launch_bounds__(RB, CRT_SHADE_MIN_BLOCKS)
+__global__ void __launch_bounds__(RB, CRT_SHADE_MIN_BLOCKS * 128 / RB)
 k_shade(RenderParams P, AccelView A, const DMat* __restrict__ mats, const float4* __restrict__ q_in,
         const float4* __restrict__ hits, const uint32_t* __restrict__ n_in_ptr, float4* __restrict__ q_out,
         uint32_t* __restrict__ n_out_ptr, float4* __restrict__ rad, unsigned long long* __restrict__ counters,
@@ -466,6 +472,16 @@ k_shade(RenderParams P, AccelView A, const DMat* __restrict__ mats, const float4
         const bool live = i < n_in;
         bool next = false;
         PathState S;
+#if CRT_SHADE_PREFETCH
+        {   // the next iteration's queue entry and hit record on their way into L2 while this one is shaded (development switch)
+            const uint32_t i_next = i + gridDim.x * RB;
+            if (i_next < n_in) {
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(q_in + i_next));
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(q_in + (size_t)P.cap + i_next));
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(hits + i_next));
+            }
+        }
+#endif
         if (live) {
             load_path(P, q_in, i, S);
             const float4 hr = __ldcs(hits + i);
