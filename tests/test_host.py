@@ -274,6 +274,34 @@ def test_d3_shortcut_implies_the_definition():
     assert total[1] > 0                                                   # and the definition does reject something here
 
 
+def test_python_constants_match_the_header():
+    """The ctypes binding restates the header's enums: every CRT_OPT_* / CRT_POSE_* / CRT_SHADE_* / CRT_ACCEL_* /
+    CRT_BUILDER_* value in include/crt.h equals the Python constant of the same name (minus the CRT_ prefix)."""
+    hdr = open(os.path.join(ROOT, "include", "crt.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    found = dict(re.findall(r"\b(CRT_(?:OPT|POSE|SHADE|ACCEL|BUILDER)_[A-Z0-9_]+)\s*=\s*(\d+)", hdr))
+    assert len([k for k in found if k.startswith("CRT_OPT_")]) >= 15
+    for name, value in found.items():
+        py = name[len("CRT_"):]
+        assert hasattr(crt, py), "cudaraytracer_b200 has no %s" % py
+        assert getattr(crt, py) == int(value), "%s: header %s, Python %r" % (name, value, getattr(crt, py))
+
+
+def test_c4_scene_carries_one_part_per_instance():
+    """bench.py --workload c4 moves the instanced scene with one translation per instance (crt_scene_set_parts +
+    CRT_POSE_PARTS): the generator names the part of every triangle, instances in order, the ground last."""
+    sc = scenes.c4_instanced(grid=3, n_theta=24, n_phi=13)
+    n_inst = (len(sc["tri"]) - 2) // 9
+    part = sc["part_of_tri"]
+    assert part.dtype == np.uint32 and part.shape == (len(sc["tri"]),) and sc["n_parts"] == 10
+    assert np.array_equal(part[:-2], np.repeat(np.arange(9, dtype=np.uint32), n_inst)) and (part[-2:] == 9).all()
+    assert "points" not in sc and "tri_idx" not in sc      # the base mesh's point form does not describe this scene
+    # every instance is the first one moved by a multiple of the pitch
+    v = sc["tri"][:, :9].reshape(-1, 3, 3)
+    d = v[n_inst:2 * n_inst] - v[:n_inst]
+    assert np.allclose(d, d[0, 0], atol=1e-3) and abs(np.linalg.norm(d[0, 0]) - 250.0) < 1e-3
+
+
 def test_scene_generators():
     c3 = scenes.c3_mesh(n_theta=100, n_phi=50)
     assert len(c3["tri"]) == 2 * 100 * 49 + 2 and np.isfinite(c3["tri"]).all()
