@@ -1,4 +1,4 @@
-"""Turn the ncu exports of scripts/gpu_r2_n.sh into what bench.py and the judge read:
+"""Turn the ncu exports of scripts/gpu_r2_n.sh (or gpu_r2_v.sh: gpurun_out/v) into what bench.py and the judge read:
   profiles/closest_hit_ncu.json   DRAM traffic and limiter counters of the closest-hit launches of ONE warm C3 frame
   profiles/<tag>_summary.md       per-kernel table of that frame, launch list shares of the bench command, build kernels
   profiles/<tag>_*.csv            trimmed copies of the raw exports (the columns used here)
@@ -72,7 +72,7 @@ def fmt(v, nd=1):
     return "-" if v is None else ("%.*f" % (nd, v))
 
 
-md = ["# Round 2, final code: ncu evidence (`scripts/gpu_r2_n.sh`, one B200, `--clock-control none`)", ""]
+md = ["# Round 2, final code: ncu evidence (`scripts/gpu_%s.sh`, one B200, `--clock-control none`)" % tag.replace("r02", "r2"), ""]
 
 # ---- 1. the frame ----
 frame, trimmed = read_raw(os.path.join(src, "n_frame_raw.csv"))
