@@ -242,6 +242,22 @@ __device__ __forceinline__ float sortable2f(uint32_t s)
 __device__ __forceinline__ float warp_min_f(float v) { return sortable2f(__reduce_min_sync(0xffffffffu, f2sortable(v))); }
 __device__ __forceinline__ float warp_max_f(float v) { return sortable2f(__reduce_max_sync(0xffffffffu, f2sortable(v))); }
 
+// The direction the primitive tests see (ray_dir_local of the raw direction): read from the source when it keeps it
+// (Src::load_local - the render queues, whose writer computed it once for this kernel and for the shading kernel
+// behind it), else computed here from the raw direction.
+template <class Src>
+__device__ __forceinline__ auto load_ray_local(const Src& s, uint32_t i, v3& o, v3& d, int) -> decltype(s.load_local(i, o, d), void())
+{
+    s.load_local(i, o, d);
+}
+template <class Src>
+__device__ __forceinline__ void load_ray_local(const Src& s, uint32_t i, v3& o, v3& d, long)
+{
+    v3 dr;
+    s.load(i, o, dr);
+    d = ray_dir_local(dr);
+}
+
 // Src: bool load(uint32_t i, v3& o, v3& d)  -> origin and raw direction of ray i
 // Sink: void store(uint32_t i, const Hit& h) -> h.k = sorted primitive position or ~0u, h.id = caller's id
 // work_ctr: zeroed queue cursor.
@@ -338,9 +354,7 @@ __device__ __forceinline__ void traverse_persistent(const AccelView& A, const ui
                     const uint32_t rank = (uint32_t)__popc(idle_mask & lt_mask);
                     if (node == CRT_NODE_DONE && rank < avail) {
                         ray_i = chunk_next + rank;
-                        v3 dr;
-                        src.load(ray_i, o, dr);
-                        d = ray_dir_local(dr);
+                        load_ray_local(src, ray_i, o, d, 0);
                         S = make_slabs(o, d);
                         best.t = t_max; best.k = 0xFFFFFFFFu; best.id = CRT_MISS_ID; best.u = best.v = 0.f;
                         sp = 0;
@@ -524,11 +538,7 @@ __device__ __forceinline__ void traverse_packets(const AccelView& A, const uint3
             const uint32_t ray_i = first + lane;
             const bool live = ray_i < end;
             v3 o = V(0.f, 0.f, 0.f), d = V(0.f, 0.f, 1.f);
-            if (live) {
-                v3 dr;
-                src.load(ray_i, o, dr);
-                d = ray_dir_local(dr);
-            }
+            if (live) load_ray_local(src, ray_i, o, d, 0);
             const RaySlabs S = make_slabs(o, d);
             // lane 0 is always live; a dead lane takes its ray so that it widens nothing
             const float o0x = __shfl_sync(FULL, o.x, 0), o0y = __shfl_sync(FULL, o.y, 0), o0z = __shfl_sync(FULL, o.z, 0);

@@ -39,6 +39,19 @@
 
 namespace crt {
 
+// CRT_QUEUE_LOCAL_DIR: a queue entry carries the direction the primitive tests see (ray_dir_local of the ray's direction:
+// two normalisations, 2 square roots and 6 divisions) beside the raw direction, computed ONCE by the kernel that
+// writes the entry (k_raygen, k_shade), instead of once in the closest-hit kernel - at a refill, with a dozen of 32
+// lanes active - and once more in k_shade for the hit point. Words of an entry (SoA, `cap` apart):
+//   0: {o.xyz, dl.x}  1: {dl.yz, path_id, ctr|depth}  2, 3: material ids  4: {d.xyz raw, 0}
+// The closest-hit kernels still read words 0 and 1 only; k_shade reads word 4 as well (sky, reflect, refract use
+// the raw direction). 0: words 0 and 1 hold the raw direction and there is no word 4.
+// Measured (profiles/r02_zz_*): the closest-hit launches of a C3 frame 0.561 -> 0.533 ms each, k_raygen and k_shade
+// pay for what they save, the frame stays at 6.8 ms (end to end 7.47 -> 7.42 ms); queues grow from 64 to 80 B a path.
+#ifndef CRT_QUEUE_LOCAL_DIR
+#define CRT_QUEUE_LOCAL_DIR 1
+#endif
+#define CRT_QUEUE_WORDS (CRT_QUEUE_LOCAL_DIR ? 5 : 4)
 #ifndef CRT_RB
 #define CRT_RB 128
 #endif
@@ -163,6 +176,9 @@ k_raygen(RenderParams P, float4* __restrict__ q, uint32_t* __restrict__ q_count)
         const uint32_t id = bbase + threadIdx.x;
         bool live = id < total;
         float4 w0 = make_float4(0, 0, 0, 0), w1 = w0;
+#if CRT_QUEUE_LOCAL_DIR
+        float4 w4 = w0;
+#endif
         if (live) {
             uint32_t slot, s_local;
             split_path_id(P, id, slot, s_local);
@@ -177,14 +193,24 @@ k_raygen(RenderParams P, float4* __restrict__ q, uint32_t* __restrict__ q_count)
                 const float v = x::div(x::add((float)y, rnd(rng)), (float)P.ny);   // render.h:117
                 v3 o, d;
                 camera_get_ray(P.cam, u, v, rng, o, d);                            // render.h:118
+#if CRT_QUEUE_LOCAL_DIR
+                const v3 dl = ray_dir_local(d);
+                w0 = make_float4(o.x, o.y, o.z, dl.x);
+                w1 = make_float4(dl.y, dl.z, __uint_as_float(id), __uint_as_float(rng.ctr | ((uint32_t)P.max_depth << 24)));
+                w4 = make_float4(d.x, d.y, d.z, 0.0f);
+#else
                 w0 = make_float4(o.x, o.y, o.z, d.x);
                 w1 = make_float4(d.y, d.z, __uint_as_float(id), __uint_as_float(rng.ctr | ((uint32_t)P.max_depth << 24)));
+#endif
             }
         }
         const uint32_t pos = block_append<RB>(live, q_count, s_cnt, it);
         if (live) {   // the material-id words (2, 3) are first written by k_shade and never read at bounce 0
             __stcs(q + pos, w0);
             __stcs(q + (size_t)P.cap + pos, w1);
+#if CRT_QUEUE_LOCAL_DIR
+            __stcs(q + 4 * (size_t)P.cap + pos, w4);
+#endif
         }
     }
 }
@@ -215,10 +241,26 @@ struct QueueSrc {
         // queue entries and hit records stream through once per launch (GB per bounce): evict-first loads and
         // stores keep them from pushing the node and record working set (which does fit) out of the 126 MB L2
         const float4 w0 = __ldcs(q + i);
+#if CRT_QUEUE_LOCAL_DIR
+        const float4 w4 = __ldcs(q + 4 * cap + i);      // the raw direction (chained primitives normalise per level)
+        o = V(w0.x, w0.y, w0.z);
+        d = V(w4.x, w4.y, w4.z);
+#else
         const float4 w1 = __ldcs(q + cap + i);
         o = V(w0.x, w0.y, w0.z);
         d = V(w0.w, w1.x, w1.y);
+#endif
     }
+#if CRT_QUEUE_LOCAL_DIR
+    // origin and the direction the primitive tests see, as the entry's writer computed it
+    __device__ __forceinline__ void load_local(uint32_t i, v3& o, v3& dl) const
+    {
+        const float4 w0 = __ldcs(q + i);
+        const float4 w1 = __ldcs(q + cap + i);
+        o = V(w0.x, w0.y, w0.z);
+        dl = V(w0.w, w1.x, w1.y);
+    }
+#endif
 };
 struct QueueSink {
     float4* hits;   // {t, sorted primitive position, u, v} per queue entry
@@ -328,6 +370,7 @@ k_trace_deferred(AccelView A, const float4* __restrict__ q, uint32_t cap, const 
 // ---- shade(): the body of the reference's recursion for one path segment ----
 struct PathState {
     v3 o, d;              // the ray that was traced (d as shade() holds it: not normalised)
+    v3 dl;                // CRT_QUEUE_LOCAL_DIR: ray_dir_local(d), carried by the queue entry
     uint32_t path_id;     // slot * s_count + sample of the batch
     uint32_t pack;        // draw counter | depth_left << 24
     uint32_t ms[8];       // material ids of the bounces so far, 16 bits each
@@ -364,7 +407,11 @@ __device__ __forceinline__ bool shade_step(const RenderParams& P, const AccelVie
         // the ray in the hit primitive's own frame: hit point and normal are reported there
         v3 ol = o, dl;
         if (HAS_SPH && chain != 0u) chain_ray(A.frames, chain, o, d, ol, dl);
+#if CRT_QUEUE_LOCAL_DIR
+        else dl = S.dl;
+#else
         else dl = ray_dir_local(d);
+#endif
         v3 p, n;
         if (HAS_SPH && (inf_y & CRT_KIND_SPHERE)) {
             p = vadd(vsub(ol, V(r0.x, r0.y, r0.z)), vscale(ht, dl));       // sphere.h:40 (local frame)
@@ -393,6 +440,9 @@ __device__ __forceinline__ bool shade_step(const RenderParams& P, const AccelVie
                         S.ms[j] = (bounces & 1) ? ((S.ms[j] & 0xFFFFu) | (hist << 16)) : hist;
                 S.o = p;
                 S.d = out_d;
+#if CRT_QUEUE_LOCAL_DIR
+                S.dl = ray_dir_local(out_d);
+#endif
                 S.pack = (rng.ctr & 0xFFFFFFu) | ((uint32_t)(depth_left - 1) << 24);
             } else {
                 L = vadd(e, V(0.1f, 0.1f, 0.1f));                          // render.h:61
@@ -429,7 +479,14 @@ __device__ __forceinline__ void load_path(const RenderParams& P, const float4* _
     const float4 w0 = __ldcs(q + i);
     const float4 w1 = __ldcs(q + (size_t)P.cap + i);
     S.o = V(w0.x, w0.y, w0.z);
+#if CRT_QUEUE_LOCAL_DIR
+    const float4 w4 = __ldcs(q + 4 * (size_t)P.cap + i);
+    S.dl = V(w0.w, w1.x, w1.y);
+    S.d = V(w4.x, w4.y, w4.z);
+#else
     S.d = V(w0.w, w1.x, w1.y);
+    S.dl = S.d;           // unused
+#endif
     S.path_id = __float_as_uint(w1.z);
     S.pack = __float_as_uint(w1.w);
 #pragma unroll
@@ -491,8 +548,14 @@ k_shade(RenderParams P, AccelView A, const DMat* __restrict__ mats, const float4
         }
         const uint32_t pos = block_append<RB>(next, n_out_ptr, s_cnt, it);
         if (next) {
+#if CRT_QUEUE_LOCAL_DIR
+            __stcs(q_out + pos, make_float4(S.o.x, S.o.y, S.o.z, S.dl.x));
+            __stcs(q_out + (size_t)P.cap + pos, make_float4(S.dl.y, S.dl.z, __uint_as_float(S.path_id), __uint_as_float(S.pack)));
+            __stcs(q_out + 4 * (size_t)P.cap + pos, make_float4(S.d.x, S.d.y, S.d.z, 0.0f));
+#else
             __stcs(q_out + pos, make_float4(S.o.x, S.o.y, S.o.z, S.d.x));
             __stcs(q_out + (size_t)P.cap + pos, make_float4(S.d.y, S.d.z, __uint_as_float(S.path_id), __uint_as_float(S.pack)));
+#endif
             __stcs(reinterpret_cast<uint4*>(q_out) + 2 * (size_t)P.cap + pos, make_uint4(S.ms[0], S.ms[1], S.ms[2], S.ms[3]));
             if (P.max_depth > 8)
                 __stcs(reinterpret_cast<uint4*>(q_out) + 3 * (size_t)P.cap + pos, make_uint4(S.ms[4], S.ms[5], S.ms[6], S.ms[7]));
@@ -809,8 +872,8 @@ int render_accum(crt_ctx* c, const crt_camera* cam, int nx, int ny, int s0, int 
         const int n_levels = CRT_MAX_DEPTH + 3;
         for (int l = 0; l < n_lanes; l++) {
             crt_lane& L = c->lane[l];
-            CRT_CUDA(L.queue[0].reserve(cap * 64));
-            CRT_CUDA(L.queue[1].reserve(cap * 64));
+            CRT_CUDA(L.queue[0].reserve(cap * 16 * CRT_QUEUE_WORDS));
+            CRT_CUDA(L.queue[1].reserve(cap * 16 * CRT_QUEUE_WORDS));
             CRT_CUDA(L.rad.reserve(cap * 16));
             CRT_CUDA(L.qcount.reserve(sizeof(uint32_t) * n_levels));
             CRT_CUDA(L.work_ctr.reserve(sizeof(uint32_t) * 128));
